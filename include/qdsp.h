@@ -1,0 +1,149 @@
+/*
+ * qdsp.h -- C ABI of the B200-native sparse linear-algebra path that sits behind Quadrants'
+ *           qd.linalg.{SparseMatrixBuilder,SparseMatrix,SparseCG} and qd.algorithms.{parallel_sort,PrefixSumExecutor}.
+ *
+ * This is the drop-in boundary.  The reference has no C API; its boundary is the nanobind surface of
+ * quadrants/python/export_lang.cpp:518-531,1166-1295 over the C++ classes of quadrants/program/sparse_matrix.{h,cpp}
+ * and conjugate_gradient.{h,cpp}.  Every entry point below names the reference member it replaces; INTEGRATION.md
+ * shows the ~100-line patch that makes those members call this ABI.
+ *
+ * Conventions: plain C, opaque handles, raw device pointers (void*), `void *stream` is a cudaStream_t (NULL = legacy
+ * default stream, which is what the reference's library handles use).  Every function returns 0 (QDSP_OK) or a
+ * qdsp_status; the message of the last failure on the calling thread is qdsp_last_error().  No exception crosses the
+ * ABI.  There is no CPU fallback: without a CUDA device every compute entry point returns QDSP_ERR_CUDA.
+ * All sizes are in elements unless the name says bytes.  Indices are int32 end to end like the reference
+ * (cuSPARSE INDEX_32I, quadrants/program/sparse_matrix.cpp:375-377).
+ */
+#ifndef QDSP_H_
+#define QDSP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library is built with -fvisibility=hidden; only this ABI is exported */
+#endif
+
+#define QDSP_ABI_VERSION 1
+
+typedef enum {
+  QDSP_OK = 0,
+  QDSP_ERR_INVALID = 1, /* bad argument / out-of-range triplet index (reference: QD_ASSERT / eigen_assert)           */
+  QDSP_ERR_CUDA = 2,    /* CUDA runtime failure (reference: QD_ERROR_IF in CUDADriverFunction, cuda_driver.h:92-95)  */
+  QDSP_ERR_STATE = 3,   /* call order misuse, e.g. build() twice (reference: QD_ASSERT(built_ == false))             */
+  QDSP_ERR_UNSUPPORTED = 4, /* reference: QD_NOT_IMPLEMENTED                                                         */
+  QDSP_ERR_COMM = 5     /* multi-GPU peer mapping / NCCL failure                                                     */
+} qdsp_status;
+
+typedef enum { QDSP_F32 = 0, QDSP_F64 = 1 } qdsp_dtype;
+
+/* key kinds of qdsp_sort_pairs: order is numeric for every kind (sign / IEEE twiddles applied on the fly) */
+typedef enum { QDSP_KEY_U32 = 0, QDSP_KEY_I32 = 1, QDSP_KEY_F32 = 2, QDSP_KEY_U64 = 3 } qdsp_key_kind;
+
+/* CG semantics.  EIGEN_JACOBI = the reference's arch=x64 path, Eigen::ConjugateGradient with the default diagonal
+ * preconditioner, zero start, relative tolerance (quadrants/program/conjugate_gradient.h:36-49).  CUCG = the
+ * reference's arch=cuda path, plain CG on the x passed in, absolute r.r <= tol^2
+ * (quadrants/program/conjugate_gradient.cpp:19-83). */
+typedef enum { QDSP_CG_EIGEN_JACOBI = 0, QDSP_CG_CUCG = 1 } qdsp_cg_mode;
+
+typedef struct qdsp_builder_s *qdsp_builder_t;
+typedef struct qdsp_csr_s *qdsp_csr_t;
+typedef struct qdsp_cg_s *qdsp_cg_t;
+
+/* ---- library ------------------------------------------------------------------------------------------------- */
+const char *qdsp_last_error(void);
+int qdsp_abi_version(void);
+/* Binds the calling thread to `device` (the reference hard-codes device 0, quadrants/rhi/cuda/cuda_context.cpp:16-26)
+ * and reports what the launch heuristics use. */
+int qdsp_init(int device);
+int qdsp_device_info(int *device, int *sm_count, int *cc_major, int *cc_minor, size_t *l2_bytes, size_t *hbm_bytes);
+/* Number of kernels of this library launched by the calling process so far (bench.py's gpu_launches). */
+int64_t qdsp_launch_count(void);
+
+/* ---- SparseMatrixBuilder (quadrants/program/sparse_matrix.h:16-53) -------------------------------------------- */
+/* ctor + create_ndarray (sparse_matrix.cpp:70-85): allocates the device triplet buffer of 3*max_triplets+1 slots of
+ * 4 (f32) or 8 (f64) bytes, layout [count | (row, col, value-bits)...] written by insert_triplet_f32/f64
+ * (quadrants/runtime/llvm/runtime_module/internal_functions.h:12-39).  Slot 0 is zeroed (the reference relies on the
+ * pool for that).  storage_format: "col_major" | "row_major"; like make_cu_sparse_matrix the device matrix is CSR
+ * either way, the format only selects which Eigen summation order SpMV mirrors bit-for-bit. */
+int qdsp_builder_create(int rows, int cols, int64_t max_triplets, int dtype, const char *storage_format,
+                        qdsp_builder_t *out);
+/* get_ndarray_data_ptr (sparse_matrix.cpp:135-137): the address JIT fill kernels receive as their u64 argument. */
+int qdsp_builder_buffer_ptr(qdsp_builder_t b, void **device_ptr);
+/* num_triplets_ as build_cuda reads it (sparse_matrix.cpp:178): D2H copy of slot 0 (synchronises `stream`). */
+int qdsp_builder_count(qdsp_builder_t b, void *stream, int64_t *count);
+/* Host-side fill for callers without a JIT kernel: copies `count` triplets already in the slot layout (without the
+ * leading count slot) from host memory and sets slot 0.  (No reference counterpart; used by the e2e path.) */
+int qdsp_builder_fill_from_host(qdsp_builder_t b, const void *host_triplets, int64_t count, void *stream);
+/* clear (sparse_matrix.cpp:224-228) */
+int qdsp_builder_clear(qdsp_builder_t b, void *stream);
+/* build_cuda (sparse_matrix.cpp:173-222) + CuSparseMatrix::build_csr_from_coo (:344-397), entirely on the device:
+ * pack -> onesweep radix sort by (row, col) -> head flags + decoupled look-back scan -> duplicate sum in buffer order
+ * -> indptr.  Result equals Eigen's row-major setFromTriplets bit-for-bit (indptr, indices, values). */
+int qdsp_builder_build(qdsp_builder_t b, void *stream, qdsp_csr_t *out);
+/* print_triplets_cuda (sparse_matrix.cpp:119-133) */
+int qdsp_builder_print_triplets(qdsp_builder_t b);
+/* delete_ndarray + dtor */
+int qdsp_builder_destroy(qdsp_builder_t b);
+
+/* ---- CuSparseMatrix (quadrants/program/sparse_matrix.h:206-299) ------------------------------------------------ */
+/* build_csr_from_coo (sparse_matrix.cpp:344-397): device COO (unsorted, duplicates allowed and summed in array
+ * order) -> CSR.  The inputs are only read (the reference takes ownership of them). */
+int qdsp_csr_from_device_coo(int rows, int cols, int64_t nnz, const int32_t *row, const int32_t *col, const void *val,
+                             int dtype, void *stream, qdsp_csr_t *out);
+/* Adopts device CSR arrays by copy (make_cu_sparse_matrix(mat, rows, cols, ...), sparse_matrix.cpp:304-316). */
+int qdsp_csr_from_device_csr(int rows, int cols, int64_t nnz, const int32_t *indptr, const int32_t *indices,
+                             const void *values, int dtype, int order_row_major, void *stream, qdsp_csr_t *out);
+int qdsp_csr_info(qdsp_csr_t m, int *rows, int *cols, int64_t *nnz, int *dtype);
+/* Borrowed device pointers to csr_row_ptr_/csr_col_ind_/csr_val_ (valid until qdsp_csr_destroy). */
+int qdsp_csr_export(qdsp_csr_t m, const int32_t **indptr, const int32_t **indices, const void **values);
+/* spmv / nd_spmv (sparse_matrix.cpp:654-686): y = A x, x has cols elements, y rows elements, both dense device. */
+int qdsp_csr_spmv(qdsp_csr_t m, const void *x, void *y, void *stream);
+/* Same through host buffers (H2D x, SpMV, D2H y): the reference-facing call bench.py's e2e leg times. */
+int qdsp_csr_spmv_host(qdsp_csr_t m, const void *x_host, void *y_host, void *stream);
+/* get_element (sparse_matrix.cpp:688-712): 0 when absent */
+int qdsp_csr_get_element(qdsp_csr_t m, int row, int col, double *out);
+/* addition / subtraction / scalar multiply / transpose / matmul (sparse_matrix.cpp:413-652) */
+int qdsp_csr_add(qdsp_csr_t a, qdsp_csr_t b, double alpha, double beta, void *stream, qdsp_csr_t *out);
+int qdsp_csr_scale(qdsp_csr_t a, double alpha, void *stream, qdsp_csr_t *out);
+int qdsp_csr_transpose(qdsp_csr_t a, void *stream, qdsp_csr_t *out);
+int qdsp_csr_matmul(qdsp_csr_t a, qdsp_csr_t b, void *stream, qdsp_csr_t *out);
+/* mmwrite (sparse_matrix.cpp:748-780): Matrix Market coordinate real general, 1-based */
+int qdsp_csr_mmwrite(qdsp_csr_t m, const char *path);
+int qdsp_csr_destroy(qdsp_csr_t m);
+
+/* ---- CG<EigenT,DT> / CUCG (quadrants/program/conjugate_gradient.h) -------------------------------------------- */
+/* make_{float,double}_cg_solver / make_cucg_solver (conjugate_gradient.h:67-70, conjugate_gradient.cpp:85-87).
+ * The solver keeps a reference to `m` like the reference does; destroy the solver first. */
+int qdsp_cg_create(qdsp_csr_t m, int max_iters, double tol, int mode, int verbose, qdsp_cg_t *out);
+/* solve (conjugate_gradient.h:36-49 / conjugate_gradient.cpp:19-83).  x, b: dense device vectors.  EIGEN_JACOBI
+ * overwrites x from a zero start; CUCG starts from the x passed in.  iterations/error/success follow Eigen's
+ * iterations()/error()/info()==Success; in CUCG mode error is r.r and success is r.r <= tol^2. */
+int qdsp_cg_solve(qdsp_cg_t s, void *x, const void *b, void *stream, int *iterations, double *error, int *success);
+int qdsp_cg_solve_host(qdsp_cg_t s, void *x_host, const void *b_host, void *stream, int *iterations, double *error,
+                       int *success);
+/* Runs exactly `iters` iterations with the convergence exit disabled (throughput timing; not a reference call). */
+int qdsp_cg_run_fixed(qdsp_cg_t s, void *x, const void *b, int iters, void *stream);
+int qdsp_cg_destroy(qdsp_cg_t s);
+
+/* ---- qd.algorithms.parallel_sort / PrefixSumExecutor ----------------------------------------------------------- */
+/* parallel_sort (python/quadrants/algorithms/_algorithms.py:19-56): in-place ascending sort of keys, values (or
+ * NULL) permuted alike.  Stable (the reference network is not; its tests never observe tie order).  value_bytes is
+ * 0, 4 or 8.  tmp: caller-owned scratch of qdsp_sort_tmp_bytes(). */
+size_t qdsp_sort_tmp_bytes(int64_t n, int key_kind, int value_bytes);
+int qdsp_sort_pairs(void *keys, void *values, int64_t n, int key_kind, int value_bytes, void *tmp, size_t tmp_bytes,
+                    void *stream);
+/* PrefixSumExecutor.run (_algorithms.py:109-163): in-place inclusive i32 prefix sum, wrapping. */
+size_t qdsp_scan_tmp_bytes(int64_t n);
+int qdsp_inclusive_scan_i32(int32_t *inout, int64_t n, void *tmp, size_t tmp_bytes, void *stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* QDSP_H_ */

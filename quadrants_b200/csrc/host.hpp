@@ -1,0 +1,98 @@
+// host.hpp -- C++ host orchestration layer above the kernels and below the C ABI (include/qdsp.h).
+// One class per reference class of quadrants/program/{sparse_matrix,conjugate_gradient}.h.
+#pragma once
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace qdsp {
+
+// ---- algorithms (scan.cu, radix_sort.cu) -----------------------------------------------------------------------------
+size_t scan_tmp_bytes(int64_t n);
+void inclusive_scan_i32(int32_t *inout, int64_t n, void *tmp, size_t tmp_bytes, cudaStream_t stream);
+size_t sort_tmp_bytes(int64_t n, int key_bytes, int value_bytes);
+void sort_pairs(void *keys, void *values, int64_t n, int key_kind, int value_bytes, void *tmp, size_t tmp_bytes,
+                cudaStream_t stream);
+void sort_build_keys(void *keys, void *values, int64_t n, int key_bytes, int value_bytes, int key_bits, void *tmp,
+                     cudaStream_t stream, void **keys_out, void **values_out);
+
+// ---- CuSparseMatrix (quadrants/program/sparse_matrix.h:206-299) -------------------------------------------------------
+// Owns csr_row_ptr_/csr_col_ind_/csr_val_ on the device.  Unlike the reference's shallow copy-ctor
+// (sparse_matrix.h:233-234, a double-free hazard) it is move-only.
+class CsrMatrix {
+ public:
+  int rows = 0, cols = 0;
+  int64_t nnz = 0;
+  int dtype = QDSP_F32;
+  // which Eigen product order the short-row SpMV path mirrors bit-for-bit: false = col_major (the reference's
+  // default storage_format: one accumulator, entries of a row added left to right with fma), true = row_major
+  // (two alternating accumulators, SparseDenseProduct.h:66-80)
+  bool row_major_order = false;
+  DeviceBuffer indptr, indices, values;  // indices/values carry 64 bytes of zeroed padding for 128-bit loads
+
+  size_t value_bytes() const { return dtype == QDSP_F64 ? 8 : 4; }
+  void allocate(int rows_, int cols_, int64_t nnz_, int dtype_);
+  void spmv(const void *x, void *y, cudaStream_t stream) const;
+  double get_element(int r, int c) const;
+  void mmwrite(const std::string &path) const;
+  void to_host(std::vector<int32_t> &ip, std::vector<int32_t> &ix, std::vector<char> &vals) const;
+
+  static std::unique_ptr<CsrMatrix> from_device_coo(int rows, int cols, int64_t n, const int32_t *row,
+                                                    const int32_t *col, const void *val, int dtype,
+                                                    cudaStream_t stream);
+  static std::unique_ptr<CsrMatrix> from_device_csr(int rows, int cols, int64_t nnz, const int32_t *indptr,
+                                                    const int32_t *indices, const void *values, int dtype,
+                                                    bool row_major_order, cudaStream_t stream);
+  std::unique_ptr<CsrMatrix> add(const CsrMatrix &b, double alpha, double beta, cudaStream_t stream) const;
+  std::unique_ptr<CsrMatrix> scale(double alpha, cudaStream_t stream) const;
+  std::unique_ptr<CsrMatrix> transpose(cudaStream_t stream) const;
+  std::unique_ptr<CsrMatrix> matmul(const CsrMatrix &b, cudaStream_t stream) const;
+};
+
+// Shared by Builder::build and CsrMatrix::from_device_coo: keys/vals already packed on the device.
+std::unique_ptr<CsrMatrix> csr_from_packed(int rows, int cols, int64_t n, int dtype, int key_bytes, int col_bits,
+                                           DeviceBuffer &keys, DeviceBuffer &vals, cudaStream_t stream);
+
+// ---- SparseMatrixBuilder (quadrants/program/sparse_matrix.h:16-53) ----------------------------------------------------
+class Builder {
+ public:
+  Builder(int rows, int cols, int64_t max_triplets, int dtype, const std::string &storage_format);
+  void *buffer_ptr() const { return buf_.get(); }
+  int64_t count(cudaStream_t stream) const;
+  void fill_from_host(const void *triplets, int64_t count, cudaStream_t stream);
+  void clear(cudaStream_t stream);
+  std::unique_ptr<CsrMatrix> build(cudaStream_t stream);
+  void print_triplets() const;
+  int rows() const { return rows_; }
+  int cols() const { return cols_; }
+  int dtype() const { return dtype_; }
+
+ private:
+  int rows_, cols_;
+  int64_t max_triplets_;
+  int dtype_;
+  bool row_major_;
+  bool built_ = false;
+  DeviceBuffer buf_;
+  size_t slot_bytes() const { return dtype_ == QDSP_F64 ? 8 : 4; }
+};
+
+// ---- CG<EigenT,DT> and CUCG (quadrants/program/conjugate_gradient.h) ---------------------------------------------------
+struct CgScalars;  // device-resident scalar block, cg.cu
+class DistPlan;    // dist.cu
+
+class CgSolver {
+ public:
+  CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool verbose, DistPlan *dist = nullptr);
+  ~CgSolver();
+  void solve(void *x, const void *b, cudaStream_t stream, int *iterations, double *error, int *success);
+  void run_fixed(void *x, const void *b, int iters, cudaStream_t stream);
+  struct Impl;
+
+ private:
+  std::unique_ptr<Impl> impl_;
+};
+
+}  // namespace qdsp

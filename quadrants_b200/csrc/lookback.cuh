@@ -1,0 +1,61 @@
+// lookback.cuh -- single-pass "decoupled look-back" prefix machinery (Merrill & Garland) shared by the scan, the
+// duplicate-collapse pass of the CSR build and (per digit) the onesweep sort.
+#pragma once
+#include "common.cuh"
+
+namespace qdsp {
+
+// descriptor word: status in the top 2 bits, value in the low 62.  cudaMemsetAsync(0) == all tiles INVALID.
+constexpr unsigned long long LB_INVALID = 0ull;
+constexpr unsigned long long LB_AGGREGATE = 1ull << 62;
+constexpr unsigned long long LB_PREFIX = 2ull << 62;
+constexpr unsigned long long LB_STATUS_MASK = 3ull << 62;
+constexpr unsigned long long LB_VALUE_MASK = ~LB_STATUS_MASK;
+
+#ifdef __CUDACC__
+// Tiles take their index from an atomic ticket, so every tile with a smaller index has already started running:
+// the spin below cannot deadlock whatever order the hardware schedules CTAs in.
+__device__ __forceinline__ unsigned take_ticket(unsigned *counter, unsigned *smem_slot) {
+  if (threadIdx.x == 0) *smem_slot = atomicAdd(counter, 1u);
+  __syncthreads();
+  return *smem_slot;
+}
+
+// Called by ONE full warp of the CTA.  Publishes this tile's aggregate, walks back over the predecessors' descriptors
+// 32 at a time and returns (to every lane) the exclusive prefix of the tile; finally publishes the inclusive prefix.
+// Values are summed modulo 2^62 (callers truncate to their width, so i32 wrap-around is preserved).
+__device__ __forceinline__ unsigned long long lookback_exclusive(unsigned long long *desc, unsigned tile,
+                                                                 unsigned long long aggregate) {
+  const unsigned lane = lane_id();
+  aggregate &= LB_VALUE_MASK;
+  if (tile == 0) {
+    if (lane == 0) st_relaxed_u64(&desc[0], LB_PREFIX | aggregate);
+    return 0ull;
+  }
+  if (lane == 0) st_relaxed_u64(&desc[tile], LB_AGGREGATE | aggregate);
+  unsigned long long exclusive = 0ull;
+  long long idx = static_cast<long long>(tile) - 1;
+  while (true) {
+    const long long t = idx - lane;
+    unsigned long long d;
+    do {
+      d = (t >= 0) ? ld_relaxed_u64(&desc[t]) : LB_PREFIX;  // before tile 0: a prefix of zero
+    } while (__any_sync(FULL, (d & LB_STATUS_MASK) == LB_INVALID));
+    const unsigned pmask = __ballot_sync(FULL, (d & LB_STATUS_MASK) == LB_PREFIX);
+    unsigned long long v = d & LB_VALUE_MASK;
+    if (pmask) {
+      const unsigned first = __ffs(pmask) - 1;  // nearest predecessor that already knows its inclusive prefix
+      if (lane > first) v = 0ull;
+      exclusive += warp_sum(v);
+      break;
+    }
+    exclusive += warp_sum(v);
+    idx -= 32;
+  }
+  exclusive &= LB_VALUE_MASK;
+  if (lane == 0) st_relaxed_u64(&desc[tile], LB_PREFIX | ((exclusive + aggregate) & LB_VALUE_MASK));
+  return exclusive;
+}
+#endif
+
+}  // namespace qdsp

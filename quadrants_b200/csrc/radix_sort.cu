@@ -1,0 +1,364 @@
+// radix_sort.cu -- "onesweep" least-significant-digit radix sort (Adinets & Merrill): one histogram pass over the keys,
+// then ONE read + ONE write of keys/values per 8-bit digit, the per-digit global offsets being resolved inside the
+// sweep by decoupled look-back instead of a separate scan pass.  Stable.
+//
+// Replaces qd.algorithms.parallel_sort (python/quadrants/algorithms/_algorithms.py:19-56 +
+// python/quadrants/_kernels.py:227-253: a Batcher odd-even merge network, 406 launches + sync() at N = 2^28) and the
+// cusparseXcoosortByRow + cusparseGather of CuSparseMatrix::build_csr_from_coo
+// (quadrants/program/sparse_matrix.cpp:358-368).
+//
+// HBM-bound: algorithmic traffic N*kb + P*2*N*(kb+vb) bytes for P digit passes.
+// Tile = 256 threads x ITEMS keys, warp-striped so that (warp, item, lane) order == input order:
+//   1. coalesced loads of keys (+values) into registers;
+//   2. per-warp ranking with match.any: peers holding the same digit elect a leader that bumps the warp's private
+//      digit counter in shared memory -> rank inside the warp, stable by construction;
+//   3. thread d (256 threads == 256 digits): scan of the 8 warp counters, publish the tile count of digit d,
+//      look back over the preceding tiles' descriptors for digit d, publish the inclusive prefix;
+//   4. scatter to shared memory in tile-sorted order, then write out so that consecutive threads store runs of
+//      consecutive global addresses.
+#include "common.cuh"
+
+namespace qdsp {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_RADIX = 256;
+constexpr size_t RS_HEADER_BYTES = 256;  // per-pass ticket counters (8 passes max)
+constexpr unsigned RS_FLAG_AGG = 1u << 30, RS_FLAG_PREFIX = 2u << 30, RS_FLAG_MASK = 3u << 30, RS_VAL_MASK = ~RS_FLAG_MASK;
+
+struct NoValue {};  // keys-only instantiation
+
+template <typename KeyT>
+__device__ __forceinline__ KeyT twiddle_in(KeyT k, int kind) {
+  if constexpr (sizeof(KeyT) == 4) {
+    if (kind == QDSP_KEY_I32) return k ^ 0x80000000u;
+    if (kind == QDSP_KEY_F32) return (k & 0x80000000u) ? ~k : (k | 0x80000000u);
+  }
+  return k;
+}
+template <typename KeyT>
+__device__ __forceinline__ KeyT twiddle_out(KeyT k, int kind) {
+  if constexpr (sizeof(KeyT) == 4) {
+    if (kind == QDSP_KEY_I32) return k ^ 0x80000000u;
+    if (kind == QDSP_KEY_F32) return (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+  }
+  return k;
+}
+
+// ---- pass 0: digit histograms of every pass in one read of the keys -----------------------------------------------
+template <typename KeyT>
+__global__ void __launch_bounds__(RS_THREADS)
+rs_histogram_kernel(const KeyT *__restrict__ keys, long long n, int kind, int begin_bit, int end_bit, int passes,
+                    unsigned *__restrict__ hist /* passes x 256 */) {
+  extern __shared__ unsigned s_hist[];  // passes x 256
+  for (int i = threadIdx.x; i < passes * RS_RADIX; i += RS_THREADS) s_hist[i] = 0;
+  __syncthreads();
+  const long long stride = static_cast<long long>(gridDim.x) * RS_THREADS;
+  for (long long i = static_cast<long long>(blockIdx.x) * RS_THREADS + threadIdx.x; i < n; i += stride) {
+    const KeyT k = twiddle_in(keys[i], kind);
+#pragma unroll 1
+    for (int p = 0; p < passes; ++p) {
+      const int shift = begin_bit + 8 * p;
+      const int nb = min(8, end_bit - shift);
+      const unsigned d = static_cast<unsigned>(k >> shift) & ((1u << nb) - 1u);
+      atomicAdd(&s_hist[p * RS_RADIX + d], 1u);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < passes * RS_RADIX; i += RS_THREADS)
+    if (s_hist[i]) atomicAdd(&hist[i], s_hist[i]);
+}
+
+// exclusive scan of each pass's 256 bins (one CTA per pass)
+__global__ void __launch_bounds__(RS_RADIX) rs_scan_bins_kernel(unsigned *__restrict__ hist) {
+  __shared__ unsigned s_w[RS_RADIX / 32];
+  unsigned *h = hist + blockIdx.x * RS_RADIX;
+  const unsigned v = h[threadIdx.x];
+  const unsigned incl = warp_inclusive_scan(v);
+  if (lane_id() == 31) s_w[threadIdx.x >> 5] = incl;
+  __syncthreads();
+  unsigned base = 0;
+  for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) base += s_w[w];
+  h[threadIdx.x] = base + incl - v;
+}
+
+// ---- one digit pass -------------------------------------------------------------------------------------------------
+template <typename KeyT, typename ValT, int ITEMS>
+struct RsSmem {
+  unsigned warp_hist[RS_WARPS][RS_RADIX];
+  unsigned digit_start[RS_RADIX];  // first tile-sorted position of each digit
+  unsigned gbase[RS_RADIX];        // global output index of tile-sorted position p of digit d is gbase[d] + p
+  unsigned warp_tot[RS_WARPS];
+  unsigned ticket;
+  KeyT keys[RS_THREADS * ITEMS];
+};
+
+template <typename KeyT, typename ValT, int ITEMS>
+__global__ void __launch_bounds__(RS_THREADS)
+rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const ValT *__restrict__ vin,
+                   ValT *__restrict__ vout, long long n, int shift, int nbits, int kind, int tw_in, int tw_out,
+                   unsigned *__restrict__ ticket, unsigned *__restrict__ lookback /* tiles x 256 */,
+                   const unsigned *__restrict__ bins /* exclusive-scanned histogram of this pass */) {
+  constexpr bool HAS_VAL = !std::is_same<ValT, NoValue>::value;
+  constexpr int TILE = RS_THREADS * ITEMS;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  auto &S = *reinterpret_cast<RsSmem<KeyT, ValT, ITEMS> *>(s_raw);
+  ValT *s_vals = reinterpret_cast<ValT *>(s_raw + sizeof(RsSmem<KeyT, ValT, ITEMS>));
+
+  if (threadIdx.x == 0) S.ticket = atomicAdd(ticket, 1u);
+  for (int i = threadIdx.x; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&S.warp_hist[0][0])[i] = 0;
+  __syncthreads();
+  const unsigned tile = S.ticket;
+  const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
+  const long long tile_base = static_cast<long long>(tile) * TILE;
+  const int valid_n = static_cast<int>(min(static_cast<long long>(TILE), n - tile_base));
+  const unsigned dmask = (1u << nbits) - 1u;
+
+  // 1. loads: item i of lane l of warp w <-> tile position w*32*ITEMS + i*32 + l
+  KeyT key[ITEMS];
+  ValT val[ITEMS];
+  const int wbase = warp * 32 * ITEMS + lane;
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const int p = wbase + i * 32;
+    if (p < valid_n) {
+      KeyT k = kin[tile_base + p];
+      key[i] = tw_in ? twiddle_in(k, kind) : k;
+      if constexpr (HAS_VAL) val[i] = vin[tile_base + p];
+    } else {
+      key[i] = static_cast<KeyT>(~KeyT(0));
+    }
+  }
+  // 2. warp-private ranking
+  unsigned rank[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const bool ok = (wbase + i * 32) < valid_n;
+    const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
+    const unsigned peers = __match_any_sync(FULL, ok ? d : 0x100u);
+    const unsigned leader = __ffs(peers) - 1;
+    unsigned old = 0;
+    if (lane == leader && ok) {
+      old = S.warp_hist[warp][d];
+      S.warp_hist[warp][d] = old + __popc(peers);
+    }
+    old = __shfl_sync(FULL, old, leader);
+    rank[i] = old + __popc(peers & lanemask_lt());
+    __syncwarp();
+  }
+  __syncthreads();
+  // 3. thread d owns digit d
+  {
+    const unsigned d = threadIdx.x;
+    unsigned sum = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w) {
+      const unsigned t = S.warp_hist[w][d];
+      S.warp_hist[w][d] = sum;  // exclusive offset of warp w inside digit d
+      sum += t;
+    }
+    const unsigned count = sum;
+    unsigned *my = lookback + static_cast<size_t>(tile) * RS_RADIX + d;
+    unsigned exclusive = 0;
+    if (tile == 0) {
+      st_relaxed_u32(my, RS_FLAG_PREFIX | count);
+    } else {
+      st_relaxed_u32(my, RS_FLAG_AGG | count);
+      const unsigned *q = my - RS_RADIX;
+      while (true) {
+        unsigned v;
+        do { v = ld_relaxed_u32(q); } while ((v & RS_FLAG_MASK) == 0u);
+        exclusive += v & RS_VAL_MASK;
+        if ((v & RS_FLAG_MASK) == RS_FLAG_PREFIX) break;
+        q -= RS_RADIX;
+      }
+      st_relaxed_u32(my, RS_FLAG_PREFIX | ((exclusive + count) & RS_VAL_MASK));
+    }
+    // block-exclusive scan of count over the 256 digits
+    const unsigned incl = warp_inclusive_scan(count);
+    if (lane == 31) S.warp_tot[warp] = incl;
+    __syncthreads();
+    unsigned wpre = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w)
+      if (w < (int)warp) wpre += S.warp_tot[w];
+    const unsigned start = wpre + incl - count;
+    S.digit_start[d] = start;
+    S.gbase[d] = bins[d] + exclusive - start;
+  }
+  __syncthreads();
+  // 4. tile-sorted order in shared memory, then coalesced runs to global memory
+  unsigned pos[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
+    pos[i] = S.digit_start[d] + S.warp_hist[warp][d] + rank[i];
+    if ((wbase + i * 32) < valid_n) S.keys[pos[i]] = key[i];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const int p = threadIdx.x + i * RS_THREADS;
+    if (p < valid_n) {
+      const KeyT k = S.keys[p];
+      const unsigned d = static_cast<unsigned>(k >> shift) & dmask;
+      kout[S.gbase[d] + p] = tw_out ? twiddle_out(k, kind) : k;
+    }
+  }
+  if constexpr (HAS_VAL) {
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i)
+      if ((wbase + i * 32) < valid_n) s_vals[pos[i]] = val[i];
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int p = threadIdx.x + i * RS_THREADS;
+      if (p < valid_n) {
+        const unsigned d = static_cast<unsigned>(S.keys[p] >> shift) & dmask;
+        vout[S.gbase[d] + p] = s_vals[p];
+      }
+    }
+  }
+}
+
+// ---- host driver ---------------------------------------------------------------------------------------------------
+template <int KB, int VB> struct RsItems { static constexpr int value = 16; };
+template <> struct RsItems<4, 8> { static constexpr int value = 12; };
+template <> struct RsItems<8, 0> { static constexpr int value = 12; };
+template <> struct RsItems<8, 4> { static constexpr int value = 12; };
+template <> struct RsItems<8, 8> { static constexpr int value = 8; };
+
+static int rs_items(int kb, int vb) {
+  if (kb == 4) return vb == 8 ? 12 : 16;
+  return vb == 8 ? 8 : 12;
+}
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct RsLayout {
+  size_t hist_off, lookback_off, keys_off, vals_off, total;
+  int64_t tiles;
+};
+static RsLayout rs_layout(int64_t n, int kb, int vb) {
+  RsLayout L{};
+  const int tile = RS_THREADS * rs_items(kb, vb);
+  L.tiles = n > 0 ? (n + tile - 1) / tile : 1;
+  L.hist_off = RS_HEADER_BYTES;
+  L.lookback_off = align_up(L.hist_off + 8 * RS_RADIX * sizeof(unsigned), 256);
+  L.keys_off = align_up(L.lookback_off + static_cast<size_t>(L.tiles) * RS_RADIX * sizeof(unsigned), 256);
+  L.vals_off = align_up(L.keys_off + static_cast<size_t>(n) * kb, 256);
+  L.total = align_up(L.vals_off + static_cast<size_t>(n) * vb, 256);
+  return L;
+}
+
+size_t sort_tmp_bytes(int64_t n, int key_bytes, int value_bytes) { return rs_layout(n, key_bytes, value_bytes).total; }
+
+template <typename KeyT, typename ValT>
+static void *rs_run(KeyT *keys, ValT *vals, int64_t n, int kind, int begin_bit, int end_bit, void *tmp,
+                    cudaStream_t stream, void **vals_result) {
+  constexpr int KB = sizeof(KeyT);
+  constexpr int VB = std::is_same<ValT, NoValue>::value ? 0 : sizeof(ValT);
+  constexpr int ITEMS = RsItems<KB, VB>::value;
+  constexpr int TILE = RS_THREADS * ITEMS;
+  const RsLayout L = rs_layout(n, KB, VB);
+  const int passes = (end_bit - begin_bit + 7) / 8;
+  char *base = static_cast<char *>(tmp);
+  unsigned *tickets = reinterpret_cast<unsigned *>(base);
+  unsigned *hist = reinterpret_cast<unsigned *>(base + L.hist_off);
+  unsigned *lookback = reinterpret_cast<unsigned *>(base + L.lookback_off);
+  KeyT *kalt = reinterpret_cast<KeyT *>(base + L.keys_off);
+  ValT *valt = reinterpret_cast<ValT *>(base + L.vals_off);
+  const size_t lookback_bytes = static_cast<size_t>(L.tiles) * RS_RADIX * sizeof(unsigned);
+
+  QDSP_CUDA(cudaMemsetAsync(base, 0, L.lookback_off, stream));  // tickets + histograms
+  const int hist_grid = static_cast<int>(std::min<int64_t>((n + RS_THREADS - 1) / RS_THREADS,
+                                                          static_cast<int64_t>(device_props().sm_count) * 8));
+  rs_histogram_kernel<KeyT><<<hist_grid, RS_THREADS, passes * RS_RADIX * sizeof(unsigned), stream>>>(
+      keys, n, kind, begin_bit, end_bit, passes, hist);
+  QDSP_LAUNCH_CHECK();
+  rs_scan_bins_kernel<<<passes, RS_RADIX, 0, stream>>>(hist);
+  QDSP_LAUNCH_CHECK();
+
+  auto kernel = rs_onesweep_kernel<KeyT, ValT, ITEMS>;
+  const size_t smem = sizeof(RsSmem<KeyT, ValT, ITEMS>) + static_cast<size_t>(TILE) * (VB ? VB : 0);
+  static bool attr_set = false;  // per instantiation
+  if (!attr_set) {
+    QDSP_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    attr_set = true;
+  }
+  KeyT *kin = keys, *kout = kalt;
+  ValT *vin = vals, *vout = valt;
+  for (int p = 0; p < passes; ++p) {
+    const int shift = begin_bit + 8 * p;
+    const int nbits = std::min(8, end_bit - shift);
+    QDSP_CUDA(cudaMemsetAsync(lookback, 0, lookback_bytes, stream));
+    kernel<<<static_cast<unsigned>(L.tiles), RS_THREADS, smem, stream>>>(
+        kin, kout, vin, vout, n, shift, nbits, kind, p == 0, p == passes - 1, tickets + p, lookback,
+        hist + p * RS_RADIX);
+    QDSP_LAUNCH_CHECK();
+    std::swap(kin, kout);
+    std::swap(vin, vout);
+  }
+  if (vals_result) *vals_result = vin;
+  return kin;  // where the sorted keys now live (caller buffer if `passes` is even)
+}
+
+// Sorts in place: if the pass count is odd the result is copied back from the scratch buffer.
+template <typename KeyT, typename ValT>
+static void rs_sort_inplace(KeyT *keys, ValT *vals, int64_t n, int kind, int begin_bit, int end_bit, void *tmp,
+                            cudaStream_t stream) {
+  void *vres = nullptr;
+  void *kres = rs_run<KeyT, ValT>(keys, vals, n, kind, begin_bit, end_bit, tmp, stream, &vres);
+  if (kres != keys) {
+    QDSP_CUDA(cudaMemcpyAsync(keys, kres, static_cast<size_t>(n) * sizeof(KeyT), cudaMemcpyDeviceToDevice, stream));
+    if constexpr (!std::is_same<ValT, NoValue>::value)
+      QDSP_CUDA(cudaMemcpyAsync(vals, vres, static_cast<size_t>(n) * sizeof(ValT), cudaMemcpyDeviceToDevice, stream));
+  }
+}
+
+static int key_bytes_of(int kind) { return kind == QDSP_KEY_U64 ? 8 : 4; }
+
+// Public entry: in-place ascending stable sort of `keys` (and `values`).
+void sort_pairs(void *keys, void *values, int64_t n, int key_kind, int value_bytes, void *tmp, size_t tmp_bytes,
+                cudaStream_t stream) {
+  QDSP_REQUIRE(n >= 0, QDSP_ERR_INVALID, "sort: negative length");
+  QDSP_REQUIRE(key_kind >= QDSP_KEY_U32 && key_kind <= QDSP_KEY_U64, QDSP_ERR_INVALID, "sort: bad key kind");
+  QDSP_REQUIRE(value_bytes == 0 || value_bytes == 4 || value_bytes == 8, QDSP_ERR_INVALID,
+               "sort: value_bytes must be 0, 4 or 8");
+  QDSP_REQUIRE(n < (int64_t{1} << 30), QDSP_ERR_UNSUPPORTED, "sort: n must be below 2^30");
+  if (values == nullptr) value_bytes = 0;
+  if (n <= 1) return;
+  QDSP_REQUIRE(keys != nullptr && tmp != nullptr, QDSP_ERR_INVALID, "sort: null pointer");
+  const int kb = key_bytes_of(key_kind);
+  QDSP_REQUIRE(tmp_bytes >= sort_tmp_bytes(n, kb, value_bytes), QDSP_ERR_INVALID, "sort: tmp buffer too small");
+  const int end_bit = kb * 8;
+  if (kb == 4) {
+    auto *k = static_cast<uint32_t *>(keys);
+    if (value_bytes == 0) rs_sort_inplace<uint32_t, NoValue>(k, nullptr, n, key_kind, 0, end_bit, tmp, stream);
+    else if (value_bytes == 4) rs_sort_inplace<uint32_t, uint32_t>(k, static_cast<uint32_t *>(values), n, key_kind, 0, end_bit, tmp, stream);
+    else rs_sort_inplace<uint32_t, uint64_t>(k, static_cast<uint64_t *>(values), n, key_kind, 0, end_bit, tmp, stream);
+  } else {
+    auto *k = static_cast<uint64_t *>(keys);
+    if (value_bytes == 0) rs_sort_inplace<uint64_t, NoValue>(k, nullptr, n, key_kind, 0, end_bit, tmp, stream);
+    else if (value_bytes == 4) rs_sort_inplace<uint64_t, uint32_t>(k, static_cast<uint32_t *>(values), n, key_kind, 0, end_bit, tmp, stream);
+    else rs_sort_inplace<uint64_t, uint64_t>(k, static_cast<uint64_t *>(values), n, key_kind, 0, end_bit, tmp, stream);
+  }
+}
+
+// Internal entry for the CSR build: sorts only bits [0, key_bits) and returns where the result lives (no copy back).
+void sort_build_keys(void *keys, void *values, int64_t n, int key_bytes, int value_bytes, int key_bits, void *tmp,
+                     cudaStream_t stream, void **keys_out, void **values_out) {
+  QDSP_REQUIRE(n < (int64_t{1} << 30), QDSP_ERR_UNSUPPORTED, "build: more than 2^30 triplets");
+  if (key_bits < 1) key_bits = 1;
+  void *kr = nullptr, *vr = nullptr;
+  if (key_bytes == 4) {
+    if (value_bytes == 4) kr = rs_run<uint32_t, uint32_t>(static_cast<uint32_t *>(keys), static_cast<uint32_t *>(values), n, QDSP_KEY_U32, 0, key_bits, tmp, stream, &vr);
+    else kr = rs_run<uint32_t, uint64_t>(static_cast<uint32_t *>(keys), static_cast<uint64_t *>(values), n, QDSP_KEY_U32, 0, key_bits, tmp, stream, &vr);
+  } else {
+    if (value_bytes == 4) kr = rs_run<uint64_t, uint32_t>(static_cast<uint64_t *>(keys), static_cast<uint32_t *>(values), n, QDSP_KEY_U64, 0, key_bits, tmp, stream, &vr);
+    else kr = rs_run<uint64_t, uint64_t>(static_cast<uint64_t *>(keys), static_cast<uint64_t *>(values), n, QDSP_KEY_U64, 0, key_bits, tmp, stream, &vr);
+  }
+  *keys_out = kr;
+  *values_out = vr;
+}
+
+}  // namespace qdsp

@@ -1,0 +1,572 @@
+"""Parity of the CUDA path against the oracle, through the public API (-> ctypes -> C ABI -> kernels).  Needs a B200.
+
+Bars (BASELINE.json): CSR indptr / indices / values, sort and scan outputs: bit-exact.  SpMV: bit-exact where the
+stream path mirrors Eigen's order (all short-row matrices), else |y_i - y_ref_i| <= eps * sum_j |a_ij x_j| with
+eps = 1e-5 (fp32) / 1e-12 (fp64).  CG: same stopping rule and budget; see test_cg_* for the tolerances.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import make_triplet_buffer
+from tests import workloads as W
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "eigen_golden.npz")
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32 if a.dtype.itemsize == 4 else np.uint64)
+
+
+@pytest.fixture(scope="module")
+def qd():
+    import quadrants_b200 as qd
+
+    qd.init(arch=qd.cuda)
+    return qd
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(GOLD)
+
+
+def qd_dtype(qd, np_dtype):
+    return {np.dtype(np.float32): qd.f32, np.dtype(np.float64): qd.f64, np.dtype(np.int32): qd.i32,
+            np.dtype(np.uint32): qd.u32}[np.dtype(np_dtype)]
+
+
+def build_from_buffer(qd, buf, rows, cols, storage_format="col_major"):
+    dt = qd.f32 if buf.dtype == np.int32 else qd.f64
+    n = int(buf[0])
+    K = qd.linalg.SparseMatrixBuilder(rows, cols, max_num_triplets=max(n, 1), dtype=dt, storage_format=storage_format)
+    K.ptr.fill_from_host(buf)
+    return K.build()
+
+
+def to_nd(qd, a):
+    x = qd.ndarray(qd_dtype(qd, a.dtype), a.shape[0])
+    x.from_numpy(a)
+    return x
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# scan (A14)
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [512, 1024, 4096])
+@pytest.mark.parametrize("offset", [0, -1, 1, 256, -256, -23333, 23333])
+def test_scan_reference_cases(qd, oracle, n, offset):
+    # tests/python/test_scan.py:9-63
+    rng = np.random.default_rng(n + offset)
+    a = (rng.random(n) * n).astype(np.int32)
+    arr = qd.field(qd.i32, n, offset=offset)
+    arr.from_numpy(a)
+    ex = qd.algorithms.PrefixSumExecutor(n)
+    ex.run(arr)
+    out = arr.to_numpy()
+    assert np.array_equal(out, oracle.inclusive_scan(a))
+    assert arr[offset] == a[0] and arr[n - 1 + offset] == int(np.sum(a, dtype=np.int64))
+
+
+@pytest.mark.parametrize("n", [1, 2, 31, 4095, 4097, 100001, (1 << 22) + 13])
+def test_scan_wrapping_random(qd, oracle, n):
+    rng = np.random.default_rng(5)
+    a = rng.integers(-2**31, 2**31, n, dtype=np.int64).astype(np.int32)
+    arr = qd.field(qd.i32, n)
+    arr.from_numpy(a)
+    qd.algorithms.PrefixSumExecutor(n).run(arr)
+    assert np.array_equal(arr.to_numpy(), oracle.inclusive_scan(a))
+
+
+def test_scan_full_size_2p28(qd):
+    """C3 at full size: bit-exact against numpy's wrapping cumsum (the oracle's definition), 2^28 random i32."""
+    import torch
+
+    n = 1 << 28
+    g = torch.Generator(device="cuda").manual_seed(5)
+    t = torch.randint(-2**31, 2**31, (n,), dtype=torch.int64, device="cuda", generator=g).to(torch.int32)
+    arr = qd.field(qd.i32, n)
+    arr.tensor.copy_(t)
+    ex = qd.algorithms.PrefixSumExecutor(n)
+    ex.run(arr)
+    ref = np.cumsum(t.cpu().numpy(), dtype=np.int32)
+    assert np.array_equal(arr.to_numpy(), ref)
+    # idempotence of the executor object (scratch is re-initialised on every run)
+    arr.tensor.copy_(t)
+    ex.run(arr)
+    assert np.array_equal(arr.to_numpy(), ref)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# sort (A13)
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", [np.int32, np.float32])
+@pytest.mark.parametrize("n", [1, 256, 100001])
+@pytest.mark.parametrize("offset", [0, -1, 128, -23333])
+def test_sort_reference_cases(qd, oracle, dtype, n, offset):
+    # tests/python/test_sort.py:9-62: keys = floor(rand*N), values = keys
+    rng = np.random.default_rng(n)
+    k = (rng.random(n) * n).astype(dtype)
+    keys = qd.field(qd_dtype(qd, dtype), n, offset=offset)
+    values = qd.field(qd_dtype(qd, dtype), n, offset=offset)
+    keys.from_numpy(k)
+    values.from_numpy(k)
+    qd.algorithms.parallel_sort(keys, values)
+    kh, vh = keys.to_numpy(), values.to_numpy()
+    assert np.all(kh[:-1] <= kh[1:]) and np.array_equal(bits(kh), bits(vh))
+    ok, _ = oracle.stable_sort(k, None)
+    assert np.array_equal(bits(kh), bits(ok))
+
+
+@pytest.mark.parametrize("dtype", [np.uint32, np.int32, np.float32])
+@pytest.mark.parametrize("n", [2, 257, 4096, 4097, 65536, 1000003])
+def test_sort_stable_vs_oracle(qd, oracle, dtype, n):
+    # tests/python/test_algorithms.py:541-590 style: ties, +-0, +-inf, denormals; payload = original index
+    rng = np.random.default_rng(1357)
+    if dtype == np.float32:
+        k = rng.standard_normal(n).astype(np.float32)
+        sp = np.array([0.0, -0.0, np.inf, -np.inf, 1e-45, -1e-45, 1.0, -1.0], np.float32)
+        k[: min(8, n)] = sp[: min(8, n)]
+        rng.shuffle(k)
+    else:
+        info = np.iinfo(dtype)
+        k = rng.integers(info.min, info.max, n, dtype=np.int64, endpoint=True).astype(dtype)
+    k[: n // 3] = k[n // 3: 2 * (n // 3)]  # many ties
+    v = np.arange(n, dtype=np.uint32)
+    keys, values = to_nd(qd, k), to_nd(qd, v)
+    qd.algorithms.parallel_sort(keys, values)
+    ok, ov = oracle.stable_sort(k, v)
+    assert np.array_equal(bits(keys.to_numpy()), bits(ok))
+    assert np.array_equal(values.to_numpy(), ov)
+
+
+def test_sort_keys_only_and_small_range(qd, oracle):
+    rng = np.random.default_rng(3)
+    k = rng.integers(0, 16, 300000).astype(np.int32)
+    keys = to_nd(qd, k)
+    qd.algorithms.parallel_sort(keys)
+    assert np.array_equal(keys.to_numpy(), np.sort(k))
+
+
+def test_sort_full_size_2p28(qd):
+    """C3 at full size (2^28 i32 keys, values = arange): sortedness, stability (values ascending inside each run of equal
+    keys <=> (key, value) pairs strictly increasing), permutation (checksum of values and of keys)."""
+    import torch
+
+    n = 1 << 28
+    g = torch.Generator(device="cuda").manual_seed(4)
+    k = torch.randint(-2**31, 2**31, (n,), dtype=torch.int64, device="cuda", generator=g).to(torch.int32)
+    ksum = int(k.to(torch.int64).sum().item())
+    keys, values = qd.field(qd.i32, n), qd.field(qd.i32, n)
+    keys.tensor.copy_(k)
+    values.tensor.copy_(torch.arange(n, dtype=torch.int32, device="cuda"))
+    qd.algorithms.parallel_sort(keys, values)
+    ks, vs = keys.tensor, values.tensor
+    assert bool((ks[1:] >= ks[:-1]).all())
+    tie = ks[1:] == ks[:-1]
+    assert int(tie.sum().item()) > 1_000_000  # ~8.4 M tied pairs expected
+    assert bool((vs[1:][tie] > vs[:-1][tie]).all())
+    assert int(ks.to(torch.int64).sum().item()) == ksum
+    assert int(vs.to(torch.int64).sum().item()) == n * (n - 1) // 2
+    assert bool((k[vs.to(torch.int64)] == ks).all())  # values really are the permutation that sorts the keys
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# build (A1-A5)
+# ---------------------------------------------------------------------------------------------------------------------
+NAMES = ["poisson2d_float32", "poisson2d_float64", "random_float32", "random_float64", "fem_float32", "fem_float64"]
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_build_bit_exact_vs_eigen_fixture(qd, gold, name):
+    rows, cols = (int(v) for v in gold[f"{name}/shape"])
+    A = build_from_buffer(qd, gold[f"{name}/buf"], rows, cols)
+    ip, ix, v = A.matrix.to_scipy_arrays()
+    assert np.array_equal(ip, gold[f"{name}/rm/outer"])
+    assert np.array_equal(ix, gold[f"{name}/rm/inner"])
+    assert np.array_equal(bits(v), bits(gold[f"{name}/rm/vals"]))
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_build_c1_poisson512_vs_oracle(qd, oracle, dtype):
+    r, c, v = W.poisson2d_triplets(512, dtype=dtype, split_diag=True)
+    p = np.random.default_rng(0).permutation(r.shape[0])
+    buf = make_triplet_buffer(r[p], c[p], v[p], dtype)
+    n = 512 * 512
+    A = build_from_buffer(qd, buf, n, n)
+    ip, ix, vals = A.matrix.to_scipy_arrays()
+    oo, oi, ov = oracle.build_matrix(buf, n, n, True)
+    assert ip[-1] == 1308672
+    assert np.array_equal(ip, oo) and np.array_equal(ix, oi) and np.array_equal(bits(vals), bits(ov))
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_build_random_duplicates_vs_oracle(qd, oracle, dtype):
+    # C4 in miniature, non-square, > 32 key bits is NOT needed here (u32 keys); the u64 path is covered below
+    r, c, v = W.random_triplets(5000, 7000, 140000, 60000, seed=6, dtype=dtype)
+    buf = make_triplet_buffer(r, c, v, dtype)
+    A = build_from_buffer(qd, buf, 5000, 7000)
+    ip, ix, vals = A.matrix.to_scipy_arrays()
+    oo, oi, ov = oracle.build_matrix(buf, 5000, 7000, True)
+    assert np.array_equal(ip, oo) and np.array_equal(ix, oi) and np.array_equal(bits(vals), bits(ov))
+
+
+def test_build_u64_keys_and_empty_rows(qd, oracle):
+    # rows*cols needs 40 key bits -> u64 keys; the reference's host dedupe overflows int here (sparse_matrix.cpp:188)
+    rows, cols = 1 << 20, 1 << 20
+    rng = np.random.default_rng(9)
+    r = rng.integers(0, rows, 300000) // 7 * 7   # most rows empty
+    c = rng.integers(0, cols, 300000)
+    r[:1000], c[:1000] = r[1000:2000], c[1000:2000]
+    v = rng.uniform(-1, 1, 300000).astype(np.float32)
+    buf = make_triplet_buffer(r, c, v, np.float32)
+    A = build_from_buffer(qd, buf, rows, cols)
+    ip, ix, vals = A.matrix.to_scipy_arrays()
+    oo, oi, ov = oracle.build_matrix(buf, rows, cols, True)
+    assert np.array_equal(ip, oo) and np.array_equal(ix, oi) and np.array_equal(bits(vals), bits(ov))
+
+
+def test_build_edge_cases(qd, oracle):
+    # empty builder
+    K = qd.linalg.SparseMatrixBuilder(5, 3, max_num_triplets=10)
+    A = K.build()
+    ip, ix, v = A.matrix.to_scipy_arrays()
+    assert ip.tolist() == [0] * 6 and ix.size == 0
+    # single triplet, 1x1, all-duplicates, explicit zeros kept, builder reusable after build
+    K = qd.linalg.SparseMatrixBuilder(1, 1, max_num_triplets=100)
+    K.insert_triplets([0] * 50, [0] * 50, np.full(50, 0.1, np.float32))
+    A = K.build()
+    want = np.float32(0)
+    for _ in range(50):
+        want = np.float32(want + np.float32(0.1)) if _ else np.float32(0.1)
+    assert A[0, 0] == float(want)
+    K[0, 0] += 2.0
+    K[0, 0] -= 0.5
+    A2 = K.build()
+    assert A2[0, 0] == 1.5
+    K2 = qd.linalg.SparseMatrixBuilder(4, 4, max_num_triplets=20)
+    K2.insert_triplets([1, 3, 1], [3, 0, 3], np.array([1.0, 0.0, -1.0], np.float32))
+    A3 = K2.build()
+    ip, ix, v = A3.matrix.to_scipy_arrays()
+    assert ip.tolist() == [0, 0, 1, 1, 2] and ix.tolist() == [3, 0] and v.tolist() == [0.0, 0.0]
+    # out-of-range index -> error, not UB
+    K3 = qd.linalg.SparseMatrixBuilder(4, 4, max_num_triplets=20)
+    K3.insert_triplets([1, 4], [0, 0], np.array([1.0, 1.0], np.float32))
+    with pytest.raises(RuntimeError):
+        K3.build()
+
+
+def test_build_20m_triplets_properties(qd):
+    """C4 scaled to 20 M triplets (u64 keys, 30 % repeats): size-independent properties checked on the device."""
+    import torch
+
+    rows = cols = 1 << 24
+    nu, nd = 14_000_000, 6_000_000
+    g = torch.Generator(device="cuda").manual_seed(6)
+    r = torch.randint(0, rows, (nu,), device="cuda", generator=g)
+    c = torch.randint(0, cols, (nu,), device="cuda", generator=g)
+    pick = torch.randint(0, nu, (nd,), device="cuda", generator=g)
+    r, c = torch.cat([r, r[pick]]), torch.cat([c, c[pick]])
+    perm = torch.randperm(nu + nd, device="cuda", generator=g)
+    r, c = r[perm], c[perm]
+    v = torch.rand(nu + nd, device="cuda", generator=g, dtype=torch.float32) * 2 - 1
+    K = qd.linalg.SparseMatrixBuilder(rows, cols, max_num_triplets=nu + nd)
+    K.insert_triplets(r, c, v)
+    A = K.build()
+    ip, ix, vals = A.matrix.csr_tensors()
+    key = r * cols + c
+    uniq = torch.unique(key)
+    assert A.matrix.nnz() == uniq.numel() == int(ip[-1].item())
+    assert bool((ip[1:] >= ip[:-1]).all())
+    rows_of = torch.repeat_interleave(torch.arange(rows, device="cuda"), (ip[1:] - ip[:-1]).to(torch.int64))
+    got = rows_of * cols + ix.to(torch.int64)
+    assert bool((got[1:] > got[:-1]).all()) and bool((got == uniq).all())
+    assert abs(float(vals.double().sum().item()) - float(v.double().sum().item())) < 1e-2
+    # linearity check of the build: A @ 1 == row sums of the triplets
+    ones = qd.ndarray(qd.f32, cols)
+    ones.fill(1.0)
+    y = (A @ ones).tensor.double()
+    ref = torch.zeros(rows, dtype=torch.float64, device="cuda").index_add_(0, r, v.double())
+    assert float((y - ref).abs().max().item()) < 1e-4
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# SpMV (A7/A8)
+# ---------------------------------------------------------------------------------------------------------------------
+def test_spmv_g1_known_answer(qd):
+    # tests/python/test_sparse_matrix.py:414-451
+    K = qd.linalg.SparseMatrixBuilder(num_rows=4, num_cols=4, dtype=qd.f32, max_num_triplets=50)
+    K.insert_triplets([0, 0, 0, 1, 2, 2, 2, 3, 3], [0, 2, 3, 1, 0, 2, 3, 1, 3], np.arange(1, 10, dtype=np.float32))
+    A = K.build()
+    X = to_nd(qd, np.array([1, 2, 3, 4], np.float32))
+    Y = A @ X
+    assert [Y[i] for i in range(4)] == [19.0, 8.0, 51.0, 52.0]
+    assert (A @ np.array([1, 2, 3, 4], np.float32)).tolist() == [19.0, 8.0, 51.0, 52.0]  # host-buffer entry point
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("fmt", ["col_major", "row_major"])
+def test_spmv_g2_g3(qd, dtype, fmt):
+    # tests/python/test_spmv.py:18-103 and test_sparse_matrix.py:44-57,395-411
+    n = 8
+    i, j = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    for case, val, want in (("i", i, [8 * k for k in range(n)]), ("i-j", i - j, [-28, -20, -12, -4, 4, 12, 20, 28]),
+                            ("i+j", i + j, [28, 36, 44, 52, 60, 68, 76, 84])):
+        K = qd.linalg.SparseMatrixBuilder(n, n, max_num_triplets=100, dtype=qd_dtype(qd, dtype), storage_format=fmt)
+        K.insert_triplets(i.ravel(), j.ravel(), val.ravel().astype(dtype))
+        A = K.build()
+        x = qd.ndarray(qd_dtype(qd, dtype), n)
+        x.fill(1.0)
+        assert (A @ x).to_numpy().tolist() == [float(w) for w in want]
+        if case == "i+j":
+            for a in range(n):
+                for b in range(n):
+                    assert A[a, b] == float(a + b)
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("fmt", ["col_major", "row_major"])
+def test_spmv_vs_eigen_fixture(qd, gold, name, fmt):
+    """Short-row matrices take the stream path, whose fma order mirrors Eigen's product for the builder's
+    storage_format: bit-exact.  The power-law FEM fixture has slices on the warp-per-row path: tolerance."""
+    rows, cols = (int(v) for v in gold[f"{name}/shape"])
+    A = build_from_buffer(qd, gold[f"{name}/buf"], rows, cols, storage_format=fmt)
+    x = gold[f"{name}/x"]
+    y = (A @ to_nd(qd, x)).to_numpy()
+    tag = "cm" if fmt == "col_major" else "rm"
+    yref = gold[f"{name}/{tag}/y"]
+    ip, ix, v = gold[f"{name}/rm/outer"], gold[f"{name}/rm/inner"], gold[f"{name}/rm/vals"]
+    lens = np.diff(ip)
+    slice_mean = np.add.reduceat(lens, np.arange(0, rows, 256)) / np.minimum(256, rows - np.arange(0, rows, 256))
+    if slice_mean.max() <= 24:
+        assert np.array_equal(bits(y), bits(yref))
+    else:
+        scale = np.zeros(rows)
+        np.add.at(scale, np.repeat(np.arange(rows), lens), np.abs(v.astype(np.float64) * x[ix].astype(np.float64)))
+        eps = 1e-5 if x.dtype == np.float32 else 1e-12
+        assert np.all(np.abs(y.astype(np.float64) - yref) <= eps * scale + 1e-300)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_spmv_c1_bit_exact_and_long_rows(qd, oracle, dtype):
+    r, c, v = W.poisson2d_triplets(512, dtype=dtype)
+    n = 512 * 512
+    buf = make_triplet_buffer(r, c, v, dtype)
+    x = np.random.default_rng(1).uniform(-1, 1, n).astype(dtype)
+    for fmt, rm in (("col_major", False), ("row_major", True)):
+        A = build_from_buffer(qd, buf, n, n, storage_format=fmt)
+        y = (A @ to_nd(qd, x)).to_numpy()
+        oo, oi, ov = oracle.build_matrix(buf, n, n, rm)
+        assert np.array_equal(bits(y), bits(oracle.spmv(oo, oi, ov, x, n, n, rm)))
+    # a matrix with a few very long rows among short ones (chunked stream path + vector path in one launch)
+    rng = np.random.default_rng(2)
+    rows = 3000
+    rr = np.concatenate([np.repeat(np.arange(rows), 3), np.full(40000, 5), np.full(9000, 2900)])
+    cc = rng.integers(0, rows, rr.shape[0])
+    vv = rng.uniform(-1, 1, rr.shape[0]).astype(dtype)
+    buf = make_triplet_buffer(rr, cc, vv, dtype)
+    A = build_from_buffer(qd, buf, rows, rows)
+    xs = rng.uniform(-1, 1, rows).astype(dtype)
+    y = (A @ to_nd(qd, xs)).to_numpy().astype(np.float64)
+    oo, oi, ov = oracle.build_matrix(buf, rows, rows, True)
+    yref = oracle.spmv(oo, oi, ov, xs, rows, rows, True).astype(np.float64)
+    scale = np.zeros(rows)
+    np.add.at(scale, np.repeat(np.arange(rows), np.diff(oo)), np.abs(ov.astype(np.float64) * xs[oi]))
+    eps = 1e-5 if dtype == np.float32 else 1e-12
+    assert np.all(np.abs(y - yref) <= eps * scale + 1e-300)
+
+
+def test_spmv_c2_poisson3d_256_full_size(qd):
+    """C2 at full size (16.7 M rows, 117 M nnz): built on the device from 117 M triplets; nnz and indptr checked in
+    closed form, y = A x checked against the 7-point stencil applied with torch (fp64 accumulate) at the per-row
+    1e-5 tolerance, and linearity A(ax+by) = aAx + bAy."""
+    import torch
+
+    n = 256
+    N = n ** 3
+    idx = torch.arange(N, device="cuda", dtype=torch.int64)
+    i, j, k = idx // (n * n), (idx // n) % n, idx % n
+    rows, cols, vals = [idx], [idx], [torch.full((N,), 6.0, device="cuda")]
+    for ok, off in ((i > 0, -n * n), (i < n - 1, n * n), (j > 0, -n), (j < n - 1, n), (k > 0, -1), (k < n - 1, 1)):
+        rows.append(idx[ok]); cols.append(idx[ok] + off); vals.append(torch.full((int(ok.sum()),), -1.0, device="cuda"))
+    r, c, v = torch.cat(rows), torch.cat(cols), torch.cat(vals)
+    nnz = r.numel()
+    assert nnz == 117047296 - 0 or nnz == 7 * N - 6 * n * n
+    K = qd.linalg.SparseMatrixBuilder(N, N, max_num_triplets=nnz)
+    K.insert_triplets(r, c, v)
+    del rows, cols, vals, r, c, v
+    A = K.build()
+    del K
+    assert A.matrix.nnz() == 7 * N - 6 * n * n
+    g = torch.Generator(device="cuda").manual_seed(2)
+    x = qd.ndarray(qd.f32, N)
+    x.tensor.copy_(torch.rand(N, device="cuda", generator=g) * 2 - 1)
+    y = (A @ x).tensor
+
+    def stencil(t):
+        t3 = t.double().view(n, n, n)
+        out = 6.0 * t3
+        out[1:] -= t3[:-1]; out[:-1] -= t3[1:]
+        out[:, 1:] -= t3[:, :-1]; out[:, :-1] -= t3[:, 1:]
+        out[:, :, 1:] -= t3[:, :, :-1]; out[:, :, :-1] -= t3[:, :, 1:]
+        return out.view(-1)
+
+    ref = stencil(x.tensor)
+    scale = stencil(-x.tensor.abs()) + 12.0 * x.tensor.abs().double()  # sum_j |a_ij x_j|
+    assert bool(((y.double() - ref).abs() <= 1e-5 * scale + 1e-30).all())
+    x2 = qd.ndarray(qd.f32, N)
+    x2.tensor.copy_(torch.rand(N, device="cuda", generator=g))
+    y2 = (A @ x2).tensor
+    x3 = qd.ndarray(qd.f32, N)
+    x3.tensor.copy_(2.0 * x.tensor + 0.5 * x2.tensor)
+    y3 = (A @ x3).tensor
+    assert float((y3 - (2.0 * y + 0.5 * y2)).abs().max().item()) < 1e-4
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# CG (A9/A10)
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["poisson2d_float32", "poisson2d_float64", "fem_float32", "fem_float64"])
+def test_cg_vs_eigen_fixture(qd, gold, name):
+    rows, cols = (int(v) for v in gold[f"{name}/shape"])
+    A = build_from_buffer(qd, gold[f"{name}/buf"], rows, cols)
+    ok_ref, it_ref, err_ref, tol, budget = gold[f"{name}/cg/meta"]
+    b = gold[f"{name}/cg/b"]
+    cg = qd.linalg.SparseCG(A, to_nd(qd, b), max_iter=int(budget), atol=float(tol))
+    x, ok = cg.solve()
+    x = x.to_numpy()
+    xr = gold[f"{name}/cg/x"]
+    f32 = b.dtype == np.float32
+    assert ok == bool(ok_ref)
+    assert cg.error <= tol
+    # same stopping rule, same budget; reduction order differs from Eigen's packets, so the stopping iteration may
+    # move by a few in fp32
+    assert abs(cg.iterations - it_ref) <= (0.25 * it_ref if f32 else 2)
+    rel = np.linalg.norm(x.astype(np.float64) - xr) / np.linalg.norm(xr)
+    assert rel < ((2e-3 if name.startswith("fem") else 1e-5) if f32 else 1e-9)
+    # numpy right-hand side -> numpy solution (the reference's CPU call shape)
+    x2, ok2 = qd.linalg.SparseCG(A, b, max_iter=int(budget), atol=float(tol)).solve()
+    assert ok2 and isinstance(x2, np.ndarray) and np.array_equal(bits(x2), bits(x))
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_cg_g5_10x10(qd, dtype):
+    # tests/python/test_sparse_cg.py:9-70
+    i, j, v, a, b = W.spd_dense_10(0, dtype)
+    K = qd.linalg.SparseMatrixBuilder(10, 10, max_num_triplets=500, dtype=qd_dtype(qd, dtype))
+    K.insert_triplets(i, j, v)
+    A = K.build()
+    x, ok = qd.linalg.SparseCG(A, to_nd(qd, b), max_iter=50, atol=1e-6).solve()
+    x = x.to_numpy()
+    res = np.linalg.norm(a.astype(np.float64) @ x - b) / np.linalg.norm(b)
+    assert res < (5e-3 if dtype == np.float32 else 1e-5)
+    want = np.linalg.solve(a.astype(np.float64), b.astype(np.float64))
+    assert np.allclose(x, want, rtol=1.0, atol=1e-2 * np.abs(want).max())
+    if dtype == np.float32:  # reference CUDA semantics
+        x2, ok2 = qd.linalg.SparseCG(A, to_nd(qd, b), max_iter=50, atol=1e-6, semantics="cucg").solve()
+        assert ok2 is True
+        res2 = np.linalg.norm(a.astype(np.float64) @ x2.to_numpy() - b) / np.linalg.norm(b)
+        assert res2 < 5e-2
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_cg_c1_poisson512(qd, oracle, dtype):
+    """C1: CG to 1e-6 (budget 2000) against the oracle (== the reference's Eigen, bit for bit)."""
+    r, c, v = W.poisson2d_triplets(512, dtype=dtype)
+    n = 512 * 512
+    buf = make_triplet_buffer(r, c, v, dtype)
+    A = build_from_buffer(qd, buf, n, n)
+    b = np.ones(n, dtype)
+    cg = qd.linalg.SparseCG(A, to_nd(qd, b), max_iter=2000, atol=1e-6)
+    x, ok = cg.solve()
+    x = x.to_numpy().astype(np.float64)
+    oo, oi, ov = oracle.build_matrix(buf, n, n, False)
+    xo, oko, ito, erro = oracle.cg(oo, oi, ov, b, 2000, 1e-6)
+    assert ok and oko
+    assert abs(cg.iterations - ito) <= 0.15 * ito
+    # true residual of the GPU solution, fp64
+    import scipy.sparse as sp
+    Ad = sp.csr_matrix((ov.astype(np.float64), oi, oo), shape=(n, n))
+    res = np.linalg.norm(Ad @ x - b) / np.linalg.norm(b)
+    assert res < (5e-6 if dtype == np.float32 else 1.5e-6)
+    rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+    # cond(A) ~ 1e5: two fp32 solves that both meet |r|/|b| <= 1e-6 agree to ~1e-2 at best; fp64 to ~1e-6
+    assert rel < (2e-2 if dtype == np.float32 else 1e-5)
+    # SparseCG's default budget (max_iter=50) cannot converge here: success flag must say so
+    x50, ok50 = qd.linalg.SparseCG(A, to_nd(qd, b)).solve()
+    assert ok50 is False
+
+
+def test_cucg_vs_oracle(qd, oracle):
+    r, c, v = W.poisson2d_triplets(64, dtype=np.float32)
+    n = 64 * 64
+    buf = make_triplet_buffer(r, c, v, np.float32)
+    A = build_from_buffer(qd, buf, n, n)
+    b = np.random.default_rng(3).uniform(-1, 1, n).astype(np.float32)
+    cg = qd.linalg.SparseCG(A, to_nd(qd, b), max_iter=500, atol=1e-4, semantics="cucg")
+    x, ok = cg.solve()
+    oo, oi, ov = oracle.build_matrix(buf, n, n, True)
+    xo, k, r1 = oracle.cucg(oo, oi, ov, b, 500, 1e-4)
+    assert ok is True and abs(cg.iterations - k) <= max(3, 0.1 * k)
+    assert cg.error <= 1e-8 and r1 <= 1e-8
+    assert np.linalg.norm(x.to_numpy() - xo) / np.linalg.norm(xo) < 1e-4
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# matrix algebra (A15) and I/O
+# ---------------------------------------------------------------------------------------------------------------------
+def test_g4_sparse_matrix_ops(qd, tmp_path):
+    # tests/python/test_sparse_matrix.py:454-523
+    from numpy.random import default_rng
+    from scipy import stats
+    from scipy.sparse import random
+
+    rng = default_rng(2)
+    rvs = stats.poisson(3, loc=1).rvs
+    S1 = random(5, 4, density=0.5, random_state=rng, data_rvs=rvs).astype(np.float32).tocoo()
+    S2 = random(5, 4, density=0.5, random_state=rng, data_rvs=rvs).astype(np.float32).tocoo()
+
+    def mk(S):
+        K = qd.linalg.SparseMatrixBuilder(num_rows=5, num_cols=4, dtype=qd.f32, max_num_triplets=S.nnz)
+        K.insert_triplets(S.row, S.col, S.data)
+        return K.build()
+
+    A, B = mk(S1), mk(S2)
+
+    def verify(S, Q):
+        S = S.tocoo()
+        assert Q.shape == S.shape
+        for i, j, v in zip(S.row, S.col, S.data):
+            assert v == pytest.approx(Q[i, j], rel=1e-5)
+
+    C = A + B
+    verify(S1 + S2, C)
+    verify((S1 + S2) - S1, C - A)
+    verify(S1 * 2.5, A * 2.5)
+    verify(S1 * 2.5, 2.5 * A)
+    verify(S1.T, A.transpose())
+    verify(S1 @ S2.T, A @ B.transpose())
+    p = tmp_path / "a.mtx"
+    A.mmwrite(str(p))
+    from scipy.io import mmread
+    assert np.array_equal(mmread(str(p)).toarray(), S1.toarray())
+    assert "[" in str(A)
+
+
+def test_error_behaviour(qd):
+    K = qd.linalg.SparseMatrixBuilder(4, 4, max_num_triplets=4)
+    with pytest.raises(RuntimeError):
+        K.insert_triplets([0] * 5, [0] * 5, np.zeros(5, np.float32))  # overflow of max_num_triplets
+    A = K.build()
+    x = qd.ndarray(qd.f32, 5)
+    with pytest.raises(qd.QuadrantsRuntimeError):
+        A @ x
+    with pytest.raises(qd.QuadrantsRuntimeError):
+        A @ "nope"
+    with pytest.raises(RuntimeError):
+        qd.algorithms.PrefixSumExecutor(8).run(qd.ndarray(qd.f32, 8))
+    with pytest.raises(RuntimeError):
+        qd.linalg.SparseMatrixBuilder(4, 4, max_num_triplets=4, storage_format="diag")
