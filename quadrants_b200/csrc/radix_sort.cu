@@ -93,6 +93,12 @@ struct RsSmem {
   KeyT keys[RS_THREADS * ITEMS];
 };
 
+// the staged values follow the struct, 16-byte aligned (8-byte values after a 4-byte-aligned struct would fault)
+template <typename KeyT, typename ValT, int ITEMS>
+__host__ __device__ constexpr size_t rs_vals_offset() {
+  return (sizeof(RsSmem<KeyT, ValT, ITEMS>) + 15) / 16 * 16;
+}
+
 template <typename KeyT, typename ValT, int ITEMS>
 __global__ void __launch_bounds__(RS_THREADS)
 rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const ValT *__restrict__ vin,
@@ -103,7 +109,7 @@ rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const 
   constexpr int TILE = RS_THREADS * ITEMS;
   extern __shared__ __align__(16) unsigned char s_raw[];
   auto &S = *reinterpret_cast<RsSmem<KeyT, ValT, ITEMS> *>(s_raw);
-  ValT *s_vals = reinterpret_cast<ValT *>(s_raw + sizeof(RsSmem<KeyT, ValT, ITEMS>));
+  ValT *s_vals = reinterpret_cast<ValT *>(s_raw + rs_vals_offset<KeyT, ValT, ITEMS>());
 
   if (threadIdx.x == 0) S.ticket = atomicAdd(ticket, 1u);
   for (int i = threadIdx.x; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&S.warp_hist[0][0])[i] = 0;
@@ -279,7 +285,7 @@ static void *rs_run(KeyT *keys, ValT *vals, int64_t n, int kind, int begin_bit, 
   QDSP_LAUNCH_CHECK();
 
   auto kernel = rs_onesweep_kernel<KeyT, ValT, ITEMS>;
-  const size_t smem = sizeof(RsSmem<KeyT, ValT, ITEMS>) + static_cast<size_t>(TILE) * (VB ? VB : 0);
+  const size_t smem = rs_vals_offset<KeyT, ValT, ITEMS>() + static_cast<size_t>(TILE) * (VB ? VB : 0);
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     QDSP_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));

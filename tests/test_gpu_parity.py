@@ -60,7 +60,7 @@ def to_nd(qd, a):
 @pytest.mark.parametrize("offset", [0, -1, 1, 256, -256, -23333, 23333])
 def test_scan_reference_cases(qd, oracle, n, offset):
     # tests/python/test_scan.py:9-63
-    rng = np.random.default_rng(n + offset)
+    rng = np.random.default_rng(abs(n + offset))
     a = (rng.random(n) * n).astype(np.int32)
     arr = qd.field(qd.i32, n, offset=offset)
     arr.from_numpy(a)
@@ -486,7 +486,20 @@ def test_cg_c1_poisson512(qd, oracle, dtype):
     oo, oi, ov = oracle.build_matrix(buf, n, n, False)
     xo, oko, ito, erro = oracle.cg(oo, oi, ov, b, 2000, 1e-6)
     assert ok and oko
-    assert abs(cg.iterations - ito) <= 0.15 * ito
+    # fp64: same trajectory as Eigen up to reduction order.  fp32: Eigen's sequential fp32 dots lose orthogonality and
+    # need 1106 iterations here against 828 in fp64; the GPU sums its dots pairwise with double partials,
+    # so its fp32 run tracks the fp64 trajectory (834).  Bar: never slower than the reference, never faster than fp64.
+    if dtype == np.float64:
+        assert abs(cg.iterations - ito) <= 2
+    else:
+        r64, c64, v64 = W.poisson2d_triplets(512, dtype=np.float64)
+        o2, i2, v2 = oracle.build_matrix(make_triplet_buffer(r64, c64, v64, np.float64), n, n, False)
+        x64, ok64, it64, _ = oracle.cg(o2, i2, v2, np.ones(n), 2000, 1e-6)
+        assert ok64 and 0.95 * it64 <= cg.iterations <= 1.05 * ito
+        # and it is at least as close to the fp64 solution as the reference's own fp32 solve is
+        e_gpu = np.linalg.norm(x - x64) / np.linalg.norm(x64)
+        e_ref = np.linalg.norm(xo.astype(np.float64) - x64) / np.linalg.norm(x64)
+        assert e_gpu <= 1.5 * e_ref + 1e-6, (e_gpu, e_ref)
     # true residual of the GPU solution, fp64
     import scipy.sparse as sp
     Ad = sp.csr_matrix((ov.astype(np.float64), oi, oo), shape=(n, n))
