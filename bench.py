@@ -1,0 +1,427 @@
+#!/usr/bin/env python
+"""bench.py -- the headline benchmark of BASELINE.json: CG iterations/s (+ SpMV GB/s against the HBM roofline) on the
+3-D 7-point Poisson matrix 256^3 (16.7 M rows, 117 M non-zeros), fp32, row-block partitioned over 1/2/4/8 B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
+    python bench.py --impl reference [...]                          # the reference's Eigen CPU path on the host cores
+    torchrun --nproc-per-node N ... bench.py --gpus N ...           # one rank per GPU
+
+One "step" = one fixed-budget SparseCG solve of `--iters-per-step` iterations (Eigen/Jacobi recurrence, the convergence
+exit disabled so that every step does the same work).  value = CG iterations per second over all timed steps,
+inputs resident in HBM; e2e = the same through the host-buffer C-ABI call (b H2D, x D2H inside the timed region).
+Prints ONE JSON line on rank 0.  The matrix (1.0 GB) is ~8x the 126 MB L2, so no L2 flush is needed between steps.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# workload: C2 of SURVEY 8(d)
+# ---------------------------------------------------------------------------------------------------------------------
+def poisson3d_triplets_device(n, lo, hi, device):
+    """7-point Laplacian rows of z-planes [lo, hi) of an n^3 grid, global numbering r = (i*n + j)*n + k; diag 6,
+    off-diag -1 (Dirichlet).  Emitted diagonal by diagonal (not row-sorted) so the device build's sort does real work.
+    Same matrix as tests/workloads.poisson3d_triplets, generated with torch on the device (plumbing)."""
+    import torch
+
+    i = torch.arange(lo, hi, device=device, dtype=torch.int64).view(-1, 1, 1)
+    j = torch.arange(n, device=device, dtype=torch.int64).view(1, -1, 1)
+    k = torch.arange(n, device=device, dtype=torch.int64).view(1, 1, -1)
+    r = ((i * n + j) * n + k).reshape(-1)
+    rows, cols, vals = [], [], []
+    for d, (di, dj, dk) in enumerate(((0, 0, 0), (-1, 0, 0), (1, 0, 0), (0, -1, 0), (0, 1, 0), (0, 0, -1), (0, 0, 1))):
+        ii, jj, kk = i + di, j + dj, k + dk
+        ok = ((ii >= 0) & (ii < n) & (jj >= 0) & (jj < n) & (kk >= 0) & (kk < n)).reshape(-1)
+        c = ((ii * n + jj) * n + kk).reshape(-1)
+        rows.append(r[ok])
+        cols.append(c[ok])
+        vals.append(torch.full((int(ok.sum()),), 6.0 if d == 0 else -1.0, device=device, dtype=torch.float32))
+    return torch.cat(rows), torch.cat(cols), torch.cat(vals)
+
+
+def spmv_bytes(n, m, nnz, sv):
+    """Algorithmic bytes of one SpMV: every array once."""
+    return nnz * (sv + 4) + (n + 1) * 4 + m * sv + n * sv
+
+
+def cg_iter_bytes(n, nnz, sv):
+    """Algorithmic bytes of one Jacobi-PCG iteration: SpMV + 11 vector passes."""
+    return nnz * (sv + 4) + (n + 1) * 4 + 13 * n * sv
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# clocks during the timed region
+# ---------------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.samples, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append((time.time(), line.strip()))
+
+    def stop(self, t0=None, t1=None):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ts, line in self.samples:
+            if t0 is not None and not (t0 - 0.05 <= ts <= t1 + 0.15):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# CPU arm: the reference's Eigen path (oracle/_ref), else the C port (oracle/qd_oracle.c)
+# ---------------------------------------------------------------------------------------------------------------------
+def poisson3d_csr_host(n):
+    """The C2 matrix as CSR on the host (numpy; symmetric, so the same arrays are Eigen's col-major storage)."""
+    idx = np.arange(n, dtype=np.int64)
+    i, j, k = np.meshgrid(idx, idx, idx, indexing="ij")
+    r = ((i * n + j) * n + k).ravel()
+    cols = np.full((n ** 3, 7), -1, dtype=np.int64)
+    vals = np.zeros((n ** 3, 7), dtype=np.float32)
+    # ascending column order inside a row: -n^2, -n, -1, 0, +1, +n, +n^2
+    for s, (di, dj, dk) in enumerate(((-1, 0, 0), (0, -1, 0), (0, 0, -1), (0, 0, 0), (0, 0, 1), (0, 1, 0), (1, 0, 0))):
+        ii, jj, kk = i + di, j + dj, k + dk
+        ok = ((ii >= 0) & (ii < n) & (jj >= 0) & (jj < n) & (kk >= 0) & (kk < n)).ravel()
+        cols[ok, s] = (r + (di * n + dj) * n + dk)[ok]
+        vals[ok, s] = 6.0 if s == 3 else -1.0
+    keep = cols >= 0
+    indptr = np.zeros(n ** 3 + 1, dtype=np.int32)
+    np.cumsum(keep.sum(axis=1), out=indptr[1:])
+    return indptr, cols[keep].astype(np.int32), vals[keep]
+
+
+class CpuCg:
+    """The reference's Eigen Jacobi-PCG on the host cores (oracle/_ref), else the C port (oracle/qd_oracle.c).
+    As shipped the reference is single-threaded (no -fopenmp in its cmake) on a col-major matrix, the only storage
+    SparseCG accepts (conjugate_gradient.h:40); the best-effort variant lets Eigen thread the row-major product with
+    OpenMP on every core.  Both are timed; the faster one is reported."""
+
+    def __init__(self, csr, n_rows):
+        import oracle
+
+        self.n = n_rows
+        self.b = np.ones(n_rows, np.float32)
+        self.cores = os.cpu_count() or 1
+        indptr, indices, vals = csr
+        self.variants = {}
+        if oracle.EigenRef.available():
+            self.kind = "reference"
+            ref = oracle.EigenRef()
+            m = ref.matrix_from_compressed(indptr, indices, vals, n_rows, n_rows, row_major=False)
+            self.variants["shipped"] = (1, lambda it, m=m: m.cg(self.b, it, 1e-30)[2])
+            if oracle.EigenRef.available(omp=True) and self.cores > 1:
+                refo = oracle.EigenRef(omp=True)
+                refo.set_threads(self.cores)
+                mo = refo.matrix_from_compressed(indptr, indices, vals, n_rows, n_rows, row_major=True)
+                self.variants["omp"] = (self.cores, lambda it, mo=mo: mo.cg(self.b, it, 1e-30, allow_row_major=True)[2])
+        else:
+            self.kind = "port"
+            orc = oracle.Oracle()
+            self.variants["shipped"] = (1, lambda it: orc.cg(indptr, indices, vals, self.b, it, 1e-30)[2])
+
+    def rate(self, name, iters):
+        t0 = time.perf_counter()
+        done = self.variants[name][1](iters)
+        return done / (time.perf_counter() - t0)
+
+    def baseline(self, iters):
+        rates = {k: self.rate(k, iters) for k in self.variants}
+        best = max(rates, key=rates.get)
+        what = ("Eigen 3.4.90 ConjugateGradient (oracle/_ref, the reference's flags)" if self.kind == "reference"
+                else "C restatement of Eigen's Jacobi-PCG (oracle/qd_oracle.c)")
+        sample = f"{iters} Jacobi-PCG iterations of {what} on the full workload matrix; " + "; ".join(
+            f"{'1 thread col-major as the reference ships' if k == 'shipped' else f'{self.cores} OpenMP threads row-major, best effort'}: {v:.3f} it/s"
+            for k, v in rates.items())
+        return {"value": rates[best], "unit": "iters/s", "cores": self.variants[best][0], "kind": self.kind,
+                "sample": sample, "variant": best}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import oracle
+
+    oracle.build()
+    n = args.grid
+    csr = poisson3d_csr_host(n)
+    n_rows = n ** 3
+    cpu = CpuCg(csr, n_rows)
+    it = args.cpu_iters
+    base = cpu.baseline(it)            # untimed warm-up that also picks the faster variant
+    name = base["variant"]
+    for _ in range(max(0, args.warmup - 1)):
+        cpu.rate(name, it)
+    t0 = time.perf_counter()
+    steps = 0
+    for _ in range(args.steps):
+        cpu.variants[name][1](it)
+        steps += 1
+        if time.perf_counter() - t0 > 150:   # bounded: the whole arm must end within a few minutes
+            break
+    dt = time.perf_counter() - t0
+    value = steps * it / dt
+    base["value"] = value
+    line = {"impl": "reference", "metric": "cg_iters_per_s", "value": value, "unit": "iters/s", "n_gpus": args.gpus,
+            "steps": steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"3D 7-point Poisson {n}^3 fp32 Jacobi-PCG (C2), full matrix; one step = {it} "
+                                   "iterations on the host cores (bounded sample of the GPU arm's step)",
+                       "rows": n_rows, "nnz": int(csr[1].shape[0]), "iters_per_step": it},
+            "cpu_baseline": base,
+            "e2e": {"value": value, "unit": "iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------------------
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+
+    import quadrants_b200 as qd
+    from quadrants_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    qd.init(arch=qd.cuda, device=local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+    n = args.grid
+    n_rows = n ** 3
+    sv = 4
+    ips = args.iters_per_step
+
+    # ---- assemble through the public API: builder -> device CSR (K2-K4 replacement) ---------------------------------
+    if world > 1:
+        from quadrants_b200 import distributed as qdist
+        ctx = qdist.bench_setup(qd, n, rank, world, dev)  # row-block plan, local matrix, halo lists, solver
+        A, cg, xg, bg, nnz_total = ctx["A"], ctx["cg"], ctx["x"], ctx["b"], ctx["nnz_total"]
+        build_ms = ctx["build_ms"]
+    else:
+        r, c, v = poisson3d_triplets_device(n, 0, n, dev)
+        ntrip = int(r.shape[0])
+        K = qd.linalg.SparseMatrixBuilder(n_rows, n_rows, max_num_triplets=ntrip, dtype=qd.f32)
+        K.ptr.insert_triplets(r, c, v)
+        del r, c, v
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        A = K.build()
+        e1.record()
+        torch.cuda.synchronize()
+        build_ms = e0.elapsed_time(e1)
+        del K
+        nnz_total = A.matrix.nnz()
+        bg = qd.ndarray(qd.f32, n_rows)
+        bg.fill(1.0)
+        xg = qd.ndarray(qd.f32, n_rows)
+        cg = qd.linalg.SparseCG(A, bg, max_iter=ips, atol=1e-30)
+    stream = torch.cuda.current_stream()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def step_device():
+        cg.cg_solver.run_fixed(xg, bg, ips)
+
+    # ---- value: K steps, inputs resident in HBM -----------------------------------------------------------------------
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.25)
+    l0 = _lib.launch_count()
+    t_wall0 = time.time()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    barrier()
+    t_wall1 = time.time()
+    launches = _lib.launch_count() - l0
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.stop(t_wall0, t_wall1)
+    ms_per_step = ms_total / args.steps
+    value = ips * args.steps / (ms_total * 1e-3)
+
+    # ---- roofline of the dominant kernel: SpMV (the same CTA code the CG's A.p kernel runs) ---------------------------
+    roofline, spmv_gbs = None, None
+    if world == 1:
+        xs = qd.ndarray(qd.f32, n_rows)
+        xs.tensor.uniform_(-1.0, 1.0, generator=torch.Generator(device=dev).manual_seed(2))
+        ys = qd.ndarray(qd.f32, n_rows)
+        for _ in range(5):
+            A.matrix.spmv(None, xs, ys)
+        reps = 50
+        torch.cuda.synchronize()
+        e0.record(stream)
+        for _ in range(reps):
+            A.matrix.spmv(None, xs, ys)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        spmv_ms = e0.elapsed_time(e1) / reps
+        alg = spmv_bytes(n_rows, n_rows, nnz_total, sv)
+        spmv_gbs = alg / (spmv_ms * 1e-3) / 1e9
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "spmv_traffic.json"))).get("dram_bytes_per_launch")
+        except (OSError, ValueError):
+            pass
+        roofline = {"bound": "hbm", "kernel": "spmv_kernel<float> (== cg_spmv_dot_kernel body)", "achieved": spmv_gbs,
+                    "peak": peak, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
+                    "unit": "GB/s", "frac": spmv_gbs / peak, "frac_of_nominal_8000": spmv_gbs / 8000.0,
+                    "algorithmic_bytes_per_launch": alg, "ms_per_launch": spmv_ms, "traffic": traffic}
+        del xs, ys
+
+    # ---- e2e: the host-buffer C-ABI call (qdsp_cg_solve_host): b H2D + x D2H inside the timed region -------------------
+    e2e = None
+    if world == 1:
+        bh = torch.ones(n_rows, dtype=torch.float32).pin_memory()
+        xh = torch.zeros(n_rows, dtype=torch.float32).pin_memory()
+        it, err, ok = C.c_int(), C.c_double(), C.c_int()
+        h = cg.cg_solver._h
+
+        def step_host():
+            _lib.check(lib.qdsp_cg_solve_host(h, xh.data_ptr(), bh.data_ptr(), stream.cuda_stream, C.byref(it),
+                                              C.byref(err), C.byref(ok)))
+
+        for _ in range(max(1, args.warmup)):
+            step_host()
+        torch.cuda.synchronize()
+        e0.record(stream)
+        done_iters = 0
+        for _ in range(args.steps):
+            step_host()
+            done_iters += it.value
+        e1.record(stream)
+        torch.cuda.synchronize()
+        e2e_ms = e0.elapsed_time(e1)
+        e2e = {"value": done_iters / (e2e_ms * 1e-3), "unit": "iters/s", "h2d_bytes_per_step": n_rows * sv,
+               "d2h_bytes_per_step": n_rows * sv, "call": "qdsp_cg_solve_host", "iters_per_step": done_iters // args.steps,
+               "final_rel_residual": err.value}
+
+    # ---- CPU baseline on a bounded sample (rank 0, N = 1 only) ----------------------------------------------------------
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        import oracle
+
+        oracle.build()
+        ip, ix, vv = A.matrix.to_scipy_arrays()
+        cpu = CpuCg((ip, ix, vv), n_rows).baseline(args.cpu_iters)
+
+    if rank == 0:
+        iter_bytes = cg_iter_bytes(n_rows, nnz_total, sv)
+        line = {"metric": "cg_iters_per_s", "value": value, "unit": "iters/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"3D 7-point Poisson {n}^3 fp32 (C2): SparseMatrixBuilder->CSR on device, then "
+                                       f"Jacobi-PCG; one step = one {ips}-iteration SparseCG solve",
+                           "rows": n_rows, "nnz": int(nnz_total), "iters_per_step": ips,
+                           "partition": f"row-block x{world}" if world > 1 else "single GPU",
+                           "l2": "no flush: matrix stream 0.94 GB per iteration >> 126 MB L2",
+                           "csr_build_ms": build_ms},
+                "cg_gbs": value * iter_bytes / 1e9, "cg_algorithmic_bytes_per_iter": iter_bytes,
+                "spmv_gbs": spmv_gbs, "gpu_launches": int(launches), "clocks": clocks}
+        if roofline:
+            line["roofline"] = roofline
+        if e2e:
+            line["e2e"] = e2e
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--grid", type=int, default=256, help="n of the n^3 Poisson grid (BASELINE C2: 256)")
+    ap.add_argument("--iters-per-step", type=int, default=100)
+    ap.add_argument("--cpu-iters", type=int, default=12, help="CG iterations of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -184,6 +184,8 @@ class EigenRef:
         L.ref_matrix_build.restype = _VOIDP
         L.ref_matrix_build.argtypes = [_VOIDP, C.c_int, C.c_int, C.c_int, C.c_int]
         L.ref_matrix_free.argtypes = [_VOIDP]
+        L.ref_matrix_from_compressed.restype = _VOIDP
+        L.ref_matrix_from_compressed.argtypes = [C.c_int, C.c_int, C.c_int64, _VOIDP, _VOIDP, _VOIDP, C.c_int, C.c_int]
         L.ref_matrix_nnz.restype = C.c_int64
         L.ref_matrix_nnz.argtypes = [_VOIDP]
         L.ref_matrix_is_compressed.argtypes = [_VOIDP]
@@ -210,8 +212,17 @@ class EigenRef:
         self.lib.ref_set_num_threads(int(n))
 
     class Matrix:
-        def __init__(self, ref, buf, rows, cols, row_major):
+        def __init__(self, ref, buf, rows, cols, row_major, compressed=None):
             self.ref, self.rows, self.cols, self.row_major = ref, rows, cols, row_major
+            if compressed is not None:
+                outer, inner, vals = (np.ascontiguousarray(a) for a in compressed)
+                assert outer.dtype == np.int32 and inner.dtype == np.int32
+                self.f64 = vals.dtype == np.float64
+                self.dtype = vals.dtype.type
+                self.h = ref.lib.ref_matrix_from_compressed(rows, cols, inner.shape[0], outer.ctypes.data,
+                                                            inner.ctypes.data, vals.ctypes.data, int(self.f64),
+                                                            int(row_major))
+                return
             self.f64 = buf.dtype == np.int64
             self.dtype = np.float64 if self.f64 else np.float32
             self.h = ref.lib.ref_matrix_build(buf.ctypes.data, rows, cols, int(self.f64), int(row_major))
@@ -247,3 +258,7 @@ class EigenRef:
 
     def matrix(self, buf, rows, cols, row_major=True):
         return EigenRef.Matrix(self, buf, rows, cols, row_major)
+
+    def matrix_from_compressed(self, outer, inner, vals, rows, cols, row_major=True):
+        """Eigen matrix over existing compressed arrays (copied); same arithmetic afterwards."""
+        return EigenRef.Matrix(self, None, rows, cols, row_major, compressed=(outer, inner, vals))
