@@ -52,6 +52,7 @@ typedef enum { QDSP_CG_EIGEN_JACOBI = 0, QDSP_CG_CUCG = 1 } qdsp_cg_mode;
 typedef struct qdsp_builder_s *qdsp_builder_t;
 typedef struct qdsp_csr_s *qdsp_csr_t;
 typedef struct qdsp_cg_s *qdsp_cg_t;
+typedef struct qdsp_dist_s *qdsp_dist_t;
 
 /* ---- library ------------------------------------------------------------------------------------------------- */
 const char *qdsp_last_error(void);
@@ -128,6 +129,37 @@ int qdsp_cg_solve_host(qdsp_cg_t s, void *x_host, const void *b_host, void *stre
 /* Runs exactly `iters` iterations with the convergence exit disabled (throughput timing; not a reference call). */
 int qdsp_cg_run_fixed(qdsp_cg_t s, void *x, const void *b, int iters, void *stream);
 int qdsp_cg_destroy(qdsp_cg_t s);
+
+/* ---- multi-GPU: row-block partition, one process per GPU (no reference counterpart: the reference opens device 0 only,
+ * quadrants/rhi/cuda/cuda_context.cpp:16-26; design in SURVEY.md 8(e)) -------------------------------------------------
+ * Rank g owns global rows and columns [row_offsets[g], row_offsets[g+1]).  Each rank builds the CSR of ITS rows with
+ * global column ids (rows = n_local, cols = global size), then:
+ *   qdsp_dist_localize      renumbers the columns (owned first, then ghosts ascending by global id) and allocates the
+ *                           peer-visible buffer that holds the SpMV operand [owned | ghosts];
+ *   qdsp_dist_ghost_ids     the ghost ids, grouped by owner (owner_offsets): the caller ships each group to its owner
+ *                           (any transport; quadrants_b200.distributed uses torch.distributed), which registers it with
+ *   qdsp_dist_set_send_list (dst_offset = the requester's n_local + its owner_offsets[owner]);
+ *   qdsp_dist_comm_handle / qdsp_dist_attach   exchange and map the CUDA IPC handles of the buffers (NVLink P2P).
+ * After that qdsp_dist_spmv and a solver from qdsp_cg_create_dist run with the halo of x pushed by peer stores and the
+ * CG dot products all-reduced inside the kernels over peer memory (QDSP_ALLREDUCE=nccl: by ncclAllReduce instead, after
+ * qdsp_dist_nccl_init).  x, b, y are the rank's owned slices (n_local elements).  Every rank must make the same calls. */
+/* Pure host helper behind qdsp_dist_localize (no CUDA needed): plans one rank from its global column ids. */
+int qdsp_dist_plan_host(int rank, int world, const int64_t *row_offsets, int32_t *indices_inout, int64_t nnz,
+                        int32_t *ghost_ids_out, int64_t ghost_capacity, int64_t *n_ghost, int32_t *owner_offsets_out);
+int qdsp_dist_create(int rank, int world, qdsp_dist_t *out);
+int qdsp_dist_destroy(qdsp_dist_t d);
+int qdsp_dist_localize(qdsp_dist_t d, qdsp_csr_t m, const int64_t *row_offsets, void *stream, int *n_local,
+                       int *n_ghost, int32_t *owner_offsets_out /* world + 1 */);
+int qdsp_dist_ghost_ids(qdsp_dist_t d, const int32_t **host_ids);
+int qdsp_dist_set_send_list(qdsp_dist_t d, int peer, const int32_t *global_ids, int count, int dst_offset);
+int qdsp_dist_comm_handle(qdsp_dist_t d, void *out64);
+int qdsp_dist_attach(qdsp_dist_t d, const void *handles /* world x 64 bytes in rank order */);
+int qdsp_dist_nccl_unique_id(void *out128);
+int qdsp_dist_nccl_init(qdsp_dist_t d, const void *id128);
+int qdsp_dist_spmv(qdsp_dist_t d, qdsp_csr_t m, const void *x_local, void *y_local, void *stream);
+/* Like qdsp_cg_create on the localized matrix of `d` (QDSP_CG_EIGEN_JACOBI only).  iterations / error / success are
+ * identical on every rank: all ranks sum the all-reduced scalars in the same order. */
+int qdsp_cg_create_dist(qdsp_csr_t m, qdsp_dist_t d, int max_iters, double tol, int mode, int verbose, qdsp_cg_t *out);
 
 /* ---- qd.algorithms.parallel_sort / PrefixSumExecutor ----------------------------------------------------------- */
 /* parallel_sort (python/quadrants/algorithms/_algorithms.py:19-56): in-place ascending sort of keys, values (or

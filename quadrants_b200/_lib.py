@@ -53,6 +53,18 @@ SIGNATURES = {
     "qdsp_cg_solve_host": (_i, [_vp, _vp, _vp, _vp, _P(_i), _P(_d), _P(_i)]),
     "qdsp_cg_run_fixed": (_i, [_vp, _vp, _vp, _i, _vp]),
     "qdsp_cg_destroy": (_i, [_vp]),
+    "qdsp_dist_plan_host": (_i, [_i, _i, _vp, _vp, _i64, _vp, _i64, _P(_i64), _vp]),
+    "qdsp_dist_create": (_i, [_i, _i, _P(_vp)]),
+    "qdsp_dist_destroy": (_i, [_vp]),
+    "qdsp_dist_localize": (_i, [_vp, _vp, _vp, _vp, _P(_i), _P(_i), _vp]),
+    "qdsp_dist_ghost_ids": (_i, [_vp, _P(_vp)]),
+    "qdsp_dist_set_send_list": (_i, [_vp, _i, _vp, _i, _i]),
+    "qdsp_dist_comm_handle": (_i, [_vp, _vp]),
+    "qdsp_dist_attach": (_i, [_vp, _vp]),
+    "qdsp_dist_nccl_unique_id": (_i, [_vp]),
+    "qdsp_dist_nccl_init": (_i, [_vp, _vp]),
+    "qdsp_dist_spmv": (_i, [_vp, _vp, _vp, _vp, _vp]),
+    "qdsp_cg_create_dist": (_i, [_vp, _vp, _i, _d, _i, _i, _P(_vp)]),
     "qdsp_sort_tmp_bytes": (_sz, [_i64, _i, _i]),
     "qdsp_sort_pairs": (_i, [_vp, _vp, _i64, _i, _i, _vp, _sz, _vp]),
     "qdsp_scan_tmp_bytes": (_sz, [_i64]),

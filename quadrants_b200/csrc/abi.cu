@@ -3,6 +3,7 @@
 #include <cstring>
 #include <new>
 
+#include "dist.hpp"
 #include "host.hpp"
 
 using namespace qdsp;
@@ -10,6 +11,7 @@ using namespace qdsp;
 struct qdsp_builder_s { std::unique_ptr<Builder> impl; };
 struct qdsp_csr_s { std::unique_ptr<CsrMatrix> impl; };
 struct qdsp_cg_s { std::unique_ptr<CgSolver> impl; qdsp_csr_s *matrix; };
+struct qdsp_dist_s { std::unique_ptr<DistContext> impl; };
 
 namespace {
 thread_local std::string g_last_error;
@@ -210,23 +212,82 @@ int qdsp_cg_solve(qdsp_cg_t s, void *x, const void *b, void *stream, int *iterat
 }
 int qdsp_cg_solve_host(qdsp_cg_t s, void *x_host, const void *b_host, void *stream, int *iterations, double *error,
                        int *success) {
-  return guarded([&] {
-    NOT_NULL(s); NOT_NULL(x_host); NOT_NULL(b_host);
-    const CsrMatrix &A = *s->matrix->impl;
-    const size_t bytes = A.value_bytes() * static_cast<size_t>(A.rows);
-    DeviceBuffer x(bytes), b(bytes);
-    QDSP_CUDA(cudaMemcpyAsync(b.get(), b_host, bytes, cudaMemcpyHostToDevice, S(stream)));
-    QDSP_CUDA(cudaMemcpyAsync(x.get(), x_host, bytes, cudaMemcpyHostToDevice, S(stream)));  // CUCG starts from x
-    s->impl->solve(x.get(), b.get(), S(stream), iterations, error, success);
-    QDSP_CUDA(cudaMemcpyAsync(x_host, x.get(), bytes, cudaMemcpyDeviceToHost, S(stream)));
-    QDSP_CUDA(cudaStreamSynchronize(S(stream)));
-  });
+  return guarded([&] { NOT_NULL(s); s->impl->solve_host(x_host, b_host, S(stream), iterations, error, success); });
 }
 int qdsp_cg_run_fixed(qdsp_cg_t s, void *x, const void *b, int iters, void *stream) {
   return guarded([&] { NOT_NULL(s); s->impl->run_fixed(x, b, iters, S(stream)); });
 }
 int qdsp_cg_destroy(qdsp_cg_t s) {
   return guarded([&] { delete s; });
+}
+
+// ---- multi-GPU ------------------------------------------------------------------------------------------------------------
+int qdsp_dist_plan_host(int rank, int world, const int64_t *row_offsets, int32_t *indices_inout, int64_t nnz,
+                        int32_t *ghost_ids_out, int64_t ghost_capacity, int64_t *n_ghost, int32_t *owner_offsets_out) {
+  return guarded([&] {
+    NOT_NULL(n_ghost); NOT_NULL(owner_offsets_out);
+    const DistPlan p = dist_plan_host(rank, world, row_offsets, indices_inout, nnz);
+    *n_ghost = static_cast<int64_t>(p.ghost_ids.size());
+    for (int q = 0; q <= world; ++q) owner_offsets_out[q] = p.owner_offsets[q];
+    if (ghost_ids_out) {
+      QDSP_REQUIRE(ghost_capacity >= *n_ghost, QDSP_ERR_INVALID, "dist plan: ghost_ids_out too small");
+      std::memcpy(ghost_ids_out, p.ghost_ids.data(), sizeof(int32_t) * p.ghost_ids.size());
+    }
+  });
+}
+int qdsp_dist_create(int rank, int world, qdsp_dist_t *out) {
+  return guarded([&] {
+    NOT_NULL(out);
+    auto *h = new qdsp_dist_s();
+    try { h->impl = std::make_unique<DistContext>(rank, world); } catch (...) { delete h; throw; }
+    *out = h;
+  });
+}
+int qdsp_dist_destroy(qdsp_dist_t d) {
+  return guarded([&] { delete d; });
+}
+int qdsp_dist_localize(qdsp_dist_t d, qdsp_csr_t m, const int64_t *row_offsets, void *stream, int *n_local,
+                       int *n_ghost, int32_t *owner_offsets_out) {
+  return guarded([&] {
+    NOT_NULL(d); NOT_NULL(m);
+    d->impl->localize(*m->impl, row_offsets, S(stream));
+    if (n_local) *n_local = d->impl->n_local();
+    if (n_ghost) *n_ghost = d->impl->n_ghost();
+    if (owner_offsets_out)
+      for (int q = 0; q <= d->impl->world(); ++q) owner_offsets_out[q] = d->impl->plan().owner_offsets[q];
+  });
+}
+int qdsp_dist_ghost_ids(qdsp_dist_t d, const int32_t **host_ids) {
+  return guarded([&] { NOT_NULL(d); NOT_NULL(host_ids); *host_ids = d->impl->plan().ghost_ids.data(); });
+}
+int qdsp_dist_set_send_list(qdsp_dist_t d, int peer, const int32_t *global_ids, int count, int dst_offset) {
+  return guarded([&] { NOT_NULL(d); d->impl->set_send_list(peer, global_ids, count, dst_offset); });
+}
+int qdsp_dist_comm_handle(qdsp_dist_t d, void *out64) {
+  return guarded([&] { NOT_NULL(d); NOT_NULL(out64); d->impl->comm_handle(out64); });
+}
+int qdsp_dist_attach(qdsp_dist_t d, const void *handles) {
+  return guarded([&] { NOT_NULL(d); NOT_NULL(handles); d->impl->attach(handles); });
+}
+int qdsp_dist_nccl_unique_id(void *out128) {
+  return guarded([&] { NOT_NULL(out128); DistContext::nccl_unique_id(out128); });
+}
+int qdsp_dist_nccl_init(qdsp_dist_t d, const void *id128) {
+  return guarded([&] { NOT_NULL(d); NOT_NULL(id128); d->impl->nccl_init(id128); });
+}
+int qdsp_dist_spmv(qdsp_dist_t d, qdsp_csr_t m, const void *x_local, void *y_local, void *stream) {
+  return guarded([&] { NOT_NULL(d); NOT_NULL(m); NOT_NULL(x_local); NOT_NULL(y_local); d->impl->spmv(*m->impl, x_local, y_local, S(stream)); });
+}
+int qdsp_cg_create_dist(qdsp_csr_t m, qdsp_dist_t d, int max_iters, double tol, int mode, int verbose, qdsp_cg_t *out) {
+  return guarded([&] {
+    NOT_NULL(m); NOT_NULL(d); NOT_NULL(out);
+    auto *h = new qdsp_cg_s();
+    try {
+      h->impl = std::make_unique<CgSolver>(*m->impl, max_iters, tol, mode, verbose != 0, d->impl.get());
+    } catch (...) { delete h; throw; }
+    h->matrix = m;
+    *out = h;
+  });
 }
 
 // ---- algorithms -----------------------------------------------------------------------------------------------------------

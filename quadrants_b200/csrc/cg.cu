@@ -1,4 +1,4 @@
-// cg.cu -- fused conjugate gradient on the device.
+// cg.cu -- fused conjugate gradient on the device, one GPU or row-block partitioned over several.
 //
 // Semantics (mode QDSP_CG_EIGEN_JACOBI) = CG<EigenT,DT>::solve (quadrants/program/conjugate_gradient.h:36-49), i.e.
 // Eigen::internal::conjugate_gradient with DiagonalPreconditioner
@@ -12,20 +12,25 @@
 // (+ handle/malloc/free), Sscal + 3 Saxpy, 2 blocking Sdot per iteration (~15 vector passes, >= 3 host syncs).
 //
 // Here one iteration is THREE kernels and no host round trip; every scalar stays on the device:
-//   A  cg_spmv_dot : tmp = A p fused with the partial sums of p.tmp            (matrix + 2n)
-//   B  cg_update   : x += a p, r -= a tmp, |r|^2 and r.(D^-1 r) in one pass     (5n read, 2n write)
-//   C  cg_direction: p = D^-1 r + beta p                                        (3n read, 1n write)
-// => nnz*(sv+4) + (n+1)*4 + 13*n*sv bytes per iteration, the model of SURVEY 8(d).
-// Dot products: per-thread partials in T, block tree in double, per-block partial to memory, and the LAST block to
-// finish (atomic ticket) adds the partials in a fixed order -> deterministic, no atomics on the sums, no extra launch.
-// That block also advances the scalar recurrence (alpha, beta, convergence flag, iteration counter).  Once the flag
-// is up every later kernel exits immediately, so the host may enqueue iterations ahead of the convergence test and
-// only polls the flag every `check_every` iterations.  Iterations are replayed from a CUDA graph.
+//   A  cg_spmv_dot : tmp = A p fused with p.tmp (persistent TMA-fed SpMV, spmv_kernels.cuh)   matrix + 2n
+//   B  cg_residual : r -= alpha tmp, |r|^2 and r.(D^-1 r) in the same pass                     3n read, 1n write
+//   C  cg_direction: x += alpha p (deferred: x is not needed earlier), p = D^-1 r + beta p,    4n read, 2n write
+//                    and the halo of the new p pushed to the neighbour ranks
+// => nnz*(sv+4) + (n+1)*4 + 12*n*sv bytes per iteration (one vector pass below the 13n model of SURVEY 8(d)).
+// Dot products: per-thread partials, block tree in double, per-block partial to memory, and the LAST block to finish
+// (atomic ticket) adds the partials in a fixed order -> deterministic, no atomics on the sums, no extra launch.  With
+// several ranks that block then all-reduces the sums over NVLink peer memory (dist_dev.cuh: one NVLink latency, no
+// NCCL call, no kernel boundary) -- or leaves them for ncclAllReduce when QDSP_ALLREDUCE=nccl.  It also advances the
+// scalar recurrence (alpha, beta, convergence flag, iteration counter).  Once the flag is up every later kernel
+// exits immediately, so the host enqueues iterations ahead of the convergence test and polls the flag every batch.
+// Iterations are replayed from a CUDA graph.
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <vector>
 
+#include "dist.hpp"
 #include "host.hpp"
 #include "spmv_kernels.cuh"
 
@@ -36,35 +41,37 @@ constexpr int CG_THREADS = 256;
 struct CgScalars {
   double pAp, abs_new, abs_old, res2, rhs2, thr;
   double alpha, beta;
+  double red[4];  // local sums handed to ncclAllReduce (QDSP_ALLREDUCE=nccl)
   int iters;      // Eigen's i: completed loop bodies
-  int done;       // 0 running, 1 converged, 2 budget exhausted
+  int done;       // 0 running, 1 converged, 2 budget exhausted, 3 communication failure
   int max_iters;
   int stop_le;    // 1: stop when res2 <= thr (CUCG), 0: when res2 < thr (Eigen)
+  int relative;
+  double tol;
   unsigned ticket[4];
 };
 
-// ---- block reduction helpers ----------------------------------------------------------------------------------------
+// ---- block / grid reductions ----------------------------------------------------------------------------------------
 template <int NV>
-__device__ __forceinline__ void block_sum(double (&v)[NV], double *s_red /* NV * 8 */) {
-  const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
+__device__ __forceinline__ void block_sum(double (&v)[NV], double *s_red /* NV * 16 */) {
+  const unsigned lane = lane_id(), warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
 #pragma unroll
   for (int j = 0; j < NV; ++j) {
     v[j] = warp_sum(v[j]);
-    if (lane == 0) s_red[j * 8 + warp] = v[j];
+    if (lane == 0) s_red[j * 16 + warp] = v[j];
   }
   __syncthreads();
 #pragma unroll
   for (int j = 0; j < NV; ++j) {
     double t = 0.0;
-#pragma unroll
-    for (int w = 0; w < CG_THREADS / 32; ++w) t += s_red[j * 8 + w];
+    for (unsigned w = 0; w < nw; ++w) t += s_red[j * 16 + w];
     v[j] = t;  // every thread holds the block total
   }
   __syncthreads();
 }
 
-// Publishes this block's NV partial sums; returns true in the last block to finish, with v[] = grand totals summed in a
-// fixed order (thread-strided, then the block tree above).
+// Publishes this block's NV partial sums; returns true in the last block to finish, with v[] = this rank's totals summed
+// in a fixed order (thread-strided, then the block tree above).
 template <int NV>
 __device__ __forceinline__ bool grid_sum_last_block(double (&v)[NV], double *partials /* NV x gridDim.x */,
                                                     unsigned *ticket, double *s_red, unsigned *s_flag) {
@@ -82,7 +89,7 @@ __device__ __forceinline__ bool grid_sum_last_block(double (&v)[NV], double *par
 #pragma unroll
   for (int j = 0; j < NV; ++j) {
     double t = 0.0;
-    for (unsigned i = threadIdx.x; i < gridDim.x; i += CG_THREADS)
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x)
       t += __ldcg(&partials[static_cast<size_t>(j) * gridDim.x + i]);
     v[j] = t;
   }
@@ -91,8 +98,88 @@ __device__ __forceinline__ bool grid_sum_last_block(double (&v)[NV], double *par
   return true;
 }
 
+// ---- the scalar recurrence (one thread) --------------------------------------------------------------------------------
+// scalars are kept in double but rounded through T where Eigen's RealScalar would be T
+template <typename T>
+__device__ __forceinline__ void cg_finish_init(CgScalars *sc, const double (&v)[3]) {
+  const double rhs2 = static_cast<double>(static_cast<T>(v[0]));
+  const double res2 = static_cast<double>(static_cast<T>(v[1]));
+  sc->rhs2 = rhs2;
+  sc->res2 = res2;
+  sc->abs_new = static_cast<double>(static_cast<T>(v[2]));
+  sc->abs_old = 0.0;
+  sc->iters = 0;
+  sc->alpha = 0.0;
+  sc->beta = 0.0;
+  const double tol = sc->tol;
+  const double tiny = sizeof(T) == 4 ? static_cast<double>(FLT_MIN) : DBL_MIN;
+  double thr = sc->relative
+                   ? static_cast<double>(static_cast<T>(static_cast<T>(tol) * static_cast<T>(tol) * static_cast<T>(rhs2)))
+                   : static_cast<double>(static_cast<T>(tol) * static_cast<T>(tol));
+  if (sc->relative && thr < tiny) thr = tiny;
+  if (tol < 0.0) thr = -1.0;  // fixed-iteration timing runs: never converge
+  sc->thr = thr;
+  int done = 0;
+  if (tol >= 0.0 && sc->relative && rhs2 == 0.0) done = 1;
+  else if (sc->stop_le ? (res2 <= thr) : (res2 < thr)) done = 1;
+  else if (sc->max_iters <= 0) done = 2;
+  sc->done = done;
+}
+template <typename T>
+__device__ __forceinline__ void cg_finish_A(CgScalars *sc, double pap_sum) {
+  const T pap = static_cast<T>(pap_sum);
+  sc->pAp = static_cast<double>(pap);
+  sc->alpha = static_cast<double>(static_cast<T>(sc->abs_new) / pap);
+}
+template <typename T>
+__device__ __forceinline__ void cg_finish_B(CgScalars *sc, double rr, double rz) {
+  const double res2 = static_cast<double>(static_cast<T>(rr));
+  sc->res2 = res2;
+  if (sc->stop_le ? (res2 <= sc->thr) : (res2 < sc->thr)) {
+    sc->done = 1;                     // Eigen breaks before ++i
+    if (sc->stop_le) sc->iters += 1;  // CUCG counts the body it just finished (k++)
+    sc->beta = 0.0;
+  } else {
+    const T abs_old = static_cast<T>(sc->abs_new);
+    const T abs_new = static_cast<T>(rz);
+    sc->abs_old = static_cast<double>(abs_old);
+    sc->abs_new = static_cast<double>(abs_new);
+    sc->beta = static_cast<double>(abs_new / abs_old);
+    sc->iters += 1;
+    if (sc->iters >= sc->max_iters) sc->done = 2;
+  }
+}
+
+// QDSP_ALLREDUCE=nccl: the sums were all-reduced in sc->red by NCCL between two kernels
+template <typename T>
+__global__ void cg_scalars_kernel(CgScalars *sc, int which) {
+  if (which != 0 && sc->done) return;
+  if (which == 0) { const double v[3] = {sc->red[0], sc->red[1], sc->red[2]}; cg_finish_init<T>(sc, v); }
+  else if (which == 1) cg_finish_A<T>(sc, sc->red[0]);
+  else cg_finish_B<T>(sc, sc->red[0], sc->red[1]);
+}
+
+// Last block: all-reduce across ranks (in-kernel, or deferred to NCCL) and hand the totals to `fin` on one thread.
+template <int NV, typename Fin>
+__device__ __forceinline__ void cg_reduce_and_finish(double (&v)[NV], const DistDev &d, int use_nccl, CgScalars *sc,
+                                                     Fin fin) {
+  if (d.world > 1 && use_nccl) {
+    if (threadIdx.x == 0)
+      for (int j = 0; j < NV; ++j) sc->red[j] = v[j];
+    return;
+  }
+  if (threadIdx.x < 32) {
+    dist_allreduce<NV>(d, v);
+    if (threadIdx.x == 0) {
+      if (d.world > 1 && *reinterpret_cast<volatile int *>(d.error)) sc->done = 3;
+      else fin(v);
+    }
+  }
+}
+
 // ---- setup kernels ----------------------------------------------------------------------------------------------------
 // DiagonalPreconditioner::factorize: 1/a_jj, or 1 when the diagonal is missing or zero.  identity != 0 -> all ones.
+// `diag_shift`: column index of row 0's diagonal (0 on one GPU; the local numbering keeps owned columns first, so 0).
 template <typename T>
 __global__ void __launch_bounds__(CG_THREADS)
 cg_invdiag_kernel(int n, const int *__restrict__ indptr, const int *__restrict__ indices,
@@ -111,18 +198,27 @@ cg_invdiag_kernel(int n, const int *__restrict__ indptr, const int *__restrict__
   dinv[j] = d;
 }
 
-// r = b - tmp (tmp = A x0); p = D^-1 r; rhs2 = b.b, res2 = r.r, abs_new = r.p; thresholds and early exits.
+// contiguous chunk of CTA `b` when n elements are split over `g` CTAs in multiples of 1024
+__device__ __forceinline__ void cta_chunk(int n, int &lo, int &hi) {
+  const int per = ((n + gridDim.x - 1) / gridDim.x + 1023) & ~1023;
+  lo = min(n, static_cast<int>(blockIdx.x) * per);
+  hi = min(n, lo + per);
+}
+
+// r = b - tmp (tmp = A x0, or absent when x0 = 0); p = D^-1 r (+ halo push); rhs2 = b.b, res2 = r.r, abs_new = r.p
 template <typename T>
 __global__ void __launch_bounds__(CG_THREADS)
 cg_init_kernel(int n, const T *__restrict__ b, const T *__restrict__ tmp, const T *__restrict__ dinv,
-               T *__restrict__ r, T *__restrict__ p, double tol, int relative, CgScalars *__restrict__ sc,
-               double *__restrict__ partials) {
-  __shared__ double s_red[3 * 8];
+               T *__restrict__ r, T *__restrict__ p, CgScalars *__restrict__ sc, double *__restrict__ partials,
+               DistDev d, int use_nccl) {
+  __shared__ double s_red[3 * 16];
   __shared__ unsigned s_flag;
+  int lo, hi;
+  cta_chunk(n, lo, hi);
   T s0 = T(0), s1 = T(0), s2 = T(0);
-  for (int i = blockIdx.x * CG_THREADS + threadIdx.x; i < n; i += gridDim.x * CG_THREADS) {
+  for (int i = lo + threadIdx.x; i < hi; i += CG_THREADS) {
     const T bi = b[i];
-    const T ri = bi - tmp[i];
+    const T ri = tmp ? bi - tmp[i] : bi;
     const T pi = dinv[i] * ri;
     r[i] = ri;
     p[i] = pi;
@@ -130,97 +226,120 @@ cg_init_kernel(int n, const T *__restrict__ b, const T *__restrict__ tmp, const 
     s1 = fma_t(ri, ri, s1);
     s2 = fma_t(ri, pi, s2);
   }
-  double v[3] = {static_cast<double>(s0), static_cast<double>(s1), static_cast<double>(s2)};
-  if (grid_sum_last_block<3>(v, partials, &sc->ticket[0], s_red, &s_flag) && threadIdx.x == 0) {
-    // scalars are kept in double but rounded through T where Eigen's RealScalar would be T
-    const double rhs2 = static_cast<double>(static_cast<T>(v[0]));
-    const double res2 = static_cast<double>(static_cast<T>(v[1]));
-    sc->rhs2 = rhs2;
-    sc->res2 = res2;
-    sc->abs_new = static_cast<double>(static_cast<T>(v[2]));
-    sc->abs_old = 0.0;
-    sc->iters = 0;
-    sc->alpha = 0.0;
-    sc->beta = 0.0;
-    const double tiny = sizeof(T) == 4 ? static_cast<double>(FLT_MIN) : DBL_MIN;
-    double thr = relative ? static_cast<double>(static_cast<T>(static_cast<T>(tol) * static_cast<T>(tol) * static_cast<T>(rhs2)))
-                          : static_cast<double>(static_cast<T>(tol) * static_cast<T>(tol));
-    if (relative && thr < tiny) thr = tiny;
-    if (tol < 0.0) thr = -1.0;  // fixed-iteration timing runs: never converge
-    sc->thr = thr;
-    int done = 0;
-    if (tol >= 0.0 && relative && rhs2 == 0.0) done = 1;
-    else if (sc->stop_le ? (res2 <= thr) : (res2 < thr)) done = 1;
-    else if (sc->max_iters <= 0) done = 2;
-    sc->done = done;
+  if (d.world > 1) {
+    __syncthreads();
+    dist_halo_push<T>(d, p, lo, hi);
+    dist_halo_signal(d, &s_flag);
   }
+  double v[3] = {static_cast<double>(s0), static_cast<double>(s1), static_cast<double>(s2)};
+  if (grid_sum_last_block<3>(v, partials, &sc->ticket[0], s_red, &s_flag))
+    cg_reduce_and_finish<3>(v, d, use_nccl, sc, [&](const double (&t)[3]) { cg_finish_init<T>(sc, t); });
 }
 
 // ---- iteration kernels --------------------------------------------------------------------------------------------------
-template <typename T, bool ROW_MAJOR_ORDER>
-__global__ void __launch_bounds__(SPMV_ROWS)
+template <typename T, int LPR, bool ROW_MAJOR_ORDER>
+__global__ void __launch_bounds__(SPMV_THREADS)
 cg_spmv_dot_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ indices,
                    const T *__restrict__ values, const T *__restrict__ p, T *__restrict__ tmp,
-                   CgScalars *__restrict__ sc, double *__restrict__ partials) {
-  __shared__ SpmvSmem<T> S;
+                   CgScalars *__restrict__ sc, double *__restrict__ partials, DistDev d, int use_nccl) {
+  extern __shared__ unsigned char smem_raw[];
+  __shared__ double s_red[16];
   __shared__ unsigned s_flag;
-  if (sc->done) return;
-  const T yi = spmv_cta<T, ROW_MAJOR_ORDER>(S, rows, indptr, indices, values, p, tmp);
-  const int row = blockIdx.x * SPMV_ROWS + threadIdx.x;
-  const T pi = row < rows ? p[row] : T(0);
-  __syncthreads();  // S.val may still be read by the vector path
-  double v[1] = {static_cast<double>(pi * yi)};
-  if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], S.red, &s_flag) && threadIdx.x == 0) {
-    const T pap = static_cast<T>(v[0]);
-    sc->pAp = static_cast<double>(pap);
-    sc->alpha = static_cast<double>(static_cast<T>(sc->abs_new) / pap);
+  if (sc->done) {
+    // the deferred x += alpha p of the final iteration has been applied by the direction kernel before this launch:
+    // retire alpha so that a replayed direction kernel is a no-op
+    if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;
+    return;
   }
+  if (d.world > 1) {
+    if (threadIdx.x == 0) dist_halo_wait(d);
+    __syncthreads();
+  }
+  double v[1] = {spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, p)};
+  if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag))
+    cg_reduce_and_finish<1>(v, d, use_nccl, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
 }
+
+template <typename T> struct Vec4T;
+template <> struct Vec4T<float> { using type = float4; };
+template <> struct Vec4T<double> { using type = double4; };
 
 template <typename T>
 __global__ void __launch_bounds__(CG_THREADS)
-cg_update_kernel(int n, const T *__restrict__ p, const T *__restrict__ tmp, const T *__restrict__ dinv,
-                 T *__restrict__ x, T *__restrict__ r, CgScalars *__restrict__ sc, double *__restrict__ partials) {
-  __shared__ double s_red[2 * 8];
+cg_residual_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv, T *__restrict__ r,
+                   CgScalars *__restrict__ sc, double *__restrict__ partials, DistDev d, int use_nccl) {
+  __shared__ double s_red[2 * 16];
   __shared__ unsigned s_flag;
   if (sc->done) return;
   const T alpha = static_cast<T>(sc->alpha);
   T s_rr = T(0), s_rz = T(0);
-  for (int i = blockIdx.x * CG_THREADS + threadIdx.x; i < n; i += gridDim.x * CG_THREADS) {
-    x[i] = fma_t(alpha, p[i], x[i]);
-    const T ri = fma_t(-alpha, tmp[i], r[i]);
-    r[i] = ri;
-    const T zi = dinv[i] * ri;
-    s_rr = fma_t(ri, ri, s_rr);
-    s_rz = fma_t(ri, zi, s_rz);
+  using V = typename Vec4T<T>::type;
+  const int n4 = n >> 2;
+  for (int i = blockIdx.x * CG_THREADS + threadIdx.x; i < n4; i += gridDim.x * CG_THREADS) {
+    const V t4 = reinterpret_cast<const V *>(tmp)[i];
+    const V d4 = reinterpret_cast<const V *>(dinv)[i];
+    V r4 = reinterpret_cast<V *>(r)[i];
+    r4.x = fma_t(-alpha, t4.x, r4.x); r4.y = fma_t(-alpha, t4.y, r4.y);
+    r4.z = fma_t(-alpha, t4.z, r4.z); r4.w = fma_t(-alpha, t4.w, r4.w);
+    reinterpret_cast<V *>(r)[i] = r4;
+    s_rr = fma_t(r4.x, r4.x, s_rr); s_rz = fma_t(r4.x, d4.x * r4.x, s_rz);
+    s_rr = fma_t(r4.y, r4.y, s_rr); s_rz = fma_t(r4.y, d4.y * r4.y, s_rz);
+    s_rr = fma_t(r4.z, r4.z, s_rr); s_rz = fma_t(r4.z, d4.z * r4.z, s_rz);
+    s_rr = fma_t(r4.w, r4.w, s_rr); s_rz = fma_t(r4.w, d4.w * r4.w, s_rz);
   }
-  double v[2] = {static_cast<double>(s_rr), static_cast<double>(s_rz)};
-  if (grid_sum_last_block<2>(v, partials, &sc->ticket[2], s_red, &s_flag) && threadIdx.x == 0) {
-    const double res2 = static_cast<double>(static_cast<T>(v[0]));
-    sc->res2 = res2;
-    if (sc->stop_le ? (res2 <= sc->thr) : (res2 < sc->thr)) {
-      sc->done = 1;  // Eigen breaks before ++i
-      if (sc->stop_le) sc->iters += 1;  // CUCG counts the body it just finished (k++)
-    } else {
-      const T abs_old = static_cast<T>(sc->abs_new);
-      const T abs_new = static_cast<T>(v[1]);
-      sc->abs_old = static_cast<double>(abs_old);
-      sc->abs_new = static_cast<double>(abs_new);
-      sc->beta = static_cast<double>(abs_new / abs_old);
-      sc->iters += 1;
-      if (sc->iters >= sc->max_iters) sc->done = 2;
+  if (blockIdx.x == 0) {
+    for (int i = (n4 << 2) + threadIdx.x; i < n; i += CG_THREADS) {
+      const T ri = fma_t(-alpha, tmp[i], r[i]);
+      r[i] = ri;
+      s_rr = fma_t(ri, ri, s_rr);
+      s_rz = fma_t(ri, dinv[i] * ri, s_rz);
     }
   }
+  double v[2] = {static_cast<double>(s_rr), static_cast<double>(s_rz)};
+  if (grid_sum_last_block<2>(v, partials, &sc->ticket[2], s_red, &s_flag))
+    cg_reduce_and_finish<2>(v, d, use_nccl, sc, [&](const double (&t)[2]) { cg_finish_B<T>(sc, t[0], t[1]); });
 }
 
 template <typename T>
 __global__ void __launch_bounds__(CG_THREADS)
-cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, T *__restrict__ p,
-                    const CgScalars *__restrict__ sc) {
-  if (sc->done == 1) return;  // converged: p is dead.  (done == 2: Eigen still updates p before leaving the loop)
+cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, T *__restrict__ p, T *__restrict__ x,
+                    const CgScalars *__restrict__ sc, DistDev d) {
+  __shared__ unsigned s_flag;
+  const int done = sc->done;
+  if (done == 3) return;
+  if (done != 0 && sc->alpha == 0.0) return;  // replayed after the end of the solve: x already has its last update
+  const T alpha = static_cast<T>(sc->alpha);
   const T beta = static_cast<T>(sc->beta);
-  for (int i = blockIdx.x * CG_THREADS + threadIdx.x; i < n; i += gridDim.x * CG_THREADS)
-    p[i] = fma_t(beta, p[i], dinv[i] * r[i]);
+  int lo, hi;
+  cta_chunk(n, lo, hi);
+  using V = typename Vec4T<T>::type;
+  // converged (done == 1): only the deferred x += alpha p is still owed; p is dead.  done == 2: Eigen still updates p
+  const bool update_p = done != 1;
+  const int lo4 = lo >> 2, hi4 = hi >> 2;  // chunks are multiples of 1024 except the last one's end
+  for (int i = lo4 + threadIdx.x; i < hi4; i += CG_THREADS) {
+    V p4 = reinterpret_cast<V *>(p)[i];
+    V x4 = reinterpret_cast<V *>(x)[i];
+    x4.x = fma_t(alpha, p4.x, x4.x); x4.y = fma_t(alpha, p4.y, x4.y);
+    x4.z = fma_t(alpha, p4.z, x4.z); x4.w = fma_t(alpha, p4.w, x4.w);
+    reinterpret_cast<V *>(x)[i] = x4;
+    if (update_p) {
+      const V r4 = reinterpret_cast<const V *>(r)[i];
+      const V d4 = reinterpret_cast<const V *>(dinv)[i];
+      p4.x = fma_t(beta, p4.x, d4.x * r4.x); p4.y = fma_t(beta, p4.y, d4.y * r4.y);
+      p4.z = fma_t(beta, p4.z, d4.z * r4.z); p4.w = fma_t(beta, p4.w, d4.w * r4.w);
+      reinterpret_cast<V *>(p)[i] = p4;
+    }
+  }
+  for (int i = (hi4 << 2) + threadIdx.x; i < hi; i += CG_THREADS) {
+    const T pi = p[i];
+    x[i] = fma_t(alpha, pi, x[i]);
+    if (update_p) p[i] = fma_t(beta, pi, dinv[i] * r[i]);
+  }
+  if (d.world > 1 && done == 0) {
+    __syncthreads();
+    dist_halo_push<T>(d, p, lo, hi);
+    dist_halo_signal(d, &s_flag);
+  }
 }
 
 // ---- host ------------------------------------------------------------------------------------------------------------------
@@ -230,73 +349,87 @@ struct CgSolver::Impl {
   double tol;
   int mode;
   bool verbose;
-  DeviceBuffer r, p, tmp, dinv, partials, scalars;
+  DistContext *dist;
+  bool use_nccl = false;
+  DeviceBuffer r, p_own, tmp, dinv, partials, scalars, xstage, bstage;
+  void *p = nullptr;          // operand vector of the SpMV: p_own, or the comm buffer's vector when distributed
   CgScalars *h_sc = nullptr;  // pinned mirror
   cudaStream_t stream = nullptr;
   cudaEvent_t ev_in = nullptr, ev_out = nullptr;
   cudaGraphExec_t graph = nullptr;
   void *graph_x = nullptr;
   int graph_iters = 0;
-  int vec_grid = 0, spmv_grid = 0;
+  int vec_grid = 0, spmv_grid = 0, lpr = 1;
+  int n = 0;  // owned rows
 
-  Impl(const CsrMatrix &A_, int mi, double t, int m, bool v) : A(A_), max_iters(mi), tol(t), mode(m), verbose(v) {}
+  Impl(const CsrMatrix &A_, int mi, double t, int m, bool v, DistContext *d)
+      : A(A_), max_iters(mi), tol(t), mode(m), verbose(v), dist(d) {}
+  DistDev dev() const { return dist ? dist->dev() : DistDev{}; }
 };
-
-CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool verbose, DistPlan *dist)
-    : impl_(new Impl(A, max_iters, tol, mode, verbose)) {
-  (void)dist;
-  QDSP_REQUIRE(A.rows == A.cols, QDSP_ERR_INVALID, "CG needs a square matrix");
-  QDSP_REQUIRE(mode == QDSP_CG_EIGEN_JACOBI || mode == QDSP_CG_CUCG, QDSP_ERR_INVALID, "CG: unknown mode");
-  Impl &I = *impl_;
-  const size_t n = static_cast<size_t>(A.rows), sv = A.value_bytes();
-  I.r.alloc(n * sv); I.p.alloc(n * sv); I.tmp.alloc(n * sv); I.dinv.alloc(n * sv);
-  I.spmv_grid = ceil_div(A.rows, SPMV_ROWS);
-  I.vec_grid = std::max(1, std::min(ceil_div(A.rows, CG_THREADS), device_props().sm_count * 8));
-  I.partials.alloc(sizeof(double) * 3 * static_cast<size_t>(std::max(I.spmv_grid, I.vec_grid)));
-  I.scalars.alloc(sizeof(CgScalars));
-  QDSP_CUDA(cudaMemset(I.scalars.get(), 0, sizeof(CgScalars)));
-  QDSP_CUDA(cudaHostAlloc(reinterpret_cast<void **>(&I.h_sc), sizeof(CgScalars), cudaHostAllocDefault));
-  QDSP_CUDA(cudaStreamCreateWithFlags(&I.stream, cudaStreamNonBlocking));
-  QDSP_CUDA(cudaEventCreateWithFlags(&I.ev_in, cudaEventDisableTiming));
-  QDSP_CUDA(cudaEventCreateWithFlags(&I.ev_out, cudaEventDisableTiming));
-  const int identity = mode == QDSP_CG_CUCG;
-  const unsigned g = static_cast<unsigned>(ceil_div(A.rows, CG_THREADS));
-  if (A.dtype == QDSP_F32)
-    cg_invdiag_kernel<float><<<g, CG_THREADS, 0, I.stream>>>(A.rows, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<float>(), identity, I.dinv.get<float>());
-  else
-    cg_invdiag_kernel<double><<<g, CG_THREADS, 0, I.stream>>>(A.rows, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<double>(), identity, I.dinv.get<double>());
-  QDSP_LAUNCH_CHECK();
-  QDSP_CUDA(cudaStreamSynchronize(I.stream));
-}
-
-CgSolver::~CgSolver() {
-  if (!impl_) return;
-  Impl &I = *impl_;
-  if (I.graph) cudaGraphExecDestroy(I.graph);
-  if (I.ev_in) cudaEventDestroy(I.ev_in);
-  if (I.ev_out) cudaEventDestroy(I.ev_out);
-  if (I.stream) cudaStreamDestroy(I.stream);
-  if (I.h_sc) cudaFreeHost(I.h_sc);
-}
 
 namespace {
 
-template <typename T>
-void launch_iteration(CgSolver::Impl &I, T *x) {
+template <typename T, int LPR>
+void launch_spmv_dot(CgSolver::Impl &I) {
   const CsrMatrix &A = I.A;
   auto *sc = I.scalars.get<CgScalars>();
-  double *part = I.partials.get<double>();
-  const int n = A.rows;
-  if (A.row_major_order)
-    cg_spmv_dot_kernel<T, true><<<I.spmv_grid, SPMV_ROWS, 0, I.stream>>>(n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), I.p.get<T>(), I.tmp.get<T>(), sc, part);
+  const size_t smem = spmv_smem_bytes<T>();
+  if (A.row_major_order && LPR == 1)
+    cg_spmv_dot_kernel<T, LPR, true><<<I.spmv_grid, SPMV_THREADS, smem, I.stream>>>(
+        I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+        sc, I.partials.get<double>(), I.dev(), I.use_nccl);
   else
-    cg_spmv_dot_kernel<T, false><<<I.spmv_grid, SPMV_ROWS, 0, I.stream>>>(n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), I.p.get<T>(), I.tmp.get<T>(), sc, part);
-  QDSP_LAUNCH_CHECK();
-  cg_update_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, I.p.get<T>(), I.tmp.get<T>(), I.dinv.get<T>(), x, I.r.get<T>(), sc, part);
-  QDSP_LAUNCH_CHECK();
-  cg_direction_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, I.r.get<T>(), I.dinv.get<T>(), I.p.get<T>(), sc);
+    cg_spmv_dot_kernel<T, LPR, false><<<I.spmv_grid, SPMV_THREADS, smem, I.stream>>>(
+        I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+        sc, I.partials.get<double>(), I.dev(), I.use_nccl);
   QDSP_LAUNCH_CHECK();
 }
+
+template <typename T, int LPR>
+int spmv_dot_occupancy() {
+  const size_t smem = spmv_smem_bytes<T>();
+  int occ = 0;
+  QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_dot_kernel<T, LPR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_dot_kernel<T, LPR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  QDSP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, cg_spmv_dot_kernel<T, LPR, false>, SPMV_THREADS, smem));
+  return std::max(1, occ);
+}
+
+#define QDSP_LPR_SWITCH(lpr, CALL) \
+  switch (lpr) {                   \
+    case 1: CALL(1); break;        \
+    case 2: CALL(2); break;        \
+    case 4: CALL(4); break;        \
+    case 8: CALL(8); break;        \
+    case 16: CALL(16); break;      \
+    default: CALL(32); break;      \
+  }
+
+template <typename T>
+void nccl_reduce_then(CgSolver::Impl &I, int count, int which) {
+  auto *sc = I.scalars.get<CgScalars>();
+  I.dist->nccl_allreduce_double(reinterpret_cast<double *>(reinterpret_cast<char *>(sc) + offsetof(CgScalars, red)), count, I.stream);
+  cg_scalars_kernel<T><<<1, 1, 0, I.stream>>>(sc, which);
+  QDSP_LAUNCH_CHECK();
+}
+
+template <typename T>
+void launch_iteration(CgSolver::Impl &I, T *x) {
+  auto *sc = I.scalars.get<CgScalars>();
+  double *part = I.partials.get<double>();
+  const int n = I.n;
+#define QDSP_CALL(L) launch_spmv_dot<T, L>(I)
+  QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
+#undef QDSP_CALL
+  if (I.use_nccl) nccl_reduce_then<T>(I, 1, 1);
+  cg_residual_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(), sc, part, I.dev(), I.use_nccl);
+  QDSP_LAUNCH_CHECK();
+  if (I.use_nccl) nccl_reduce_then<T>(I, 2, 2);
+  cg_direction_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, I.r.get<T>(), I.dinv.get<T>(), static_cast<T *>(I.p), x, sc, I.dev());
+  QDSP_LAUNCH_CHECK();
+}
+
+int kernels_per_iteration(const CgSolver::Impl &I) { return I.use_nccl ? 5 : 3; }
 
 // (Re)captures `iters` iterations on x into an executable graph.
 template <typename T>
@@ -324,22 +457,27 @@ void ensure_graph(CgSolver::Impl &I, T *x, int iters) {
 template <typename T>
 void start(CgSolver::Impl &I, T *x, const T *b, int max_iters, double tol, bool never_converge) {
   const CsrMatrix &A = I.A;
-  const int n = A.rows;
+  const int n = I.n;
   auto *sc = I.scalars.get<CgScalars>();
   CgScalars init{};
   init.max_iters = max_iters;
   init.stop_le = (I.mode == QDSP_CG_CUCG) ? 1 : 0;
+  init.relative = I.mode == QDSP_CG_EIGEN_JACOBI;
+  init.tol = never_converge ? -1.0 : tol;
   QDSP_CUDA(cudaMemcpyAsync(sc, &init, sizeof(init), cudaMemcpyHostToDevice, I.stream));
-  if (I.mode == QDSP_CG_EIGEN_JACOBI)  // IterativeSolverBase::_solve_impl: x.setZero()
+  const T *tmp = nullptr;
+  if (I.mode == QDSP_CG_EIGEN_JACOBI) {
+    // IterativeSolverBase::_solve_impl: x.setZero()  =>  r = b, no product needed
     QDSP_CUDA(cudaMemsetAsync(x, 0, sizeof(T) * static_cast<size_t>(n), I.stream));
-  cudaStream_t s = I.stream;
-  // tmp = A x0 through the plain SpMV path on the solver's stream
-  A.spmv(x, I.tmp.get(), s);
-  const int relative = I.mode == QDSP_CG_EIGEN_JACOBI;
-  cg_init_kernel<T><<<I.vec_grid, CG_THREADS, 0, s>>>(n, b, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(), I.p.get<T>(),
-                                                      never_converge ? -1.0 : tol, relative, sc,
-                                                      I.partials.get<double>());
+  } else {
+    QDSP_REQUIRE(I.dist == nullptr, QDSP_ERR_UNSUPPORTED, "CUCG mode (start from the x passed in) is single-GPU only");
+    A.spmv(x, I.tmp.get(), I.stream);  // tmp = A x0
+    tmp = I.tmp.get<T>();
+  }
+  cg_init_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, b, tmp, I.dinv.get<T>(), I.r.get<T>(), static_cast<T *>(I.p), sc,
+                                                             I.partials.get<double>(), I.dev(), I.use_nccl);
   QDSP_LAUNCH_CHECK();
+  if (I.use_nccl) nccl_reduce_then<T>(I, 3, 0);
 }
 
 template <typename T>
@@ -360,11 +498,12 @@ void solve_t(CgSolver::Impl &I, void *xv, const void *bv, cudaStream_t user, int
     if (h.done || launched >= I.max_iters) break;
     ensure_graph<T>(I, x, batch);
     QDSP_CUDA(cudaGraphLaunch(I.graph, I.stream));
-    count_launch(3 * batch);
+    count_launch(kernels_per_iteration(I) * batch);
     launched += batch;
   }
   QDSP_CUDA(cudaEventRecord(I.ev_out, I.stream));
   QDSP_CUDA(cudaStreamWaitEvent(user, I.ev_out, 0));
+  QDSP_REQUIRE(h.done != 3, QDSP_ERR_COMM, "CG: a peer rank did not answer (halo / all-reduce spin timed out)");
   if (iterations) *iterations = h.iters;
   if (I.mode == QDSP_CG_EIGEN_JACOBI) {
     const double err = h.rhs2 == 0.0 ? 0.0 : std::sqrt(static_cast<double>(static_cast<T>(h.res2 / h.rhs2)));
@@ -380,7 +519,79 @@ void solve_t(CgSolver::Impl &I, void *xv, const void *bv, cudaStream_t user, int
   }
 }
 
+template <typename T>
+void run_fixed_t(CgSolver::Impl &I, void *x, const void *b, int iters, cudaStream_t stream) {
+  QDSP_CUDA(cudaEventRecord(I.ev_in, stream));
+  QDSP_CUDA(cudaStreamWaitEvent(I.stream, I.ev_in, 0));
+  const int batch = std::max(1, std::min(iters, 16));
+  start<T>(I, static_cast<T *>(x), static_cast<const T *>(b), iters + 1, 0.0, true);
+  ensure_graph<T>(I, static_cast<T *>(x), batch);
+  int left = iters;
+  while (left >= batch) {
+    QDSP_CUDA(cudaGraphLaunch(I.graph, I.stream));
+    count_launch(kernels_per_iteration(I) * batch);
+    left -= batch;
+  }
+  for (; left > 0; --left) launch_iteration<T>(I, static_cast<T *>(x));
+  QDSP_CUDA(cudaEventRecord(I.ev_out, I.stream));
+  QDSP_CUDA(cudaStreamWaitEvent(stream, I.ev_out, 0));
+}
+
 }  // namespace
+
+CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool verbose, DistContext *dist)
+    : impl_(new Impl(A, max_iters, tol, mode, verbose, dist)) {
+  Impl &I = *impl_;
+  QDSP_REQUIRE(mode == QDSP_CG_EIGEN_JACOBI || mode == QDSP_CG_CUCG, QDSP_ERR_INVALID, "CG: unknown mode");
+  if (dist) {
+    QDSP_REQUIRE(dist->ready() && dist->n_local() == A.rows && dist->n_local() + dist->n_ghost() == A.cols &&
+                     dist->dtype() == A.dtype,
+                 QDSP_ERR_STATE, "distributed CG: the matrix must be localized on this context and peers attached");
+    I.p = dist->vector_ptr();
+    const char *e = std::getenv("QDSP_ALLREDUCE");
+    I.use_nccl = e && std::string(e) == "nccl";
+    if (I.use_nccl) QDSP_REQUIRE(dist->has_nccl(), QDSP_ERR_STATE, "QDSP_ALLREDUCE=nccl but no NCCL communicator was initialised");
+  } else {
+    QDSP_REQUIRE(A.rows == A.cols, QDSP_ERR_INVALID, "CG needs a square matrix");
+  }
+  I.n = A.rows;
+  const size_t n = static_cast<size_t>(A.rows), sv = A.value_bytes();
+  I.r.alloc(n * sv); I.tmp.alloc(n * sv); I.dinv.alloc(n * sv);
+  if (!dist) { I.p_own.alloc(n * sv); I.p = I.p_own.get(); }
+  I.lpr = spmv_lanes_per_row(A.nnz, A.rows);
+  int occ = 1;
+#define QDSP_CALL(L) occ = (A.dtype == QDSP_F32) ? spmv_dot_occupancy<float, L>() : spmv_dot_occupancy<double, L>()
+  QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
+#undef QDSP_CALL
+  const int R = SPMV_CONSUMERS / I.lpr;
+  I.spmv_grid = std::max(1, std::min(ceil_div(A.rows, R), device_props().sm_count * occ));
+  I.vec_grid = std::max(1, std::min(ceil_div(A.rows, 1024), device_props().sm_count * 8));
+  I.partials.alloc(sizeof(double) * 3 * static_cast<size_t>(std::max(I.spmv_grid, I.vec_grid)));
+  I.scalars.alloc(sizeof(CgScalars));
+  QDSP_CUDA(cudaMemset(I.scalars.get(), 0, sizeof(CgScalars)));
+  QDSP_CUDA(cudaHostAlloc(reinterpret_cast<void **>(&I.h_sc), sizeof(CgScalars), cudaHostAllocDefault));
+  QDSP_CUDA(cudaStreamCreateWithFlags(&I.stream, cudaStreamNonBlocking));
+  QDSP_CUDA(cudaEventCreateWithFlags(&I.ev_in, cudaEventDisableTiming));
+  QDSP_CUDA(cudaEventCreateWithFlags(&I.ev_out, cudaEventDisableTiming));
+  const int identity = mode == QDSP_CG_CUCG;
+  const unsigned g = static_cast<unsigned>(ceil_div(A.rows, CG_THREADS));
+  if (A.dtype == QDSP_F32)
+    cg_invdiag_kernel<float><<<g, CG_THREADS, 0, I.stream>>>(A.rows, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<float>(), identity, I.dinv.get<float>());
+  else
+    cg_invdiag_kernel<double><<<g, CG_THREADS, 0, I.stream>>>(A.rows, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<double>(), identity, I.dinv.get<double>());
+  QDSP_LAUNCH_CHECK();
+  QDSP_CUDA(cudaStreamSynchronize(I.stream));
+}
+
+CgSolver::~CgSolver() {
+  if (!impl_) return;
+  Impl &I = *impl_;
+  if (I.graph) cudaGraphExecDestroy(I.graph);
+  if (I.ev_in) cudaEventDestroy(I.ev_in);
+  if (I.ev_out) cudaEventDestroy(I.ev_out);
+  if (I.stream) cudaStreamDestroy(I.stream);
+  if (I.h_sc) cudaFreeHost(I.h_sc);
+}
 
 void CgSolver::solve(void *x, const void *b, cudaStream_t stream, int *iterations, double *error, int *success) {
   QDSP_REQUIRE(x != nullptr && b != nullptr, QDSP_ERR_INVALID, "CG: null vector");
@@ -388,31 +599,25 @@ void CgSolver::solve(void *x, const void *b, cudaStream_t stream, int *iteration
   else solve_t<double>(*impl_, x, b, stream, iterations, error, success);
 }
 
+// Host-buffer entry (qdsp_cg_solve_host): staging buffers live with the solver, so a call costs two copies, no malloc.
+void CgSolver::solve_host(void *x_host, const void *b_host, cudaStream_t stream, int *iterations, double *error,
+                          int *success) {
+  QDSP_REQUIRE(x_host != nullptr && b_host != nullptr, QDSP_ERR_INVALID, "CG: null vector");
+  Impl &I = *impl_;
+  const size_t bytes = I.A.value_bytes() * static_cast<size_t>(I.n);
+  if (I.xstage.bytes() < bytes) { I.xstage.alloc(bytes); I.bstage.alloc(bytes); }
+  QDSP_CUDA(cudaMemcpyAsync(I.bstage.get(), b_host, bytes, cudaMemcpyHostToDevice, stream));
+  if (I.mode == QDSP_CG_CUCG)  // CUCG starts from the x passed in; Eigen's solve(b) zeroes it
+    QDSP_CUDA(cudaMemcpyAsync(I.xstage.get(), x_host, bytes, cudaMemcpyHostToDevice, stream));
+  solve(I.xstage.get(), I.bstage.get(), stream, iterations, error, success);
+  QDSP_CUDA(cudaMemcpyAsync(x_host, I.xstage.get(), bytes, cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+}
+
 void CgSolver::run_fixed(void *x, const void *b, int iters, cudaStream_t stream) {
   QDSP_REQUIRE(x != nullptr && b != nullptr && iters >= 0, QDSP_ERR_INVALID, "CG: bad arguments");
-  Impl &I = *impl_;
-  QDSP_CUDA(cudaEventRecord(I.ev_in, stream));
-  QDSP_CUDA(cudaStreamWaitEvent(I.stream, I.ev_in, 0));
-  const int batch = std::max(1, std::min(iters, 16));
-  if (I.A.dtype == QDSP_F32) {
-    start<float>(I, static_cast<float *>(x), static_cast<const float *>(b), iters + 1, 0.0, true);
-    ensure_graph<float>(I, static_cast<float *>(x), batch);
-  } else {
-    start<double>(I, static_cast<double *>(x), static_cast<const double *>(b), iters + 1, 0.0, true);
-    ensure_graph<double>(I, static_cast<double *>(x), batch);
-  }
-  int left = iters;
-  while (left >= batch) {
-    QDSP_CUDA(cudaGraphLaunch(I.graph, I.stream));
-    count_launch(3 * batch);
-    left -= batch;
-  }
-  for (; left > 0; --left) {
-    if (I.A.dtype == QDSP_F32) launch_iteration<float>(I, static_cast<float *>(x));
-    else launch_iteration<double>(I, static_cast<double *>(x));
-  }
-  QDSP_CUDA(cudaEventRecord(I.ev_out, I.stream));
-  QDSP_CUDA(cudaStreamWaitEvent(stream, I.ev_out, 0));
+  if (impl_->A.dtype == QDSP_F32) run_fixed_t<float>(*impl_, x, b, iters, stream);
+  else run_fixed_t<double>(*impl_, x, b, iters, stream);
 }
 
 }  // namespace qdsp

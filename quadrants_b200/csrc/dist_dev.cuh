@@ -1,0 +1,185 @@
+// dist_dev.cuh -- device side of the multi-GPU path: what a CG / SpMV kernel needs to talk to the other ranks over
+// NVLink peer memory, with no collective library in the loop.
+//
+// The reference has nothing here (single device, quadrants/rhi/cuda/cuda_context.cpp:16-26); the design is SURVEY 8(e):
+// row-block partition, ghost entries of x written by their owner straight into the consumer's vector (peer stores
+// through NVSwitch), CG scalars all-reduced in-kernel.
+//
+// Every rank owns one "comm buffer" (cudaMalloc, exported with cudaIpcGetMemHandle, mapped by every peer):
+//   [0, 2048)      reduction slots   slots[2 parity][8 ranks][4 values][2 words]   8-byte words {payload32 | seq32}
+//   [2048, 2112)   halo flags        flags[8 ranks]                                 8-byte, monotone sequence numbers
+//   [4096, ...)    the operand vector of SpMV: n_loc owned entries followed by n_ghost ghost entries
+// Protocol:
+//   * halo: after a rank has produced its owned part of the vector it stores the entries each neighbour needs into
+//     that neighbour's ghost segment, fences at system scope, and stores its push count into the neighbour's
+//     flags[rank].  A consumer kernel spins (ld.acquire.sys) until flags[q] >= its own push count for every
+//     neighbour q it receives from -- ranks run the same kernel sequence, so "my push count" is the expected value.
+//   * all-reduce of up to 4 doubles (NCCL "LL" style): each 64-bit value travels as two 8-byte words carrying 32 data
+//     bits + the 32-bit sequence number; an aligned 8-byte store is single-copy atomic, so data and flag arrive
+//     together and one NVLink latency is the whole cost.  Slots alternate by sequence parity: a rank can be at most
+//     one reduction ahead of a peer (it needs the peer's value to finish the current one).  Every rank sums the 8
+//     contributions in rank order, so all ranks compute bit-identical scalars and take identical decisions.
+//   * a spin that lasts longer than ~4 s raises *error and stops: a dead peer cannot hang the GPU.
+#pragma once
+#include "common.cuh"
+
+namespace qdsp {
+
+constexpr int DIST_MAX_RANKS = 8;
+constexpr int DIST_MAX_VALUES = 4;
+constexpr size_t DIST_SLOTS_OFF = 0;
+constexpr size_t DIST_FLAGS_OFF = 2048;
+constexpr size_t DIST_VECTOR_OFF = 4096;
+constexpr long long DIST_SPIN_LIMIT = 8000000000LL;  // clock64 ticks (~4 s)
+
+struct DistDev {
+  int rank = 0, world = 1;
+  unsigned char *self = nullptr;                 // my comm buffer
+  unsigned char *peer[DIST_MAX_RANKS] = {};      // peer[q] = rank q's comm buffer mapped here (peer[rank] == self)
+  // halo: what I send
+  int n_send = 0;
+  int send_peer[DIST_MAX_RANKS] = {};
+  const int *send_list[DIST_MAX_RANKS] = {};     // device, sorted local row ids
+  int send_count[DIST_MAX_RANKS] = {};
+  int send_dst[DIST_MAX_RANKS] = {};             // element offset inside the peer's operand vector (its ghost slot)
+  // halo: whom I receive from
+  int n_recv = 0;
+  int recv_peer[DIST_MAX_RANKS] = {};
+  unsigned *counters = nullptr;                  // device, local: [0] reduction seq, [1] halo push count, [2] ticket
+  int *error = nullptr;                          // device, local: != 0 after a timeout
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void st_sys_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_release_sys_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_sys_u64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ unsigned long long *dist_slot(unsigned char *buf, unsigned parity, int from_rank, int j) {
+  return reinterpret_cast<unsigned long long *>(buf + DIST_SLOTS_OFF) +
+         ((static_cast<size_t>(parity) * DIST_MAX_RANKS + from_rank) * DIST_MAX_VALUES + j) * 2;
+}
+__device__ __forceinline__ unsigned long long *dist_flag(unsigned char *buf, int from_rank) {
+  return reinterpret_cast<unsigned long long *>(buf + DIST_FLAGS_OFF) + from_rank;
+}
+
+// All-reduce (sum) of v[0..NV) across ranks.  Called by ALL 32 lanes of ONE warp of ONE CTA per rank; every lane
+// returns the totals.  world == 1: identity.
+template <int NV>
+__device__ __forceinline__ void dist_allreduce(const DistDev &d, double (&v)[NV]) {
+  static_assert(NV <= DIST_MAX_VALUES, "too many values");
+  if (d.world <= 1) return;
+  const int lane = lane_id();
+  unsigned seq = 0;
+  if (lane == 0) seq = ++d.counters[0];
+  seq = __shfl_sync(FULL, seq, 0);
+  const unsigned parity = seq & 1u;
+  // lane q talks to rank q
+  if (lane < d.world && lane != d.rank) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const unsigned long long bits = static_cast<unsigned long long>(__double_as_longlong(v[j]));
+      unsigned long long *dst = dist_slot(d.peer[lane], parity, d.rank, j);
+      st_sys_u64(dst, ((bits & 0xffffffffull) << 32) | seq);
+      st_sys_u64(dst + 1, ((bits >> 32) << 32) | seq);
+    }
+  }
+  double got[NV];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) got[j] = v[j];
+  if (lane < d.world && lane != d.rank) {
+    const long long t0 = clock64();
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const unsigned long long *src = dist_slot(d.self, parity, lane, j);
+      unsigned long long lo, hi;
+      while (true) {
+        lo = ld_sys_u64(src);
+        hi = ld_sys_u64(src + 1);
+        if (static_cast<unsigned>(lo) == seq && static_cast<unsigned>(hi) == seq) break;
+        if (clock64() - t0 > DIST_SPIN_LIMIT) {
+          atomicExch(d.error, 1);
+          lo = hi = 0;
+          break;
+        }
+      }
+      got[j] = __longlong_as_double(static_cast<long long>((lo >> 32) | ((hi >> 32) << 32)));
+    }
+  }
+  // fixed rank order: identical bits on every rank
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    double s = 0.0;
+    for (int q = 0; q < d.world; ++q) s += __shfl_sync(FULL, got[j], q);
+    v[j] = s;
+  }
+}
+
+// Stores the entries of vec[lo, hi) that neighbours need into their ghost segments.  Called by all threads of a CTA
+// that has just written vec[lo, hi) (after a __syncthreads()).
+template <typename T>
+__device__ __forceinline__ void dist_halo_push(const DistDev &d, const T *vec, int lo, int hi) {
+  for (int s = 0; s < d.n_send; ++s) {
+    const int *list = d.send_list[s];
+    const int cnt = d.send_count[s];
+    // first list position with row >= lo / >= hi (binary search, every thread: the lists are tiny and L1-resident)
+    int a = 0, b = cnt;
+    while (a < b) { const int m = (a + b) >> 1; if (list[m] < lo) a = m + 1; else b = m; }
+    const int jlo = a;
+    b = cnt;
+    while (a < b) { const int m = (a + b) >> 1; if (list[m] < hi) a = m + 1; else b = m; }
+    const int jhi = a;
+    T *dst = reinterpret_cast<T *>(d.peer[d.send_peer[s]] + DIST_VECTOR_OFF) + d.send_dst[s];
+    for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[list[j]];
+  }
+}
+
+// Called by every thread of every CTA after its pushes; the last CTA to arrive publishes the new push count to the
+// neighbours.  `s_flag` is a shared-memory word.
+__device__ __forceinline__ void dist_halo_signal(const DistDev &d, unsigned *s_flag) {
+  if (d.world <= 1) return;
+  __threadfence_system();  // my pushes are visible system-wide before my ticket
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned t = atomicAdd(&d.counters[2], 1u);
+    *s_flag = (t == gridDim.x - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (*s_flag && threadIdx.x == 0) {
+    __threadfence_system();
+    d.counters[2] = 0u;
+    const unsigned count = ++d.counters[1];
+    for (int s = 0; s < d.n_send; ++s) st_release_sys_u64(dist_flag(d.peer[d.send_peer[s]], d.rank), count);
+  }
+}
+
+// Called by thread 0 of a CTA before the CTA's first read of a ghost entry; follow with __syncthreads().
+__device__ __forceinline__ void dist_halo_wait(const DistDev &d) {
+  if (d.world <= 1) return;
+  const unsigned want = *reinterpret_cast<volatile unsigned *>(&d.counters[1]);
+  const long long t0 = clock64();
+  for (int r = 0; r < d.n_recv; ++r) {
+    const unsigned long long *f = dist_flag(d.self, d.recv_peer[r]);
+    while (ld_acquire_sys_u64(f) < want) {
+      if (clock64() - t0 > DIST_SPIN_LIMIT) {
+        atomicExch(d.error, 2);
+        break;
+      }
+    }
+  }
+}
+#endif  // __CUDACC__
+
+}  // namespace qdsp

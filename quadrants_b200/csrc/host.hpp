@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "dist_dev.cuh"
 
 namespace qdsp {
 
@@ -30,7 +31,9 @@ class CsrMatrix {
   // default storage_format: one accumulator, entries of a row added left to right with fma), true = row_major
   // (two alternating accumulators, SparseDenseProduct.h:66-80)
   bool row_major_order = false;
-  DeviceBuffer indptr, indices, values;  // indices/values carry 64 bytes of zeroed padding for 128-bit loads
+  DeviceBuffer indptr, indices, values;  // each carries 64 bytes of padding: TMA bulk copies read whole 16-byte units
+  // lanes per row of the SpMV kernels (1, 2, 4 ... 32), chosen from the mean row length on first use; 0 = not yet
+  mutable int spmv_lpr = 0;
 
   size_t value_bytes() const { return dtype == QDSP_F64 ? 8 : 4; }
   void allocate(int rows_, int cols_, int64_t nnz_, int dtype_);
@@ -79,15 +82,19 @@ class Builder {
   size_t slot_bytes() const { return dtype_ == QDSP_F64 ? 8 : 4; }
 };
 
+// y = A x with the persistent TMA-fed kernel; `d` (world > 1) makes every CTA wait for the halo of x first (spmv.cu)
+void launch_spmv(const CsrMatrix &A, const void *x, void *y, const DistDev &d, cudaStream_t stream);
+
 // ---- CG<EigenT,DT> and CUCG (quadrants/program/conjugate_gradient.h) ---------------------------------------------------
-struct CgScalars;  // device-resident scalar block, cg.cu
-class DistPlan;    // dist.cu
+struct CgScalars;    // device-resident scalar block, cg.cu
+class DistContext;   // dist.hpp
 
 class CgSolver {
  public:
-  CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool verbose, DistPlan *dist = nullptr);
+  CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool verbose, DistContext *dist = nullptr);
   ~CgSolver();
   void solve(void *x, const void *b, cudaStream_t stream, int *iterations, double *error, int *success);
+  void solve_host(void *x_host, const void *b_host, cudaStream_t stream, int *iterations, double *error, int *success);
   void run_fixed(void *x, const void *b, int iters, cudaStream_t stream);
   struct Impl;
 

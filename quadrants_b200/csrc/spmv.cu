@@ -2,6 +2,7 @@
 // (quadrants/program/sparse_matrix.cpp:654-780).
 #include <cstring>
 #include <fstream>
+#include <algorithm>
 #include <vector>
 
 #include "host.hpp"
@@ -28,32 +29,75 @@ const DeviceProps &device_props() {
   return cached;
 }
 
-template <typename T, bool ROW_MAJOR_ORDER>
-__global__ void __launch_bounds__(SPMV_ROWS)
+template <typename T, int LPR, bool ROW_MAJOR_ORDER>
+__global__ void __launch_bounds__(SPMV_THREADS)
 spmv_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ indices, const T *__restrict__ values,
-            const T *__restrict__ x, T *__restrict__ y) {
-  __shared__ SpmvSmem<T> S;
-  spmv_cta<T, ROW_MAJOR_ORDER>(S, rows, indptr, indices, values, x, y);
+            const T *__restrict__ x, T *__restrict__ y, DistDev d) {
+  extern __shared__ unsigned char smem_raw[];
+  if (d.world > 1) {
+    if (threadIdx.x == 0) dist_halo_wait(d);
+    __syncthreads();
+  }
+  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, x, y, nullptr);
+}
+
+namespace {
+
+// persistent grid = SM count x resident CTAs of this instantiation (queried once per instantiation)
+template <typename T, int LPR>
+int spmv_ctas_per_sm() {
+  static int occ = 0;
+  if (occ == 0) {
+    const size_t smem = spmv_smem_bytes<T>();
+    QDSP_CUDA(cudaFuncSetAttribute(spmv_kernel<T, LPR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    QDSP_CUDA(cudaFuncSetAttribute(spmv_kernel<T, LPR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    int o = 0;
+    QDSP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, spmv_kernel<T, LPR, false>, SPMV_THREADS, smem));
+    occ = std::max(1, o);
+  }
+  return occ;
+}
+
+template <typename T, int LPR>
+void launch_spmv_t(const CsrMatrix &A, const T *x, T *y, const DistDev &d, cudaStream_t stream) {
+  constexpr int R = SPMV_CONSUMERS / LPR;
+  const int grid = std::max(1, std::min(ceil_div(A.rows, R), device_props().sm_count * spmv_ctas_per_sm<T, LPR>()));
+  const size_t smem = spmv_smem_bytes<T>();
+  const int *ip = A.indptr.get<int>(), *ix = A.indices.get<int>();
+  if (A.row_major_order && LPR == 1)
+    spmv_kernel<T, LPR, true><<<grid, SPMV_THREADS, smem, stream>>>(A.rows, ip, ix, A.values.get<T>(), x, y, d);
+  else
+    spmv_kernel<T, LPR, false><<<grid, SPMV_THREADS, smem, stream>>>(A.rows, ip, ix, A.values.get<T>(), x, y, d);
+  QDSP_LAUNCH_CHECK();
+}
+
+template <typename T>
+void launch_spmv_lpr(const CsrMatrix &A, const void *x, void *y, const DistDev &d, cudaStream_t stream) {
+  const T *xv = static_cast<const T *>(x);
+  T *yv = static_cast<T *>(y);
+  switch (A.spmv_lpr) {
+    case 1: launch_spmv_t<T, 1>(A, xv, yv, d, stream); break;
+    case 2: launch_spmv_t<T, 2>(A, xv, yv, d, stream); break;
+    case 4: launch_spmv_t<T, 4>(A, xv, yv, d, stream); break;
+    case 8: launch_spmv_t<T, 8>(A, xv, yv, d, stream); break;
+    case 16: launch_spmv_t<T, 16>(A, xv, yv, d, stream); break;
+    default: launch_spmv_t<T, 32>(A, xv, yv, d, stream); break;
+  }
+}
+
+}  // namespace
+
+void launch_spmv(const CsrMatrix &A, const void *x, void *y, const DistDev &d, cudaStream_t stream) {
+  if (A.rows == 0) return;
+  if (A.spmv_lpr == 0) A.spmv_lpr = spmv_lanes_per_row(A.nnz, A.rows);
+  if (A.dtype == QDSP_F32) launch_spmv_lpr<float>(A, x, y, d, stream);
+  else launch_spmv_lpr<double>(A, x, y, d, stream);
 }
 
 void CsrMatrix::spmv(const void *x, void *y, cudaStream_t stream) const {
   QDSP_REQUIRE(x != nullptr && y != nullptr, QDSP_ERR_INVALID, "spmv: null vector");
   QDSP_REQUIRE(x != y, QDSP_ERR_INVALID, "spmv: x and y must not alias");
-  if (rows == 0) return;
-  const unsigned grid = static_cast<unsigned>((rows + SPMV_ROWS - 1) / SPMV_ROWS);
-  const int *ip = indptr.get<int>(), *ix = indices.get<int>();
-  if (dtype == QDSP_F32) {
-    if (row_major_order)
-      spmv_kernel<float, true><<<grid, SPMV_ROWS, 0, stream>>>(rows, ip, ix, values.get<float>(), static_cast<const float *>(x), static_cast<float *>(y));
-    else
-      spmv_kernel<float, false><<<grid, SPMV_ROWS, 0, stream>>>(rows, ip, ix, values.get<float>(), static_cast<const float *>(x), static_cast<float *>(y));
-  } else {
-    if (row_major_order)
-      spmv_kernel<double, true><<<grid, SPMV_ROWS, 0, stream>>>(rows, ip, ix, values.get<double>(), static_cast<const double *>(x), static_cast<double *>(y));
-    else
-      spmv_kernel<double, false><<<grid, SPMV_ROWS, 0, stream>>>(rows, ip, ix, values.get<double>(), static_cast<const double *>(x), static_cast<double *>(y));
-  }
-  QDSP_LAUNCH_CHECK();
+  launch_spmv(*this, x, y, DistDev{}, stream);
 }
 
 void CsrMatrix::to_host(std::vector<int32_t> &ip, std::vector<int32_t> &ix, std::vector<char> &vals) const {

@@ -504,7 +504,10 @@ def test_cg_c1_poisson512(qd, oracle, dtype):
     import scipy.sparse as sp
     Ad = sp.csr_matrix((ov.astype(np.float64), oi, oo), shape=(n, n))
     res = np.linalg.norm(Ad @ x - b) / np.linalg.norm(b)
-    assert res < (5e-6 if dtype == np.float32 else 1.5e-6)
+    res_ref = np.linalg.norm(Ad @ xo.astype(np.float64) - b) / np.linalg.norm(b)
+    # fp32: the recurrence residual meets 1e-6 but the TRUE residual of Eigen's own fp32 solve stalls at 2.7e-2
+    # (cond ~ 1e5); the GPU must do no worse than the reference
+    assert res < (1.2 * res_ref if dtype == np.float32 else 1.5e-6), (res, res_ref)
     rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
     # cond(A) ~ 1e5: two fp32 solves that both meet |r|/|b| <= 1e-6 agree to ~1e-2 at best; fp64 to ~1e-6
     assert rel < (2e-2 if dtype == np.float32 else 1e-5)
