@@ -270,9 +270,7 @@ def run_gpu(args):
         xg = qd.ndarray(qd.f32, hi - lo)
         dcg = ctx.cg(ips, 1e-30)
 
-        class _Shim:  # same call shape as the single-GPU solver below
-            cg_solver = dcg
-        cg = _Shim()
+        cg = argparse.Namespace(cg_solver=dcg)  # same call shape as the single-GPU solver below
     else:
         r, c, v = poisson3d_triplets_device(n, 0, n, dev)
         ntrip = int(r.shape[0])
@@ -426,7 +424,12 @@ def run_gpu(args):
             line["cpu_baseline"] = cpu
         print(json.dumps(line))
     if world > 1:
+        # tear the solver and the peer mappings down while every rank is still alive
+        torch.cuda.synchronize()
+        dcg.close()
+        ctx.close()
         dist.barrier()
+        torch.cuda.synchronize()
         dist.destroy_process_group()
     return 0
 
@@ -442,6 +445,9 @@ def main():
     ap.add_argument("--cpu-iters", type=int, default=12, help="CG iterations of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    if os.environ.get("QDSP_DEBUG_HANG"):
+        import faulthandler
+        faulthandler.dump_traceback_later(float(os.environ["QDSP_DEBUG_HANG"]), exit=True)
     if args.warmup < 3:
         args.warmup = 3
     if args.impl == "reference":

@@ -134,22 +134,24 @@ int qdsp_cg_destroy(qdsp_cg_t s);
  * quadrants/rhi/cuda/cuda_context.cpp:16-26; design in SURVEY.md 8(e)) -------------------------------------------------
  * Rank g owns global rows and columns [row_offsets[g], row_offsets[g+1]).  Each rank builds the CSR of ITS rows with
  * global column ids (rows = n_local, cols = global size), then:
- *   qdsp_dist_localize      renumbers the columns (owned first, then ghosts ascending by global id) and allocates the
+ *   qdsp_dist_localize      renumbers the columns (owned first, then from ghost_base -- n_local rounded up to a 128-byte
+ *                           boundary -- the ghosts ascending by global id) and allocates the
  *                           peer-visible buffer that holds the SpMV operand [owned | ghosts];
  *   qdsp_dist_ghost_ids     the ghost ids, grouped by owner (owner_offsets): the caller ships each group to its owner
  *                           (any transport; quadrants_b200.distributed uses torch.distributed), which registers it with
- *   qdsp_dist_set_send_list (dst_offset = the requester's n_local + its owner_offsets[owner]);
+ *   qdsp_dist_set_send_list (dst_offset = the requester's ghost_base + its owner_offsets[owner]);
  *   qdsp_dist_comm_handle / qdsp_dist_attach   exchange and map the CUDA IPC handles of the buffers (NVLink P2P).
  * After that qdsp_dist_spmv and a solver from qdsp_cg_create_dist run with the halo of x pushed by peer stores and the
  * CG dot products all-reduced inside the kernels over peer memory (QDSP_ALLREDUCE=nccl: by ncclAllReduce instead, after
  * qdsp_dist_nccl_init).  x, b, y are the rank's owned slices (n_local elements).  Every rank must make the same calls. */
 /* Pure host helper behind qdsp_dist_localize (no CUDA needed): plans one rank from its global column ids. */
 int qdsp_dist_plan_host(int rank, int world, const int64_t *row_offsets, int32_t *indices_inout, int64_t nnz,
-                        int32_t *ghost_ids_out, int64_t ghost_capacity, int64_t *n_ghost, int32_t *owner_offsets_out);
+                        int ghost_base /* local id of the first ghost; < 0: n_local */, int32_t *ghost_ids_out,
+                        int64_t ghost_capacity, int64_t *n_ghost, int32_t *owner_offsets_out);
 int qdsp_dist_create(int rank, int world, qdsp_dist_t *out);
 int qdsp_dist_destroy(qdsp_dist_t d);
 int qdsp_dist_localize(qdsp_dist_t d, qdsp_csr_t m, const int64_t *row_offsets, void *stream, int *n_local,
-                       int *n_ghost, int32_t *owner_offsets_out /* world + 1 */);
+                       int *ghost_base, int *n_ghost, int32_t *owner_offsets_out /* world + 1 */);
 int qdsp_dist_ghost_ids(qdsp_dist_t d, const int32_t **host_ids);
 int qdsp_dist_set_send_list(qdsp_dist_t d, int peer, const int32_t *global_ids, int count, int dst_offset);
 int qdsp_dist_comm_handle(qdsp_dist_t d, void *out64);

@@ -53,10 +53,10 @@ SIGNATURES = {
     "qdsp_cg_solve_host": (_i, [_vp, _vp, _vp, _vp, _P(_i), _P(_d), _P(_i)]),
     "qdsp_cg_run_fixed": (_i, [_vp, _vp, _vp, _i, _vp]),
     "qdsp_cg_destroy": (_i, [_vp]),
-    "qdsp_dist_plan_host": (_i, [_i, _i, _vp, _vp, _i64, _vp, _i64, _P(_i64), _vp]),
+    "qdsp_dist_plan_host": (_i, [_i, _i, _vp, _vp, _i64, _i, _vp, _i64, _P(_i64), _vp]),
     "qdsp_dist_create": (_i, [_i, _i, _P(_vp)]),
     "qdsp_dist_destroy": (_i, [_vp]),
-    "qdsp_dist_localize": (_i, [_vp, _vp, _vp, _vp, _P(_i), _P(_i), _vp]),
+    "qdsp_dist_localize": (_i, [_vp, _vp, _vp, _vp, _P(_i), _P(_i), _P(_i), _vp]),
     "qdsp_dist_ghost_ids": (_i, [_vp, _P(_vp)]),
     "qdsp_dist_set_send_list": (_i, [_vp, _i, _vp, _i, _i]),
     "qdsp_dist_comm_handle": (_i, [_vp, _vp]),

@@ -223,10 +223,11 @@ int qdsp_cg_destroy(qdsp_cg_t s) {
 
 // ---- multi-GPU ------------------------------------------------------------------------------------------------------------
 int qdsp_dist_plan_host(int rank, int world, const int64_t *row_offsets, int32_t *indices_inout, int64_t nnz,
-                        int32_t *ghost_ids_out, int64_t ghost_capacity, int64_t *n_ghost, int32_t *owner_offsets_out) {
+                        int ghost_base, int32_t *ghost_ids_out, int64_t ghost_capacity, int64_t *n_ghost,
+                        int32_t *owner_offsets_out) {
   return guarded([&] {
     NOT_NULL(n_ghost); NOT_NULL(owner_offsets_out);
-    const DistPlan p = dist_plan_host(rank, world, row_offsets, indices_inout, nnz);
+    const DistPlan p = dist_plan_host(rank, world, row_offsets, indices_inout, nnz, ghost_base);
     *n_ghost = static_cast<int64_t>(p.ghost_ids.size());
     for (int q = 0; q <= world; ++q) owner_offsets_out[q] = p.owner_offsets[q];
     if (ghost_ids_out) {
@@ -247,11 +248,12 @@ int qdsp_dist_destroy(qdsp_dist_t d) {
   return guarded([&] { delete d; });
 }
 int qdsp_dist_localize(qdsp_dist_t d, qdsp_csr_t m, const int64_t *row_offsets, void *stream, int *n_local,
-                       int *n_ghost, int32_t *owner_offsets_out) {
+                       int *ghost_base, int *n_ghost, int32_t *owner_offsets_out) {
   return guarded([&] {
     NOT_NULL(d); NOT_NULL(m);
     d->impl->localize(*m->impl, row_offsets, S(stream));
     if (n_local) *n_local = d->impl->n_local();
+    if (ghost_base) *ghost_base = d->impl->ghost_base();
     if (n_ghost) *n_ghost = d->impl->n_ghost();
     if (owner_offsets_out)
       for (int q = 0; q <= d->impl->world(); ++q) owner_offsets_out[q] = d->impl->plan().owner_offsets[q];

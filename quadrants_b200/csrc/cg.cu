@@ -226,11 +226,7 @@ cg_init_kernel(int n, const T *__restrict__ b, const T *__restrict__ tmp, const 
     s1 = fma_t(ri, ri, s1);
     s2 = fma_t(ri, pi, s2);
   }
-  if (d.world > 1) {
-    __syncthreads();
-    dist_halo_push<T>(d, p, lo, hi);
-    dist_halo_signal(d, &s_flag);
-  }
+  dist_halo_push_signal<T>(d, p, lo, hi, &s_flag);
   double v[3] = {static_cast<double>(s0), static_cast<double>(s1), static_cast<double>(s2)};
   if (grid_sum_last_block<3>(v, partials, &sc->ticket[0], s_red, &s_flag))
     cg_reduce_and_finish<3>(v, d, use_nccl, sc, [&](const double (&t)[3]) { cg_finish_init<T>(sc, t); });
@@ -251,11 +247,7 @@ cg_spmv_dot_kernel(int rows, const int *__restrict__ indptr, const int *__restri
     if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;
     return;
   }
-  if (d.world > 1) {
-    if (threadIdx.x == 0) dist_halo_wait(d);
-    __syncthreads();
-  }
-  double v[1] = {spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, p)};
+  double v[1] = {spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, p, d)};
   if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag))
     cg_reduce_and_finish<1>(v, d, use_nccl, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
 }
@@ -335,11 +327,7 @@ cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, 
     x[i] = fma_t(alpha, pi, x[i]);
     if (update_p) p[i] = fma_t(beta, pi, dinv[i] * r[i]);
   }
-  if (d.world > 1 && done == 0) {
-    __syncthreads();
-    dist_halo_push<T>(d, p, lo, hi);
-    dist_halo_signal(d, &s_flag);
-  }
+  if (done == 0) dist_halo_push_signal<T>(d, p, lo, hi, &s_flag);
 }
 
 // ---- host ------------------------------------------------------------------------------------------------------------------
@@ -519,20 +507,61 @@ void solve_t(CgSolver::Impl &I, void *xv, const void *bv, cudaStream_t user, int
   }
 }
 
+// QDSP_CG_TRACE=1: no graph, CUDA events around every kernel of the last iterations, averages printed to stderr
+// (a debugging aid for the multi-GPU overheads; never used for a reported number)
+template <typename T>
+void run_traced(CgSolver::Impl &I, T *x, int iters) {
+  const int K = 3, keep = std::min(iters, 64);
+  std::vector<cudaEvent_t> ev(static_cast<size_t>(keep) * (K + 1));
+  for (auto &e : ev) QDSP_CUDA(cudaEventCreate(&e));
+  auto *sc = I.scalars.get<CgScalars>();
+  double *part = I.partials.get<double>();
+  for (int it = 0; it < iters; ++it) {
+    const int slot = it - (iters - keep);
+    auto mark = [&](int k) { if (slot >= 0) QDSP_CUDA(cudaEventRecord(ev[static_cast<size_t>(slot) * (K + 1) + k], I.stream)); };
+    mark(0);
+#define QDSP_CALL(L) launch_spmv_dot<T, L>(I)
+    QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
+#undef QDSP_CALL
+    mark(1);
+    cg_residual_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(I.n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(), sc, part, I.dev(), I.use_nccl);
+    mark(2);
+    cg_direction_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(I.n, I.r.get<T>(), I.dinv.get<T>(), static_cast<T *>(I.p), x, sc, I.dev());
+    mark(3);
+  }
+  QDSP_CUDA(cudaStreamSynchronize(I.stream));
+  double sum[K] = {0, 0, 0}, total = 0;
+  for (int s = 0; s < keep; ++s)
+    for (int k = 0; k < K; ++k) {
+      float ms = 0;
+      QDSP_CUDA(cudaEventElapsedTime(&ms, ev[static_cast<size_t>(s) * (K + 1) + k], ev[static_cast<size_t>(s) * (K + 1) + k + 1]));
+      sum[k] += ms;
+      total += ms;
+    }
+  std::fprintf(stderr, "[qdsp trace rank %d] per iteration over %d: spmv_dot %.2f us, residual %.2f us, direction %.2f us, total %.2f us\n",
+               I.dist ? I.dist->rank() : 0, keep, 1e3 * sum[0] / keep, 1e3 * sum[1] / keep, 1e3 * sum[2] / keep, 1e3 * total / keep);
+  for (auto &e : ev) cudaEventDestroy(e);
+}
+
 template <typename T>
 void run_fixed_t(CgSolver::Impl &I, void *x, const void *b, int iters, cudaStream_t stream) {
   QDSP_CUDA(cudaEventRecord(I.ev_in, stream));
   QDSP_CUDA(cudaStreamWaitEvent(I.stream, I.ev_in, 0));
   const int batch = std::max(1, std::min(iters, 16));
   start<T>(I, static_cast<T *>(x), static_cast<const T *>(b), iters + 1, 0.0, true);
-  ensure_graph<T>(I, static_cast<T *>(x), batch);
-  int left = iters;
-  while (left >= batch) {
-    QDSP_CUDA(cudaGraphLaunch(I.graph, I.stream));
-    count_launch(kernels_per_iteration(I) * batch);
-    left -= batch;
+  const char *trace = std::getenv("QDSP_CG_TRACE");
+  if (trace && trace[0] == '1' && !I.use_nccl) {
+    run_traced<T>(I, static_cast<T *>(x), iters);
+  } else {
+    ensure_graph<T>(I, static_cast<T *>(x), batch);
+    int left = iters;
+    while (left >= batch) {
+      QDSP_CUDA(cudaGraphLaunch(I.graph, I.stream));
+      count_launch(kernels_per_iteration(I) * batch);
+      left -= batch;
+    }
+    for (; left > 0; --left) launch_iteration<T>(I, static_cast<T *>(x));
   }
-  for (; left > 0; --left) launch_iteration<T>(I, static_cast<T *>(x));
   QDSP_CUDA(cudaEventRecord(I.ev_out, I.stream));
   QDSP_CUDA(cudaStreamWaitEvent(stream, I.ev_out, 0));
 }
@@ -544,7 +573,7 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
   Impl &I = *impl_;
   QDSP_REQUIRE(mode == QDSP_CG_EIGEN_JACOBI || mode == QDSP_CG_CUCG, QDSP_ERR_INVALID, "CG: unknown mode");
   if (dist) {
-    QDSP_REQUIRE(dist->ready() && dist->n_local() == A.rows && dist->n_local() + dist->n_ghost() == A.cols &&
+    QDSP_REQUIRE(dist->ready() && dist->n_local() == A.rows && dist->ghost_base() + dist->n_ghost() == A.cols &&
                      dist->dtype() == A.dtype,
                  QDSP_ERR_STATE, "distributed CG: the matrix must be localized on this context and peers attached");
     I.p = dist->vector_ptr();

@@ -6,11 +6,13 @@
 #include <cstring>
 
 #include "dist.hpp"
+#include "spmv_kernels.cuh"
 
 namespace qdsp {
 
 // ---- plan (pure host) ------------------------------------------------------------------------------------------------
-DistPlan dist_plan_host(int rank, int world, const int64_t *row_offsets, int32_t *indices, int64_t nnz) {
+DistPlan dist_plan_host(int rank, int world, const int64_t *row_offsets, int32_t *indices, int64_t nnz,
+                        int ghost_base) {
   QDSP_REQUIRE(world >= 1 && world <= DIST_MAX_RANKS && rank >= 0 && rank < world, QDSP_ERR_INVALID,
                "dist plan: rank/world out of range (1..8 ranks)");
   QDSP_REQUIRE(row_offsets != nullptr && (nnz == 0 || indices != nullptr), QDSP_ERR_INVALID, "dist plan: null array");
@@ -21,6 +23,8 @@ DistPlan dist_plan_host(int rank, int world, const int64_t *row_offsets, int32_t
   const int64_t lo = row_offsets[rank], hi = row_offsets[rank + 1], total = row_offsets[world];
   DistPlan plan;
   plan.n_local = static_cast<int>(hi - lo);
+  plan.ghost_base = ghost_base < 0 ? plan.n_local : ghost_base;
+  QDSP_REQUIRE(plan.ghost_base >= plan.n_local, QDSP_ERR_INVALID, "dist plan: ghost_base below n_local");
   std::vector<int32_t> ghosts;
   for (int64_t k = 0; k < nnz; ++k) {
     const int64_t c = indices[k];
@@ -37,7 +41,7 @@ DistPlan dist_plan_host(int rank, int world, const int64_t *row_offsets, int32_t
   for (int64_t k = 0; k < nnz; ++k) {
     const int64_t c = indices[k];
     if (c >= lo && c < hi) indices[k] = static_cast<int32_t>(c - lo);
-    else indices[k] = plan.n_local + static_cast<int32_t>(std::lower_bound(ghosts.begin(), ghosts.end(), static_cast<int32_t>(c)) - ghosts.begin());
+    else indices[k] = plan.ghost_base + static_cast<int32_t>(std::lower_bound(ghosts.begin(), ghosts.end(), static_cast<int32_t>(c)) - ghosts.begin());
   }
   plan.ghost_ids = std::move(ghosts);
   return plan;
@@ -56,9 +60,11 @@ DistContext::~DistContext() {
   for (void *p : opened_)
     if (p) cudaIpcCloseMemHandle(p);
   if (nccl_comm_) {
-    using destroy_t = int (*)(void *);
+    // ncclCommAbort frees the communicator locally without waiting for the other ranks (ncclCommDestroy may block when
+    // this runs at interpreter shutdown, after the peers have gone)
+    using abort_t = int (*)(void *);
     if (void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD))
-      if (auto fn = reinterpret_cast<destroy_t>(dlsym(h, "ncclCommDestroy"))) fn(nccl_comm_);
+      if (auto fn = reinterpret_cast<abort_t>(dlsym(h, "ncclCommAbort"))) fn(nccl_comm_);
   }
 }
 
@@ -73,17 +79,38 @@ void DistContext::localize(CsrMatrix &A, const int64_t *row_offsets, cudaStream_
     QDSP_CUDA(cudaMemcpyAsync(idx.data(), A.indices.get(), sizeof(int32_t) * idx.size(), cudaMemcpyDeviceToHost, stream));
     QDSP_CUDA(cudaStreamSynchronize(stream));
   }
-  plan_ = dist_plan_host(rank_, world_, row_offsets, idx.data(), A.nnz);
+  // ghosts start on a 128-byte boundary of the operand vector (fp32: 32 elements; also fine for fp64)
+  const int n_loc = static_cast<int>(row_offsets[rank_ + 1] - row_offsets[rank_]);
+  plan_ = dist_plan_host(rank_, world_, row_offsets, idx.data(), A.nnz, (n_loc + 31) & ~31);
   if (A.nnz) {
     QDSP_CUDA(cudaMemcpyAsync(A.indices.get(), idx.data(), sizeof(int32_t) * idx.size(), cudaMemcpyHostToDevice, stream));
     QDSP_CUDA(cudaStreamSynchronize(stream));
   }
-  A.cols = plan_.n_local + n_ghost();
-  A.spmv_lpr = 0;
+  A.cols = plan_.ghost_base + n_ghost();
+  A.spmv_lpr = spmv_lanes_per_row(A.nnz, A.rows);
   dtype_ = A.dtype;
   row0_ = row_offsets[rank_];
+  // which row blocks of the SpMV kernel read a ghost column
+  {
+    const int R = SPMV_CONSUMERS / A.spmv_lpr;
+    const int nblk = std::max(1, (A.rows + R - 1) / R);
+    std::vector<int32_t> ip(static_cast<size_t>(A.rows) + 1);
+    QDSP_CUDA(cudaMemcpyAsync(ip.data(), A.indptr.get(), sizeof(int32_t) * ip.size(), cudaMemcpyDeviceToHost, stream));
+    QDSP_CUDA(cudaStreamSynchronize(stream));
+    std::vector<unsigned char> flags(nblk, 0);
+    for (int b = 0; b < nblk; ++b) {
+      const int r1 = std::min(A.rows, (b + 1) * R);
+      for (int64_t k = ip[static_cast<size_t>(b) * R]; k < ip[r1]; ++k)
+        if (idx[k] >= plan_.ghost_base) { flags[b] = 1; break; }
+    }
+    ghost_blocks_.alloc(flags.size());
+    QDSP_CUDA(cudaMemcpyAsync(ghost_blocks_.get(), flags.data(), flags.size(), cudaMemcpyHostToDevice, stream));
+    QDSP_CUDA(cudaStreamSynchronize(stream));
+    dev_.ghost_blocks = ghost_blocks_.get<unsigned char>();
+    dev_.ghost_block_rows = R;
+  }
   const size_t sv = A.value_bytes();
-  comm_.alloc(DIST_VECTOR_OFF + sv * (static_cast<size_t>(plan_.n_local) + n_ghost()) + 256);
+  comm_.alloc(DIST_VECTOR_OFF + sv * (static_cast<size_t>(plan_.ghost_base) + n_ghost()) + 256);
   QDSP_CUDA(cudaMemsetAsync(comm_.get(), 0, comm_.bytes(), stream));
   ctl_.alloc(64);
   QDSP_CUDA(cudaMemsetAsync(ctl_.get(), 0, 64, stream));
@@ -117,6 +144,9 @@ void DistContext::set_send_list(int peer, const int32_t *global_ids, int count, 
   dev_.send_list[s] = buf.get<int>();
   dev_.send_count[s] = count;
   dev_.send_dst[s] = dst_offset;
+  dev_.send_first[s] = local.front();
+  dev_.send_last[s] = local.back();
+  dev_.send_contig[s] = (local.back() - local.front() == count - 1) ? 1 : 0;
 }
 
 void DistContext::comm_handle(void *out64) const {
@@ -164,14 +194,12 @@ __global__ void __launch_bounds__(256) dist_load_push_kernel(int n, const T *__r
   const int per = ((n + gridDim.x - 1) / gridDim.x + 1023) & ~1023;
   const int lo = min(n, static_cast<int>(blockIdx.x) * per), hi = min(n, lo + per);
   for (int i = lo + threadIdx.x; i < hi; i += blockDim.x) vec[i] = x[i];
-  __syncthreads();
-  dist_halo_push<T>(d, vec, lo, hi);
-  dist_halo_signal(d, &s_flag);
+  dist_halo_push_signal<T>(d, vec, lo, hi, &s_flag);
 }
 
 void DistContext::spmv(const CsrMatrix &A, const void *x_loc, void *y_loc, cudaStream_t stream) {
   QDSP_REQUIRE(attached_, QDSP_ERR_STATE, "dist: attach the peers first");
-  QDSP_REQUIRE(A.rows == plan_.n_local && A.cols == plan_.n_local + n_ghost() && A.dtype == dtype_, QDSP_ERR_INVALID,
+  QDSP_REQUIRE(A.rows == plan_.n_local && A.cols == plan_.ghost_base + n_ghost() && A.dtype == dtype_, QDSP_ERR_INVALID,
                "dist spmv: the matrix is not the one localized on this context");
   const int n = plan_.n_local;
   const int grid = std::max(1, std::min(ceil_div(n, 1024), device_props().sm_count * 4));

@@ -12,14 +12,16 @@ namespace qdsp {
 // Result of planning one rank's row block: which columns are ghosts, who owns them, and the local renumbering.
 struct DistPlan {
   int n_local = 0;
+  int ghost_base = 0;                  // local column id of the first ghost (>= n_local; 128-byte aligned on the GPU)
   std::vector<int32_t> ghost_ids;      // global column ids of the ghosts, ascending (hence grouped by owner)
   std::vector<int32_t> owner_offsets;  // world + 1: ghosts owned by rank q are ghost_ids[owner_offsets[q] .. [q+1])
 };
 
 // Pure host function (no CUDA): rank `rank` owns global rows/cols [row_offsets[rank], row_offsets[rank+1]).
 // `indices` (global column ids of the rank's CSR rows) is rewritten in place to the local numbering:
-// owned column c -> c - row_offsets[rank]; ghost -> n_local + position in ghost_ids.
-DistPlan dist_plan_host(int rank, int world, const int64_t *row_offsets, int32_t *indices, int64_t nnz);
+// owned column c -> c - row_offsets[rank]; ghost -> ghost_base + position in ghost_ids (ghost_base < 0: n_local).
+DistPlan dist_plan_host(int rank, int world, const int64_t *row_offsets, int32_t *indices, int64_t nnz,
+                        int ghost_base = -1);
 
 class DistContext {
  public:
@@ -32,6 +34,7 @@ class DistContext {
   int world() const { return world_; }
   int n_local() const { return plan_.n_local; }
   int n_ghost() const { return static_cast<int>(plan_.ghost_ids.size()); }
+  int ghost_base() const { return plan_.ghost_base; }
   int dtype() const { return dtype_; }
   const DistPlan &plan() const { return plan_; }
 
@@ -61,7 +64,7 @@ class DistContext {
   int dtype_ = QDSP_F32;
   int64_t row0_ = 0;
   DistPlan plan_;
-  DeviceBuffer comm_, ctl_;
+  DeviceBuffer comm_, ctl_, ghost_blocks_;
   std::vector<DeviceBuffer> send_lists_;
   std::vector<void *> opened_;
   DistDev dev_;

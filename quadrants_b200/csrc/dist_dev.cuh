@@ -42,9 +42,15 @@ struct DistDev {
   const int *send_list[DIST_MAX_RANKS] = {};     // device, sorted local row ids
   int send_count[DIST_MAX_RANKS] = {};
   int send_dst[DIST_MAX_RANKS] = {};             // element offset inside the peer's operand vector (its ghost slot)
+  int send_first[DIST_MAX_RANKS] = {};           // smallest / largest row of the list, and whether it is one contiguous
+  int send_last[DIST_MAX_RANKS] = {};            // run (plane halos): lets a CTA skip or index the list without searching
+  int send_contig[DIST_MAX_RANKS] = {};
   // halo: whom I receive from
   int n_recv = 0;
   int recv_peer[DIST_MAX_RANKS] = {};
+  // which SpMV row blocks (of ghost_block_rows rows) read a ghost column: only those wait for the halo
+  const unsigned char *ghost_blocks = nullptr;
+  int ghost_block_rows = 0;
   unsigned *counters = nullptr;                  // device, local: [0] reduction seq, [1] halo push count, [2] ticket
   int *error = nullptr;                          // device, local: != 0 after a timeout
 };
@@ -127,42 +133,52 @@ __device__ __forceinline__ void dist_allreduce(const DistDev &d, double (&v)[NV]
   }
 }
 
-// Stores the entries of vec[lo, hi) that neighbours need into their ghost segments.  Called by all threads of a CTA
-// that has just written vec[lo, hi) (after a __syncthreads()).
+// Stores the entries of vec[lo, hi) that neighbours need into their ghost segments, then takes a ticket; the last CTA of
+// the grid publishes the new push count to the neighbours.  Called by all threads of every CTA of a kernel that has
+// just written vec[lo, hi) (chunks of different CTAs are disjoint and cover the vector).  `s_flag`: a shared word.
 template <typename T>
-__device__ __forceinline__ void dist_halo_push(const DistDev &d, const T *vec, int lo, int hi) {
+__device__ __forceinline__ void dist_halo_push_signal(const DistDev &d, const T *vec, int lo, int hi, unsigned *s_flag) {
+  if (d.world <= 1) return;
+  __syncthreads();  // the CTA's own writes of vec[lo, hi) are visible to all its threads
+  bool pushed = false;
   for (int s = 0; s < d.n_send; ++s) {
+    if (hi <= d.send_first[s] || lo > d.send_last[s] || lo >= hi) continue;  // most CTAs own no halo row
     const int *list = d.send_list[s];
     const int cnt = d.send_count[s];
-    // first list position with row >= lo / >= hi (binary search, every thread: the lists are tiny and L1-resident)
-    int a = 0, b = cnt;
-    while (a < b) { const int m = (a + b) >> 1; if (list[m] < lo) a = m + 1; else b = m; }
-    const int jlo = a;
-    b = cnt;
-    while (a < b) { const int m = (a + b) >> 1; if (list[m] < hi) a = m + 1; else b = m; }
-    const int jhi = a;
+    int jlo, jhi;
+    if (d.send_contig[s]) {
+      jlo = max(lo, d.send_first[s]) - d.send_first[s];
+      jhi = min(hi, d.send_last[s] + 1) - d.send_first[s];
+    } else {
+      int a = 0, b = cnt;
+      while (a < b) { const int m = (a + b) >> 1; if (list[m] < lo) a = m + 1; else b = m; }
+      jlo = a;
+      b = cnt;
+      while (a < b) { const int m = (a + b) >> 1; if (list[m] < hi) a = m + 1; else b = m; }
+      jhi = a;
+    }
     T *dst = reinterpret_cast<T *>(d.peer[d.send_peer[s]] + DIST_VECTOR_OFF) + d.send_dst[s];
-    for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[list[j]];
+    if (d.send_contig[s]) {
+      const int first = d.send_first[s];
+      for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[first + j];
+    } else {
+      for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[list[j]];
+    }
+    pushed = pushed || jhi > jlo;
   }
-}
-
-// Called by every thread of every CTA after its pushes; the last CTA to arrive publishes the new push count to the
-// neighbours.  `s_flag` is a shared-memory word.
-__device__ __forceinline__ void dist_halo_signal(const DistDev &d, unsigned *s_flag) {
-  if (d.world <= 1) return;
-  __threadfence_system();  // my pushes are visible system-wide before my ticket
   __syncthreads();
   if (threadIdx.x == 0) {
+    // cumulative fence: the barrier ordered the CTA's peer stores before this thread; only CTAs that pushed need it
+    if (pushed) __threadfence_system();
     const unsigned t = atomicAdd(&d.counters[2], 1u);
-    *s_flag = (t == gridDim.x - 1) ? 1u : 0u;
+    if (t == gridDim.x - 1) {
+      __threadfence_system();
+      d.counters[2] = 0u;
+      const unsigned count = ++d.counters[1];
+      for (int s = 0; s < d.n_send; ++s) st_release_sys_u64(dist_flag(d.peer[d.send_peer[s]], d.rank), count);
+    }
   }
-  __syncthreads();
-  if (*s_flag && threadIdx.x == 0) {
-    __threadfence_system();
-    d.counters[2] = 0u;
-    const unsigned count = ++d.counters[1];
-    for (int s = 0; s < d.n_send; ++s) st_release_sys_u64(dist_flag(d.peer[d.send_peer[s]], d.rank), count);
-  }
+  (void)s_flag;
 }
 
 // Called by thread 0 of a CTA before the CTA's first read of a ghost entry; follow with __syncthreads().

@@ -34,11 +34,7 @@ __global__ void __launch_bounds__(SPMV_THREADS)
 spmv_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ indices, const T *__restrict__ values,
             const T *__restrict__ x, T *__restrict__ y, DistDev d) {
   extern __shared__ unsigned char smem_raw[];
-  if (d.world > 1) {
-    if (threadIdx.x == 0) dist_halo_wait(d);
-    __syncthreads();
-  }
-  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, x, y, nullptr);
+  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, x, y, nullptr, d);
 }
 
 namespace {

@@ -24,6 +24,7 @@
 //   Tensor cores are deliberately unused: 2 flop per 8-12 bytes.
 #pragma once
 #include "common.cuh"
+#include "dist_dev.cuh"
 
 namespace qdsp {
 
@@ -111,12 +112,16 @@ __device__ __forceinline__ SpmvStage<T> spmv_stage(unsigned char *base, int s) {
 
 // The whole SpMV of one persistent CTA.  LPR = lanes per row.  Returns, per consumer thread, the sum over the rows it
 // owned of xdot[row] * y[row] in double (0 when xdot == nullptr); producer-warp threads return 0.
+// Multi-GPU (dist.world > 1): x = [owned | ghosts]; the ghosts are stored by the neighbour ranks.  Only row blocks
+// flagged in dist.ghost_blocks read a ghost, so the producer waits for the halo flags right before it hands the first
+// such block to the consumers (its acquire reaches them through the stage's mbarrier) and interior blocks start at
+// once.  The ghost segment begins on a 128-byte boundary, so no L1 line holds both owned and ghost entries.
 // `indptr`, `indices`, `values` must be readable 16 bytes past their ends (the matrices of this library carry 64).
 template <typename T, int LPR, bool ROW_MAJOR_ORDER>
 __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int rows, const int *__restrict__ indptr,
                                                   const int *__restrict__ indices, const T *__restrict__ values,
                                                   const T *__restrict__ x, T *__restrict__ y,
-                                                  const T *__restrict__ xdot) {
+                                                  const T *__restrict__ xdot, const DistDev &dist) {
   constexpr int R = SPMV_CONSUMERS / LPR;  // rows per block
   unsigned char *base = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
   auto *full = reinterpret_cast<unsigned long long *>(base + SPMV_STAGES * spmv_stage_bytes<T>());
@@ -130,6 +135,12 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  // no per-block ghost map for this block size: every CTA waits for the halo before its first gather
+  const bool lazy_halo = dist.world > 1 && dist.ghost_blocks != nullptr && dist.ghost_block_rows == R;
+  if (dist.world > 1 && !lazy_halo) {
+    if (t == 0) dist_halo_wait(dist);
+    __syncthreads();
+  }
 
   const int nblk = (rows + R - 1) / R;
   const int per_cta = (nblk + gridDim.x - 1) / gridDim.x;
@@ -142,7 +153,12 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
     if (t == SPMV_CONSUMERS && blk0 < blk1) {
       const unsigned long long pol = l2_evict_first_policy();
       int s_next = indptr[blk0 * R];
+      bool halo_pending = lazy_halo;
       for (int blk = blk0, it = 0; blk < blk1; ++blk, ++it) {
+        if (halo_pending && dist.ghost_blocks[blk]) {
+          dist_halo_wait(dist);
+          halo_pending = false;
+        }
         const int stage = it % SPMV_STAGES;
         const unsigned phase = (it / SPMV_STAGES) & 1;
         const int r0 = blk * R;

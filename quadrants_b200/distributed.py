@@ -34,20 +34,23 @@ def nnz_balanced_row_offsets(indptr: np.ndarray, world: int) -> np.ndarray:
     return np.maximum.accumulate(np.asarray(cuts, dtype=np.int64))
 
 
-def plan_host(rank: int, world: int, row_offsets, indices_global: np.ndarray):
-    """qdsp_dist_plan_host: -> (indices_local, ghost_ids, owner_offsets).  Pure host code, no GPU needed."""
+def plan_host(rank: int, world: int, row_offsets, indices_global: np.ndarray, ghost_base: int = -1):
+    """qdsp_dist_plan_host: -> (indices_local, ghost_ids, owner_offsets).  Pure host code, no GPU needed.
+    Ghost j gets local column id ghost_base + j (default: n_local)."""
     lib = _lib.load()
     ro = np.ascontiguousarray(row_offsets, dtype=np.int64)
     idx = np.ascontiguousarray(indices_global, dtype=np.int32).copy()
     ghosts = np.empty(max(1, idx.shape[0]), np.int32)
     n_ghost = C.c_int64()
     owner = np.zeros(world + 1, np.int32)
-    _lib.check(lib.qdsp_dist_plan_host(rank, world, ro.ctypes.data, idx.ctypes.data, idx.shape[0], ghosts.ctypes.data,
+    _lib.check(lib.qdsp_dist_plan_host(rank, world, ro.ctypes.data, idx.ctypes.data, idx.shape[0], int(ghost_base),
+                                       ghosts.ctypes.data,
                                        ghosts.shape[0], C.byref(n_ghost), owner.ctypes.data))
     return idx, ghosts[: n_ghost.value].copy(), owner
 
 
-def exchange_requests(rank: int, world: int, n_local: int, ghost_ids: np.ndarray, owner_offsets: np.ndarray, group=None):
+def exchange_requests(rank: int, world: int, ghost_base: int, ghost_ids: np.ndarray, owner_offsets: np.ndarray,
+                      group=None):
     """Every rank tells every owner which of its rows it needs and where to put them.
     -> list of (peer, ids, dst_offset): what THIS rank must send.  Works on any backend (gloo on CPU, nccl on GPU)."""
     import torch.distributed as dist
@@ -56,7 +59,7 @@ def exchange_requests(rank: int, world: int, n_local: int, ghost_ids: np.ndarray
     for q in range(world):
         a, b = int(owner_offsets[q]), int(owner_offsets[q + 1])
         if q != rank and b > a:
-            mine[q] = (np.ascontiguousarray(ghost_ids[a:b]), n_local + a)
+            mine[q] = (np.ascontiguousarray(ghost_ids[a:b]), ghost_base + a)
     if world == 1:
         return []
     everyone = [None] * world
@@ -86,11 +89,16 @@ class RowBlockContext:
         self.A = None
         self.n_local = self.n_ghost = 0
 
+    def close(self):
+        """Unmaps the peers' buffers and frees the communicator.  Call it (after closing the solvers built on this
+        context) while every rank is still alive; every rank must do so."""
+        if self._h.value:
+            self._lib.qdsp_dist_destroy(self._h)
+            self._h = C.c_void_p()
+
     def __del__(self):
         try:
-            if self._h.value:
-                self._lib.qdsp_dist_destroy(self._h)
-                self._h = C.c_void_p()
+            self.close()
         except Exception:
             pass
 
@@ -103,12 +111,12 @@ class RowBlockContext:
         m = getattr(A, "matrix", A)  # linalg.SparseMatrix or _core.CuSparseMatrix
         ro = np.ascontiguousarray(row_offsets, dtype=np.int64)
         assert ro.shape[0] == self.world + 1
-        nl, ng = C.c_int(), C.c_int()
+        nl, gb, ng = C.c_int(), C.c_int(), C.c_int()
         owner = np.zeros(self.world + 1, np.int32)
-        _lib.check(self._lib.qdsp_dist_localize(self._h, m._need(), ro.ctypes.data, _stream(), C.byref(nl), C.byref(ng),
-                                                owner.ctypes.data))
-        self.n_local, self.n_ghost, self.owner_offsets = nl.value, ng.value, owner
-        m._cols = self.n_local + self.n_ghost
+        _lib.check(self._lib.qdsp_dist_localize(self._h, m._need(), ro.ctypes.data, _stream(), C.byref(nl), C.byref(gb),
+                                                C.byref(ng), owner.ctypes.data))
+        self.n_local, self.ghost_base, self.n_ghost, self.owner_offsets = nl.value, gb.value, ng.value, owner
+        m._cols = self.ghost_base + self.n_ghost
         if hasattr(A, "m"):
             A.m = m._cols
         p = C.c_void_p()
@@ -116,7 +124,7 @@ class RowBlockContext:
         ghost_ids = (np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_int32)), shape=(self.n_ghost,)).copy()
                      if self.n_ghost else np.empty(0, np.int32))
         self.ghost_ids = ghost_ids
-        for peer, ids, dst in exchange_requests(self.rank, self.world, self.n_local, ghost_ids, owner, self.group):
+        for peer, ids, dst in exchange_requests(self.rank, self.world, self.ghost_base, ghost_ids, owner, self.group):
             _lib.check(self._lib.qdsp_dist_set_send_list(self._h, peer, ids.ctypes.data, ids.shape[0], dst))
         handle = (C.c_ubyte * 64)()
         _lib.check(self._lib.qdsp_dist_comm_handle(self._h, handle))
@@ -162,11 +170,14 @@ class DistCG:
         _lib.check(self._lib.qdsp_cg_create_dist(ctx._m._need(), ctx._h, int(max_iter), float(np.float32(tol)),
                                                  _lib.CG_EIGEN_JACOBI, int(bool(verbose)), C.byref(self._h)))
 
+    def close(self):
+        if self._h.value:
+            self._lib.qdsp_cg_destroy(self._h)
+            self._h = C.c_void_p()
+
     def __del__(self):
         try:
-            if self._h.value:
-                self._lib.qdsp_cg_destroy(self._h)
-                self._h = C.c_void_p()
+            self.close()
         except Exception:
             pass
 
