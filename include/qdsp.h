@@ -103,6 +103,12 @@ int qdsp_csr_info(qdsp_csr_t m, int *rows, int *cols, int64_t *nnz, int *dtype);
 int qdsp_csr_export(qdsp_csr_t m, const int32_t **indptr, const int32_t **indices, const void **values);
 /* spmv / nd_spmv (sparse_matrix.cpp:654-686): y = A x, x has cols elements, y rows elements, both dense device. */
 int qdsp_csr_spmv(qdsp_csr_t m, const void *x, void *y, void *stream);
+/* Pure host helper (no CUDA needed): how the SpMV of an irregular matrix (row lengths far above the mean) cuts the rows
+ * into work blocks of at most 2044 non-zeros and 256 rows; a longer row becomes several single-row segments.
+ * blocks_out: 4 int32 per block {row0, nrows (> 0) or -(segment id + 1), nz_begin, nz_end}.  No reference counterpart
+ * (cuSPARSE CSR_ALG1 hides its own partitioning); exposed so that the plan is testable without a GPU. */
+int qdsp_spmv_plan_host(const int32_t *indptr, int rows, int32_t *blocks_out, int64_t block_capacity, int64_t *n_blocks,
+                        int *n_long_rows, int *n_segments);
 /* Same through host buffers (H2D x, SpMV, D2H y): the reference-facing call bench.py's e2e leg times. */
 int qdsp_csr_spmv_host(qdsp_csr_t m, const void *x_host, void *y_host, void *stream);
 /* get_element (sparse_matrix.cpp:688-712): 0 when absent */

@@ -2,6 +2,7 @@
 // exception -> (status, thread-local message) translation.  No exception crosses this file.
 #include <cstring>
 #include <new>
+#include <vector>
 
 #include "dist.hpp"
 #include "host.hpp"
@@ -219,6 +220,26 @@ int qdsp_cg_run_fixed(qdsp_cg_t s, void *x, const void *b, int iters, void *stre
 }
 int qdsp_cg_destroy(qdsp_cg_t s) {
   return guarded([&] { delete s; });
+}
+
+// ---- SpMV plan (pure host) ------------------------------------------------------------------------------------------------
+int qdsp_spmv_plan_host(const int32_t *indptr, int rows, int32_t *blocks_out, int64_t block_capacity, int64_t *n_blocks,
+                        int *n_long_rows, int *n_segments) {
+  return guarded([&] {
+    NOT_NULL(indptr); NOT_NULL(n_blocks);
+    QDSP_REQUIRE(rows >= 0, QDSP_ERR_INVALID, "spmv plan: negative row count");
+    std::vector<int4> blocks;
+    std::vector<int2> long_rows;
+    int nseg = 0;
+    spmv_plan_host(indptr, rows, blocks, long_rows, nseg);
+    *n_blocks = static_cast<int64_t>(blocks.size());
+    if (n_long_rows) *n_long_rows = static_cast<int>(long_rows.size()) - 1;
+    if (n_segments) *n_segments = nseg;
+    if (blocks_out) {
+      QDSP_REQUIRE(block_capacity >= *n_blocks, QDSP_ERR_INVALID, "spmv plan: blocks_out too small");
+      std::memcpy(blocks_out, blocks.data(), sizeof(int4) * blocks.size());
+    }
+  });
 }
 
 // ---- multi-GPU ------------------------------------------------------------------------------------------------------------

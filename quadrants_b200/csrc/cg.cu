@@ -49,6 +49,7 @@ struct CgScalars {
   int relative;
   double tol;
   unsigned ticket[4];
+  unsigned flag[2];  // fused iteration kernel: "alpha is ready" / "beta is ready" sequence numbers (2*iters+1, +2)
 };
 
 // ---- block / grid reductions ----------------------------------------------------------------------------------------
@@ -252,22 +253,35 @@ cg_spmv_dot_kernel(int rows, const int *__restrict__ indptr, const int *__restri
     cg_reduce_and_finish<1>(v, d, use_nccl, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
 }
 
+// the same for an irregular matrix (stream path of spmv_kernels.cuh)
+template <typename T>
+__global__ void __launch_bounds__(SPMV_THREADS)
+cg_spmv_dot_stream_kernel(const int *__restrict__ indptr, const int *__restrict__ indices, const T *__restrict__ values,
+                          const T *__restrict__ p, T *__restrict__ tmp, SpmvPlanDev plan, CgScalars *__restrict__ sc,
+                          double *__restrict__ partials, DistDev d, int use_nccl) {
+  extern __shared__ unsigned char smem_raw[];
+  __shared__ double s_red[16];
+  __shared__ unsigned s_flag;
+  if (sc->done) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;
+    return;
+  }
+  double v[1] = {spmv_stream<T>(smem_raw, indptr, indices, values, p, tmp, p, plan, d)};
+  if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag))
+    cg_reduce_and_finish<1>(v, d, use_nccl, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
+}
+
 template <typename T> struct Vec4T;
 template <> struct Vec4T<float> { using type = float4; };
 template <> struct Vec4T<double> { using type = double4; };
 
+// r -= alpha tmp over the whole vector (grid-stride), accumulating |r|^2 and r.(D^-1 r)
 template <typename T>
-__global__ void __launch_bounds__(CG_THREADS)
-cg_residual_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv, T *__restrict__ r,
-                   CgScalars *__restrict__ sc, double *__restrict__ partials, DistDev d, int use_nccl) {
-  __shared__ double s_red[2 * 16];
-  __shared__ unsigned s_flag;
-  if (sc->done) return;
-  const T alpha = static_cast<T>(sc->alpha);
-  T s_rr = T(0), s_rz = T(0);
+__device__ __forceinline__ void cg_residual_body(int n, const T *__restrict__ tmp, const T *__restrict__ dinv,
+                                                 T *__restrict__ r, T alpha, T &s_rr, T &s_rz) {
   using V = typename Vec4T<T>::type;
   const int n4 = n >> 2;
-  for (int i = blockIdx.x * CG_THREADS + threadIdx.x; i < n4; i += gridDim.x * CG_THREADS) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
     const V t4 = reinterpret_cast<const V *>(tmp)[i];
     const V d4 = reinterpret_cast<const V *>(dinv)[i];
     V r4 = reinterpret_cast<V *>(r)[i];
@@ -280,35 +294,36 @@ cg_residual_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv,
     s_rr = fma_t(r4.w, r4.w, s_rr); s_rz = fma_t(r4.w, d4.w * r4.w, s_rz);
   }
   if (blockIdx.x == 0) {
-    for (int i = (n4 << 2) + threadIdx.x; i < n; i += CG_THREADS) {
+    for (int i = (n4 << 2) + threadIdx.x; i < n; i += blockDim.x) {
       const T ri = fma_t(-alpha, tmp[i], r[i]);
       r[i] = ri;
       s_rr = fma_t(ri, ri, s_rr);
       s_rz = fma_t(ri, dinv[i] * ri, s_rz);
     }
   }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(CG_THREADS)
+cg_residual_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv, T *__restrict__ r,
+                   CgScalars *__restrict__ sc, double *__restrict__ partials, DistDev d, int use_nccl) {
+  __shared__ double s_red[2 * 16];
+  __shared__ unsigned s_flag;
+  if (sc->done) return;
+  T s_rr = T(0), s_rz = T(0);
+  cg_residual_body<T>(n, tmp, dinv, r, static_cast<T>(sc->alpha), s_rr, s_rz);
   double v[2] = {static_cast<double>(s_rr), static_cast<double>(s_rz)};
   if (grid_sum_last_block<2>(v, partials, &sc->ticket[2], s_red, &s_flag))
     cg_reduce_and_finish<2>(v, d, use_nccl, sc, [&](const double (&t)[2]) { cg_finish_B<T>(sc, t[0], t[1]); });
 }
 
+// x += alpha p and (update_p) p = D^-1 r + beta p on this CTA's chunk [lo, hi)
 template <typename T>
-__global__ void __launch_bounds__(CG_THREADS)
-cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, T *__restrict__ p, T *__restrict__ x,
-                    const CgScalars *__restrict__ sc, DistDev d) {
-  __shared__ unsigned s_flag;
-  const int done = sc->done;
-  if (done == 3) return;
-  if (done != 0 && sc->alpha == 0.0) return;  // replayed after the end of the solve: x already has its last update
-  const T alpha = static_cast<T>(sc->alpha);
-  const T beta = static_cast<T>(sc->beta);
-  int lo, hi;
-  cta_chunk(n, lo, hi);
+__device__ __forceinline__ void cg_direction_body(const T *__restrict__ r, const T *__restrict__ dinv, T *__restrict__ p,
+                                                  T *__restrict__ x, T alpha, T beta, bool update_p, int lo, int hi) {
   using V = typename Vec4T<T>::type;
-  // converged (done == 1): only the deferred x += alpha p is still owed; p is dead.  done == 2: Eigen still updates p
-  const bool update_p = done != 1;
   const int lo4 = lo >> 2, hi4 = hi >> 2;  // chunks are multiples of 1024 except the last one's end
-  for (int i = lo4 + threadIdx.x; i < hi4; i += CG_THREADS) {
+  for (int i = lo4 + threadIdx.x; i < hi4; i += blockDim.x) {
     V p4 = reinterpret_cast<V *>(p)[i];
     V x4 = reinterpret_cast<V *>(x)[i];
     x4.x = fma_t(alpha, p4.x, x4.x); x4.y = fma_t(alpha, p4.y, x4.y);
@@ -322,12 +337,99 @@ cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, 
       reinterpret_cast<V *>(p)[i] = p4;
     }
   }
-  for (int i = (hi4 << 2) + threadIdx.x; i < hi; i += CG_THREADS) {
+  for (int i = (hi4 << 2) + threadIdx.x; i < hi; i += blockDim.x) {
     const T pi = p[i];
     x[i] = fma_t(alpha, pi, x[i]);
     if (update_p) p[i] = fma_t(beta, pi, dinv[i] * r[i]);
   }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(CG_THREADS)
+cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, T *__restrict__ p, T *__restrict__ x,
+                    const CgScalars *__restrict__ sc, DistDev d) {
+  __shared__ unsigned s_flag;
+  const int done = sc->done;
+  if (done == 3) return;
+  if (done != 0 && sc->alpha == 0.0) return;  // replayed after the end of the solve: x already has its last update
+  int lo, hi;
+  cta_chunk(n, lo, hi);
+  // converged (done == 1): only the deferred x += alpha p is still owed; p is dead.  done == 2: Eigen still updates p
+  cg_direction_body<T>(r, dinv, p, x, static_cast<T>(sc->alpha), static_cast<T>(sc->beta), done != 1, lo, hi);
   if (done == 0) dist_halo_push_signal<T>(d, p, lo, hi, &s_flag);
+}
+
+// ---- the whole iteration as ONE kernel (multi-GPU) ---------------------------------------------------------------------
+// Same arithmetic as the three kernels above, but the two grid-wide joins (alpha known / beta known) are flag waits
+// inside one persistent grid instead of kernel boundaries: the CTA that finishes a reduction last (and has all-reduced
+// it over NVLink) publishes a sequence number, the others spin on it in L2.  Saves two launch boundaries per
+// iteration, which at 8 ranks (~35 us of HBM time per iteration) is what separates 4.6x from the 6x target.
+// All CTAs must be co-resident: the grid is sized by the occupancy API (<= SMs x resident CTAs), nothing else runs on
+// the solver's stream, and CTAs of the previous launch never wait on this one.
+__device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu_u32(unsigned *p, unsigned v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void grid_flag_wait(const unsigned *flag, unsigned want) {
+  if (threadIdx.x == 0) {
+    const long long t0 = clock64();
+    while (ld_acquire_gpu_u32(flag) != want)
+      if (clock64() - t0 > DIST_SPIN_LIMIT) break;  // a lost peer already raised the error flag: leave, do not hang
+  }
+  __syncthreads();
+}
+
+template <typename T, int LPR, bool ROW_MAJOR_ORDER>
+__global__ void __launch_bounds__(SPMV_THREADS)
+cg_iter_fused_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ indices,
+                     const T *__restrict__ values, T *__restrict__ p, T *__restrict__ tmp, const T *__restrict__ dinv,
+                     T *__restrict__ r, T *__restrict__ x, CgScalars *__restrict__ sc, double *__restrict__ partials,
+                     DistDev d) {
+  extern __shared__ unsigned char smem_raw[];
+  __shared__ double s_red[2 * 16];
+  __shared__ unsigned s_flag;
+  if (sc->done) return;
+  const unsigned seq = 2u * static_cast<unsigned>(sc->iters) + 1u;
+  // A: tmp = A p, p.tmp -> alpha
+  {
+    double v[1] = {spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, p, d)};
+    if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag)) {
+      cg_reduce_and_finish<1>(v, d, 0, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
+      if (threadIdx.x == 0) {
+        __threadfence();
+        st_release_gpu_u32(&sc->flag[0], seq);
+      }
+    }
+  }
+  grid_flag_wait(&sc->flag[0], seq);
+  // B: r -= alpha tmp, |r|^2, r.z -> beta, convergence
+  {
+    T s_rr = T(0), s_rz = T(0);
+    cg_residual_body<T>(rows, tmp, dinv, r, static_cast<T>(__ldcg(&sc->alpha)), s_rr, s_rz);
+    double v[2] = {static_cast<double>(s_rr), static_cast<double>(s_rz)};
+    if (grid_sum_last_block<2>(v, partials, &sc->ticket[2], s_red, &s_flag)) {
+      cg_reduce_and_finish<2>(v, d, 0, sc, [&](const double (&t)[2]) { cg_finish_B<T>(sc, t[0], t[1]); });
+      if (threadIdx.x == 0) {
+        __threadfence();
+        st_release_gpu_u32(&sc->flag[1], seq + 1u);
+      }
+    }
+  }
+  grid_flag_wait(&sc->flag[1], seq + 1u);
+  // C: x += alpha p, p = z + beta p, halo of the new p
+  {
+    const int done = __ldcg(&sc->done);
+    if (done == 3) return;
+    int lo, hi;
+    cta_chunk(rows, lo, hi);
+    cg_direction_body<T>(r, dinv, p, x, static_cast<T>(__ldcg(&sc->alpha)), static_cast<T>(__ldcg(&sc->beta)), done != 1,
+                         lo, hi);
+    if (done == 0) dist_halo_push_signal<T>(d, p, lo, hi, &s_flag);
+  }
 }
 
 // ---- host ------------------------------------------------------------------------------------------------------------------
@@ -373,6 +475,24 @@ void launch_spmv_dot(CgSolver::Impl &I) {
   QDSP_LAUNCH_CHECK();
 }
 
+template <typename T>
+void launch_spmv_dot_stream(CgSolver::Impl &I) {
+  const CsrMatrix &A = I.A;
+  cg_spmv_dot_stream_kernel<T><<<I.spmv_grid, SPMV_THREADS, spmv_stream_smem_bytes<T>(), I.stream>>>(
+      A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+      spmv_plan_dev(A), I.scalars.get<CgScalars>(), I.partials.get<double>(), I.dev(), I.use_nccl);
+  QDSP_LAUNCH_CHECK();
+}
+
+template <typename T>
+int spmv_dot_stream_occupancy() {
+  const size_t smem = spmv_stream_smem_bytes<T>();
+  int occ = 0;
+  QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_dot_stream_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  QDSP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, cg_spmv_dot_stream_kernel<T>, SPMV_THREADS, smem));
+  return std::max(1, occ);
+}
+
 template <typename T, int LPR>
 int spmv_dot_occupancy() {
   const size_t smem = spmv_smem_bytes<T>();
@@ -394,6 +514,17 @@ int spmv_dot_occupancy() {
   }
 
 template <typename T>
+void launch_spmv_dot_any(CgSolver::Impl &I) {
+  if (I.A.spmv_mode == 2) {
+    launch_spmv_dot_stream<T>(I);
+    return;
+  }
+#define QDSP_CALL(L) launch_spmv_dot<T, L>(I)
+  QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
+#undef QDSP_CALL
+}
+
+template <typename T>
 void nccl_reduce_then(CgSolver::Impl &I, int count, int which) {
   auto *sc = I.scalars.get<CgScalars>();
   I.dist->nccl_allreduce_double(reinterpret_cast<double *>(reinterpret_cast<char *>(sc) + offsetof(CgScalars, red)), count, I.stream);
@@ -406,9 +537,7 @@ void launch_iteration(CgSolver::Impl &I, T *x) {
   auto *sc = I.scalars.get<CgScalars>();
   double *part = I.partials.get<double>();
   const int n = I.n;
-#define QDSP_CALL(L) launch_spmv_dot<T, L>(I)
-  QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
-#undef QDSP_CALL
+  launch_spmv_dot_any<T>(I);
   if (I.use_nccl) nccl_reduce_then<T>(I, 1, 1);
   cg_residual_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(), sc, part, I.dev(), I.use_nccl);
   QDSP_LAUNCH_CHECK();
@@ -520,9 +649,7 @@ void run_traced(CgSolver::Impl &I, T *x, int iters) {
     const int slot = it - (iters - keep);
     auto mark = [&](int k) { if (slot >= 0) QDSP_CUDA(cudaEventRecord(ev[static_cast<size_t>(slot) * (K + 1) + k], I.stream)); };
     mark(0);
-#define QDSP_CALL(L) launch_spmv_dot<T, L>(I)
-    QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
-#undef QDSP_CALL
+    launch_spmv_dot_any<T>(I);
     mark(1);
     cg_residual_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(I.n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(), sc, part, I.dev(), I.use_nccl);
     mark(2);
@@ -587,13 +714,19 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
   const size_t n = static_cast<size_t>(A.rows), sv = A.value_bytes();
   I.r.alloc(n * sv); I.tmp.alloc(n * sv); I.dinv.alloc(n * sv);
   if (!dist) { I.p_own.alloc(n * sv); I.p = I.p_own.get(); }
-  I.lpr = spmv_lanes_per_row(A.nnz, A.rows);
+  spmv_prepare(A, nullptr);
+  I.lpr = A.spmv_lpr;
   int occ = 1;
+  if (A.spmv_mode == 2) {
+    occ = (A.dtype == QDSP_F32) ? spmv_dot_stream_occupancy<float>() : spmv_dot_stream_occupancy<double>();
+    I.spmv_grid = std::max(1, std::min(A.spmv_plan_nblk, device_props().sm_count * occ));
+  } else {
 #define QDSP_CALL(L) occ = (A.dtype == QDSP_F32) ? spmv_dot_occupancy<float, L>() : spmv_dot_occupancy<double, L>()
-  QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
+    QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
 #undef QDSP_CALL
-  const int R = SPMV_CONSUMERS / I.lpr;
-  I.spmv_grid = std::max(1, std::min(ceil_div(A.rows, R), device_props().sm_count * occ));
+    const int R = SPMV_CONSUMERS / I.lpr;
+    I.spmv_grid = std::max(1, std::min(ceil_div(A.rows, R), device_props().sm_count * occ));
+  }
   I.vec_grid = std::max(1, std::min(ceil_div(A.rows, 1024), device_props().sm_count * 8));
   I.partials.alloc(sizeof(double) * 3 * static_cast<size_t>(std::max(I.spmv_grid, I.vec_grid)));
   I.scalars.alloc(sizeof(CgScalars));

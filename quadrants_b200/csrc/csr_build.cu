@@ -63,6 +63,7 @@ pack_coo_kernel(const int *__restrict__ row, const int *__restrict__ col, const 
 
 // ---- collapse ---------------------------------------------------------------------------------------------------------
 constexpr int CL_ITEMS = 8;
+constexpr int CL_SHORT_RUN = 6;                 // followers a head thread adds by itself
 constexpr int CL_TILE = CB_THREADS * CL_ITEMS;   // 2048 sorted triplets per CTA
 constexpr int CL_WARP_SPAN = 32 * CL_ITEMS;      // 256 per warp, item i of lane l <-> warp_base + i*32 + l
 
@@ -116,12 +117,38 @@ collapse_kernel(const KeyT *__restrict__ keys, const T *__restrict__ vals, long 
 #pragma unroll
   for (int i = 0; i < CL_ITEMS; ++i) {
     const long long p = warp_base + i * 32 + lane;
+    // duplicates follow in buffer order (stable sort): v = ((v1 + v2) + v3) ... like Eigen's collapseDuplicates.
+    // A head adds its first CL_SHORT_RUN followers itself; a longer run (FEM assembly: a hub vertex's diagonal can
+    // collect 10^5 contributions) is finished by the whole warp -- 32 followers per coalesced load, still added
+    // strictly left to right, so the value stays bit-identical to Eigen's.
+    T v = T(0);
+    long long q = p + 1;
+    if (head[i]) {
+      v = vals[p];
+      for (int j = 0; j < CL_SHORT_RUN && q < n && keys[q] == key[i]; ++j, ++q) v = v + vals[q];
+    }
+    unsigned todo = __ballot_sync(FULL, head[i] && q < n && keys[q] == key[i]);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const KeyT k0 = __shfl_sync(FULL, key[i], src);
+      long long q0 = __shfl_sync(FULL, q, src);
+      T acc = __shfl_sync(FULL, v, src);
+      while (true) {
+        const long long qq = q0 + lane;
+        const bool same = qq < n && keys[qq] == k0;
+        const T x = same ? vals[qq] : T(0);
+        const unsigned m = __ballot_sync(FULL, same);
+        const int cnt = (m == FULL) ? 32 : __ffs(~m) - 1;  // leading run of matches
+        for (int j = 0; j < cnt; ++j) acc = acc + __shfl_sync(FULL, x, j);
+        if (cnt < 32) break;
+        q0 += 32;
+      }
+      if (lane == src) v = acc;
+    }
     if (head[i]) {
       const unsigned u = base + slot[i];
       indices[u] = static_cast<int>(key[i] & colmask);
-      // duplicates follow in buffer order (stable sort): v = ((v1 + v2) + v3) ... like Eigen's collapseDuplicates
-      T v = vals[p];
-      for (long long q = p + 1; q < n && keys[q] == key[i]; ++q) v = v + vals[q];
       values[u] = v;
       const int r = static_cast<int>(key[i] >> col_bits);
       const int pr = (p == 0) ? -1 : static_cast<int>(keys[p - 1] >> col_bits);

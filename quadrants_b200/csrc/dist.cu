@@ -87,11 +87,16 @@ void DistContext::localize(CsrMatrix &A, const int64_t *row_offsets, cudaStream_
     QDSP_CUDA(cudaStreamSynchronize(stream));
   }
   A.cols = plan_.ghost_base + n_ghost();
-  A.spmv_lpr = spmv_lanes_per_row(A.nnz, A.rows);
+  A.spmv_mode = 0;  // re-plan: the renumbering does not change row lengths, but a plan made earlier is dropped anyway
+  spmv_prepare(A, stream);
   dtype_ = A.dtype;
   row0_ = row_offsets[rank_];
-  // which row blocks of the SpMV kernel read a ghost column
-  {
+  // which row blocks of the SpMV kernel read a ghost column (uniform path only; the stream path waits up front)
+  dev_.ghost_blocks = nullptr;
+  dev_.ghost_block_rows = 0;
+  dev_.block_order = nullptr;
+  dev_.n_interior = 0;
+  if (A.spmv_mode == 1) {
     const int R = SPMV_CONSUMERS / A.spmv_lpr;
     const int nblk = std::max(1, (A.rows + R - 1) / R);
     std::vector<int32_t> ip(static_cast<size_t>(A.rows) + 1);
@@ -108,6 +113,18 @@ void DistContext::localize(CsrMatrix &A, const int64_t *row_offsets, cudaStream_
     QDSP_CUDA(cudaStreamSynchronize(stream));
     dev_.ghost_blocks = ghost_blocks_.get<unsigned char>();
     dev_.ghost_block_rows = R;
+    // work order of the SpMV: interior blocks (ascending), then the blocks that need the halo
+    std::vector<int32_t> order;
+    order.reserve(nblk);
+    for (int b = 0; b < nblk; ++b)
+      if (!flags[b]) order.push_back(b);
+    dev_.n_interior = static_cast<int>(order.size());
+    for (int b = 0; b < nblk; ++b)
+      if (flags[b]) order.push_back(b);
+    block_order_.alloc(sizeof(int32_t) * order.size());
+    QDSP_CUDA(cudaMemcpyAsync(block_order_.get(), order.data(), sizeof(int32_t) * order.size(), cudaMemcpyHostToDevice, stream));
+    QDSP_CUDA(cudaStreamSynchronize(stream));
+    dev_.block_order = block_order_.get<int>();
   }
   const size_t sv = A.value_bytes();
   comm_.alloc(DIST_VECTOR_OFF + sv * (static_cast<size_t>(plan_.ghost_base) + n_ghost()) + 256);

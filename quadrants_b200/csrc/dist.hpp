@@ -64,7 +64,7 @@ class DistContext {
   int dtype_ = QDSP_F32;
   int64_t row0_ = 0;
   DistPlan plan_;
-  DeviceBuffer comm_, ctl_, ghost_blocks_;
+  DeviceBuffer comm_, ctl_, ghost_blocks_, block_order_;
   std::vector<DeviceBuffer> send_lists_;
   std::vector<void *> opened_;
   DistDev dev_;

@@ -51,6 +51,11 @@ struct DistDev {
   // which SpMV row blocks (of ghost_block_rows rows) read a ghost column: only those wait for the halo
   const unsigned char *ghost_blocks = nullptr;
   int ghost_block_rows = 0;
+  // the same information as a work order: ids of the row blocks that read no ghost (ascending), then of those that do.
+  // Every CTA walks a contiguous run of interior blocks first and takes its share of the ghost blocks last, so the
+  // NVLink latency of the halo hides behind interior work.
+  const int *block_order = nullptr;
+  int n_interior = 0;
   unsigned *counters = nullptr;                  // device, local: [0] reduction seq, [1] halo push count, [2] ticket
   int *error = nullptr;                          // device, local: != 0 after a timeout
 };

@@ -34,6 +34,12 @@ class CsrMatrix {
   DeviceBuffer indptr, indices, values;  // each carries 64 bytes of padding: TMA bulk copies read whole 16-byte units
   // lanes per row of the SpMV kernels (1, 2, 4 ... 32), chosen from the mean row length on first use; 0 = not yet
   mutable int spmv_lpr = 0;
+  // SpMV plan, made on first use (spmv_prepare): 1 = uniform row blocks (regular matrices; bit-exact Eigen order when
+  // spmv_lpr == 1), 2 = stream path over nnz-balanced plan blocks (irregular matrices), 0 = not planned yet
+  mutable int spmv_mode = 0;
+  mutable int spmv_max_row_len = 0;
+  mutable DeviceBuffer spmv_plan_blocks, spmv_plan_long, spmv_plan_partials, spmv_plan_ticket;
+  mutable int spmv_plan_nblk = 0, spmv_plan_nlong = 0;
 
   size_t value_bytes() const { return dtype == QDSP_F64 ? 8 : 4; }
   void allocate(int rows_, int cols_, int64_t nnz_, int dtype_);
@@ -82,6 +88,13 @@ class Builder {
   size_t slot_bytes() const { return dtype_ == QDSP_F64 ? 8 : 4; }
 };
 
+// Chooses the SpMV path of A (mode, lanes per row, plan blocks); idempotent.  Synchronises `stream` the first time.
+void spmv_prepare(const CsrMatrix &A, cudaStream_t stream);
+struct SpmvPlanDev;
+// pure host: the stream-path work partition (blocks {row0, nrows | -(segment+1), nz0, nz1}; long_rows {row, first segment})
+void spmv_plan_host(const int32_t *indptr, int rows, std::vector<int4> &blocks, std::vector<int2> &long_rows,
+                    int &n_segments);
+SpmvPlanDev spmv_plan_dev(const CsrMatrix &A);
 // y = A x with the persistent TMA-fed kernel; `d` (world > 1) makes every CTA wait for the halo of x first (spmv.cu)
 void launch_spmv(const CsrMatrix &A, const void *x, void *y, const DistDev &d, cudaStream_t stream);
 

@@ -2,17 +2,20 @@
 // qd.algorithms.PrefixSumExecutor.run (python/quadrants/algorithms/_algorithms.py:109-163, which runs 2 blits +
 // 5 scan levels + 4 uniform-add levels of 64-thread blocks, python/quadrants/_kernels.py:298-352).
 //
-// HBM-bound: algorithmic traffic 2*N*4 bytes (read once, write once).  One CTA = one 4096-element tile:
-// 128-bit coalesced loads (warp w owns 512 consecutive elements, 4 x int4 per lane), warp-shuffle scans, one
+// HBM-bound: algorithmic traffic 2*N*4 bytes (read once, write once).  One CTA = one 16384-element tile:
+// 128-bit coalesced loads (warp w owns 1024 consecutive elements, 8 x int4 per lane), warp-shuffle scans, one
 // look-back per tile by warp 0, 128-bit stores.  In place.
 #include "lookback.cuh"
 
 namespace qdsp {
 
-constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_VEC = 4;                                    // int4 chunks per lane
-constexpr int SCAN_TILE = SCAN_THREADS * SCAN_VEC * 4;         // 4096
-constexpr int SCAN_WARP_SPAN = 32 * SCAN_VEC * 4;              // 512 elements per warp
+// Tile size: the look-back is a serial chain -- one L2 round trip (~0.4 us) lets a tile look at 32 predecessors, so the
+// prefix front advances by at most ~32 tiles per round trip whatever the occupancy.  At 4096-element tiles that caps
+// the kernel at ~2.8 TB/s (measured, profiles/r01d); 16384-element tiles move 4x the bytes per chain step.
+constexpr int SCAN_THREADS = 512;
+constexpr int SCAN_VEC = 8;                                    // int4 chunks per lane
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_VEC * 4;         // 16384
+constexpr int SCAN_WARP_SPAN = 32 * SCAN_VEC * 4;              // 1024 elements per warp
 constexpr size_t SCAN_HEADER_BYTES = 128;                      // ticket counter, padded
 
 __global__ void __launch_bounds__(SCAN_THREADS)
@@ -42,7 +45,7 @@ scan_inclusive_i32_kernel(int *__restrict__ data, long long n, unsigned *__restr
         v[j][e] = i < n ? static_cast<unsigned>(data[i]) : 0u;
       }
   }
-  // warp-local inclusive scan of 512 elements in 4 rounds of (4 per lane x 32 lanes)
+  // warp-local inclusive scan of the warp's span in SCAN_VEC rounds of (4 per lane x 32 lanes)
   unsigned running = 0;
 #pragma unroll
   for (int j = 0; j < SCAN_VEC; ++j) {

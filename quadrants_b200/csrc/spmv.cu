@@ -1,6 +1,8 @@
 // spmv.cu -- CsrMatrix: SpMV launcher and the small host-visible accessors of CuSparseMatrix
 // (quadrants/program/sparse_matrix.cpp:654-780).
+#include <cstdlib>
 #include <cstring>
+#include <string>
 #include <fstream>
 #include <algorithm>
 #include <vector>
@@ -37,7 +39,136 @@ spmv_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ in
   spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, x, y, nullptr, d);
 }
 
+template <typename T>
+__global__ void __launch_bounds__(SPMV_THREADS)
+spmv_stream_kernel(const int *__restrict__ indptr, const int *__restrict__ indices, const T *__restrict__ values,
+                   const T *__restrict__ x, T *__restrict__ y, SpmvPlanDev plan, DistDev d) {
+  extern __shared__ unsigned char smem_raw[];
+  spmv_stream<T>(smem_raw, indptr, indices, values, x, y, nullptr, plan, d);
+}
+
+// out[0] = longest row; out[1] = the largest stage footprint (non-zeros, counted from the 16-byte-aligned start) of a
+// uniform block of R rows
+__global__ void __launch_bounds__(256) row_stats_kernel(int rows, int R, const int *__restrict__ indptr, int *__restrict__ out) {
+  int m = 0, mb = 0;
+  for (int r = blockIdx.x * 256 + threadIdx.x; r < rows; r += gridDim.x * 256) {
+    m = max(m, indptr[r + 1] - indptr[r]);
+    if (r % R == 0) mb = max(mb, indptr[min(rows, r + R)] - (indptr[r] & ~3));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    m = max(m, __shfl_xor_sync(FULL, m, o));
+    mb = max(mb, __shfl_xor_sync(FULL, mb, o));
+  }
+  if (lane_id() == 0) {
+    if (m > 0) atomicMax(out, m);
+    if (mb > 0) atomicMax(out + 1, mb);
+  }
+}
+
+// ---- plan ----------------------------------------------------------------------------------------------------------------
+// Pure host: cuts the rows into stream-path blocks.  blocks: {row0, nrows | -(segment + 1), nz0, nz1};
+// long_rows: {row, first segment} + sentinel.
+void spmv_plan_host(const int32_t *indptr, int rows, std::vector<int4> &blocks, std::vector<int2> &long_rows,
+                    int &n_segments) {
+  blocks.clear();
+  long_rows.clear();
+  n_segments = 0;
+  int r = 0;
+  while (r < rows) {
+    const int len = indptr[r + 1] - indptr[r];
+    if (len > SPMV_STREAM_CAP) {
+      long_rows.push_back(make_int2(r, n_segments));
+      for (int s = indptr[r]; s < indptr[r + 1];) {
+        // segment starts stay 4-aligned relative to nothing in particular: the kernel copies from nz0 & ~3
+        const int e = std::min(indptr[r + 1], (s & ~3) + SPMV_STREAM_CAP);
+        blocks.push_back(make_int4(r, -(n_segments + 1), s, e));
+        ++n_segments;
+        s = e;
+      }
+      ++r;
+      continue;
+    }
+    const int r0 = r;
+    const int a0 = indptr[r0] & ~3;
+    while (r < rows && r - r0 < SPMV_CONSUMERS) {
+      const int l = indptr[r + 1] - indptr[r];
+      if (l > SPMV_STREAM_CAP || indptr[r + 1] - a0 > SPMV_CAP) break;
+      ++r;
+    }
+    blocks.push_back(make_int4(r0, r - r0, indptr[r0], indptr[r]));
+  }
+  long_rows.push_back(make_int2(rows, n_segments));
+}
+
+void spmv_prepare(const CsrMatrix &A, cudaStream_t stream) {
+  if (A.spmv_mode != 0 || A.rows == 0) return;
+  // uniform row blocks (bit-exact Eigen order when one lane per row) iff no block of R rows overflows a stage
+  const int L = spmv_lanes_per_row(A.nnz, A.rows);
+  DeviceBuffer mx(2 * sizeof(int));
+  QDSP_CUDA(cudaMemsetAsync(mx.get(), 0, 2 * sizeof(int), stream));
+  const int g = std::max(1, std::min(ceil_div(A.rows, 256), device_props().sm_count * 8));
+  row_stats_kernel<<<g, 256, 0, stream>>>(A.rows, SPMV_CONSUMERS / L, A.indptr.get<int>(), mx.get<int>());
+  QDSP_LAUNCH_CHECK();
+  int stats[2] = {0, 0};
+  QDSP_CUDA(cudaMemcpyAsync(stats, mx.get(), 2 * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+  A.spmv_max_row_len = stats[0];
+  const char *force = std::getenv("QDSP_SPMV_PATH");  // "uniform" | "stream": testing aid
+  const bool uniform = force ? std::string(force) != "stream" : stats[1] <= SPMV_CAP;
+  A.spmv_lpr = L;
+  if (uniform) {
+    A.spmv_mode = 1;
+    return;
+  }
+  std::vector<int32_t> ip(static_cast<size_t>(A.rows) + 1);
+  QDSP_CUDA(cudaMemcpyAsync(ip.data(), A.indptr.get(), sizeof(int32_t) * ip.size(), cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+  std::vector<int4> blocks;
+  std::vector<int2> long_rows;
+  int nseg = 0;
+  spmv_plan_host(ip.data(), A.rows, blocks, long_rows, nseg);
+  A.spmv_plan_blocks.alloc(sizeof(int4) * blocks.size());
+  A.spmv_plan_long.alloc(sizeof(int2) * long_rows.size());
+  A.spmv_plan_partials.alloc(A.value_bytes() * static_cast<size_t>(std::max(1, nseg)));
+  A.spmv_plan_ticket.alloc(sizeof(unsigned));
+  QDSP_CUDA(cudaMemcpyAsync(A.spmv_plan_blocks.get(), blocks.data(), sizeof(int4) * blocks.size(), cudaMemcpyHostToDevice, stream));
+  QDSP_CUDA(cudaMemcpyAsync(A.spmv_plan_long.get(), long_rows.data(), sizeof(int2) * long_rows.size(), cudaMemcpyHostToDevice, stream));
+  QDSP_CUDA(cudaMemsetAsync(A.spmv_plan_ticket.get(), 0, sizeof(unsigned), stream));
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+  A.spmv_plan_nblk = static_cast<int>(blocks.size());
+  A.spmv_plan_nlong = static_cast<int>(long_rows.size()) - 1;
+  A.spmv_mode = 2;
+}
+
+SpmvPlanDev spmv_plan_dev(const CsrMatrix &A) {
+  SpmvPlanDev p;
+  p.blocks = A.spmv_plan_blocks.get<int4>();
+  p.nblk = A.spmv_plan_nblk;
+  p.n_long = A.spmv_plan_nlong;
+  p.long_rows = A.spmv_plan_long.get<int2>();
+  p.partials = A.spmv_plan_partials.get();
+  p.ticket = A.spmv_plan_ticket.get<unsigned>();
+  return p;
+}
+
 namespace {
+
+template <typename T>
+void launch_spmv_stream(const CsrMatrix &A, const T *x, T *y, const DistDev &d, cudaStream_t stream) {
+  static int occ = 0;
+  const size_t smem = spmv_stream_smem_bytes<T>();
+  if (occ == 0) {
+    QDSP_CUDA(cudaFuncSetAttribute(spmv_stream_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    int o = 0;
+    QDSP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, spmv_stream_kernel<T>, SPMV_THREADS, smem));
+    occ = std::max(1, o);
+  }
+  const int grid = std::max(1, std::min(A.spmv_plan_nblk, device_props().sm_count * occ));
+  spmv_stream_kernel<T><<<grid, SPMV_THREADS, smem, stream>>>(A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), x,
+                                                              y, spmv_plan_dev(A), d);
+  QDSP_LAUNCH_CHECK();
+}
 
 // persistent grid = SM count x resident CTAs of this instantiation (queried once per instantiation)
 template <typename T, int LPR>
@@ -85,7 +216,12 @@ void launch_spmv_lpr(const CsrMatrix &A, const void *x, void *y, const DistDev &
 
 void launch_spmv(const CsrMatrix &A, const void *x, void *y, const DistDev &d, cudaStream_t stream) {
   if (A.rows == 0) return;
-  if (A.spmv_lpr == 0) A.spmv_lpr = spmv_lanes_per_row(A.nnz, A.rows);
+  spmv_prepare(A, stream);
+  if (A.spmv_mode == 2) {
+    if (A.dtype == QDSP_F32) launch_spmv_stream<float>(A, static_cast<const float *>(x), static_cast<float *>(y), d, stream);
+    else launch_spmv_stream<double>(A, static_cast<const double *>(x), static_cast<double *>(y), d, stream);
+    return;
+  }
   if (A.dtype == QDSP_F32) launch_spmv_lpr<float>(A, x, y, d, stream);
   else launch_spmv_lpr<double>(A, x, y, d, stream);
 }

@@ -32,7 +32,12 @@ constexpr int SPMV_CONSUMERS = 256;                 // consumer threads per CTA 
 constexpr int SPMV_THREADS = SPMV_CONSUMERS + 32;   // + the producer warp
 constexpr int SPMV_CAP = 2048;                      // non-zeros per stage
 constexpr int SPMV_STAGES = 3;
-constexpr int SPMV_PTR_SLOTS = 260;                 // R + 1 <= 257, rounded up to a multiple of 4
+constexpr int SPMV_STREAM_STAGES = 2;                // stream path: gather latency, not the TMA depth, is what needs
+                                                    // hiding, so fewer stages -> more resident CTAs per SM
+constexpr int SPMV_PTR_SLOTS = 264;                 // indptr slice (<= 3 + 257 entries) + the 4-word block descriptor
+constexpr int SPMV_DESC_SLOT = 260;                 // stream path: where the producer leaves the block descriptor
+constexpr int SPMV_STREAM_CAP = SPMV_CAP - 4;       // non-zeros per block of the stream path (16-byte alignment slack)
+constexpr int SPMV_STREAM_THREAD_ROWS = 64;         // blocks with more rows than this sum one row per thread
 
 __device__ __forceinline__ float fma_t(float a, float b, float c) { return fmaf(a, b, c); }
 __device__ __forceinline__ double fma_t(double a, double b, double c) { return fma(a, b, c); }
@@ -95,6 +100,11 @@ __device__ __forceinline__ void tma_bulk_g2s(void *dst, const void *src, unsigne
 }
 
 template <typename T>
+__host__ __device__ constexpr size_t spmv_stream_smem_bytes() {
+  return SPMV_STREAM_STAGES * spmv_stage_bytes<T>() + 2 * SPMV_STREAM_STAGES * sizeof(unsigned long long) + 128;
+}
+
+template <typename T>
 struct SpmvStage {
   int *idx;
   T *val;
@@ -109,6 +119,21 @@ __device__ __forceinline__ SpmvStage<T> spmv_stage(unsigned char *base, int s) {
   st.ptr = reinterpret_cast<int *>(p + SPMV_CAP * sizeof(T) + SPMV_CAP * sizeof(int));
   return st;
 }
+
+// Irregular matrices (row lengths far from the mean: FEM power-law tails) use the "stream" path instead of fixed-size
+// row blocks.  The plan (host-built once per matrix, spmv.cu) cuts the rows into blocks of <= SPMV_STREAM_CAP
+// non-zeros and <= 256 rows; a row longer than that becomes several single-row SEGMENT blocks whose partial sums are
+// added in segment order by the last CTA to finish (deterministic).  CSR-adaptive in spirit (Greathouse & Daga).
+struct SpmvPlanDev {
+  const int4 *blocks = nullptr;    // {row0, nrows (> 0) or -(segment id + 1), nz0, nz1}
+  int nblk = 0;
+  int n_long = 0;
+  const int2 *long_rows = nullptr; // n_long + 1 entries {row, first segment id}; the last one is a sentinel
+  void *partials = nullptr;        // one T per segment
+  unsigned *ticket = nullptr;
+};
+
+__device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(SPMV_CONSUMERS) : "memory"); }
 
 // The whole SpMV of one persistent CTA.  LPR = lanes per row.  Returns, per consumer thread, the sum over the rows it
 // owned of xdot[row] * y[row] in double (0 when xdot == nullptr); producer-warp threads return 0.
@@ -143,19 +168,28 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
   }
 
   const int nblk = (rows + R - 1) / R;
-  const int per_cta = (nblk + gridDim.x - 1) / gridDim.x;
-  const int blk0 = blockIdx.x * per_cta;
-  const int blk1 = min(nblk, blk0 + per_cta);
+  // work items of this CTA.  Plain: a contiguous run of blocks.  Ordered (multi-GPU): a contiguous run of the interior
+  // blocks, then every gridDim.x-th ghost block; the producer leaves the block id in the stage for the consumers.
+  const bool ordered = lazy_halo && dist.block_order != nullptr;
+  const int n_first = ordered ? dist.n_interior : nblk;
+  const int per_cta = (n_first + gridDim.x - 1) / gridDim.x;
+  const int blk0 = min(n_first, static_cast<int>(blockIdx.x) * per_cta);
+  const int n_run = min(n_first, blk0 + per_cta) - blk0;
+  const int n_ghost_blk = ordered ? nblk - n_first : 0;
+  const int n_tail = n_ghost_blk > static_cast<int>(blockIdx.x) ? (n_ghost_blk - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+  const int n_items = n_run + n_tail;
   double dot = 0.0;
 
   if (t >= SPMV_CONSUMERS) {
     // ---- producer: one thread ----
-    if (t == SPMV_CONSUMERS && blk0 < blk1) {
+    if (t == SPMV_CONSUMERS && n_items > 0) {
       const unsigned long long pol = l2_evict_first_policy();
-      int s_next = indptr[blk0 * R];
       bool halo_pending = lazy_halo;
-      for (int blk = blk0, it = 0; blk < blk1; ++blk, ++it) {
-        if (halo_pending && dist.ghost_blocks[blk]) {
+      int s_next = 0, blk_prev = -2;
+      for (int it = 0; it < n_items; ++it) {
+        int blk = blk0 + it;
+        if (ordered) blk = dist.block_order[it < n_run ? blk0 + it : n_first + blockIdx.x + (it - n_run) * gridDim.x];
+        if (halo_pending && (ordered ? it >= n_run : dist.ghost_blocks[blk] != 0)) {
           dist_halo_wait(dist);
           halo_pending = false;
         }
@@ -163,11 +197,13 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
         const unsigned phase = (it / SPMV_STAGES) & 1;
         const int r0 = blk * R;
         const int nr = min(R, rows - r0);
-        const int s = s_next;
+        const int s = (blk == blk_prev + 1) ? s_next : indptr[r0];  // consecutive blocks: one indptr load per block
         const int e = indptr[r0 + nr];
         s_next = e;
+        blk_prev = blk;
         mbar_wait(&empty[stage], phase ^ 1u);
         const SpmvStage<T> st = spmv_stage<T>(base, stage);
+        if (ordered) st.ptr[SPMV_DESC_SLOT] = blk;  // published by the arrive below (release)
         const int a0 = s & ~3;
         const int cnt = e - a0;
         const unsigned ptr_bytes = static_cast<unsigned>(((nr + 1) * 4 + 15) & ~15);
@@ -188,13 +224,14 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
     // ---- consumers ----
     const int lane = t & 31, warp = t >> 5;
     const int row_in_blk = t / LPR, q = t % LPR;
-    for (int blk = blk0, it = 0; blk < blk1; ++blk, ++it) {
+    for (int it = 0; it < n_items; ++it) {
       const int stage = it % SPMV_STAGES;
       const unsigned phase = (it / SPMV_STAGES) & 1;
-      const int r0 = blk * R;
-      const int nr = min(R, rows - r0);
       const SpmvStage<T> st = spmv_stage<T>(base, stage);
       mbar_wait(&full[stage], phase);
+      const int blk = ordered ? st.ptr[SPMV_DESC_SLOT] : blk0 + it;
+      const int r0 = blk * R;
+      const int nr = min(R, rows - r0);
       const int s = st.ptr[0], e = st.ptr[nr];
       const int a0 = s & ~3;
       if (e - a0 <= SPMV_CAP) {
@@ -269,6 +306,166 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[stage]);
+    }
+  }
+  return dot;
+}
+
+// ---- stream path ---------------------------------------------------------------------------------------------------------
+// Same persistent, warp-specialised TMA pipeline; the work unit is a plan block.  Consumers: (1) all 256 threads form the
+// products val[k] * x[idx[k]] in place in shared memory -- perfectly balanced whatever the row lengths --, (2) after a
+// consumer-only barrier the rows of the block are summed from shared memory, one row per thread (many short rows) or
+// one row per warp (few long rows); a SEGMENT block reduces to one partial sum.  Not bit-identical to Eigen's order
+// (held to the 1e-5 / 1e-12 per-row tolerance).  Returns the per-thread part of sum xdot[row] * y[row] like above.
+template <typename T>
+__device__ __forceinline__ double spmv_stream(unsigned char *smem_raw, const int *__restrict__ indptr,
+                                              const int *__restrict__ indices, const T *__restrict__ values,
+                                              const T *__restrict__ x, T *__restrict__ y, const T *__restrict__ xdot,
+                                              const SpmvPlanDev &plan, const DistDev &dist) {
+  unsigned char *base = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  auto *full = reinterpret_cast<unsigned long long *>(base + SPMV_STREAM_STAGES * spmv_stage_bytes<T>());
+  auto *empty = full + SPMV_STREAM_STAGES;
+  __shared__ unsigned s_last;
+  const int t = threadIdx.x;
+  if (t == 0) {
+    for (int s = 0; s < SPMV_STREAM_STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], SPMV_CONSUMERS / 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (dist.world > 1) {  // no per-block ghost map on this path: wait for the halo before the first gather
+    if (t == 0) dist_halo_wait(dist);
+    __syncthreads();
+  }
+  const int per_cta = (plan.nblk + gridDim.x - 1) / gridDim.x;
+  const int blk0 = blockIdx.x * per_cta;
+  const int blk1 = min(plan.nblk, blk0 + per_cta);
+  double dot = 0.0;
+
+  if (t >= SPMV_CONSUMERS) {
+    if (t == SPMV_CONSUMERS && blk0 < blk1) {
+      const unsigned long long pol = l2_evict_first_policy();
+      int4 next = plan.blocks[blk0];
+      for (int blk = blk0, it = 0; blk < blk1; ++blk, ++it) {
+        const int4 d = next;
+        if (blk + 1 < blk1) next = plan.blocks[blk + 1];
+        const int stage = it % SPMV_STREAM_STAGES;
+        const unsigned phase = (it / SPMV_STREAM_STAGES) & 1;
+        mbar_wait(&empty[stage], phase ^ 1u);
+        const SpmvStage<T> st = spmv_stage<T>(base, stage);
+        *reinterpret_cast<int4 *>(st.ptr + SPMV_DESC_SLOT) = d;  // published by the arrive below (release)
+        const int a0 = d.z & ~3;
+        const int cnt = d.w - a0;
+        unsigned bytes = 0;
+        const unsigned ib = static_cast<unsigned>((cnt * 4 + 15) & ~15);
+        const unsigned vb = static_cast<unsigned>((cnt * static_cast<int>(sizeof(T)) + 15) & ~15);
+        unsigned pb = 0;
+        if (d.y > 0) pb = static_cast<unsigned>((((d.x & 3) + d.y + 1) * 4 + 15) & ~15);
+        if (cnt > 0) bytes += ib + vb;
+        bytes += pb;
+        if (bytes == 0) {
+          mbar_arrive(&full[stage]);
+          continue;
+        }
+        mbar_expect_tx(&full[stage], bytes);
+        if (pb) tma_bulk_g2s(st.ptr, indptr + (d.x & ~3), pb, &full[stage], pol);
+        if (cnt > 0) {
+          tma_bulk_g2s(st.idx, indices + a0, ib, &full[stage], pol);
+          tma_bulk_g2s(st.val, values + a0, vb, &full[stage], pol);
+        }
+      }
+    }
+  } else {
+    const int lane = t & 31, warp = t >> 5;
+    for (int blk = blk0, it = 0; blk < blk1; ++blk, ++it) {
+      const int stage = it % SPMV_STREAM_STAGES;
+      const unsigned phase = (it / SPMV_STREAM_STAGES) & 1;
+      const SpmvStage<T> st = spmv_stage<T>(base, stage);
+      mbar_wait(&full[stage], phase);
+      const int4 d = *reinterpret_cast<const int4 *>(st.ptr + SPMV_DESC_SLOT);
+      const int a0 = d.z & ~3;
+      const int lo = d.z - a0, cnt = d.w - a0;
+      // (1) products, in place
+      // (8 independent gathers in flight per thread: the x of an irregular matrix comes from L2, not L1)
+      for (int k = lo + t; k < cnt; k += 8 * SPMV_CONSUMERS) {
+        T xv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int kk = k + j * SPMV_CONSUMERS;
+          xv[j] = kk < cnt ? __ldg(x + st.idx[kk]) : T(0);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int kk = k + j * SPMV_CONSUMERS;
+          if (kk < cnt) st.val[kk] = st.val[kk] * xv[j];
+        }
+      }
+      consumer_bar();
+      // (2) row sums
+      if (d.y > 0) {
+        const int nr = d.y, poff = d.x & 3;
+        if (nr > SPMV_STREAM_THREAD_ROWS) {
+          if (t < nr) {
+            const int b = st.ptr[poff + t] - a0, e = st.ptr[poff + t + 1] - a0;
+            T acc = T(0);
+            for (int k = b; k < e; ++k) acc += st.val[k];
+            y[d.x + t] = acc;
+            if (xdot) dot += static_cast<double>(xdot[d.x + t] * acc);
+          }
+        } else {
+          for (int r = warp; r < nr; r += SPMV_CONSUMERS / 32) {
+            const int b = st.ptr[poff + r] - a0, e = st.ptr[poff + r + 1] - a0;
+            T acc = T(0);
+            for (int k = b + lane; k < e; k += 32) acc += st.val[k];
+            acc = warp_sum(acc);
+            if (lane == 0) {
+              y[d.x + r] = acc;
+              if (xdot) dot += static_cast<double>(xdot[d.x + r] * acc);
+            }
+          }
+        }
+      } else {
+        // one segment of a long row: block-wide sum -> partials[segment]
+        T acc = T(0);
+        for (int k = lo + t; k < cnt; k += SPMV_CONSUMERS) acc += st.val[k];
+        acc = warp_sum(acc);
+        T *red = reinterpret_cast<T *>(st.ptr);  // the indptr slice is unused for a segment
+        if (lane == 0) red[warp] = acc;
+        consumer_bar();
+        if (t == 0) {
+          T tot = T(0);
+          for (int w = 0; w < SPMV_CONSUMERS / 32; ++w) tot += red[w];
+          static_cast<T *>(plan.partials)[-d.y - 1] = tot;
+          if (xdot) dot += static_cast<double>(xdot[d.x] * tot);
+        }
+      }
+      // the stage was written through the generic proxy (products); order that before the next TMA fill
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[stage]);
+    }
+    // long rows: the last CTA to get here adds each row's segment sums in segment order
+    if (plan.n_long > 0) {
+      consumer_bar();
+      if (t == 0) {
+        __threadfence();
+        s_last = (atomicAdd(plan.ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+      }
+      consumer_bar();
+      if (s_last) {
+        __threadfence();
+        const T *part = static_cast<const T *>(plan.partials);
+        for (int i = t; i < plan.n_long; i += SPMV_CONSUMERS) {
+          const int2 a = plan.long_rows[i];
+          const int end = plan.long_rows[i + 1].y;
+          T acc = T(0);
+          for (int sgm = a.y; sgm < end; ++sgm) acc += __ldcg(part + sgm);
+          y[a.x] = acc;
+        }
+        if (t == 0) *plan.ticket = 0u;
+      }
     }
   }
   return dot;

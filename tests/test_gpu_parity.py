@@ -379,6 +379,63 @@ def test_spmv_c1_bit_exact_and_long_rows(qd, oracle, dtype):
     assert np.all(np.abs(y - yref) <= eps * scale + 1e-300)
 
 
+def _row_scale(oo, oi, ov, x, rows):
+    scale = np.zeros(rows)
+    np.add.at(scale, np.repeat(np.arange(rows), np.diff(oo)), np.abs(ov.astype(np.float64) * x[oi].astype(np.float64)))
+    return scale
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_spmv_and_cg_irregular_fem_stream_path(qd, oracle, dtype):
+    """C5-shaped input at a size the oracle finishes in seconds: power-law row lengths (a few rows of > 2044 non-zeros,
+    which the plan splits into segments) -> the nnz-balanced stream path.  SpMV per-row tolerance, then Jacobi-PCG."""
+    r, c, v, n = W.fem_tet_triplets(30000, 200000, seed=7, dtype=dtype, compact=True)
+    buf = make_triplet_buffer(r, c, v, dtype)
+    A = build_from_buffer(qd, buf, n, n)
+    oo, oi, ov = oracle.build_matrix(buf, n, n, True)
+    ip, ix, vals = A.matrix.to_scipy_arrays()
+    assert np.array_equal(ip, oo) and np.array_equal(ix, oi) and np.array_equal(bits(vals), bits(ov))
+    lens = np.diff(oo)
+    assert lens.max() > 2044 and lens.min() >= 4  # really irregular, and no empty row after compaction
+    x = np.random.default_rng(8).uniform(-1, 1, n).astype(dtype)
+    y = (A @ to_nd(qd, x)).to_numpy().astype(np.float64)
+    yref = oracle.spmv(oo, oi, ov, x, n, n, True).astype(np.float64)
+    eps = 1e-5 if dtype == np.float32 else 1e-12
+    assert np.all(np.abs(y - yref) <= eps * _row_scale(oo, oi, ov, x, n) + 1e-300)
+    # CG: same rule and budget as the oracle
+    b = np.random.default_rng(9).uniform(-1, 1, n).astype(dtype)
+    tol = 1e-5 if dtype == np.float32 else 1e-10
+    cg = qd.linalg.SparseCG(A, to_nd(qd, b), max_iter=5000, atol=tol)
+    xs, ok = cg.solve()
+    co, ci, cv = oracle.build_matrix(buf, n, n, False)
+    xo, oko, ito, _ = oracle.cg(co, ci, cv, b, 5000, tol)
+    assert ok and oko, (cg.iterations, cg.error, ito)
+    assert abs(cg.iterations - ito) <= max(3, 0.1 * ito), (cg.iterations, ito)
+    rel = np.linalg.norm(xs.to_numpy().astype(np.float64) - xo) / np.linalg.norm(xo)
+    assert rel < (1e-3 if dtype == np.float32 else 1e-8), rel
+
+
+def test_spmv_stream_path_forced_on_regular_matrix(qd, oracle, monkeypatch):
+    """The stream path must also be right where it is not chosen: Poisson 2-D 256^2 with QDSP_SPMV_PATH=stream."""
+    monkeypatch.setenv("QDSP_SPMV_PATH", "stream")
+    r, c, v = W.poisson2d_triplets(256, dtype=np.float32)
+    n = 256 * 256
+    buf = make_triplet_buffer(r, c, v, np.float32)
+    A = build_from_buffer(qd, buf, n, n)
+    x = np.random.default_rng(3).uniform(-1, 1, n).astype(np.float32)
+    y = (A @ to_nd(qd, x)).to_numpy().astype(np.float64)
+    oo, oi, ov = oracle.build_matrix(buf, n, n, True)
+    yref = oracle.spmv(oo, oi, ov, x, n, n, True).astype(np.float64)
+    assert np.all(np.abs(y - yref) <= 1e-5 * _row_scale(oo, oi, ov, x, n) + 1e-300)
+    b = np.ones(n, np.float32)
+    cg = qd.linalg.SparseCG(A, to_nd(qd, b), max_iter=2000, atol=1e-6)
+    xs, ok = cg.solve()
+    co, ci, cv = oracle.build_matrix(buf, n, n, False)
+    xo, oko, ito, _ = oracle.cg(co, ci, cv, b, 2000, 1e-6)
+    assert ok and oko and cg.iterations <= 1.05 * ito
+    assert np.linalg.norm(xs.to_numpy() - xo) / np.linalg.norm(xo) < 2e-2
+
+
 def test_spmv_c2_poisson3d_256_full_size(qd):
     """C2 at full size (16.7 M rows, 117 M nnz): built on the device from 117 M triplets; nnz and indptr checked in
     closed form, y = A x checked against the 7-point stencil applied with torch (fp64 accumulate) at the per-row

@@ -59,7 +59,8 @@ def random_triplets(rows: int, cols: int, n_unique: int, n_dup: int, seed: int =
     return r[perm], c[perm], v
 
 
-def fem_tet_triplets(n_vertices: int, n_tets: int, seed: int = 7, zipf: float = 0.8, dtype=np.float64):
+def fem_tet_triplets(n_vertices: int, n_tets: int, seed: int = 7, zipf: float = 0.8, dtype=np.float64,
+                     compact: bool = False):
     """C5: random points in the unit cube; tets whose 4 distinct vertices are drawn with probability ~ rank^-zipf
     (power-law vertex degree => power-law row lengths); element matrix = P1 Laplacian stiffness from the actual
     coordinates (PSD) + 1e-2 * lumped mass on the diagonal (=> SPD).  16 triplets per tet, lots of duplicates."""
@@ -88,6 +89,11 @@ def fem_tet_triplets(n_vertices: int, n_tets: int, seed: int = 7, zipf: float = 
     g[:, 0, :] = -g[:, 1:, :].sum(axis=1)
     ke = np.einsum("tad,tbd->tab", g, g) * vol[:, None, None]
     ke[:, np.arange(4), np.arange(4)] += 1e-2 * vol[:, None] / 4.0
+    if compact:
+        # drop the vertices no tet touches (their rows would be empty => a singular matrix): renumber the used ones
+        used, tets = np.unique(tets, return_inverse=True)
+        tets = tets.reshape(-1, 4)
+        n_vertices = int(used.shape[0])
     rows = np.repeat(tets, 4, axis=1).ravel()
     cols = np.tile(tets, (1, 4)).ravel()
     return rows.astype(np.int64), cols.astype(np.int64), ke.reshape(-1).astype(dtype), n_vertices

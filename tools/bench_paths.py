@@ -1,0 +1,162 @@
+#!/usr/bin/env python
+"""Secondary throughput harness (NOT the driver's bench line): the other BASELINE.json configs on one B200.
+
+    python tools/bench_paths.py [scan] [sort] [build] [fem]        # default: all, one JSON line per config
+
+C3  inclusive scan and key-value sort of 2^28 random i32                     (byte models of SURVEY 8(d))
+C4  triplet -> CSR build of 200 M random f32 triplets, ~30 % duplicates, rows = cols = 2^24
+C5  fp64 SpMV + Jacobi-PCG on an irregular FEM-like matrix (power-law row lengths)
+All through the C ABI (ctypes), CUDA events on the launching stream, inputs resident in HBM and far larger than L2."""
+import ctypes as C
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+import torch
+
+import quadrants_b200 as qd
+from quadrants_b200 import _lib
+
+PEAK = 6551.7
+try:
+    PEAK = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+except (OSError, KeyError, ValueError):
+    pass
+
+
+def timed(fn, reps, setup=None):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    total = 0.0
+    for _ in range(reps):
+        if setup:
+            setup()
+        torch.cuda.synchronize()
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        total += e0.elapsed_time(e1)
+    return total / reps
+
+
+def emit(name, ms, nbytes, **extra):
+    gbs = nbytes / (ms * 1e-3) / 1e9
+    print(json.dumps({"config": name, "ms": round(ms, 4), "algorithmic_bytes": int(nbytes), "gbs": round(gbs, 1),
+                      "frac_of_measured_peak": round(gbs / PEAK, 4), "frac_of_nominal_8000": round(gbs / 8000, 4),
+                      **extra}), flush=True)
+
+
+def bench_scan(lib, stream):
+    n = 1 << 28
+    g = torch.Generator(device="cuda").manual_seed(5)
+    src = torch.randint(-2**31, 2**31, (n,), dtype=torch.int64, device="cuda", generator=g).to(torch.int32)
+    a = torch.empty_like(src)
+    tmp = torch.empty(lib.qdsp_scan_tmp_bytes(n), dtype=torch.uint8, device="cuda")
+    run = lambda: _lib.check(lib.qdsp_inclusive_scan_i32(a.data_ptr(), n, tmp.data_ptr(), tmp.numel(), stream))
+    for _ in range(3):
+        a.copy_(src); run()
+    ms = timed(run, 10, setup=lambda: a.copy_(src))
+    emit("C3 inclusive scan 2^28 i32", ms, 2 * n * 4, gkeys_per_s=round(n / ms / 1e6, 2))
+
+
+def bench_sort(lib, stream):
+    n = 1 << 28
+    g = torch.Generator(device="cuda").manual_seed(4)
+    src = torch.randint(-2**31, 2**31, (n,), dtype=torch.int64, device="cuda", generator=g).to(torch.int32)
+    k = torch.empty_like(src)
+    v = torch.empty_like(src)
+    ar = torch.arange(n, dtype=torch.int32, device="cuda")
+    tmp = torch.empty(lib.qdsp_sort_tmp_bytes(n, _lib.KEY_I32, 4), dtype=torch.uint8, device="cuda")
+    def setup():
+        k.copy_(src); v.copy_(ar)
+    run = lambda: _lib.check(lib.qdsp_sort_pairs(k.data_ptr(), v.data_ptr(), n, _lib.KEY_I32, 4, tmp.data_ptr(), tmp.numel(), stream))
+    for _ in range(2):
+        setup(); run()
+    ms = timed(run, 5, setup=setup)
+    emit("C3 parallel_sort 2^28 i32 keys + i32 values", ms, n * 4 + 4 * 2 * n * 8, two_touch_bytes=2 * n * 8,
+         gpairs_per_s=round(n / ms / 1e6, 2))
+    tmpk = torch.empty(lib.qdsp_sort_tmp_bytes(n, _lib.KEY_I32, 0), dtype=torch.uint8, device="cuda")
+    runk = lambda: _lib.check(lib.qdsp_sort_pairs(k.data_ptr(), None, n, _lib.KEY_I32, 0, tmpk.data_ptr(), tmpk.numel(), stream))
+    setup(); runk()
+    ms = timed(runk, 5, setup=setup)
+    emit("C3 parallel_sort 2^28 i32 keys only", ms, n * 4 + 4 * 2 * n * 4, gkeys_per_s=round(n / ms / 1e6, 2))
+
+
+def bench_build(lib, stream):
+    rows = cols = 1 << 24
+    nu, nd = 140_000_000, 60_000_000
+    g = torch.Generator(device="cuda").manual_seed(6)
+    r = torch.randint(0, rows, (nu,), dtype=torch.int32, device="cuda", generator=g)
+    c = torch.randint(0, cols, (nu,), dtype=torch.int32, device="cuda", generator=g)
+    pick = torch.randint(0, nu, (nd,), dtype=torch.int64, device="cuda", generator=g)
+    r = torch.cat([r, r[pick]]); c = torch.cat([c, c[pick]])
+    perm = torch.randperm(nu + nd, device="cuda", generator=g)
+    r, c = r[perm].contiguous(), c[perm].contiguous()
+    del perm, pick
+    v = torch.empty(nu + nd, dtype=torch.float32, device="cuda").uniform_(-1, 1, generator=g)
+    t = nu + nd
+    K = qd.linalg.SparseMatrixBuilder(rows, cols, max_num_triplets=t, dtype=qd.f32)
+    K.ptr.insert_triplets(r, c, v)
+    buf = K.ptr.buffer_tensor().clone()      # the filled buffer, restored before every timed build
+    del r, c, v
+    out = []
+    def setup():
+        K.ptr.buffer_tensor().copy_(buf)
+        out.clear()
+    def run():
+        out.append(K.build())
+    setup(); run(); nnz = out[0].matrix.nnz()
+    ms = timed(run, 3, setup=setup)
+    s, kb = 4, 8
+    P = 6
+    model = 3 * t * s + t * (kb + s) + t * kb + P * 2 * t * (kb + s) + t * (kb + s) + nnz * (4 + s) + (rows + 1) * 4
+    emit("C4 triplet->CSR build, 200 M f32 triplets (~30 % duplicates), 2^24 x 2^24", ms, model, triplets=t, nnz=int(nnz),
+         mtriplets_per_s=round(t / ms / 1e3, 1))
+
+
+def bench_fem(lib, stream):
+    from tests import workloads as W
+    nv, nt = 400_000, 2_000_000
+    r, c, v, n = W.fem_tet_triplets(nv, nt, seed=7, dtype=np.float64, compact=True)
+    K = qd.linalg.SparseMatrixBuilder(n, n, max_num_triplets=int(r.shape[0]), dtype=qd.f64)
+    K.ptr.insert_triplets(torch.from_numpy(r).cuda(), torch.from_numpy(c).cuda(), torch.from_numpy(v).cuda())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); A = K.build(); e1.record(); torch.cuda.synchronize()
+    ms_build = e0.elapsed_time(e1)
+    nnz = A.matrix.nnz()
+    ip = A.matrix.to_scipy_arrays()[0]
+    lens = np.diff(ip)
+    x = qd.ndarray(qd.f64, n); x.tensor.uniform_(-1, 1)
+    y = qd.ndarray(qd.f64, n)
+    run = lambda: A.matrix.spmv(None, x, y)
+    for _ in range(5):
+        run()
+    reps = 200
+    ms = timed(lambda: [run() for _ in range(reps)], 3) / reps
+    emit("C5 FEM tet stiffness fp64 SpMV (L2-resident: matrix %.0f MB)" % (nnz * 12 / 1e6), ms, nnz * 12 + (n + 1) * 4 + 2 * n * 8,
+         rows=n, nnz=int(nnz), row_len_min=int(lens.min()), row_len_mean=round(float(lens.mean()), 1), row_len_max=int(lens.max()),
+         triplets=int(r.shape[0]), build_ms=round(ms_build, 3))
+    b = qd.ndarray(qd.f64, n); b.tensor.uniform_(-1, 1)
+    cg = qd.linalg.SparseCG(A, b, max_iter=5000, atol=1e-10)
+    xs, ok = cg.solve()
+    torch.cuda.synchronize()
+    ms = timed(lambda: cg.solve(), 3)
+    emit("C5 FEM fp64 Jacobi-PCG to 1e-10", ms, cg.iterations * (nnz * 12 + (n + 1) * 4 + 12 * n * 8), iterations=cg.iterations,
+         success=bool(ok), rel_residual=cg.error, iters_per_s=round(cg.iterations / ms * 1e3, 1))
+
+
+def main():
+    qd.init(arch=qd.cuda, device=0)
+    lib = _lib.load()
+    stream = torch.cuda.current_stream().cuda_stream
+    which = sys.argv[1:] or ["scan", "sort", "build", "fem"]
+    for w in which:
+        {"scan": bench_scan, "sort": bench_sort, "build": bench_build, "fem": bench_fem}[w](lib, stream)
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    main()
