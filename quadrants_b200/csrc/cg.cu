@@ -41,7 +41,7 @@ constexpr int CG_THREADS = 256;
 struct CgScalars {
   double pAp, abs_new, abs_old, res2, rhs2, thr;
   double alpha, beta;
-  double red[4];  // local sums handed to ncclAllReduce (QDSP_ALLREDUCE=nccl)
+  double red[8];  // local sums handed to ncclAllReduce (QDSP_ALLREDUCE=nccl)
   int iters;      // Eigen's i: completed loop bodies
   int done;       // 0 running, 1 converged, 2 budget exhausted, 3 communication failure
   int max_iters;
@@ -49,7 +49,6 @@ struct CgScalars {
   int relative;
   double tol;
   unsigned ticket[4];
-  unsigned flag[2];  // fused iteration kernel: "alpha is ready" / "beta is ready" sequence numbers (2*iters+1, +2)
 };
 
 // ---- block / grid reductions ----------------------------------------------------------------------------------------
@@ -151,13 +150,36 @@ __device__ __forceinline__ void cg_finish_B(CgScalars *sc, double rr, double rz)
   }
 }
 
+// One-reduction iteration (variant "merged").  With t = A p, z = D^-1 r and the seven sums of MergedSink,
+//   alpha = r.z / p.t,   |r'|^2 = r.r - 2 alpha r.t + alpha^2 t.t,   r'.z' = r.z - 2 alpha t.z + alpha^2 t.D^-1 t
+// are the values the classic recurrence obtains with a second reduction after r' = r - alpha t.  r.z and r.r are
+// recomputed from the stored r every iteration, so the prediction never drifts; the sums are in double, so the
+// cancellation costs ~1e-15 |r|^2 / |r'|^2 -- below the rounding of the stored r' itself.  Same scalar roundings
+// through T as cg_finish_A/B, same stopping rule, same iteration count convention.
+template <typename T>
+__device__ __forceinline__ void cg_finish_merged(CgScalars *sc, const double (&v)[7]) {
+  const T pap = static_cast<T>(v[0]);
+  const T rho = static_cast<T>(v[5]);
+  const T alpha_t = rho / pap;
+  const double a = static_cast<double>(alpha_t);
+  double rr = v[6] - 2.0 * a * v[3] + a * a * v[4];
+  double rz = v[5] - 2.0 * a * v[1] + a * a * v[2];
+  if (rr < 0.0) rr = 0.0;
+  if (rz < 0.0) rz = 0.0;
+  sc->pAp = static_cast<double>(pap);
+  sc->alpha = a;
+  sc->abs_new = static_cast<double>(rho);
+  cg_finish_B<T>(sc, rr, rz);
+}
+
 // QDSP_ALLREDUCE=nccl: the sums were all-reduced in sc->red by NCCL between two kernels
 template <typename T>
 __global__ void cg_scalars_kernel(CgScalars *sc, int which) {
   if (which != 0 && sc->done) return;
   if (which == 0) { const double v[3] = {sc->red[0], sc->red[1], sc->red[2]}; cg_finish_init<T>(sc, v); }
   else if (which == 1) cg_finish_A<T>(sc, sc->red[0]);
-  else cg_finish_B<T>(sc, sc->red[0], sc->red[1]);
+  else if (which == 2) cg_finish_B<T>(sc, sc->red[0], sc->red[1]);
+  else { const double v[7] = {sc->red[0], sc->red[1], sc->red[2], sc->red[3], sc->red[4], sc->red[5], sc->red[6]}; cg_finish_merged<T>(sc, v); }
 }
 
 // Last block: all-reduce across ranks (in-kernel, or deferred to NCCL) and hand the totals to `fin` on one thread.
@@ -200,8 +222,8 @@ cg_invdiag_kernel(int n, const int *__restrict__ indptr, const int *__restrict__
 }
 
 // contiguous chunk of CTA `b` when n elements are split over `g` CTAs in multiples of 1024
-__device__ __forceinline__ void cta_chunk(int n, int &lo, int &hi) {
-  const int per = ((n + gridDim.x - 1) / gridDim.x + 1023) & ~1023;
+__device__ __forceinline__ void cta_chunk(int n, int &lo, int &hi, int &per) {
+  per = ((n + gridDim.x - 1) / gridDim.x + 1023) & ~1023;
   lo = min(n, static_cast<int>(blockIdx.x) * per);
   hi = min(n, lo + per);
 }
@@ -214,8 +236,8 @@ cg_init_kernel(int n, const T *__restrict__ b, const T *__restrict__ tmp, const 
                DistDev d, int use_nccl) {
   __shared__ double s_red[3 * 16];
   __shared__ unsigned s_flag;
-  int lo, hi;
-  cta_chunk(n, lo, hi);
+  int lo, hi, per;
+  cta_chunk(n, lo, hi, per);
   T s0 = T(0), s1 = T(0), s2 = T(0);
   for (int i = lo + threadIdx.x; i < hi; i += CG_THREADS) {
     const T bi = b[i];
@@ -227,7 +249,7 @@ cg_init_kernel(int n, const T *__restrict__ b, const T *__restrict__ tmp, const 
     s1 = fma_t(ri, ri, s1);
     s2 = fma_t(ri, pi, s2);
   }
-  dist_halo_push_signal<T>(d, p, lo, hi, &s_flag);
+  dist_halo_push_signal<T>(d, p, lo, hi, per);
   double v[3] = {static_cast<double>(s0), static_cast<double>(s1), static_cast<double>(s2)};
   if (grid_sum_last_block<3>(v, partials, &sc->ticket[0], s_red, &s_flag))
     cg_reduce_and_finish<3>(v, d, use_nccl, sc, [&](const double (&t)[3]) { cg_finish_init<T>(sc, t); });
@@ -248,7 +270,9 @@ cg_spmv_dot_kernel(int rows, const int *__restrict__ indptr, const int *__restri
     if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;
     return;
   }
-  double v[1] = {spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, p, d)};
+  DotSink<T> sink{p};
+  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, sink, d);
+  double v[1] = {sink.acc};
   if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag))
     cg_reduce_and_finish<1>(v, d, use_nccl, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
 }
@@ -266,7 +290,9 @@ cg_spmv_dot_stream_kernel(const int *__restrict__ indptr, const int *__restrict_
     if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;
     return;
   }
-  double v[1] = {spmv_stream<T>(smem_raw, indptr, indices, values, p, tmp, p, plan, d)};
+  DotSink<T> sink{p};
+  spmv_stream<T>(smem_raw, indptr, indices, values, p, tmp, sink, plan, d);
+  double v[1] = {sink.acc};
   if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag))
     cg_reduce_and_finish<1>(v, d, use_nccl, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
 }
@@ -348,88 +374,82 @@ template <typename T>
 __global__ void __launch_bounds__(CG_THREADS)
 cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, T *__restrict__ p, T *__restrict__ x,
                     const CgScalars *__restrict__ sc, DistDev d) {
-  __shared__ unsigned s_flag;
   const int done = sc->done;
   if (done == 3) return;
   if (done != 0 && sc->alpha == 0.0) return;  // replayed after the end of the solve: x already has its last update
-  int lo, hi;
-  cta_chunk(n, lo, hi);
+  int lo, hi, per;
+  cta_chunk(n, lo, hi, per);
   // converged (done == 1): only the deferred x += alpha p is still owed; p is dead.  done == 2: Eigen still updates p
   cg_direction_body<T>(r, dinv, p, x, static_cast<T>(sc->alpha), static_cast<T>(sc->beta), done != 1, lo, hi);
-  if (done == 0) dist_halo_push_signal<T>(d, p, lo, hi, &s_flag);
+  if (done == 0) dist_halo_push_signal<T>(d, p, lo, hi, per);
 }
 
-// ---- the whole iteration as ONE kernel (multi-GPU) ---------------------------------------------------------------------
-// Same arithmetic as the three kernels above, but the two grid-wide joins (alpha known / beta known) are flag waits
-// inside one persistent grid instead of kernel boundaries: the CTA that finishes a reduction last (and has all-reduced
-// it over NVLink) publishes a sequence number, the others spin on it in L2.  Saves two launch boundaries per
-// iteration, which at 8 ranks (~35 us of HBM time per iteration) is what separates 4.6x from the 6x target.
-// All CTAs must be co-resident: the grid is sized by the occupancy API (<= SMs x resident CTAs), nothing else runs on
-// the solver's stream, and CTAs of the previous launch never wait on this one.
-__device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned *p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_gpu_u32(unsigned *p, unsigned v) {
-  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ void grid_flag_wait(const unsigned *flag, unsigned want) {
-  if (threadIdx.x == 0) {
-    const long long t0 = clock64();
-    while (ld_acquire_gpu_u32(flag) != want)
-      if (clock64() - t0 > DIST_SPIN_LIMIT) break;  // a lost peer already raised the error flag: leave, do not hang
-  }
-  __syncthreads();
-}
-
+// ---- variant "merged": two kernels and ONE reduction per iteration -----------------------------------------------------
+//   A' cg_spmv_merged : tmp = A p and the seven sums (reads r and D^-1 on top of the classic kernel)      matrix + 4n
+//   B' cg_update_merged: r -= alpha tmp, x += alpha p, p = D^-1 r + beta p, halo of the new p             5n read, 3n write
+// Same 12n vector traffic as the classic three kernels, one grid-wide join and one cross-rank all-reduce fewer: at 8
+// ranks an iteration is ~35 us of HBM time, and each join costs ~7 us of NVLink + launch latency.
 template <typename T, int LPR, bool ROW_MAJOR_ORDER>
 __global__ void __launch_bounds__(SPMV_THREADS)
-cg_iter_fused_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ indices,
-                     const T *__restrict__ values, T *__restrict__ p, T *__restrict__ tmp, const T *__restrict__ dinv,
-                     T *__restrict__ r, T *__restrict__ x, CgScalars *__restrict__ sc, double *__restrict__ partials,
-                     DistDev d) {
+cg_spmv_merged_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ indices,
+                      const T *__restrict__ values, const T *__restrict__ p, T *__restrict__ tmp,
+                      const T *__restrict__ r, const T *__restrict__ dinv, CgScalars *__restrict__ sc,
+                      double *__restrict__ partials, DistDev d, int use_nccl) {
   extern __shared__ unsigned char smem_raw[];
-  __shared__ double s_red[2 * 16];
+  __shared__ double s_red[7 * 16];
   __shared__ unsigned s_flag;
-  if (sc->done) return;
-  const unsigned seq = 2u * static_cast<unsigned>(sc->iters) + 1u;
-  // A: tmp = A p, p.tmp -> alpha
-  {
-    double v[1] = {spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, p, d)};
-    if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag)) {
-      cg_reduce_and_finish<1>(v, d, 0, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
-      if (threadIdx.x == 0) {
-        __threadfence();
-        st_release_gpu_u32(&sc->flag[0], seq);
-      }
+  if (sc->done) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;  // see cg_spmv_dot_kernel
+    return;
+  }
+  MergedSink<T> sink{p, r, dinv};
+  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, sink, d);
+  double v[7];
+#pragma unroll
+  for (int j = 0; j < 7; ++j) v[j] = sink.v[j];
+  if (grid_sum_last_block<7>(v, partials, &sc->ticket[1], s_red, &s_flag))
+    cg_reduce_and_finish<7>(v, d, use_nccl, sc, [&](const double (&t)[7]) { cg_finish_merged<T>(sc, t); });
+}
+
+template <typename T>
+__global__ void __launch_bounds__(CG_THREADS)
+cg_update_merged_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv, T *__restrict__ r,
+                        T *__restrict__ p, T *__restrict__ x, const CgScalars *__restrict__ sc, DistDev d) {
+  const int done = sc->done;
+  if (done == 3) return;
+  if (done != 0 && sc->alpha == 0.0) return;  // replayed after the end of the solve
+  const T alpha = static_cast<T>(sc->alpha), beta = static_cast<T>(sc->beta);
+  const bool update_p = done != 1;
+  int lo, hi, per;
+  cta_chunk(n, lo, hi, per);
+  using V = typename Vec4T<T>::type;
+  const int lo4 = lo >> 2, hi4 = hi >> 2;
+  for (int i = lo4 + threadIdx.x; i < hi4; i += blockDim.x) {
+    const V t4 = reinterpret_cast<const V *>(tmp)[i];
+    const V d4 = reinterpret_cast<const V *>(dinv)[i];
+    V r4 = reinterpret_cast<V *>(r)[i];
+    V p4 = reinterpret_cast<V *>(p)[i];
+    V x4 = reinterpret_cast<V *>(x)[i];
+    r4.x = fma_t(-alpha, t4.x, r4.x); r4.y = fma_t(-alpha, t4.y, r4.y);
+    r4.z = fma_t(-alpha, t4.z, r4.z); r4.w = fma_t(-alpha, t4.w, r4.w);
+    x4.x = fma_t(alpha, p4.x, x4.x); x4.y = fma_t(alpha, p4.y, x4.y);
+    x4.z = fma_t(alpha, p4.z, x4.z); x4.w = fma_t(alpha, p4.w, x4.w);
+    reinterpret_cast<V *>(r)[i] = r4;
+    reinterpret_cast<V *>(x)[i] = x4;
+    if (update_p) {
+      p4.x = fma_t(beta, p4.x, d4.x * r4.x); p4.y = fma_t(beta, p4.y, d4.y * r4.y);
+      p4.z = fma_t(beta, p4.z, d4.z * r4.z); p4.w = fma_t(beta, p4.w, d4.w * r4.w);
+      reinterpret_cast<V *>(p)[i] = p4;
     }
   }
-  grid_flag_wait(&sc->flag[0], seq);
-  // B: r -= alpha tmp, |r|^2, r.z -> beta, convergence
-  {
-    T s_rr = T(0), s_rz = T(0);
-    cg_residual_body<T>(rows, tmp, dinv, r, static_cast<T>(__ldcg(&sc->alpha)), s_rr, s_rz);
-    double v[2] = {static_cast<double>(s_rr), static_cast<double>(s_rz)};
-    if (grid_sum_last_block<2>(v, partials, &sc->ticket[2], s_red, &s_flag)) {
-      cg_reduce_and_finish<2>(v, d, 0, sc, [&](const double (&t)[2]) { cg_finish_B<T>(sc, t[0], t[1]); });
-      if (threadIdx.x == 0) {
-        __threadfence();
-        st_release_gpu_u32(&sc->flag[1], seq + 1u);
-      }
-    }
+  for (int i = (hi4 << 2) + threadIdx.x; i < hi; i += blockDim.x) {
+    const T ri = fma_t(-alpha, tmp[i], r[i]);
+    const T pi = p[i];
+    r[i] = ri;
+    x[i] = fma_t(alpha, pi, x[i]);
+    if (update_p) p[i] = fma_t(beta, pi, dinv[i] * ri);
   }
-  grid_flag_wait(&sc->flag[1], seq + 1u);
-  // C: x += alpha p, p = z + beta p, halo of the new p
-  {
-    const int done = __ldcg(&sc->done);
-    if (done == 3) return;
-    int lo, hi;
-    cta_chunk(rows, lo, hi);
-    cg_direction_body<T>(r, dinv, p, x, static_cast<T>(__ldcg(&sc->alpha)), static_cast<T>(__ldcg(&sc->beta)), done != 1,
-                         lo, hi);
-    if (done == 0) dist_halo_push_signal<T>(d, p, lo, hi, &s_flag);
-  }
+  if (done == 0) dist_halo_push_signal<T>(d, p, lo, hi, per);
 }
 
 // ---- host ------------------------------------------------------------------------------------------------------------------
@@ -450,6 +470,7 @@ struct CgSolver::Impl {
   void *graph_x = nullptr;
   int graph_iters = 0;
   int vec_grid = 0, spmv_grid = 0, lpr = 1;
+  bool merged = false;  // one-reduction variant (cg_spmv_merged_kernel + cg_update_merged_kernel)
   int n = 0;  // owned rows
 
   Impl(const CsrMatrix &A_, int mi, double t, int m, bool v, DistContext *d)
@@ -513,6 +534,33 @@ int spmv_dot_occupancy() {
     default: CALL(32); break;      \
   }
 
+template <typename T, int LPR>
+void launch_spmv_merged(CgSolver::Impl &I) {
+  const CsrMatrix &A = I.A;
+  auto *sc = I.scalars.get<CgScalars>();
+  const size_t smem = spmv_smem_bytes<T, 2>();
+  if (A.row_major_order && LPR == 1)
+    cg_spmv_merged_kernel<T, LPR, true><<<I.spmv_grid, SPMV_THREADS, smem, I.stream>>>(
+        I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+        I.r.get<T>(), I.dinv.get<T>(), sc, I.partials.get<double>(), I.dev(), I.use_nccl);
+  else
+    cg_spmv_merged_kernel<T, LPR, false><<<I.spmv_grid, SPMV_THREADS, smem, I.stream>>>(
+        I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+        I.r.get<T>(), I.dinv.get<T>(), sc, I.partials.get<double>(), I.dev(), I.use_nccl);
+  QDSP_LAUNCH_CHECK();
+}
+
+template <typename T, int LPR>
+int spmv_merged_occupancy() {
+  const size_t smem = spmv_smem_bytes<T, 2>();
+  int occ = 0, occ2 = 0;
+  QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_merged_kernel<T, LPR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_merged_kernel<T, LPR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  QDSP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, cg_spmv_merged_kernel<T, LPR, false>, SPMV_THREADS, smem));
+  QDSP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, cg_spmv_merged_kernel<T, LPR, true>, SPMV_THREADS, smem));
+  return std::max(1, std::min(occ, occ2));
+}
+
 template <typename T>
 void launch_spmv_dot_any(CgSolver::Impl &I) {
   if (I.A.spmv_mode == 2) {
@@ -537,6 +585,16 @@ void launch_iteration(CgSolver::Impl &I, T *x) {
   auto *sc = I.scalars.get<CgScalars>();
   double *part = I.partials.get<double>();
   const int n = I.n;
+  if (I.merged) {
+#define QDSP_CALL(L) launch_spmv_merged<T, L>(I)
+    QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
+#undef QDSP_CALL
+    if (I.use_nccl) nccl_reduce_then<T>(I, 7, 3);
+    cg_update_merged_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(),
+                                                                         static_cast<T *>(I.p), x, sc, I.dev());
+    QDSP_LAUNCH_CHECK();
+    return;
+  }
   launch_spmv_dot_any<T>(I);
   if (I.use_nccl) nccl_reduce_then<T>(I, 1, 1);
   cg_residual_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(), sc, part, I.dev(), I.use_nccl);
@@ -546,7 +604,7 @@ void launch_iteration(CgSolver::Impl &I, T *x) {
   QDSP_LAUNCH_CHECK();
 }
 
-int kernels_per_iteration(const CgSolver::Impl &I) { return I.use_nccl ? 5 : 3; }
+int kernels_per_iteration(const CgSolver::Impl &I) { return I.merged ? (I.use_nccl ? 3 : 2) : (I.use_nccl ? 5 : 3); }
 
 // (Re)captures `iters` iterations on x into an executable graph.
 template <typename T>
@@ -640,7 +698,7 @@ void solve_t(CgSolver::Impl &I, void *xv, const void *bv, cudaStream_t user, int
 // (a debugging aid for the multi-GPU overheads; never used for a reported number)
 template <typename T>
 void run_traced(CgSolver::Impl &I, T *x, int iters) {
-  const int K = 3, keep = std::min(iters, 64);
+  const int K = I.merged ? 2 : 3, keep = std::min(iters, 64);
   std::vector<cudaEvent_t> ev(static_cast<size_t>(keep) * (K + 1));
   for (auto &e : ev) QDSP_CUDA(cudaEventCreate(&e));
   auto *sc = I.scalars.get<CgScalars>();
@@ -649,6 +707,16 @@ void run_traced(CgSolver::Impl &I, T *x, int iters) {
     const int slot = it - (iters - keep);
     auto mark = [&](int k) { if (slot >= 0) QDSP_CUDA(cudaEventRecord(ev[static_cast<size_t>(slot) * (K + 1) + k], I.stream)); };
     mark(0);
+    if (I.merged) {
+#define QDSP_CALL(L) launch_spmv_merged<T, L>(I)
+      QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
+#undef QDSP_CALL
+      mark(1);
+      cg_update_merged_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(I.n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(),
+                                                                           static_cast<T *>(I.p), x, sc, I.dev());
+      mark(2);
+      continue;
+    }
     launch_spmv_dot_any<T>(I);
     mark(1);
     cg_residual_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(I.n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(), sc, part, I.dev(), I.use_nccl);
@@ -657,7 +725,7 @@ void run_traced(CgSolver::Impl &I, T *x, int iters) {
     mark(3);
   }
   QDSP_CUDA(cudaStreamSynchronize(I.stream));
-  double sum[K] = {0, 0, 0}, total = 0;
+  double sum[3] = {0, 0, 0}, total = 0;
   for (int s = 0; s < keep; ++s)
     for (int k = 0; k < K; ++k) {
       float ms = 0;
@@ -665,8 +733,12 @@ void run_traced(CgSolver::Impl &I, T *x, int iters) {
       sum[k] += ms;
       total += ms;
     }
-  std::fprintf(stderr, "[qdsp trace rank %d] per iteration over %d: spmv_dot %.2f us, residual %.2f us, direction %.2f us, total %.2f us\n",
-               I.dist ? I.dist->rank() : 0, keep, 1e3 * sum[0] / keep, 1e3 * sum[1] / keep, 1e3 * sum[2] / keep, 1e3 * total / keep);
+  if (I.merged)
+    std::fprintf(stderr, "[qdsp trace rank %d] per iteration over %d: spmv_merged %.2f us, update %.2f us, total %.2f us\n",
+                 I.dist ? I.dist->rank() : 0, keep, 1e3 * sum[0] / keep, 1e3 * sum[1] / keep, 1e3 * total / keep);
+  else
+    std::fprintf(stderr, "[qdsp trace rank %d] per iteration over %d: spmv_dot %.2f us, residual %.2f us, direction %.2f us, total %.2f us\n",
+                 I.dist ? I.dist->rank() : 0, keep, 1e3 * sum[0] / keep, 1e3 * sum[1] / keep, 1e3 * sum[2] / keep, 1e3 * total / keep);
   for (auto &e : ev) cudaEventDestroy(e);
 }
 
@@ -728,7 +800,23 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
     I.spmv_grid = std::max(1, std::min(ceil_div(A.rows, R), device_props().sm_count * occ));
   }
   I.vec_grid = std::max(1, std::min(ceil_div(A.rows, 1024), device_props().sm_count * 8));
-  I.partials.alloc(sizeof(double) * 3 * static_cast<size_t>(std::max(I.spmv_grid, I.vec_grid)));
+  // variant: "merged" (one reduction per iteration) by default for the multi-GPU solver, "classic" (Eigen's two
+  // reductions) on one GPU; QDSP_CG_VARIANT=classic|merged overrides.  The merged sums are quadratic in A p, so the
+  // stream path (long rows in segments) stays classic.
+  {
+    const char *e = std::getenv("QDSP_CG_VARIANT");
+    const bool want = e ? std::string(e) == "merged" : (dist != nullptr && dist->world() > 1);
+    I.merged = want && A.spmv_mode == 1;
+    if (I.merged) {
+      int mocc = 1;
+#define QDSP_CALL(L) mocc = (A.dtype == QDSP_F32) ? spmv_merged_occupancy<float, L>() : spmv_merged_occupancy<double, L>()
+      QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
+#undef QDSP_CALL
+      const int R = SPMV_CONSUMERS / I.lpr;
+      I.spmv_grid = std::max(1, std::min(ceil_div(A.rows, R), device_props().sm_count * mocc));
+    }
+  }
+  I.partials.alloc(sizeof(double) * 8 * static_cast<size_t>(std::max(I.spmv_grid, I.vec_grid)));
   I.scalars.alloc(sizeof(CgScalars));
   QDSP_CUDA(cudaMemset(I.scalars.get(), 0, sizeof(CgScalars)));
   QDSP_CUDA(cudaHostAlloc(reinterpret_cast<void **>(&I.h_sc), sizeof(CgScalars), cudaHostAllocDefault));

@@ -3,6 +3,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "dist.hpp"
@@ -125,6 +126,8 @@ void DistContext::localize(CsrMatrix &A, const int64_t *row_offsets, cudaStream_
     QDSP_CUDA(cudaMemcpyAsync(block_order_.get(), order.data(), sizeof(int32_t) * order.size(), cudaMemcpyHostToDevice, stream));
     QDSP_CUDA(cudaStreamSynchronize(stream));
     dev_.block_order = block_order_.get<int>();
+    if (const char *e = std::getenv("QDSP_HALO_ORDER"))  // "0": keep the natural block order (measurement aid)
+      if (e[0] == '0') dev_.block_order = nullptr;
   }
   const size_t sv = A.value_bytes();
   comm_.alloc(DIST_VECTOR_OFF + sv * (static_cast<size_t>(plan_.ghost_base) + n_ghost()) + 256);
@@ -207,11 +210,10 @@ int DistContext::error_flag(cudaStream_t stream) const {
 // ---- stand-alone distributed SpMV ---------------------------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) dist_load_push_kernel(int n, const T *__restrict__ x, T *__restrict__ vec, DistDev d) {
-  __shared__ unsigned s_flag;
   const int per = ((n + gridDim.x - 1) / gridDim.x + 1023) & ~1023;
   const int lo = min(n, static_cast<int>(blockIdx.x) * per), hi = min(n, lo + per);
   for (int i = lo + threadIdx.x; i < hi; i += blockDim.x) vec[i] = x[i];
-  dist_halo_push_signal<T>(d, vec, lo, hi, &s_flag);
+  dist_halo_push_signal<T>(d, vec, lo, hi, per);
 }
 
 void DistContext::spmv(const CsrMatrix &A, const void *x_loc, void *y_loc, cudaStream_t stream) {

@@ -6,7 +6,7 @@
 // through NVSwitch), CG scalars all-reduced in-kernel.
 //
 // Every rank owns one "comm buffer" (cudaMalloc, exported with cudaIpcGetMemHandle, mapped by every peer):
-//   [0, 2048)      reduction slots   slots[2 parity][8 ranks][4 values][2 words]   8-byte words {payload32 | seq32}
+//   [0, 2048)      reduction slots   slots[2 parity][8 ranks][8 values][2 words]   8-byte words {payload32 | seq32}
 //   [2048, 2112)   halo flags        flags[8 ranks]                                 8-byte, monotone sequence numbers
 //   [4096, ...)    the operand vector of SpMV: n_loc owned entries followed by n_ghost ghost entries
 // Protocol:
@@ -14,7 +14,7 @@
 //     that neighbour's ghost segment, fences at system scope, and stores its push count into the neighbour's
 //     flags[rank].  A consumer kernel spins (ld.acquire.sys) until flags[q] >= its own push count for every
 //     neighbour q it receives from -- ranks run the same kernel sequence, so "my push count" is the expected value.
-//   * all-reduce of up to 4 doubles (NCCL "LL" style): each 64-bit value travels as two 8-byte words carrying 32 data
+//   * all-reduce of up to 8 doubles (NCCL "LL" style): each 64-bit value travels as two 8-byte words carrying 32 data
 //     bits + the 32-bit sequence number; an aligned 8-byte store is single-copy atomic, so data and flag arrive
 //     together and one NVLink latency is the whole cost.  Slots alternate by sequence parity: a rank can be at most
 //     one reduction ahead of a peer (it needs the peer's value to finish the current one).  Every rank sums the 8
@@ -26,7 +26,8 @@
 namespace qdsp {
 
 constexpr int DIST_MAX_RANKS = 8;
-constexpr int DIST_MAX_VALUES = 4;
+constexpr int DIST_MAX_VALUES = 8;
+static_assert(2 * DIST_MAX_RANKS * DIST_MAX_VALUES * 2 * 8 <= 2048, "reduction slots overlap the halo flags");
 constexpr size_t DIST_SLOTS_OFF = 0;
 constexpr size_t DIST_FLAGS_OFF = 2048;
 constexpr size_t DIST_VECTOR_OFF = 4096;
@@ -94,7 +95,7 @@ __device__ __forceinline__ void dist_allreduce(const DistDev &d, double (&v)[NV]
   if (d.world <= 1) return;
   const int lane = lane_id();
   unsigned seq = 0;
-  if (lane == 0) seq = ++d.counters[0];
+  if (lane == 0) seq = atomicAdd(&d.counters[0], 1u) + 1u;  // one round trip (a load + store pair would be two)
   seq = __shfl_sync(FULL, seq, 0);
   const unsigned parity = seq & 1u;
   // lane q talks to rank q
@@ -138,52 +139,76 @@ __device__ __forceinline__ void dist_allreduce(const DistDev &d, double (&v)[NV]
   }
 }
 
-// Stores the entries of vec[lo, hi) that neighbours need into their ghost segments, then takes a ticket; the last CTA of
-// the grid publishes the new push count to the neighbours.  Called by all threads of every CTA of a kernel that has
-// just written vec[lo, hi) (chunks of different CTAs are disjoint and cover the vector).  `s_flag`: a shared word.
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+
+// Stores the entries of vec[lo, hi) that neighbours need into their ghost segments and signals them.  Called by all
+// threads of every CTA of a kernel that has just written vec[lo, hi); the chunks [lo, hi) of the CTAs are the
+// cta-chunk partition of [0, n): CTA b owns [b * per, (b + 1) * per), per = chunk size (a multiple of 1024).
+// Only the CTAs that own a halo row take part: each stores its part (16-byte stores where the run is contiguous and
+// aligned), fences ONCE at system scope (the wait for the NVLink write acknowledgements) and takes a ticket; the last
+// of them publishes the new push count to the neighbours.  The other CTAs -- all but a few dozen -- do nothing, and
+// the signal leaves as soon as the halo rows are done instead of at the end of the kernel (measured at 8 ranks: the
+// direction kernel took 25 us with an all-CTA ticket against 10 us without any push, profiles/r01h_8gpu_trace.txt).
 template <typename T>
-__device__ __forceinline__ void dist_halo_push_signal(const DistDev &d, const T *vec, int lo, int hi, unsigned *s_flag) {
+__device__ __forceinline__ void dist_halo_push_signal(const DistDev &d, const T *vec, int lo, int hi, int per) {
   if (d.world <= 1) return;
+  bool mine = false;
+  for (int s = 0; s < d.n_send; ++s) mine = mine || (lo < hi && hi > d.send_first[s] && lo <= d.send_last[s]);
+  if (!mine) return;
   __syncthreads();  // the CTA's own writes of vec[lo, hi) are visible to all its threads
-  bool pushed = false;
   for (int s = 0; s < d.n_send; ++s) {
-    if (hi <= d.send_first[s] || lo > d.send_last[s] || lo >= hi) continue;  // most CTAs own no halo row
+    if (hi <= d.send_first[s] || lo > d.send_last[s]) continue;
     const int *list = d.send_list[s];
     const int cnt = d.send_count[s];
-    int jlo, jhi;
-    if (d.send_contig[s]) {
-      jlo = max(lo, d.send_first[s]) - d.send_first[s];
-      jhi = min(hi, d.send_last[s] + 1) - d.send_first[s];
-    } else {
-      int a = 0, b = cnt;
-      while (a < b) { const int m = (a + b) >> 1; if (list[m] < lo) a = m + 1; else b = m; }
-      jlo = a;
-      b = cnt;
-      while (a < b) { const int m = (a + b) >> 1; if (list[m] < hi) a = m + 1; else b = m; }
-      jhi = a;
-    }
     T *dst = reinterpret_cast<T *>(d.peer[d.send_peer[s]] + DIST_VECTOR_OFF) + d.send_dst[s];
     if (d.send_contig[s]) {
       const int first = d.send_first[s];
-      for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[first + j];
+      const int jlo = max(lo, first) - first, jhi = min(hi, d.send_last[s] + 1) - first;
+      constexpr int V = 16 / sizeof(T);
+      const bool vec_ok = ((reinterpret_cast<uintptr_t>(dst + jlo) | reinterpret_cast<uintptr_t>(vec + first + jlo)) & 15u) == 0;
+      if (vec_ok) {
+        const int nv = (jhi - jlo) / V;
+        const int4 *src4 = reinterpret_cast<const int4 *>(vec + first + jlo);
+        int4 *dst4 = reinterpret_cast<int4 *>(dst + jlo);
+        for (int j = threadIdx.x; j < nv; j += blockDim.x) dst4[j] = src4[j];
+        for (int j = jlo + nv * V + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[first + j];
+      } else {
+        for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[first + j];
+      }
     } else {
+      int a = 0, b = cnt;
+      while (a < b) { const int m = (a + b) >> 1; if (list[m] < lo) a = m + 1; else b = m; }
+      const int jlo = a;
+      b = cnt;
+      while (a < b) { const int m = (a + b) >> 1; if (list[m] < hi) a = m + 1; else b = m; }
+      const int jhi = a;
       for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[list[j]];
     }
-    pushed = pushed || jhi > jlo;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
-    // cumulative fence: the barrier ordered the CTA's peer stores before this thread; only CTAs that pushed need it
-    if (pushed) __threadfence_system();
+    // number of CTAs that own a halo row: chunks [c * per, (c + 1) * per) meeting any [send_first, send_last]
+    int owners = 0, covered_to = -1;  // send ranges are visited in ascending order of their first row
+    int order[DIST_MAX_RANKS];
+    for (int s = 0; s < d.n_send; ++s) order[s] = s;
+    for (int i = 1; i < d.n_send; ++i)
+      for (int j = i; j > 0 && d.send_first[order[j]] < d.send_first[order[j - 1]]; --j) {
+        const int t = order[j]; order[j] = order[j - 1]; order[j - 1] = t;
+      }
+    for (int i = 0; i < d.n_send; ++i) {
+      const int s = order[i];
+      const int c0 = max(d.send_first[s] / per, covered_to + 1), c1 = d.send_last[s] / per;
+      if (c1 >= c0) { owners += c1 - c0 + 1; covered_to = c1; }
+    }
+    fence_acq_rel_sys();  // my peer stores (and, cumulatively, the CTA's) are performed before the ticket is visible
     const unsigned t = atomicAdd(&d.counters[2], 1u);
-    if (t == gridDim.x - 1) {
-      __threadfence_system();
+    if (t == static_cast<unsigned>(owners) - 1u) {
       d.counters[2] = 0u;
       const unsigned count = ++d.counters[1];
-      for (int s = 0; s < d.n_send; ++s) st_release_sys_u64(dist_flag(d.peer[d.send_peer[s]], d.rank), count);
+      fence_acq_rel_sys();  // the other owners' tickets (hence their stores) are ordered before the flags
+      for (int s = 0; s < d.n_send; ++s) st_sys_u64(dist_flag(d.peer[d.send_peer[s]], d.rank), count);
     }
   }
-  (void)s_flag;
 }
 
 // Called by thread 0 of a CTA before the CTA's first read of a ghost entry; follow with __syncthreads().

@@ -37,11 +37,18 @@ __device__ __forceinline__ unsigned long long lookback_exclusive(unsigned long l
   long long idx = static_cast<long long>(tile) - 1;
   while (true) {
     const long long t = idx - lane;
+    // wait only for the predecessors that matter: those nearer than the nearest one that already knows its inclusive
+    // prefix (a straggler further back than that is irrelevant -- waiting for all 32 made every tile pay for the
+    // slowest of its 32 predecessors)
     unsigned long long d;
-    do {
+    unsigned pmask;
+    while (true) {
       d = (t >= 0) ? ld_relaxed_u64(&desc[t]) : LB_PREFIX;  // before tile 0: a prefix of zero
-    } while (__any_sync(FULL, (d & LB_STATUS_MASK) == LB_INVALID));
-    const unsigned pmask = __ballot_sync(FULL, (d & LB_STATUS_MASK) == LB_PREFIX);
+      const unsigned inv = __ballot_sync(FULL, (d & LB_STATUS_MASK) == LB_INVALID);
+      pmask = __ballot_sync(FULL, (d & LB_STATUS_MASK) == LB_PREFIX);
+      const unsigned nearer = pmask ? ((1u << (__ffs(pmask) - 1)) - 1u) : FULL;
+      if ((inv & nearer) == 0u) break;
+    }
     unsigned long long v = d & LB_VALUE_MASK;
     if (pmask) {
       const unsigned first = __ffs(pmask) - 1;  // nearest predecessor that already knows its inclusive prefix

@@ -100,7 +100,7 @@ __host__ __device__ constexpr size_t rs_vals_offset() {
 }
 
 template <typename KeyT, typename ValT, int ITEMS>
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, 4)
 rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const ValT *__restrict__ vin,
                    ValT *__restrict__ vout, long long n, int shift, int nbits, int kind, int tw_in, int tw_out,
                    unsigned *__restrict__ ticket, unsigned *__restrict__ lookback /* tiles x 256 */,

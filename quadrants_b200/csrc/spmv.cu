@@ -36,7 +36,8 @@ __global__ void __launch_bounds__(SPMV_THREADS)
 spmv_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ indices, const T *__restrict__ values,
             const T *__restrict__ x, T *__restrict__ y, DistDev d) {
   extern __shared__ unsigned char smem_raw[];
-  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, x, y, nullptr, d);
+  NoSink sink;
+  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, x, y, sink, d);
 }
 
 template <typename T>
@@ -44,7 +45,8 @@ __global__ void __launch_bounds__(SPMV_THREADS)
 spmv_stream_kernel(const int *__restrict__ indptr, const int *__restrict__ indices, const T *__restrict__ values,
                    const T *__restrict__ x, T *__restrict__ y, SpmvPlanDev plan, DistDev d) {
   extern __shared__ unsigned char smem_raw[];
-  spmv_stream<T>(smem_raw, indptr, indices, values, x, y, nullptr, plan, d);
+  NoSink sink;
+  spmv_stream<T>(smem_raw, indptr, indices, values, x, y, sink, plan, d);
 }
 
 // out[0] = longest row; out[1] = the largest stage footprint (non-zeros, counted from the 16-byte-aligned start) of a

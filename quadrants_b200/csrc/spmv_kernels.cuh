@@ -53,13 +53,16 @@ inline int spmv_lanes_per_row(int64_t nnz, int rows) {
   return L;
 }
 
-template <typename T>
+// AUX: per-row side arrays (R <= 256 entries of T each) that travel with the block through the same TMA ring -- the
+// one-reduction CG kernel needs r[row] and D^-1[row] next to the product, and a plain load there would expose a full
+// DRAM latency per block
+template <typename T, int AUX = 0>
 __host__ __device__ constexpr size_t spmv_stage_bytes() {
-  return SPMV_CAP * sizeof(int) + SPMV_CAP * sizeof(T) + SPMV_PTR_SLOTS * sizeof(int);
+  return SPMV_CAP * sizeof(int) + SPMV_CAP * sizeof(T) + SPMV_PTR_SLOTS * sizeof(int) + AUX * SPMV_CONSUMERS * sizeof(T);
 }
-template <typename T>
+template <typename T, int AUX = 0>
 __host__ __device__ constexpr size_t spmv_smem_bytes() {
-  return SPMV_STAGES * spmv_stage_bytes<T>() + 2 * SPMV_STAGES * sizeof(unsigned long long) + 128 /*alignment slack*/;
+  return SPMV_STAGES * spmv_stage_bytes<T, AUX>() + 2 * SPMV_STAGES * sizeof(unsigned long long) + 128 /*alignment slack*/;
 }
 
 // ---- mbarrier / TMA bulk-copy primitives (sm_90+; SASS: SYNCS.*, UBLKCP) -------------------------------------------
@@ -109,14 +112,16 @@ struct SpmvStage {
   int *idx;
   T *val;
   int *ptr;
+  T *aux;  // AUX arrays of SPMV_CONSUMERS entries each
 };
-template <typename T>
+template <typename T, int AUX = 0>
 __device__ __forceinline__ SpmvStage<T> spmv_stage(unsigned char *base, int s) {
-  unsigned char *p = base + static_cast<size_t>(s) * spmv_stage_bytes<T>();
+  unsigned char *p = base + static_cast<size_t>(s) * spmv_stage_bytes<T, AUX>();
   SpmvStage<T> st;
   st.val = reinterpret_cast<T *>(p);
   st.idx = reinterpret_cast<int *>(p + SPMV_CAP * sizeof(T));
   st.ptr = reinterpret_cast<int *>(p + SPMV_CAP * sizeof(T) + SPMV_CAP * sizeof(int));
+  st.aux = reinterpret_cast<T *>(p + SPMV_CAP * sizeof(T) + SPMV_CAP * sizeof(int) + SPMV_PTR_SLOTS * sizeof(int));
   return st;
 }
 
@@ -135,21 +140,64 @@ struct SpmvPlanDev {
 
 __device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(SPMV_CONSUMERS) : "memory"); }
 
-// The whole SpMV of one persistent CTA.  LPR = lanes per row.  Returns, per consumer thread, the sum over the rows it
-// owned of xdot[row] * y[row] in double (0 when xdot == nullptr); producer-warp threads return 0.
+// ---- row sinks: what a kernel does with each finished y[row] besides storing it ----------------------------------------
+// `pre(row, stage aux, row in block)` is called before the row's products (its loads overlap them), `row(row, y, pre)` once per finished row by
+// the thread that stores it, `segment(row, partial)` for one piece of a long row of the stream path (linear sinks only).
+struct NoSink {
+  static constexpr int AUX = 0;
+  struct Pre {};
+  template <typename T> __device__ __forceinline__ Pre pre(int, const T *, int) const { return Pre{}; }
+  template <typename T> __device__ __forceinline__ void row(int, T, Pre) {}
+  template <typename T> __device__ __forceinline__ void segment(int, T) {}
+};
+// sum_i w[i] * y[i] in double (CG: p.Ap)
+template <typename T>
+struct DotSink {
+  const T *__restrict__ w;
+  double acc = 0.0;
+  static constexpr int AUX = 0;
+  struct Pre { T w; };
+  __device__ __forceinline__ Pre pre(int i, const T *, int) const { return Pre{w[i]}; }
+  __device__ __forceinline__ void row(int, T y, Pre q) { acc += static_cast<double>(q.w * y); }
+  __device__ __forceinline__ void segment(int i, T part) { acc += static_cast<double>(w[i] * part); }
+};
+// The seven inner products of the one-reduction CG iteration (cg.cu), t = A p, z = D^-1 r:
+//   v0 = p.t  v1 = t.z  v2 = t.D^-1 t  v3 = r.t  v4 = t.t  v5 = r.z  v6 = r.r      (all accumulated in double)
+template <typename T>
+struct MergedSink {
+  const T *__restrict__ p;
+  const T *__restrict__ r;
+  const T *__restrict__ dinv;
+  double v[7] = {0, 0, 0, 0, 0, 0, 0};
+  static constexpr int AUX = 2;  // r and D^-1 of the block's rows ride the TMA ring (aux_src); p[row] is an L1 hit
+  struct Pre { T p, r, d; };
+  __device__ __forceinline__ const T *aux_src(int k) const { return k == 0 ? r : dinv; }
+  __device__ __forceinline__ Pre pre(int i, const T *aux, int j) const {
+    return Pre{p[i], aux[j], aux[SPMV_CONSUMERS + j]};
+  }
+  __device__ __forceinline__ void row(int, T y, Pre q) {
+    const double t = static_cast<double>(y), pi = static_cast<double>(q.p), ri = static_cast<double>(q.r);
+    const double di = static_cast<double>(q.d), zi = static_cast<double>(static_cast<T>(q.d * q.r));
+    v[0] += pi * t; v[1] += t * zi; v[2] += t * di * t; v[3] += ri * t; v[4] += t * t; v[5] += ri * zi; v[6] += ri * ri;
+  }
+};
+
+// The whole SpMV of one persistent CTA.  LPR = lanes per row.  Every finished row is also handed to `sink` (per-thread
+// state: each consumer thread accumulates over the rows it stored; producer-warp threads never call it).
 // Multi-GPU (dist.world > 1): x = [owned | ghosts]; the ghosts are stored by the neighbour ranks.  Only row blocks
 // flagged in dist.ghost_blocks read a ghost, so the producer waits for the halo flags right before it hands the first
 // such block to the consumers (its acquire reaches them through the stage's mbarrier) and interior blocks start at
 // once.  The ghost segment begins on a 128-byte boundary, so no L1 line holds both owned and ghost entries.
 // `indptr`, `indices`, `values` must be readable 16 bytes past their ends (the matrices of this library carry 64).
-template <typename T, int LPR, bool ROW_MAJOR_ORDER>
-__device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int rows, const int *__restrict__ indptr,
-                                                  const int *__restrict__ indices, const T *__restrict__ values,
-                                                  const T *__restrict__ x, T *__restrict__ y,
-                                                  const T *__restrict__ xdot, const DistDev &dist) {
+template <typename T, int LPR, bool ROW_MAJOR_ORDER, typename Sink>
+__device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int rows, const int *__restrict__ indptr,
+                                                const int *__restrict__ indices, const T *__restrict__ values,
+                                                const T *__restrict__ x, T *__restrict__ y, Sink &sink,
+                                                const DistDev &dist) {
   constexpr int R = SPMV_CONSUMERS / LPR;  // rows per block
+  constexpr int AUX = Sink::AUX;
   unsigned char *base = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
-  auto *full = reinterpret_cast<unsigned long long *>(base + SPMV_STAGES * spmv_stage_bytes<T>());
+  auto *full = reinterpret_cast<unsigned long long *>(base + SPMV_STAGES * spmv_stage_bytes<T, AUX>());
   auto *empty = full + SPMV_STAGES;
   const int t = threadIdx.x;
   if (t == 0) {
@@ -178,7 +226,6 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
   const int n_ghost_blk = ordered ? nblk - n_first : 0;
   const int n_tail = n_ghost_blk > static_cast<int>(blockIdx.x) ? (n_ghost_blk - 1 - blockIdx.x) / gridDim.x + 1 : 0;
   const int n_items = n_run + n_tail;
-  double dot = 0.0;
 
   if (t >= SPMV_CONSUMERS) {
     // ---- producer: one thread ----
@@ -202,20 +249,27 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
         s_next = e;
         blk_prev = blk;
         mbar_wait(&empty[stage], phase ^ 1u);
-        const SpmvStage<T> st = spmv_stage<T>(base, stage);
+        const SpmvStage<T> st = spmv_stage<T, AUX>(base, stage);
         if (ordered) st.ptr[SPMV_DESC_SLOT] = blk;  // published by the arrive below (release)
         const int a0 = s & ~3;
         const int cnt = e - a0;
         const unsigned ptr_bytes = static_cast<unsigned>(((nr + 1) * 4 + 15) & ~15);
+        const unsigned aux_bytes = static_cast<unsigned>((nr * static_cast<int>(sizeof(T)) + 15) & ~15);
+        if constexpr (AUX > 0) {
+          // (expect_tx may follow the copies it accounts for: the phase cannot complete before this thread's arrive)
+#pragma unroll
+          for (int k = 0; k < AUX; ++k)
+            tma_bulk_g2s(st.aux + k * SPMV_CONSUMERS, sink.aux_src(k) + r0, aux_bytes, &full[stage], pol);
+        }
         if (cnt <= SPMV_CAP && cnt > 0) {
           const unsigned ib = static_cast<unsigned>((cnt * 4 + 15) & ~15);
           const unsigned vb = static_cast<unsigned>((cnt * static_cast<int>(sizeof(T)) + 15) & ~15);
-          mbar_expect_tx(&full[stage], ptr_bytes + ib + vb);
+          mbar_expect_tx(&full[stage], ptr_bytes + ib + vb + AUX * aux_bytes);
           tma_bulk_g2s(st.ptr, indptr + r0, ptr_bytes, &full[stage], pol);
           tma_bulk_g2s(st.idx, indices + a0, ib, &full[stage], pol);
           tma_bulk_g2s(st.val, values + a0, vb, &full[stage], pol);
         } else {
-          mbar_expect_tx(&full[stage], ptr_bytes);
+          mbar_expect_tx(&full[stage], ptr_bytes + AUX * aux_bytes);
           tma_bulk_g2s(st.ptr, indptr + r0, ptr_bytes, &full[stage], pol);
         }
       }
@@ -227,7 +281,7 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
     for (int it = 0; it < n_items; ++it) {
       const int stage = it % SPMV_STAGES;
       const unsigned phase = (it / SPMV_STAGES) & 1;
-      const SpmvStage<T> st = spmv_stage<T>(base, stage);
+      const SpmvStage<T> st = spmv_stage<T, AUX>(base, stage);
       mbar_wait(&full[stage], phase);
       const int blk = ordered ? st.ptr[SPMV_DESC_SLOT] : blk0 + it;
       const int r0 = blk * R;
@@ -236,7 +290,9 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
       const int a0 = s & ~3;
       if (e - a0 <= SPMV_CAP) {
         T result = T(0);
+        typename Sink::Pre pre{};
         if (row_in_blk < nr) {
+          if (q == 0) pre = sink.pre(r0 + row_in_blk, st.aux, row_in_blk);
           const int lo = st.ptr[row_in_blk] - a0, hi = st.ptr[row_in_blk + 1] - a0;
           if (LPR == 1) {
             T acc_a = T(0), acc_b = T(0);
@@ -289,7 +345,7 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
         }
         if (row_in_blk < nr && q == 0) {
           y[r0 + row_in_blk] = result;
-          if (xdot) dot += static_cast<double>(xdot[r0 + row_in_blk] * result);
+          sink.row(r0 + row_in_blk, result, pre);
         }
       } else {
         // ---- oversized block: warp per row straight from global memory ----
@@ -300,7 +356,7 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
           acc = warp_sum(acc);
           if (lane == 0) {
             y[r0 + r] = acc;
-            if (xdot) dot += static_cast<double>(xdot[r0 + r] * acc);
+            sink.row(r0 + r, acc, sink.pre(r0 + r, st.aux, r));
           }
         }
       }
@@ -308,7 +364,6 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
       if (lane == 0) mbar_arrive(&empty[stage]);
     }
   }
-  return dot;
 }
 
 // ---- stream path ---------------------------------------------------------------------------------------------------------
@@ -316,12 +371,12 @@ __device__ __forceinline__ double spmv_persistent(unsigned char *smem_raw, int r
 // products val[k] * x[idx[k]] in place in shared memory -- perfectly balanced whatever the row lengths --, (2) after a
 // consumer-only barrier the rows of the block are summed from shared memory, one row per thread (many short rows) or
 // one row per warp (few long rows); a SEGMENT block reduces to one partial sum.  Not bit-identical to Eigen's order
-// (held to the 1e-5 / 1e-12 per-row tolerance).  Returns the per-thread part of sum xdot[row] * y[row] like above.
-template <typename T>
-__device__ __forceinline__ double spmv_stream(unsigned char *smem_raw, const int *__restrict__ indptr,
-                                              const int *__restrict__ indices, const T *__restrict__ values,
-                                              const T *__restrict__ x, T *__restrict__ y, const T *__restrict__ xdot,
-                                              const SpmvPlanDev &plan, const DistDev &dist) {
+// (held to the 1e-5 / 1e-12 per-row tolerance).
+template <typename T, typename Sink>
+__device__ __forceinline__ void spmv_stream(unsigned char *smem_raw, const int *__restrict__ indptr,
+                                            const int *__restrict__ indices, const T *__restrict__ values,
+                                            const T *__restrict__ x, T *__restrict__ y, Sink &sink,
+                                            const SpmvPlanDev &plan, const DistDev &dist) {
   unsigned char *base = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
   auto *full = reinterpret_cast<unsigned long long *>(base + SPMV_STREAM_STAGES * spmv_stage_bytes<T>());
   auto *empty = full + SPMV_STREAM_STAGES;
@@ -342,7 +397,6 @@ __device__ __forceinline__ double spmv_stream(unsigned char *smem_raw, const int
   const int per_cta = (plan.nblk + gridDim.x - 1) / gridDim.x;
   const int blk0 = blockIdx.x * per_cta;
   const int blk1 = min(plan.nblk, blk0 + per_cta);
-  double dot = 0.0;
 
   if (t >= SPMV_CONSUMERS) {
     if (t == SPMV_CONSUMERS && blk0 < blk1) {
@@ -412,7 +466,7 @@ __device__ __forceinline__ double spmv_stream(unsigned char *smem_raw, const int
             T acc = T(0);
             for (int k = b; k < e; ++k) acc += st.val[k];
             y[d.x + t] = acc;
-            if (xdot) dot += static_cast<double>(xdot[d.x + t] * acc);
+            sink.row(d.x + t, acc, sink.pre(d.x + t, static_cast<const T *>(nullptr), 0));
           }
         } else {
           for (int r = warp; r < nr; r += SPMV_CONSUMERS / 32) {
@@ -422,7 +476,7 @@ __device__ __forceinline__ double spmv_stream(unsigned char *smem_raw, const int
             acc = warp_sum(acc);
             if (lane == 0) {
               y[d.x + r] = acc;
-              if (xdot) dot += static_cast<double>(xdot[d.x + r] * acc);
+              sink.row(d.x + r, acc, sink.pre(d.x + r, static_cast<const T *>(nullptr), 0));
             }
           }
         }
@@ -438,7 +492,7 @@ __device__ __forceinline__ double spmv_stream(unsigned char *smem_raw, const int
           T tot = T(0);
           for (int w = 0; w < SPMV_CONSUMERS / 32; ++w) tot += red[w];
           static_cast<T *>(plan.partials)[-d.y - 1] = tot;
-          if (xdot) dot += static_cast<double>(xdot[d.x] * tot);
+          sink.segment(d.x, tot);
         }
       }
       // the stage was written through the generic proxy (products); order that before the next TMA fill
@@ -468,7 +522,6 @@ __device__ __forceinline__ double spmv_stream(unsigned char *smem_raw, const int
       }
     }
   }
-  return dot;
 }
 
 }  // namespace qdsp
