@@ -28,6 +28,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <utility>
 #include <vector>
 
 #include "dist.hpp"
@@ -37,6 +38,16 @@
 namespace qdsp {
 
 constexpr int CG_THREADS = 256;
+
+// Programmatic dependent launch: every kernel of the iteration loop is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, lets its successor be scheduled as soon as all of its own CTAs
+// are running (launch_dependents) and waits for its predecessor's completion + memory flush before touching anything
+// (wait).  The successor's launch latency and prologue then overlap this kernel's tail; ordering is unchanged.
+// Both instructions are no-ops in a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_wait_then_release() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
 
 struct CgScalars {
   double pAp, abs_new, abs_old, res2, rhs2, thr;
@@ -264,6 +275,7 @@ cg_spmv_dot_kernel(int rows, const int *__restrict__ indptr, const int *__restri
   extern __shared__ unsigned char smem_raw[];
   __shared__ double s_red[16];
   __shared__ unsigned s_flag;
+  pdl_wait_then_release();
   if (sc->done) {
     // the deferred x += alpha p of the final iteration has been applied by the direction kernel before this launch:
     // retire alpha so that a replayed direction kernel is a no-op
@@ -286,6 +298,7 @@ cg_spmv_dot_stream_kernel(const int *__restrict__ indptr, const int *__restrict_
   extern __shared__ unsigned char smem_raw[];
   __shared__ double s_red[16];
   __shared__ unsigned s_flag;
+  pdl_wait_then_release();
   if (sc->done) {
     if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;
     return;
@@ -335,6 +348,7 @@ cg_residual_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv,
                    CgScalars *__restrict__ sc, double *__restrict__ partials, DistDev d, int use_nccl) {
   __shared__ double s_red[2 * 16];
   __shared__ unsigned s_flag;
+  pdl_wait_then_release();
   if (sc->done) return;
   T s_rr = T(0), s_rz = T(0);
   cg_residual_body<T>(n, tmp, dinv, r, static_cast<T>(sc->alpha), s_rr, s_rz);
@@ -374,6 +388,7 @@ template <typename T>
 __global__ void __launch_bounds__(CG_THREADS)
 cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, T *__restrict__ p, T *__restrict__ x,
                     const CgScalars *__restrict__ sc, DistDev d) {
+  pdl_wait_then_release();
   const int done = sc->done;
   if (done == 3) return;
   if (done != 0 && sc->alpha == 0.0) return;  // replayed after the end of the solve: x already has its last update
@@ -398,6 +413,7 @@ cg_spmv_merged_kernel(int rows, const int *__restrict__ indptr, const int *__res
   extern __shared__ unsigned char smem_raw[];
   __shared__ double s_red[7 * 16];
   __shared__ unsigned s_flag;
+  pdl_wait_then_release();
   if (sc->done) {
     if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;  // see cg_spmv_dot_kernel
     return;
@@ -415,6 +431,7 @@ template <typename T>
 __global__ void __launch_bounds__(CG_THREADS)
 cg_update_merged_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv, T *__restrict__ r,
                         T *__restrict__ p, T *__restrict__ x, const CgScalars *__restrict__ sc, DistDev d) {
+  pdl_wait_then_release();
   const int done = sc->done;
   if (done == 3) return;
   if (done != 0 && sc->alpha == 0.0) return;  // replayed after the end of the solve
@@ -480,29 +497,47 @@ struct CgSolver::Impl {
 
 namespace {
 
+// Launch with the programmatic-stream-serialization attribute (see pdl_wait_then_release) when QDSP_PDL=1.  Off by
+// default: measured on B200 it is neutral on small systems and 7 % SLOWER at 256^3 (337 vs 315 us per iteration) --
+// the early-scheduled successor competes with the tail of the running kernel.
+bool pdl_enabled() {
+  static const bool on = [] { const char *e = std::getenv("QDSP_PDL"); return e && e[0] == '1'; }();
+  return on;
+}
+template <typename... KArgs, typename... Args>
+void launch_pdl(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t stream, Args &&...args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(grid));
+  cfg.blockDim = dim3(static_cast<unsigned>(block));
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  QDSP_CUDA(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(std::forward<Args>(args))...));
+  count_launch();
+}
+
 template <typename T, int LPR>
 void launch_spmv_dot(CgSolver::Impl &I) {
   const CsrMatrix &A = I.A;
   auto *sc = I.scalars.get<CgScalars>();
   const size_t smem = spmv_smem_bytes<T>();
   if (A.row_major_order && LPR == 1)
-    cg_spmv_dot_kernel<T, LPR, true><<<I.spmv_grid, SPMV_THREADS, smem, I.stream>>>(
-        I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+    launch_pdl(cg_spmv_dot_kernel<T, LPR, true>, I.spmv_grid, SPMV_THREADS, smem, I.stream, I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
         sc, I.partials.get<double>(), I.dev(), I.use_nccl);
   else
-    cg_spmv_dot_kernel<T, LPR, false><<<I.spmv_grid, SPMV_THREADS, smem, I.stream>>>(
-        I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+    launch_pdl(cg_spmv_dot_kernel<T, LPR, false>, I.spmv_grid, SPMV_THREADS, smem, I.stream, I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
         sc, I.partials.get<double>(), I.dev(), I.use_nccl);
-  QDSP_LAUNCH_CHECK();
 }
 
 template <typename T>
 void launch_spmv_dot_stream(CgSolver::Impl &I) {
   const CsrMatrix &A = I.A;
-  cg_spmv_dot_stream_kernel<T><<<I.spmv_grid, SPMV_THREADS, spmv_stream_smem_bytes<T>(), I.stream>>>(
-      A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+  launch_pdl(cg_spmv_dot_stream_kernel<T>, I.spmv_grid, SPMV_THREADS, spmv_stream_smem_bytes<T>(), I.stream, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
       spmv_plan_dev(A), I.scalars.get<CgScalars>(), I.partials.get<double>(), I.dev(), I.use_nccl);
-  QDSP_LAUNCH_CHECK();
 }
 
 template <typename T>
@@ -538,21 +573,18 @@ template <typename T, int LPR>
 void launch_spmv_merged(CgSolver::Impl &I) {
   const CsrMatrix &A = I.A;
   auto *sc = I.scalars.get<CgScalars>();
-  const size_t smem = spmv_smem_bytes<T, 2>();
+  const size_t smem = spmv_smem_bytes<T, 2, SPMV_CAP_MERGED>();
   if (A.row_major_order && LPR == 1)
-    cg_spmv_merged_kernel<T, LPR, true><<<I.spmv_grid, SPMV_THREADS, smem, I.stream>>>(
-        I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+    launch_pdl(cg_spmv_merged_kernel<T, LPR, true>, I.spmv_grid, SPMV_THREADS, smem, I.stream, I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
         I.r.get<T>(), I.dinv.get<T>(), sc, I.partials.get<double>(), I.dev(), I.use_nccl);
   else
-    cg_spmv_merged_kernel<T, LPR, false><<<I.spmv_grid, SPMV_THREADS, smem, I.stream>>>(
-        I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+    launch_pdl(cg_spmv_merged_kernel<T, LPR, false>, I.spmv_grid, SPMV_THREADS, smem, I.stream, I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
         I.r.get<T>(), I.dinv.get<T>(), sc, I.partials.get<double>(), I.dev(), I.use_nccl);
-  QDSP_LAUNCH_CHECK();
 }
 
 template <typename T, int LPR>
 int spmv_merged_occupancy() {
-  const size_t smem = spmv_smem_bytes<T, 2>();
+  const size_t smem = spmv_smem_bytes<T, 2, SPMV_CAP_MERGED>();
   int occ = 0, occ2 = 0;
   QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_merged_kernel<T, LPR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_merged_kernel<T, LPR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
@@ -590,18 +622,15 @@ void launch_iteration(CgSolver::Impl &I, T *x) {
     QDSP_LPR_SWITCH(I.lpr, QDSP_CALL)
 #undef QDSP_CALL
     if (I.use_nccl) nccl_reduce_then<T>(I, 7, 3);
-    cg_update_merged_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(),
+    launch_pdl(cg_update_merged_kernel<T>, I.vec_grid, CG_THREADS, 0, I.stream, n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(),
                                                                          static_cast<T *>(I.p), x, sc, I.dev());
-    QDSP_LAUNCH_CHECK();
     return;
   }
   launch_spmv_dot_any<T>(I);
   if (I.use_nccl) nccl_reduce_then<T>(I, 1, 1);
-  cg_residual_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(), sc, part, I.dev(), I.use_nccl);
-  QDSP_LAUNCH_CHECK();
+  launch_pdl(cg_residual_kernel<T>, I.vec_grid, CG_THREADS, 0, I.stream, n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(), sc, part, I.dev(), I.use_nccl);
   if (I.use_nccl) nccl_reduce_then<T>(I, 2, 2);
-  cg_direction_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, I.r.get<T>(), I.dinv.get<T>(), static_cast<T *>(I.p), x, sc, I.dev());
-  QDSP_LAUNCH_CHECK();
+  launch_pdl(cg_direction_kernel<T>, I.vec_grid, CG_THREADS, 0, I.stream, n, I.r.get<T>(), I.dinv.get<T>(), static_cast<T *>(I.p), x, sc, I.dev());
 }
 
 int kernels_per_iteration(const CgSolver::Impl &I) { return I.merged ? (I.use_nccl ? 3 : 2) : (I.use_nccl ? 5 : 3); }
@@ -800,13 +829,14 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
     I.spmv_grid = std::max(1, std::min(ceil_div(A.rows, R), device_props().sm_count * occ));
   }
   I.vec_grid = std::max(1, std::min(ceil_div(A.rows, 1024), device_props().sm_count * 8));
-  // variant: "merged" (one reduction per iteration) by default for the multi-GPU solver, "classic" (Eigen's two
-  // reductions) on one GPU; QDSP_CG_VARIANT=classic|merged overrides.  The merged sums are quadratic in A p, so the
-  // stream path (long rows in segments) stays classic.
+  // variant: "classic" (Eigen's two reductions per iteration) unless QDSP_CG_VARIANT=merged asks for the one-reduction
+  // form.  Measured (profiles/r01h_8gpu_trace.txt): the merged SpMV kernel needs 72 registers -> 3 CTAs per SM and is
+  // 25 % slower than the classic one, which costs more than the saved all-reduce even at 8 ranks; kept as an option.
+  // The merged sums are quadratic in A p, so the stream path (long rows in segments) is always classic.
   {
     const char *e = std::getenv("QDSP_CG_VARIANT");
-    const bool want = e ? std::string(e) == "merged" : (dist != nullptr && dist->world() > 1);
-    I.merged = want && A.spmv_mode == 1;
+    const bool want = e && std::string(e) == "merged";
+    I.merged = want && A.spmv_mode == 1 && A.spmv_max_block_nnz <= SPMV_CAP_MERGED;
     if (I.merged) {
       int mocc = 1;
 #define QDSP_CALL(L) mocc = (A.dtype == QDSP_F32) ? spmv_merged_occupancy<float, L>() : spmv_merged_occupancy<double, L>()

@@ -126,8 +126,10 @@ void DistContext::localize(CsrMatrix &A, const int64_t *row_offsets, cudaStream_
     QDSP_CUDA(cudaMemcpyAsync(block_order_.get(), order.data(), sizeof(int32_t) * order.size(), cudaMemcpyHostToDevice, stream));
     QDSP_CUDA(cudaStreamSynchronize(stream));
     dev_.block_order = block_order_.get<int>();
-    if (const char *e = std::getenv("QDSP_HALO_ORDER"))  // "0": keep the natural block order (measurement aid)
-      if (e[0] == '0') dev_.block_order = nullptr;
+    // used only when QDSP_HALO_ORDER=1: with the halo signalled early by its owner CTAs the natural order measured
+    // equal or slightly faster at 2, 4 and 8 ranks
+    const char *e = std::getenv("QDSP_HALO_ORDER");
+    if (!(e && e[0] == '1')) dev_.block_order = nullptr;
   }
   const size_t sv = A.value_bytes();
   comm_.alloc(DIST_VECTOR_OFF + sv * (static_cast<size_t>(plan_.ghost_base) + n_ghost()) + 256);

@@ -38,6 +38,7 @@ class CsrMatrix {
   // spmv_lpr == 1), 2 = stream path over nnz-balanced plan blocks (irregular matrices), 0 = not planned yet
   mutable int spmv_mode = 0;
   mutable int spmv_max_row_len = 0;
+  mutable int spmv_max_block_nnz = 0;  // largest stage footprint of a uniform row block (spmv_prepare)
   mutable DeviceBuffer spmv_plan_blocks, spmv_plan_long, spmv_plan_partials, spmv_plan_ticket;
   mutable int spmv_plan_nblk = 0, spmv_plan_nlong = 0;
 

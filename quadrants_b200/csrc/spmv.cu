@@ -116,6 +116,7 @@ void spmv_prepare(const CsrMatrix &A, cudaStream_t stream) {
   QDSP_CUDA(cudaMemcpyAsync(stats, mx.get(), 2 * sizeof(int), cudaMemcpyDeviceToHost, stream));
   QDSP_CUDA(cudaStreamSynchronize(stream));
   A.spmv_max_row_len = stats[0];
+  A.spmv_max_block_nnz = stats[1];
   const char *force = std::getenv("QDSP_SPMV_PATH");  // "uniform" | "stream": testing aid
   const bool uniform = force ? std::string(force) != "stream" : stats[1] <= SPMV_CAP;
   A.spmv_lpr = L;

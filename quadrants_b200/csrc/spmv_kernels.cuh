@@ -56,13 +56,15 @@ inline int spmv_lanes_per_row(int64_t nnz, int rows) {
 // AUX: per-row side arrays (R <= 256 entries of T each) that travel with the block through the same TMA ring -- the
 // one-reduction CG kernel needs r[row] and D^-1[row] next to the product, and a plain load there would expose a full
 // DRAM latency per block
-template <typename T, int AUX = 0>
+// CAP: non-zeros per stage.  The merged CG kernel trades 192 of them for its AUX arrays so that four CTAs still fit an SM.
+constexpr int SPMV_CAP_MERGED = 1856;
+template <typename T, int AUX = 0, int CAP = SPMV_CAP>
 __host__ __device__ constexpr size_t spmv_stage_bytes() {
-  return SPMV_CAP * sizeof(int) + SPMV_CAP * sizeof(T) + SPMV_PTR_SLOTS * sizeof(int) + AUX * SPMV_CONSUMERS * sizeof(T);
+  return CAP * sizeof(int) + CAP * sizeof(T) + SPMV_PTR_SLOTS * sizeof(int) + AUX * SPMV_CONSUMERS * sizeof(T);
 }
-template <typename T, int AUX = 0>
+template <typename T, int AUX = 0, int CAP = SPMV_CAP>
 __host__ __device__ constexpr size_t spmv_smem_bytes() {
-  return SPMV_STAGES * spmv_stage_bytes<T, AUX>() + 2 * SPMV_STAGES * sizeof(unsigned long long) + 128 /*alignment slack*/;
+  return SPMV_STAGES * spmv_stage_bytes<T, AUX, CAP>() + 2 * SPMV_STAGES * sizeof(unsigned long long) + 128 /*alignment slack*/;
 }
 
 // ---- mbarrier / TMA bulk-copy primitives (sm_90+; SASS: SYNCS.*, UBLKCP) -------------------------------------------
@@ -114,14 +116,14 @@ struct SpmvStage {
   int *ptr;
   T *aux;  // AUX arrays of SPMV_CONSUMERS entries each
 };
-template <typename T, int AUX = 0>
+template <typename T, int AUX = 0, int CAP = SPMV_CAP>
 __device__ __forceinline__ SpmvStage<T> spmv_stage(unsigned char *base, int s) {
-  unsigned char *p = base + static_cast<size_t>(s) * spmv_stage_bytes<T, AUX>();
+  unsigned char *p = base + static_cast<size_t>(s) * spmv_stage_bytes<T, AUX, CAP>();
   SpmvStage<T> st;
   st.val = reinterpret_cast<T *>(p);
-  st.idx = reinterpret_cast<int *>(p + SPMV_CAP * sizeof(T));
-  st.ptr = reinterpret_cast<int *>(p + SPMV_CAP * sizeof(T) + SPMV_CAP * sizeof(int));
-  st.aux = reinterpret_cast<T *>(p + SPMV_CAP * sizeof(T) + SPMV_CAP * sizeof(int) + SPMV_PTR_SLOTS * sizeof(int));
+  st.idx = reinterpret_cast<int *>(p + CAP * sizeof(T));
+  st.ptr = reinterpret_cast<int *>(p + CAP * sizeof(T) + CAP * sizeof(int));
+  st.aux = reinterpret_cast<T *>(p + CAP * sizeof(T) + CAP * sizeof(int) + SPMV_PTR_SLOTS * sizeof(int));
   return st;
 }
 
@@ -145,6 +147,7 @@ __device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" 
 // the thread that stores it, `segment(row, partial)` for one piece of a long row of the stream path (linear sinks only).
 struct NoSink {
   static constexpr int AUX = 0;
+  static constexpr int CAP = SPMV_CAP;
   struct Pre {};
   template <typename T> __device__ __forceinline__ Pre pre(int, const T *, int) const { return Pre{}; }
   template <typename T> __device__ __forceinline__ void row(int, T, Pre) {}
@@ -156,6 +159,7 @@ struct DotSink {
   const T *__restrict__ w;
   double acc = 0.0;
   static constexpr int AUX = 0;
+  static constexpr int CAP = SPMV_CAP;
   struct Pre { T w; };
   __device__ __forceinline__ Pre pre(int i, const T *, int) const { return Pre{w[i]}; }
   __device__ __forceinline__ void row(int, T y, Pre q) { acc += static_cast<double>(q.w * y); }
@@ -170,6 +174,7 @@ struct MergedSink {
   const T *__restrict__ dinv;
   double v[7] = {0, 0, 0, 0, 0, 0, 0};
   static constexpr int AUX = 2;  // r and D^-1 of the block's rows ride the TMA ring (aux_src); p[row] is an L1 hit
+  static constexpr int CAP = SPMV_CAP_MERGED;
   struct Pre { T p, r, d; };
   __device__ __forceinline__ const T *aux_src(int k) const { return k == 0 ? r : dinv; }
   __device__ __forceinline__ Pre pre(int i, const T *aux, int j) const {
@@ -196,8 +201,9 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
                                                 const DistDev &dist) {
   constexpr int R = SPMV_CONSUMERS / LPR;  // rows per block
   constexpr int AUX = Sink::AUX;
+  constexpr int CAP = Sink::CAP;
   unsigned char *base = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
-  auto *full = reinterpret_cast<unsigned long long *>(base + SPMV_STAGES * spmv_stage_bytes<T, AUX>());
+  auto *full = reinterpret_cast<unsigned long long *>(base + SPMV_STAGES * spmv_stage_bytes<T, AUX, CAP>());
   auto *empty = full + SPMV_STAGES;
   const int t = threadIdx.x;
   if (t == 0) {
@@ -249,7 +255,7 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
         s_next = e;
         blk_prev = blk;
         mbar_wait(&empty[stage], phase ^ 1u);
-        const SpmvStage<T> st = spmv_stage<T, AUX>(base, stage);
+        const SpmvStage<T> st = spmv_stage<T, AUX, CAP>(base, stage);
         if (ordered) st.ptr[SPMV_DESC_SLOT] = blk;  // published by the arrive below (release)
         const int a0 = s & ~3;
         const int cnt = e - a0;
@@ -261,7 +267,7 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
           for (int k = 0; k < AUX; ++k)
             tma_bulk_g2s(st.aux + k * SPMV_CONSUMERS, sink.aux_src(k) + r0, aux_bytes, &full[stage], pol);
         }
-        if (cnt <= SPMV_CAP && cnt > 0) {
+        if (cnt <= CAP && cnt > 0) {
           const unsigned ib = static_cast<unsigned>((cnt * 4 + 15) & ~15);
           const unsigned vb = static_cast<unsigned>((cnt * static_cast<int>(sizeof(T)) + 15) & ~15);
           mbar_expect_tx(&full[stage], ptr_bytes + ib + vb + AUX * aux_bytes);
@@ -281,14 +287,14 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
     for (int it = 0; it < n_items; ++it) {
       const int stage = it % SPMV_STAGES;
       const unsigned phase = (it / SPMV_STAGES) & 1;
-      const SpmvStage<T> st = spmv_stage<T, AUX>(base, stage);
+      const SpmvStage<T> st = spmv_stage<T, AUX, CAP>(base, stage);
       mbar_wait(&full[stage], phase);
       const int blk = ordered ? st.ptr[SPMV_DESC_SLOT] : blk0 + it;
       const int r0 = blk * R;
       const int nr = min(R, rows - r0);
       const int s = st.ptr[0], e = st.ptr[nr];
       const int a0 = s & ~3;
-      if (e - a0 <= SPMV_CAP) {
+      if (e - a0 <= CAP) {
         T result = T(0);
         typename Sink::Pre pre{};
         if (row_in_blk < nr) {
