@@ -145,7 +145,8 @@ int qdsp_cg_destroy(qdsp_cg_t s);
  *                           peer-visible buffer that holds the SpMV operand [owned | ghosts];
  *   qdsp_dist_ghost_ids     the ghost ids, grouped by owner (owner_offsets): the caller ships each group to its owner
  *                           (any transport; quadrants_b200.distributed uses torch.distributed), which registers it with
- *   qdsp_dist_set_send_list (dst_offset = the requester's ghost_base + its owner_offsets[owner]);
+ *   qdsp_dist_set_send_list (dst_offset = the requester's ghost_base + its owner_offsets[owner]; dst_offset_z likewise
+ *                           from the requester's zbase);
  *   qdsp_dist_comm_handle / qdsp_dist_attach   exchange and map the CUDA IPC handles of the buffers (NVLink P2P).
  * After that qdsp_dist_spmv and a solver from qdsp_cg_create_dist run with the halo of x pushed by peer stores and the
  * CG dot products all-reduced inside the kernels over peer memory (QDSP_ALLREDUCE=nccl: by ncclAllReduce instead, after
@@ -159,7 +160,11 @@ int qdsp_dist_destroy(qdsp_dist_t d);
 int qdsp_dist_localize(qdsp_dist_t d, qdsp_csr_t m, const int64_t *row_offsets, void *stream, int *n_local,
                        int *ghost_base, int *n_ghost, int32_t *owner_offsets_out /* world + 1 */);
 int qdsp_dist_ghost_ids(qdsp_dist_t d, const int32_t **host_ids);
-int qdsp_dist_set_send_list(qdsp_dist_t d, int peer, const int32_t *global_ids, int count, int dst_offset);
+/* dst_offset_z: where the same rows go in the requester's SECOND ghost segment (it starts at the requester's
+ * zbase = ghost_base + n_ghost rounded up to a multiple of 32 elements); CG sends z = D^-1 r through it one kernel ahead
+ * of need and every rank updates its own ghost copies of p.  Pass -1 to keep the plain p halo. */
+int qdsp_dist_set_send_list(qdsp_dist_t d, int peer, const int32_t *global_ids, int count, int dst_offset,
+                            int dst_offset_z);
 int qdsp_dist_comm_handle(qdsp_dist_t d, void *out64);
 int qdsp_dist_attach(qdsp_dist_t d, const void *handles /* world x 64 bytes in rank order */);
 int qdsp_dist_nccl_unique_id(void *out128);

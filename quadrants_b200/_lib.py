@@ -59,7 +59,7 @@ SIGNATURES = {
     "qdsp_dist_destroy": (_i, [_vp]),
     "qdsp_dist_localize": (_i, [_vp, _vp, _vp, _vp, _P(_i), _P(_i), _P(_i), _vp]),
     "qdsp_dist_ghost_ids": (_i, [_vp, _P(_vp)]),
-    "qdsp_dist_set_send_list": (_i, [_vp, _i, _vp, _i, _i]),
+    "qdsp_dist_set_send_list": (_i, [_vp, _i, _vp, _i, _i, _i]),
     "qdsp_dist_comm_handle": (_i, [_vp, _vp]),
     "qdsp_dist_attach": (_i, [_vp, _vp]),
     "qdsp_dist_nccl_unique_id": (_i, [_vp]),

@@ -283,8 +283,9 @@ int qdsp_dist_localize(qdsp_dist_t d, qdsp_csr_t m, const int64_t *row_offsets, 
 int qdsp_dist_ghost_ids(qdsp_dist_t d, const int32_t **host_ids) {
   return guarded([&] { NOT_NULL(d); NOT_NULL(host_ids); *host_ids = d->impl->plan().ghost_ids.data(); });
 }
-int qdsp_dist_set_send_list(qdsp_dist_t d, int peer, const int32_t *global_ids, int count, int dst_offset) {
-  return guarded([&] { NOT_NULL(d); d->impl->set_send_list(peer, global_ids, count, dst_offset); });
+int qdsp_dist_set_send_list(qdsp_dist_t d, int peer, const int32_t *global_ids, int count, int dst_offset,
+                            int dst_offset_z) {
+  return guarded([&] { NOT_NULL(d); d->impl->set_send_list(peer, global_ids, count, dst_offset, dst_offset_z); });
 }
 int qdsp_dist_comm_handle(qdsp_dist_t d, void *out64) {
   return guarded([&] { NOT_NULL(d); NOT_NULL(out64); d->impl->comm_handle(out64); });

@@ -260,10 +260,19 @@ cg_init_kernel(int n, const T *__restrict__ b, const T *__restrict__ tmp, const 
     s1 = fma_t(ri, ri, s1);
     s2 = fma_t(ri, pi, s2);
   }
-  dist_halo_push_signal<T>(d, p, lo, hi, per);
   double v[3] = {static_cast<double>(s0), static_cast<double>(s1), static_cast<double>(s2)};
   if (grid_sum_last_block<3>(v, partials, &sc->ticket[0], s_red, &s_flag))
     cg_reduce_and_finish<3>(v, d, use_nccl, sc, [&](const double (&t)[3]) { cg_finish_init<T>(sc, t); });
+}
+
+// Multi-GPU: the halo of the first direction, sent by its own kernel AFTER cg_init_kernel.  The all-reduce that ends
+// cg_init_kernel is a rendezvous -- a rank gets past it only when every rank has finished the kernels of its previous
+// solve -- so these stores cannot land in a ghost segment that a slower neighbour is still reading or updating.
+template <typename T>
+__global__ void __launch_bounds__(CG_THREADS) cg_push_direction_kernel(int n, const T *__restrict__ p, DistDev d) {
+  int lo, hi, per;
+  cta_chunk(n, lo, hi, per);
+  dist_halo_push_signal<T>(d, p, lo, hi, per);
 }
 
 // ---- iteration kernels --------------------------------------------------------------------------------------------------
@@ -314,13 +323,13 @@ template <typename T> struct Vec4T;
 template <> struct Vec4T<float> { using type = float4; };
 template <> struct Vec4T<double> { using type = double4; };
 
-// r -= alpha tmp over the whole vector (grid-stride), accumulating |r|^2 and r.(D^-1 r)
+// r -= alpha tmp on this CTA's chunk [lo, hi), accumulating |r|^2 and r.(D^-1 r)
 template <typename T>
-__device__ __forceinline__ void cg_residual_body(int n, const T *__restrict__ tmp, const T *__restrict__ dinv,
-                                                 T *__restrict__ r, T alpha, T &s_rr, T &s_rz) {
+__device__ __forceinline__ void cg_residual_body(const T *__restrict__ tmp, const T *__restrict__ dinv,
+                                                 T *__restrict__ r, T alpha, int lo, int hi, T &s_rr, T &s_rz) {
   using V = typename Vec4T<T>::type;
-  const int n4 = n >> 2;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
+  const int lo4 = lo >> 2, hi4 = hi >> 2;  // chunks are multiples of 1024 except the last one's end
+  for (int i = lo4 + threadIdx.x; i < hi4; i += blockDim.x) {
     const V t4 = reinterpret_cast<const V *>(tmp)[i];
     const V d4 = reinterpret_cast<const V *>(dinv)[i];
     V r4 = reinterpret_cast<V *>(r)[i];
@@ -332,13 +341,11 @@ __device__ __forceinline__ void cg_residual_body(int n, const T *__restrict__ tm
     s_rr = fma_t(r4.z, r4.z, s_rr); s_rz = fma_t(r4.z, d4.z * r4.z, s_rz);
     s_rr = fma_t(r4.w, r4.w, s_rr); s_rz = fma_t(r4.w, d4.w * r4.w, s_rz);
   }
-  if (blockIdx.x == 0) {
-    for (int i = (n4 << 2) + threadIdx.x; i < n; i += blockDim.x) {
-      const T ri = fma_t(-alpha, tmp[i], r[i]);
-      r[i] = ri;
-      s_rr = fma_t(ri, ri, s_rr);
-      s_rz = fma_t(ri, dinv[i] * ri, s_rz);
-    }
+  for (int i = (hi4 << 2) + threadIdx.x; i < hi; i += blockDim.x) {
+    const T ri = fma_t(-alpha, tmp[i], r[i]);
+    r[i] = ri;
+    s_rr = fma_t(ri, ri, s_rr);
+    s_rz = fma_t(ri, dinv[i] * ri, s_rz);
   }
 }
 
@@ -351,10 +358,16 @@ cg_residual_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv,
   pdl_wait_then_release();
   if (sc->done) return;
   T s_rr = T(0), s_rz = T(0);
-  cg_residual_body<T>(n, tmp, dinv, r, static_cast<T>(sc->alpha), s_rr, s_rz);
+  int lo, hi, per;
+  cta_chunk(n, lo, hi, per);
+  cg_residual_body<T>(tmp, dinv, r, static_cast<T>(sc->alpha), lo, hi, s_rr, s_rz);
   double v[2] = {static_cast<double>(s_rr), static_cast<double>(s_rz)};
   if (grid_sum_last_block<2>(v, partials, &sc->ticket[2], s_red, &s_flag))
     cg_reduce_and_finish<2>(v, d, use_nccl, sc, [&](const double (&t)[2]) { cg_finish_B<T>(sc, t[0], t[1]); });
+  // multi-GPU: z' = D^-1 r' of the halo rows leaves now -- AFTER this CTA has handed in its partial sums, so that the
+  // wait for the NVLink acknowledgements runs beside the grid reduction and its all-reduce, not in front of them
+  // (pushing first cost ~9 us per iteration at 2 ranks)
+  if (d.zmode) dist_halo_push_signal_z<T>(d, r, dinv, lo, hi, per);
 }
 
 // x += alpha p and (update_p) p = D^-1 r + beta p on this CTA's chunk [lo, hi)
@@ -395,8 +408,25 @@ cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, 
   int lo, hi, per;
   cta_chunk(n, lo, hi, per);
   // converged (done == 1): only the deferred x += alpha p is still owed; p is dead.  done == 2: Eigen still updates p
-  cg_direction_body<T>(r, dinv, p, x, static_cast<T>(sc->alpha), static_cast<T>(sc->beta), done != 1, lo, hi);
-  if (done == 0) dist_halo_push_signal<T>(d, p, lo, hi, per);
+  const T beta = static_cast<T>(sc->beta);
+  cg_direction_body<T>(r, dinv, p, x, static_cast<T>(sc->alpha), beta, done != 1, lo, hi);
+  if (d.world > 1 && done == 0) {
+    if (d.zmode) {
+      // ghost copies of p, updated here from the z' the owners pushed a kernel ago: p_g = fma(beta, p_g, z_g) is the
+      // owners' own operation on the same operands, so owner and copy stay bit-identical and nothing is sent now
+      const int pg = ((d.n_ghost + gridDim.x - 1) / gridDim.x + 255) & ~255;
+      const int glo = min(d.n_ghost, static_cast<int>(blockIdx.x) * pg), ghi = min(d.n_ghost, glo + pg);
+      if (glo < ghi) {
+        if (threadIdx.x == 0) dist_halo_wait_z(d);
+        __syncthreads();
+        T *pgh = p + d.ghost_base;
+        const T *zgh = p + d.zbase;
+        for (int j = glo + threadIdx.x; j < ghi; j += blockDim.x) pgh[j] = fma_t(beta, pgh[j], __ldcg(zgh + j));
+      }
+    } else {
+      dist_halo_push_signal<T>(d, p, lo, hi, per);
+    }
+  }
 }
 
 // ---- variant "merged": two kernels and ONE reduction per iteration -----------------------------------------------------
@@ -682,6 +712,10 @@ void start(CgSolver::Impl &I, T *x, const T *b, int max_iters, double tol, bool 
                                                              I.partials.get<double>(), I.dev(), I.use_nccl);
   QDSP_LAUNCH_CHECK();
   if (I.use_nccl) nccl_reduce_then<T>(I, 3, 0);
+  if (I.dist && I.dist->world() > 1) {
+    cg_push_direction_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, static_cast<const T *>(I.p), I.dev());
+    QDSP_LAUNCH_CHECK();
+  }
 }
 
 template <typename T>

@@ -132,7 +132,7 @@ void DistContext::localize(CsrMatrix &A, const int64_t *row_offsets, cudaStream_
     if (!(e && e[0] == '1')) dev_.block_order = nullptr;
   }
   const size_t sv = A.value_bytes();
-  comm_.alloc(DIST_VECTOR_OFF + sv * (static_cast<size_t>(plan_.ghost_base) + n_ghost()) + 256);
+  comm_.alloc(DIST_VECTOR_OFF + sv * (static_cast<size_t>(zbase()) + n_ghost()) + 256);  // [owned | ghosts | z-ghosts]
   QDSP_CUDA(cudaMemsetAsync(comm_.get(), 0, comm_.bytes(), stream));
   ctl_.alloc(64);
   QDSP_CUDA(cudaMemsetAsync(ctl_.get(), 0, 64, stream));
@@ -140,12 +140,16 @@ void DistContext::localize(CsrMatrix &A, const int64_t *row_offsets, cudaStream_
   dev_.self = comm_.get<unsigned char>();
   dev_.counters = ctl_.get<unsigned>();
   dev_.error = reinterpret_cast<int *>(ctl_.get<unsigned>() + 8);
+  dev_.ghost_base = plan_.ghost_base;
+  dev_.n_ghost = n_ghost();
+  dev_.zbase = zbase();
+  dev_.zmode = 1;  // until a neighbour registers without a z slot
   dev_.n_recv = 0;
   for (int q = 0; q < world_; ++q)
     if (plan_.owner_offsets[q + 1] > plan_.owner_offsets[q]) dev_.recv_peer[dev_.n_recv++] = q;
 }
 
-void DistContext::set_send_list(int peer, const int32_t *global_ids, int count, int dst_offset) {
+void DistContext::set_send_list(int peer, const int32_t *global_ids, int count, int dst_offset, int dst_offset_z) {
   QDSP_REQUIRE(peer >= 0 && peer < world_ && peer != rank_, QDSP_ERR_INVALID, "dist: bad peer");
   QDSP_REQUIRE(count >= 0 && (count == 0 || global_ids != nullptr), QDSP_ERR_INVALID, "dist: bad send list");
   QDSP_REQUIRE(comm_.get() != nullptr, QDSP_ERR_STATE, "dist: localize first");
@@ -166,6 +170,8 @@ void DistContext::set_send_list(int peer, const int32_t *global_ids, int count, 
   dev_.send_list[s] = buf.get<int>();
   dev_.send_count[s] = count;
   dev_.send_dst[s] = dst_offset;
+  dev_.send_dst_z[s] = dst_offset_z;
+  if (dst_offset_z < 0) dev_.zmode = 0;
   dev_.send_first[s] = local.front();
   dev_.send_last[s] = local.back();
   dev_.send_contig[s] = (local.back() - local.front() == count - 1) ? 1 : 0;

@@ -35,6 +35,8 @@ class DistContext {
   int n_local() const { return plan_.n_local; }
   int n_ghost() const { return static_cast<int>(plan_.ghost_ids.size()); }
   int ghost_base() const { return plan_.ghost_base; }
+  // first element of the z-ghost segment of my vector: ghosts rounded up to a 128-byte boundary
+  int zbase() const { return (plan_.ghost_base + n_ghost() + 31) & ~31; }
   int dtype() const { return dtype_; }
   const DistPlan &plan() const { return plan_; }
 
@@ -42,7 +44,8 @@ class DistContext {
   // (A.cols becomes n_local + n_ghost), allocates the comm buffer.
   void localize(CsrMatrix &A, const int64_t *row_offsets, cudaStream_t stream);
   // rank `peer` reads `count` of my rows (global ids, ascending) and wants them at element `dst_offset` of its vector
-  void set_send_list(int peer, const int32_t *global_ids, int count, int dst_offset);
+  // dst_offset_z: where the same rows go in its z-ghost segment (< 0: the peer has none; CG then keeps pushing p)
+  void set_send_list(int peer, const int32_t *global_ids, int count, int dst_offset, int dst_offset_z = -1);
   void comm_handle(void *out64) const;
   void attach(const void *handles /* world x 64 bytes, rank order */);
   bool ready() const { return attached_; }

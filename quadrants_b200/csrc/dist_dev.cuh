@@ -8,12 +8,19 @@
 // Every rank owns one "comm buffer" (cudaMalloc, exported with cudaIpcGetMemHandle, mapped by every peer):
 //   [0, 2048)      reduction slots   slots[2 parity][8 ranks][8 values][2 words]   8-byte words {payload32 | seq32}
 //   [2048, 2112)   halo flags        flags[8 ranks]                                 8-byte, monotone sequence numbers
-//   [4096, ...)    the operand vector of SpMV: n_loc owned entries followed by n_ghost ghost entries
+//   [2112, 2176)   z-halo flags      the same for the second halo channel (below)
+//   [4096, ...)    the operand vector of SpMV: n_loc owned entries, the ghost entries (from ghost_base), and from zbase a
+//                  second ghost-sized segment for the z channel
 // Protocol:
 //   * halo: after a rank has produced its owned part of the vector it stores the entries each neighbour needs into
 //     that neighbour's ghost segment, fences at system scope, and stores its push count into the neighbour's
 //     flags[rank].  A consumer kernel spins (ld.acquire.sys) until flags[q] >= its own push count for every
 //     neighbour q it receives from -- ranks run the same kernel sequence, so "my push count" is the expected value.
+//   * second channel ("z"), used by CG: instead of pushing the new direction p' = z' + beta p at the END of an iteration
+//     (the neighbour's next SpMV then waits for it, and the push sits on the critical path), the owner pushes
+//     z' = D^-1 r' as soon as r' exists -- in the residual kernel, whose own reduction + all-reduce hides the NVLink
+//     latency -- and every rank updates its ghost copies of p itself, p_ghost = fma(beta, p_ghost, z_ghost): the same
+//     operands and the same fma as the owner's, hence the same bits.  The SpMV never waits after the first iteration.
 //   * all-reduce of up to 8 doubles (NCCL "LL" style): each 64-bit value travels as two 8-byte words carrying 32 data
 //     bits + the 32-bit sequence number; an aligned 8-byte store is single-copy atomic, so data and flag arrive
 //     together and one NVLink latency is the whole cost.  Slots alternate by sequence parity: a rank can be at most
@@ -43,6 +50,9 @@ struct DistDev {
   const int *send_list[DIST_MAX_RANKS] = {};     // device, sorted local row ids
   int send_count[DIST_MAX_RANKS] = {};
   int send_dst[DIST_MAX_RANKS] = {};             // element offset inside the peer's operand vector (its ghost slot)
+  int send_dst_z[DIST_MAX_RANKS] = {};           // the same for the z channel (the peer's zbase + its owner offset)
+  int zmode = 0;                                 // 1: every neighbour registered a z slot -> CG uses the z channel
+  int ghost_base = 0, n_ghost = 0, zbase = 0;    // my own vector: first ghost, ghost count, first z-ghost
   int send_first[DIST_MAX_RANKS] = {};           // smallest / largest row of the list, and whether it is one contiguous
   int send_last[DIST_MAX_RANKS] = {};            // run (plane halos): lets a CTA skip or index the list without searching
   int send_contig[DIST_MAX_RANKS] = {};
@@ -57,7 +67,8 @@ struct DistDev {
   // NVLink latency of the halo hides behind interior work.
   const int *block_order = nullptr;
   int n_interior = 0;
-  unsigned *counters = nullptr;                  // device, local: [0] reduction seq, [1] halo push count, [2] ticket
+  unsigned *counters = nullptr;                  // device, local: [0] reduction seq, [1] halo push count, [2] ticket,
+                                                 // [3] z push count, [4] z ticket
   int *error = nullptr;                          // device, local: != 0 after a timeout
 };
 
@@ -85,6 +96,10 @@ __device__ __forceinline__ unsigned long long *dist_slot(unsigned char *buf, uns
 }
 __device__ __forceinline__ unsigned long long *dist_flag(unsigned char *buf, int from_rank) {
   return reinterpret_cast<unsigned long long *>(buf + DIST_FLAGS_OFF) + from_rank;
+}
+
+__device__ __forceinline__ unsigned long long *dist_flag_z(unsigned char *buf, int from_rank) {
+  return reinterpret_cast<unsigned long long *>(buf + DIST_FLAGS_OFF + 64) + from_rank;
 }
 
 // All-reduce (sum) of v[0..NV) across ranks.  Called by ALL 32 lanes of ONE warp of ONE CTA per rank; every lane
@@ -149,8 +164,9 @@ __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_re
 // of them publishes the new push count to the neighbours.  The other CTAs -- all but a few dozen -- do nothing, and
 // the signal leaves as soon as the halo rows are done instead of at the end of the kernel (measured at 8 ranks: the
 // direction kernel took 25 us with an all-CTA ticket against 10 us without any push, profiles/r01h_8gpu_trace.txt).
-template <typename T>
-__device__ __forceinline__ void dist_halo_push_signal(const DistDev &d, const T *vec, int lo, int hi, int per) {
+// Z = false: channel p, pushes vec[i].  Z = true: channel z, pushes vec[i] * mul[i] (r and D^-1).
+template <typename T, bool Z>
+__device__ __forceinline__ void dist_halo_push_impl(const DistDev &d, const T *vec, const T *mul, int lo, int hi, int per) {
   if (d.world <= 1) return;
   bool mine = false;
   for (int s = 0; s < d.n_send; ++s) mine = mine || (lo < hi && hi > d.send_first[s] && lo <= d.send_last[s]);
@@ -160,20 +176,31 @@ __device__ __forceinline__ void dist_halo_push_signal(const DistDev &d, const T 
     if (hi <= d.send_first[s] || lo > d.send_last[s]) continue;
     const int *list = d.send_list[s];
     const int cnt = d.send_count[s];
-    T *dst = reinterpret_cast<T *>(d.peer[d.send_peer[s]] + DIST_VECTOR_OFF) + d.send_dst[s];
+    T *dst = reinterpret_cast<T *>(d.peer[d.send_peer[s]] + DIST_VECTOR_OFF) + (Z ? d.send_dst_z[s] : d.send_dst[s]);
     if (d.send_contig[s]) {
       const int first = d.send_first[s];
       const int jlo = max(lo, first) - first, jhi = min(hi, d.send_last[s] + 1) - first;
       constexpr int V = 16 / sizeof(T);
       const bool vec_ok = ((reinterpret_cast<uintptr_t>(dst + jlo) | reinterpret_cast<uintptr_t>(vec + first + jlo)) & 15u) == 0;
-      if (vec_ok) {
+      if (vec_ok && !Z) {
         const int nv = (jhi - jlo) / V;
         const int4 *src4 = reinterpret_cast<const int4 *>(vec + first + jlo);
         int4 *dst4 = reinterpret_cast<int4 *>(dst + jlo);
         for (int j = threadIdx.x; j < nv; j += blockDim.x) dst4[j] = src4[j];
         for (int j = jlo + nv * V + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[first + j];
+      } else if (vec_ok && ((reinterpret_cast<uintptr_t>(mul + first + jlo) & 15u) == 0)) {
+        const int nv = (jhi - jlo) / V;
+        for (int j = threadIdx.x; j < nv; j += blockDim.x) {
+          T a[V], m[V];
+          *reinterpret_cast<int4 *>(a) = reinterpret_cast<const int4 *>(vec + first + jlo)[j];
+          *reinterpret_cast<int4 *>(m) = reinterpret_cast<const int4 *>(mul + first + jlo)[j];
+#pragma unroll
+          for (int e = 0; e < V; ++e) a[e] = m[e] * a[e];
+          reinterpret_cast<int4 *>(dst + jlo)[j] = *reinterpret_cast<int4 *>(a);
+        }
+        for (int j = jlo + nv * V + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = mul[first + j] * vec[first + j];
       } else {
-        for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[first + j];
+        for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = Z ? mul[first + j] * vec[first + j] : vec[first + j];
       }
     } else {
       int a = 0, b = cnt;
@@ -182,7 +209,7 @@ __device__ __forceinline__ void dist_halo_push_signal(const DistDev &d, const T 
       b = cnt;
       while (a < b) { const int m = (a + b) >> 1; if (list[m] < hi) a = m + 1; else b = m; }
       const int jhi = a;
-      for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[list[j]];
+      for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = Z ? mul[list[j]] * vec[list[j]] : vec[list[j]];
     }
   }
   __syncthreads();
@@ -201,14 +228,27 @@ __device__ __forceinline__ void dist_halo_push_signal(const DistDev &d, const T 
       if (c1 >= c0) { owners += c1 - c0 + 1; covered_to = c1; }
     }
     fence_acq_rel_sys();  // my peer stores (and, cumulatively, the CTA's) are performed before the ticket is visible
-    const unsigned t = atomicAdd(&d.counters[2], 1u);
+    const unsigned t = atomicAdd(&d.counters[Z ? 4 : 2], 1u);
     if (t == static_cast<unsigned>(owners) - 1u) {
-      d.counters[2] = 0u;
-      const unsigned count = ++d.counters[1];
+      d.counters[Z ? 4 : 2] = 0u;
+      const unsigned count = ++d.counters[Z ? 3 : 1];
       fence_acq_rel_sys();  // the other owners' tickets (hence their stores) are ordered before the flags
-      for (int s = 0; s < d.n_send; ++s) st_sys_u64(dist_flag(d.peer[d.send_peer[s]], d.rank), count);
+      for (int s = 0; s < d.n_send; ++s) {
+        unsigned char *peer = d.peer[d.send_peer[s]];
+        st_sys_u64(Z ? dist_flag_z(peer, d.rank) : dist_flag(peer, d.rank), count);
+      }
     }
   }
+}
+
+template <typename T>
+__device__ __forceinline__ void dist_halo_push_signal(const DistDev &d, const T *vec, int lo, int hi, int per) {
+  dist_halo_push_impl<T, false>(d, vec, nullptr, lo, hi, per);
+}
+// z channel: pushes D^-1[i] * r[i] of the halo rows in [lo, hi)
+template <typename T>
+__device__ __forceinline__ void dist_halo_push_signal_z(const DistDev &d, const T *r, const T *dinv, int lo, int hi, int per) {
+  dist_halo_push_impl<T, true>(d, r, dinv, lo, hi, per);
 }
 
 // Called by thread 0 of a CTA before the CTA's first read of a ghost entry; follow with __syncthreads().
@@ -218,6 +258,21 @@ __device__ __forceinline__ void dist_halo_wait(const DistDev &d) {
   const long long t0 = clock64();
   for (int r = 0; r < d.n_recv; ++r) {
     const unsigned long long *f = dist_flag(d.self, d.recv_peer[r]);
+    while (ld_acquire_sys_u64(f) < want) {
+      if (clock64() - t0 > DIST_SPIN_LIMIT) {
+        atomicExch(d.error, 2);
+        break;
+      }
+    }
+  }
+}
+// The same for the z channel (thread 0 of a CTA, before its first read of a z-ghost; follow with __syncthreads()).
+__device__ __forceinline__ void dist_halo_wait_z(const DistDev &d) {
+  if (d.world <= 1) return;
+  const unsigned want = *reinterpret_cast<volatile unsigned *>(&d.counters[3]);
+  const long long t0 = clock64();
+  for (int r = 0; r < d.n_recv; ++r) {
+    const unsigned long long *f = dist_flag_z(d.self, d.recv_peer[r]);
     while (ld_acquire_sys_u64(f) < want) {
       if (clock64() - t0 > DIST_SPIN_LIMIT) {
         atomicExch(d.error, 2);

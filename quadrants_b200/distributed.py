@@ -52,14 +52,17 @@ def plan_host(rank: int, world: int, row_offsets, indices_global: np.ndarray, gh
 def exchange_requests(rank: int, world: int, ghost_base: int, ghost_ids: np.ndarray, owner_offsets: np.ndarray,
                       group=None):
     """Every rank tells every owner which of its rows it needs and where to put them.
-    -> list of (peer, ids, dst_offset): what THIS rank must send.  Works on any backend (gloo on CPU, nccl on GPU)."""
+    -> list of (peer, ids, dst_offset, dst_offset_z): what THIS rank must send; dst_offset_z is the slot of the same rows
+    in the requester's second ghost segment (zbase = ghost_base + n_ghost rounded up to 32 elements).
+    Works on any backend (gloo on CPU, nccl on GPU)."""
     import torch.distributed as dist
 
     mine = {}
+    zbase = (ghost_base + int(len(ghost_ids)) + 31) & ~31
     for q in range(world):
         a, b = int(owner_offsets[q]), int(owner_offsets[q + 1])
         if q != rank and b > a:
-            mine[q] = (np.ascontiguousarray(ghost_ids[a:b]), ghost_base + a)
+            mine[q] = (np.ascontiguousarray(ghost_ids[a:b]), ghost_base + a, zbase + a)
     if world == 1:
         return []
     everyone = [None] * world
@@ -67,8 +70,8 @@ def exchange_requests(rank: int, world: int, ghost_base: int, ghost_ids: np.ndar
     sends = []
     for s in range(world):
         if s != rank and rank in everyone[s]:
-            ids, dst = everyone[s][rank]
-            sends.append((s, np.ascontiguousarray(ids, dtype=np.int32), int(dst)))
+            ids, dst, dst_z = everyone[s][rank]
+            sends.append((s, np.ascontiguousarray(ids, dtype=np.int32), int(dst), int(dst_z)))
     return sends
 
 
@@ -124,8 +127,9 @@ class RowBlockContext:
         ghost_ids = (np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_int32)), shape=(self.n_ghost,)).copy()
                      if self.n_ghost else np.empty(0, np.int32))
         self.ghost_ids = ghost_ids
-        for peer, ids, dst in exchange_requests(self.rank, self.world, self.ghost_base, ghost_ids, owner, self.group):
-            _lib.check(self._lib.qdsp_dist_set_send_list(self._h, peer, ids.ctypes.data, ids.shape[0], dst))
+        for peer, ids, dst, dst_z in exchange_requests(self.rank, self.world, self.ghost_base, ghost_ids, owner,
+                                                       self.group):
+            _lib.check(self._lib.qdsp_dist_set_send_list(self._h, peer, ids.ctypes.data, ids.shape[0], dst, dst_z))
         handle = (C.c_ubyte * 64)()
         _lib.check(self._lib.qdsp_dist_comm_handle(self._h, handle))
         if self.world > 1:

@@ -82,16 +82,29 @@ sends = qdist.exchange_requests(rank, world, hi - lo, ghosts, owner)
 x = np.random.default_rng(1).uniform(-1, 1, n**3)
 # emulate the halo: every rank "pushes" the rows it was asked for into the requester's operand vector
 vec = np.concatenate([x[lo:hi], np.full(ghosts.shape[0], np.nan)])
-outbox = {{peer: (dst, x[ids]) for peer, ids, dst in sends}}
-for peer, ids, dst in sends:
+zbase = ((hi - lo) + ghosts.shape[0] + 31) & ~31
+vec = np.concatenate([vec, np.full(zbase - vec.shape[0] + ghosts.shape[0], np.nan)])   # [owned | ghosts | pad | z-ghosts]
+z = np.random.default_rng(2).uniform(-1, 1, n**3)       # stands for D^-1 r' of the whole system
+outbox = {{peer: (dst, x[ids], dst_z, z[ids]) for peer, ids, dst, dst_z in sends}}
+for peer, ids, dst, dst_z in sends:
     assert np.all(np.diff(ids) > 0) and np.all((ids >= lo) & (ids < hi))
 inbox = [None] * world
 dist.all_gather_object(inbox, outbox)
 for s in range(world):
     if s != rank and rank in inbox[s]:
-        dst, vals = inbox[s][rank]
+        dst, vals, dst_z, zvals = inbox[s][rank]
         vec[dst:dst + vals.shape[0]] = vals
-assert not np.isnan(vec).any(), "a ghost entry was never delivered"
+        assert dst_z - zbase == dst - (hi - lo), "z slot must mirror the ghost slot"
+        vec[dst_z:dst_z + zvals.shape[0]] = zvals
+ng = ghosts.shape[0]
+assert not np.isnan(vec[:hi - lo + ng]).any(), "a ghost entry was never delivered"
+assert not np.isnan(vec[zbase:zbase + ng]).any(), "a z-ghost entry was never delivered"
+# the z channel: ghost copies of p updated locally equal what the owners compute (same operands, same operation)
+beta = 0.37
+p_new = z + beta * x
+ghost_new = vec[zbase:zbase + ng] + beta * vec[hi - lo:hi - lo + ng]
+assert np.array_equal(ghost_new, p_new[ghosts]), "locally updated ghosts differ from the owners' values"
+vec = vec[:hi - lo + ng]
 Aloc = sp.csr_matrix((Al.data, idx, Al.indptr), shape=(hi - lo, vec.shape[0]))
 y = Aloc @ vec
 assert np.array_equal(y, (A @ x)[lo:hi]), "distributed product differs"

@@ -1,14 +1,8 @@
-# 8-GPU measurement script (one gpurun --gpus 8 call): where does the per-iteration time go at 8 ranks?
-TR8="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511"
-TR4="python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29512"
-B8="bench.py --gpus 8 --steps 4 --warmup 3 --no-cpu-baseline"
-B4="bench.py --gpus 4 --steps 4 --warmup 3 --no-cpu-baseline"
+# 8-GPU run: correctness at 8 ranks, then the strong-scaling series of bench.py and a per-kernel trace
+TR() { python -m torch.distributed.run --nnodes=1 --nproc-per-node $1 --master-addr 127.0.0.1 --master-port $((29500 + $1)) "${@:2}"; }
 val() { grep -o '"value": [0-9.]*\|"ms_per_step": [0-9.]*' | tr '\n' ' '; }
-echo "== N=8 classic, natural order";  QDSP_CG_VARIANT=classic QDSP_HALO_ORDER=0 timeout 200 $TR8 $B8 2>/dev/null | val; echo
-echo "== N=8 classic, ghost blocks last"; QDSP_CG_VARIANT=classic timeout 200 $TR8 $B8 2>/dev/null | val; echo
-echo "== N=8 merged, ghost blocks last"; QDSP_CG_VARIANT=merged timeout 200 $TR8 $B8 2>/dev/null | val; echo
-echo "== N=8 classic trace (no graph)"; QDSP_CG_TRACE=1 QDSP_CG_VARIANT=classic timeout 200 $TR8 $B8 2>&1 | grep "qdsp trace" | tail -8 | sort
-echo "== N=8 merged trace (no graph)"; QDSP_CG_TRACE=1 QDSP_CG_VARIANT=merged timeout 200 $TR8 $B8 2>&1 | grep "qdsp trace" | tail -8 | sort
-echo "== N=8 classic, NCCL all-reduce"; QDSP_ALLREDUCE=nccl QDSP_CG_VARIANT=classic timeout 200 $TR8 $B8 2>/dev/null | val; echo
-echo "== N=4 classic"; QDSP_CG_VARIANT=classic timeout 200 $TR4 $B4 2>/dev/null | val; echo
-echo "== N=4 classic trace"; QDSP_CG_TRACE=1 QDSP_CG_VARIANT=classic timeout 200 $TR4 $B4 2>&1 | grep "qdsp trace" | tail -4
+timeout 400 python -m pytest tests/test_dist_gpu.py -m gpu -x -q 2>&1 | tail -4
+for N in 8 4 2; do
+  echo "== N=$N"; TR $N bench.py --gpus $N --steps 5 --warmup 3 --no-cpu-baseline 2>/dev/null | tee gpurun_out/r1k_bench_n$N.json | val; echo
+done
+echo "== N=8 trace"; QDSP_CG_TRACE=1 TR 8 bench.py --gpus 8 --steps 3 --warmup 3 --no-cpu-baseline 2>&1 | grep "qdsp trace" | tail -8 | sort
