@@ -349,6 +349,35 @@ __device__ __forceinline__ void cg_residual_body(const T *__restrict__ tmp, cons
   }
 }
 
+// the same over the whole vector, grid-stride: all CTAs sweep the arrays together, which DRAM likes better (42 vs 46 us at
+// 256^3); used whenever no CTA has to own a contiguous chunk (i.e. no halo push from this kernel)
+template <typename T>
+__device__ __forceinline__ void cg_residual_body_strided(int n, const T *__restrict__ tmp, const T *__restrict__ dinv,
+                                                         T *__restrict__ r, T alpha, T &s_rr, T &s_rz) {
+  using V = typename Vec4T<T>::type;
+  const int n4 = n >> 2;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
+    const V t4 = reinterpret_cast<const V *>(tmp)[i];
+    const V d4 = reinterpret_cast<const V *>(dinv)[i];
+    V r4 = reinterpret_cast<V *>(r)[i];
+    r4.x = fma_t(-alpha, t4.x, r4.x); r4.y = fma_t(-alpha, t4.y, r4.y);
+    r4.z = fma_t(-alpha, t4.z, r4.z); r4.w = fma_t(-alpha, t4.w, r4.w);
+    reinterpret_cast<V *>(r)[i] = r4;
+    s_rr = fma_t(r4.x, r4.x, s_rr); s_rz = fma_t(r4.x, d4.x * r4.x, s_rz);
+    s_rr = fma_t(r4.y, r4.y, s_rr); s_rz = fma_t(r4.y, d4.y * r4.y, s_rz);
+    s_rr = fma_t(r4.z, r4.z, s_rr); s_rz = fma_t(r4.z, d4.z * r4.z, s_rz);
+    s_rr = fma_t(r4.w, r4.w, s_rr); s_rz = fma_t(r4.w, d4.w * r4.w, s_rz);
+  }
+  if (blockIdx.x == 0) {
+    for (int i = (n4 << 2) + threadIdx.x; i < n; i += blockDim.x) {
+      const T ri = fma_t(-alpha, tmp[i], r[i]);
+      r[i] = ri;
+      s_rr = fma_t(ri, ri, s_rr);
+      s_rz = fma_t(ri, dinv[i] * ri, s_rz);
+    }
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(CG_THREADS)
 cg_residual_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv, T *__restrict__ r,
@@ -358,9 +387,13 @@ cg_residual_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv,
   pdl_wait_then_release();
   if (sc->done) return;
   T s_rr = T(0), s_rz = T(0);
-  int lo, hi, per;
-  cta_chunk(n, lo, hi, per);
-  cg_residual_body<T>(tmp, dinv, r, static_cast<T>(sc->alpha), lo, hi, s_rr, s_rz);
+  int lo = 0, hi = 0, per = 1024;
+  if (d.zmode) {
+    cta_chunk(n, lo, hi, per);
+    cg_residual_body<T>(tmp, dinv, r, static_cast<T>(sc->alpha), lo, hi, s_rr, s_rz);
+  } else {
+    cg_residual_body_strided<T>(n, tmp, dinv, r, static_cast<T>(sc->alpha), s_rr, s_rz);
+  }
   double v[2] = {static_cast<double>(s_rr), static_cast<double>(s_rz)};
   if (grid_sum_last_block<2>(v, partials, &sc->ticket[2], s_red, &s_flag))
     cg_reduce_and_finish<2>(v, d, use_nccl, sc, [&](const double (&t)[2]) { cg_finish_B<T>(sc, t[0], t[1]); });
