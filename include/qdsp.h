@@ -41,7 +41,8 @@ typedef enum {
 typedef enum { QDSP_F32 = 0, QDSP_F64 = 1 } qdsp_dtype;
 
 /* key kinds of qdsp_sort_pairs: order is numeric for every kind (sign / IEEE twiddles applied on the fly) */
-typedef enum { QDSP_KEY_U32 = 0, QDSP_KEY_I32 = 1, QDSP_KEY_F32 = 2, QDSP_KEY_U64 = 3 } qdsp_key_kind;
+typedef enum { QDSP_KEY_U32 = 0, QDSP_KEY_I32 = 1, QDSP_KEY_F32 = 2, QDSP_KEY_U64 = 3, QDSP_KEY_I64 = 4,
+               QDSP_KEY_F64 = 5 } qdsp_key_kind;
 
 /* CG semantics.  EIGEN_JACOBI = the reference's arch=x64 path, Eigen::ConjugateGradient with the default diagonal
  * preconditioner, zero start, relative tolerance (quadrants/program/conjugate_gradient.h:36-49).  CUCG = the
@@ -184,6 +185,65 @@ int qdsp_sort_pairs(void *keys, void *values, int64_t n, int key_kind, int value
 /* PrefixSumExecutor.run (_algorithms.py:109-163): in-place inclusive i32 prefix sum, wrapping. */
 size_t qdsp_scan_tmp_bytes(int64_t n);
 int qdsp_inclusive_scan_i32(int32_t *inout, int64_t n, void *tmp, size_t tmp_bytes, void *stream);
+
+
+/* ---- qd.algorithms device-wide ops ------------------------------------------------------------ */
+/* The reference's modern algorithm library: reduce_{add,min,max} (python/quadrants/algorithms/_reduce.py:448-507),
+ * exclusive_scan_{add,min,max} (_scan.py:496-541), select (_select.py:124-169), reduce_by_key_add
+ * (_reduce_by_key.py:145-200) and sort (_radix_sort.py:277-398).  Shared conventions, mirroring the reference's:
+ *   capacity  the length of the arrays (sizes the grid and the scratch; the reference's 256**log256_max_n bound);
+ *   n_dev     optional DEVICE pointer to the live i32 count, read by the kernels (no host round trip, so a call can be
+ *             captured in a CUDA graph and replayed for any count <= capacity); NULL = the count is `capacity`;
+ *   scratch   caller-owned, uninitialised device memory of qdsp_algo_scratch_bytes(op, capacity, elem) bytes;
+ *   elem      qdsp_elem_type of the data.
+ * Integer results are exact (add wraps); float add is evaluated in a FIXED tile/warp tree order, so results are
+ * reproducible run to run (the reference's are not) but differ from a left-to-right host sum by rounding. */
+typedef enum { QDSP_I32 = 0, QDSP_U32 = 1, QDSP_ELEM_F32 = 2, QDSP_I64 = 3, QDSP_U64 = 4, QDSP_ELEM_F64 = 5 } qdsp_elem_type;
+typedef enum { QDSP_OP_ADD = 0, QDSP_OP_MIN = 1, QDSP_OP_MAX = 2 } qdsp_reduce_op;
+typedef enum { QDSP_ALGO_REDUCE = 0, QDSP_ALGO_SCAN = 1, QDSP_ALGO_SELECT = 2, QDSP_ALGO_REDUCE_BY_KEY = 3,
+               QDSP_ALGO_SORT = 4 } qdsp_algo;
+/* Scratch bytes of one op at `capacity` elements (elem_bytes: 4 or 8; for QDSP_ALGO_SORT the key width). */
+size_t qdsp_algo_scratch_bytes(int algo, int64_t capacity, int elem_bytes);
+/* out[0] = op(in[0:n]); the identity of `op` when n == 0 (0 / +max,+inf / -max,-inf,0 like _reduce.py:137-203). */
+int qdsp_reduce(const void *in, void *out, int64_t capacity, const int32_t *n_dev, int elem, int op, void *scratch,
+                size_t scratch_bytes, void *stream);
+/* out[i] = op(in[0:i]), out[0] = identity; `out` must not alias `in` (_scan.py:476-494). */
+int qdsp_exclusive_scan(const void *in, void *out, int64_t capacity, const int32_t *n_dev, int elem, int op,
+                        void *scratch, size_t scratch_bytes, void *stream);
+/* Stream compaction (_select.py:124-147): out[k] = in[i] for the k-th i with flags[i] == 1, input order kept;
+ * num_out[0] = number selected.  flags are i32 and must be exactly 0 or 1.  item_bytes: a multiple of 4 (scalars and
+ * packed structs alike -- the copy is untyped). */
+int qdsp_select(const void *in, const int32_t *flags, void *out, int32_t *num_out, int64_t capacity,
+                const int32_t *n_dev, int item_bytes, void *scratch, size_t scratch_bytes, void *stream);
+/* Run-length collapse (_reduce_by_key.py:145-177): every maximal run of equal consecutive keys becomes
+ * (key, sum of its values); num_runs[0] = number of runs; only the first num_runs entries of the outputs are written.
+ * key_elem / value_elem in {QDSP_I32, QDSP_U32, QDSP_ELEM_F32}; float keys compare as floats (NaN opens a run of its
+ * own, +0 == -0). */
+int qdsp_reduce_by_key_add(const void *keys_in, const void *values_in, void *keys_out, void *values_out,
+                           int32_t *num_runs, int64_t capacity, const int32_t *n_dev, int key_elem, int value_elem,
+                           void *scratch, size_t scratch_bytes, void *stream);
+/* sort (_radix_sort.py:277-344): ascending stable LSD radix sort of the low `end_bit` bits of keys[0:n] (values
+ * permuted alike when value_bytes is 4 or 8; 0 = keys only), ping-ponging through the caller's tmp_keys / tmp_values.
+ * end_bit: positive multiple of 8 giving an EVEN number of digit passes so the result lands in keys / values.
+ * key_elem: any qdsp_elem_type (numeric order: two's complement and IEEE twiddles applied on the fly; -0 < +0, NaNs
+ * by bit pattern at the ends). */
+int qdsp_sort(void *keys, void *tmp_keys, void *values, void *tmp_values, int64_t capacity, const int32_t *n_dev,
+              int key_elem, int value_bytes, int end_bit, void *scratch, size_t scratch_bytes, void *stream);
+
+/* ---- triplet emission ------------------------------------------------------------------------- */
+/* Bulk replacement of per-triplet insert_triplet_f32/f64 (internal_functions.h:12-39: one contended atomic_add on
+ * slot 0 per triplet): appends `count` triplets (row[k], col[k], +-val[k]) behind the triplets already in the buffer,
+ * in array order, with NO atomic -- every thread reads slot 0, writes its triplet at slot0 + k, and a second
+ * one-thread kernel bumps slot 0, all stream-ordered.  row/col: device i32; val: device f32/f64 (the builder's
+ * dtype).  Overflow beyond max_triplets is detected on the device: nothing is written, and qdsp_builder_count /
+ * qdsp_builder_build report QDSP_ERR_INVALID. */
+int qdsp_builder_append(qdsp_builder_t b, const int32_t *row, const int32_t *col, const void *val, int64_t count,
+                        int negate, void *stream);
+/* Element-wise assembly (the FEM pattern of tests/python/test_implicit_fem.py:179-204): `n_elems` elements of `k`
+ * nodes each; element e contributes the k*k triplets (nodes[e*k+a], nodes[e*k+b], mats[(e*k+a)*k+b]) in that order.
+ * nodes: device i32 [n_elems*k]; mats: device f32/f64 [n_elems*k*k]. */
+int qdsp_builder_append_elements(qdsp_builder_t b, const int32_t *nodes, const void *mats, int64_t n_elems, int k,
+                                 void *stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -171,6 +171,101 @@ class Oracle:
         return out
 
 
+# -- N1: the modern device-wide ops, restated in numpy -----------------------------------------------
+# Semantics follow docs/source/user_guide/algorithms.md ("Semantics") and the host references the reference's own tests
+# compare against (tests/python/test_algorithms.py:267-695): np.sum / min / max, np.cumsum-style prefix, boolean-mask
+# compaction, run-length collapse, np.argsort(kind="stable").  Test infrastructure only.
+def _identity(op, dtype):
+    """_reduce.py:137-203: 0 for add; largest value (+inf) for min; smallest value (-inf, 0 for unsigned) for max."""
+    dtype = np.dtype(dtype)
+    if op == "add":
+        return dtype.type(0)
+    if dtype.kind == "f":
+        return dtype.type(np.inf if op == "min" else -np.inf)
+    info = np.iinfo(dtype)
+    return dtype.type(info.max if op == "min" else info.min)
+
+
+def algo_reduce(arr, op):
+    """out[0] of reduce_{add,min,max}: integer add wraps at the dtype's width; float add is the f64-accumulated sum (the
+    device uses a tree order, so tests compare with a tolerance like test_algorithms.py:316-321)."""
+    arr = np.asarray(arr)
+    if arr.shape[0] == 0:
+        return _identity(op, arr.dtype)
+    if op == "add":
+        if arr.dtype.kind == "f":
+            return arr.dtype.type(np.sum(arr.astype(np.float64)))
+        with np.errstate(over="ignore"):
+            return np.add.reduce(arr, dtype=arr.dtype)
+    return arr.min() if op == "min" else arr.max()
+
+
+def algo_exclusive_scan(arr, op):
+    """out[i] = op(arr[0:i]), out[0] = identity (test_algorithms.py:404-451)."""
+    arr = np.asarray(arr)
+    out = np.empty_like(arr)
+    if arr.shape[0] == 0:
+        return out
+    out[0] = _identity(op, arr.dtype)
+    if arr.shape[0] > 1:
+        head = arr[:-1]
+        if op == "add":
+            if arr.dtype.kind == "f":
+                out[1:] = np.cumsum(head.astype(np.float64)).astype(arr.dtype)
+            else:
+                with np.errstate(over="ignore"):
+                    out[1:] = np.cumsum(head, dtype=arr.dtype)
+        elif op == "min":
+            out[1:] = np.minimum.accumulate(head)
+        else:
+            out[1:] = np.maximum.accumulate(head)
+    return out
+
+
+def algo_select(arr, flags):
+    """(compacted prefix, count) of select (test_algorithms.py:454-535)."""
+    arr, flags = np.asarray(arr), np.asarray(flags)
+    sel = arr[flags == 1]
+    return sel, int(sel.shape[0])
+
+
+def algo_reduce_by_key_add(keys, values):
+    """(run keys, run sums, number of runs): a run ends where key[i] != key[i-1] under the key dtype's own `!=` (NaN opens a
+    run of its own, +0 == -0).  Integer sums wrap; float sums are accumulated in f64 (compare with a tolerance)."""
+    keys, values = np.asarray(keys), np.asarray(values)
+    n = keys.shape[0]
+    if n == 0:
+        return keys[:0], values[:0], 0
+    head = np.ones(n, dtype=bool)
+    head[1:] = keys[1:] != keys[:-1]
+    starts = np.flatnonzero(head)
+    if values.dtype.kind == "f":
+        sums = np.add.reduceat(values.astype(np.float64), starts).astype(values.dtype)
+    else:
+        with np.errstate(over="ignore"):
+            sums = np.add.reduceat(values, starts, dtype=values.dtype)
+    return keys[starts], sums, int(starts.shape[0])
+
+
+def algo_sort_order(keys, end_bit=None):
+    """The permutation a stable ascending radix sort of `keys` produces: order of the sign/IEEE-twiddled bit patterns
+    (two's complement -> offset binary; floats -> total order with -0 < +0, -NaN first, +NaN last), restricted to the low
+    `end_bit` bits when given (_radix_sort.py:94-137 twiddle, :277-344 passes)."""
+    keys = np.ascontiguousarray(keys)
+    w = keys.dtype.itemsize * 8
+    ut = np.uint32 if w == 32 else np.uint64
+    b = keys.view(ut).copy()
+    sign = ut(1) << ut(w - 1)
+    if keys.dtype.kind == "i":
+        b ^= sign
+    elif keys.dtype.kind == "f":
+        neg = (b & sign) != 0
+        b = np.where(neg, ~b, b | sign)
+    if end_bit is not None and end_bit < w:
+        b &= (ut(1) << ut(end_bit)) - ut(1)
+    return np.argsort(b, kind="stable")
+
+
 class EigenRef:
     """The reference's vendored Eigen behind the reference's call sequence (oracle/eigen_ref.cpp)."""
 

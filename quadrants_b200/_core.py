@@ -90,30 +90,60 @@ class SparseMatrixBuilder:
         slot = np.int32 if self.dtype is f32 else np.int64
         return device_tensor(self.get_ndarray_data_ptr(), 3 * self.max_num_triplets + 1, slot, self)
 
-    def insert_triplets(self, rows, cols, vals, negate=False):
-        """What a JIT fill kernel does through insert_triplet_f32/f64 (internal_functions.h:12-39), vectorised: reserve
-        len(rows) slots by bumping the counter, then write (row, col, bits(value)).  `A[i, j] -= v` inserts -v."""
+    def _dev(self, x, torch_dtype):
         import torch
 
-        buf = self.buffer_tensor()
-        dev = buf.device
-        slot_t = buf.dtype
-        rows = torch.as_tensor(np.asarray(rows) if not torch.is_tensor(rows) else rows).to(dev).reshape(-1)
-        cols = torch.as_tensor(np.asarray(cols) if not torch.is_tensor(cols) else cols).to(dev).reshape(-1)
-        vals = torch.as_tensor(np.asarray(vals) if not torch.is_tensor(vals) else vals).to(dev).reshape(-1)
-        vals = vals.to(self.dtype.torch_dtype)
-        if negate:
-            vals = -vals
+        if not torch.is_tensor(x):
+            x = torch.as_tensor(np.asarray(x))
+        dev = f"cuda:{_require_prog().config().device}"
+        return x.to(device=dev, dtype=torch_dtype).reshape(-1).contiguous()
+
+    def _reserve(self, k):
+        """Host-side bound on slot 0, so an overflow raises at the call like the old synchronous path did without
+        reading the count back every time; only when the bound is hit is the true device count fetched."""
+        bound = getattr(self, "_appended", 0) + k
+        if bound > self.max_num_triplets:
+            bound = self.num_triplets() + k
+            if bound > self.max_num_triplets:
+                raise QuadrantsRuntimeError(f"builder overflow: {bound} triplets > max_num_triplets "
+                                            f"{self.max_num_triplets}")
+        self._appended = bound
+
+    def insert_triplets(self, rows, cols, vals, negate=False):
+        """What a JIT fill kernel does through insert_triplet_f32/f64 (internal_functions.h:12-39), in bulk and without
+        its per-triplet atomic: qdsp_builder_append writes (row, col, bits(value)) behind the triplets already there,
+        in array order, and bumps slot 0 on the stream.  `A[i, j] -= v` inserts -v."""
+        import torch
+
+        rows, cols = self._dev(rows, torch.int32), self._dev(cols, torch.int32)
+        vals = self._dev(vals, self.dtype.torch_dtype)
         k = rows.shape[0]
-        start = int(buf[0].item())
-        if start + k > self.max_num_triplets:
-            raise QuadrantsRuntimeError(f"builder overflow: {start + k} triplets > max_num_triplets "
-                                        f"{self.max_num_triplets}")
-        body = buf[1 + 3 * start: 1 + 3 * (start + k)].view(k, 3)
-        body[:, 0] = rows.to(slot_t)
-        body[:, 1] = cols.to(slot_t)
-        body[:, 2] = vals.view(slot_t)
-        buf[0] = start + k
+        if cols.shape[0] != k or vals.shape[0] != k:
+            raise QuadrantsRuntimeError("insert_triplets: rows, cols and vals differ in length")
+        if k == 0:
+            return
+        self._reserve(k)
+        _lib.check(self._lib.qdsp_builder_append(self._h, rows.data_ptr(), cols.data_ptr(), vals.data_ptr(), k,
+                                                 1 if negate else 0, _stream()))
+
+    def insert_elements(self, nodes, mats):
+        """Element-wise assembly (the FEM fill pattern, tests/python/test_implicit_fem.py:179-204): nodes [E, k] int,
+        mats [E, k, k]; element e adds mats[e, a, b] at (nodes[e, a], nodes[e, b])."""
+        import torch
+
+        nodes_t = nodes if torch.is_tensor(nodes) else torch.as_tensor(np.asarray(nodes))
+        if nodes_t.dim() != 2:
+            raise QuadrantsRuntimeError("insert_elements: nodes must be [n_elems, k]")
+        e, k = int(nodes_t.shape[0]), int(nodes_t.shape[1])
+        nodes_d = self._dev(nodes_t, torch.int32)
+        mats_d = self._dev(mats, self.dtype.torch_dtype)
+        if mats_d.shape[0] != e * k * k:
+            raise QuadrantsRuntimeError("insert_elements: mats must be [n_elems, k, k]")
+        if e == 0:
+            return
+        self._reserve(e * k * k)
+        _lib.check(self._lib.qdsp_builder_append_elements(self._h, nodes_d.data_ptr(), mats_d.data_ptr(), e, k,
+                                                          _stream()))
 
     def fill_from_host(self, triplet_buffer: np.ndarray):
         """Copies a host buffer already in the builder layout (slot 0 = count)."""
@@ -121,6 +151,7 @@ class SparseMatrixBuilder:
         b = np.ascontiguousarray(triplet_buffer, dtype=slot)
         n = int(b[0])
         _lib.check(self._lib.qdsp_builder_fill_from_host(self._h, b[1:].ctypes.data, n, _stream()))
+        self._appended = n
 
     def print_triplets_cuda(self):
         _lib.check(self._lib.qdsp_builder_print_triplets(self._h))
@@ -130,6 +161,7 @@ class SparseMatrixBuilder:
     def build_cuda(self):
         out = C.c_void_p()
         _lib.check(self._lib.qdsp_builder_build(self._h, _stream(), C.byref(out)))
+        self._appended = 0  # build() clears the buffer
         return CuSparseMatrix._wrap(out)
 
     build = build_cuda

@@ -14,7 +14,10 @@ LIB_PATH = os.path.join(_HERE, "lib", "libqdsp.so")
 
 QDSP_OK = 0
 F32, F64 = 0, 1
-KEY_U32, KEY_I32, KEY_F32, KEY_U64 = 0, 1, 2, 3
+KEY_U32, KEY_I32, KEY_F32, KEY_U64, KEY_I64, KEY_F64 = 0, 1, 2, 3, 4, 5
+ELEM_I32, ELEM_U32, ELEM_F32, ELEM_I64, ELEM_U64, ELEM_F64 = 0, 1, 2, 3, 4, 5  # qdsp_elem_type
+OP_ADD, OP_MIN, OP_MAX = 0, 1, 2  # qdsp_reduce_op
+ALGO_REDUCE, ALGO_SCAN, ALGO_SELECT, ALGO_REDUCE_BY_KEY, ALGO_SORT = 0, 1, 2, 3, 4  # qdsp_algo
 CG_EIGEN_JACOBI, CG_CUCG = 0, 1
 
 _vp, _i, _i64, _sz, _d = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_double
@@ -70,6 +73,14 @@ SIGNATURES = {
     "qdsp_sort_pairs": (_i, [_vp, _vp, _i64, _i, _i, _vp, _sz, _vp]),
     "qdsp_scan_tmp_bytes": (_sz, [_i64]),
     "qdsp_inclusive_scan_i32": (_i, [_vp, _i64, _vp, _sz, _vp]),
+    "qdsp_algo_scratch_bytes": (_sz, [_i, _i64, _i]),
+    "qdsp_reduce": (_i, [_vp, _vp, _i64, _vp, _i, _i, _vp, _sz, _vp]),
+    "qdsp_exclusive_scan": (_i, [_vp, _vp, _i64, _vp, _i, _i, _vp, _sz, _vp]),
+    "qdsp_select": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _vp, _sz, _vp]),
+    "qdsp_reduce_by_key_add": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _i, _i, _vp, _sz, _vp]),
+    "qdsp_sort": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _i, _i, _vp, _sz, _vp]),
+    "qdsp_builder_append": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
+    "qdsp_builder_append_elements": (_i, [_vp, _vp, _vp, _i64, _i, _vp]),
 }
 
 _lib = None

@@ -317,7 +317,7 @@ int qdsp_cg_create_dist(qdsp_csr_t m, qdsp_dist_t d, int max_iters, double tol, 
 // ---- algorithms -----------------------------------------------------------------------------------------------------------
 size_t qdsp_sort_tmp_bytes(int64_t n, int key_kind, int value_bytes) {
   if (n < 0) return 0;
-  return sort_tmp_bytes(n, key_kind == QDSP_KEY_U64 ? 8 : 4, value_bytes);
+  return sort_tmp_bytes(n, key_kind >= QDSP_KEY_U64 ? 8 : 4, value_bytes);
 }
 int qdsp_sort_pairs(void *keys, void *values, int64_t n, int key_kind, int value_bytes, void *tmp, size_t tmp_bytes,
                     void *stream) {
@@ -326,6 +326,50 @@ int qdsp_sort_pairs(void *keys, void *values, int64_t n, int key_kind, int value
 size_t qdsp_scan_tmp_bytes(int64_t n) { return n < 0 ? 0 : scan_tmp_bytes(n); }
 int qdsp_inclusive_scan_i32(int32_t *inout, int64_t n, void *tmp, size_t tmp_bytes, void *stream) {
   return guarded([&] { inclusive_scan_i32(inout, n, tmp, tmp_bytes, S(stream)); });
+}
+
+// ---- device-wide algorithms ---------------------------------------------------------------------------------
+size_t qdsp_algo_scratch_bytes(int algo, int64_t capacity, int elem_bytes) {
+  return algo_scratch_bytes(algo, capacity, elem_bytes);
+}
+int qdsp_reduce(const void *in, void *out, int64_t capacity, const int32_t *n_dev, int elem, int op, void *scratch,
+                size_t scratch_bytes, void *stream) {
+  return guarded([&] { device_reduce(in, out, capacity, n_dev, elem, op, scratch, scratch_bytes, S(stream)); });
+}
+int qdsp_exclusive_scan(const void *in, void *out, int64_t capacity, const int32_t *n_dev, int elem, int op,
+                        void *scratch, size_t scratch_bytes, void *stream) {
+  return guarded([&] { device_exclusive_scan(in, out, capacity, n_dev, elem, op, scratch, scratch_bytes, S(stream)); });
+}
+int qdsp_select(const void *in, const int32_t *flags, void *out, int32_t *num_out, int64_t capacity,
+                const int32_t *n_dev, int item_bytes, void *scratch, size_t scratch_bytes, void *stream) {
+  return guarded([&] {
+    device_select(in, flags, out, num_out, capacity, n_dev, item_bytes, scratch, scratch_bytes, S(stream));
+  });
+}
+int qdsp_reduce_by_key_add(const void *keys_in, const void *values_in, void *keys_out, void *values_out,
+                           int32_t *num_runs, int64_t capacity, const int32_t *n_dev, int key_elem, int value_elem,
+                           void *scratch, size_t scratch_bytes, void *stream) {
+  return guarded([&] {
+    device_reduce_by_key_add(keys_in, values_in, keys_out, values_out, num_runs, capacity, n_dev, key_elem, value_elem,
+                             scratch, scratch_bytes, S(stream));
+  });
+}
+int qdsp_sort(void *keys, void *tmp_keys, void *values, void *tmp_values, int64_t capacity, const int32_t *n_dev,
+              int key_elem, int value_bytes, int end_bit, void *scratch, size_t scratch_bytes, void *stream) {
+  return guarded([&] {
+    sort_modern(keys, tmp_keys, values, tmp_values, capacity, n_dev, key_elem, value_bytes, end_bit, scratch,
+                scratch_bytes, S(stream));
+  });
+}
+
+// ---- triplet emission ---------------------------------------------------------------------------------------
+int qdsp_builder_append(qdsp_builder_t b, const int32_t *row, const int32_t *col, const void *val, int64_t count,
+                        int negate, void *stream) {
+  return guarded([&] { NOT_NULL(b); b->impl->append(row, col, val, count, negate != 0, S(stream)); });
+}
+int qdsp_builder_append_elements(qdsp_builder_t b, const int32_t *nodes, const void *mats, int64_t n_elems, int k,
+                                 void *stream) {
+  return guarded([&] { NOT_NULL(b); b->impl->append_elements(nodes, mats, n_elems, k, S(stream)); });
 }
 
 }  // extern "C"

@@ -292,6 +292,103 @@ void Builder::fill_from_host(const void *triplets, int64_t count, cudaStream_t s
   QDSP_CUDA(cudaStreamSynchronize(stream));
 }
 
+// ---- bulk triplet emission ---------------------------------------------------------------------------
+// The reference's fill kernels call insert_triplet_f32/f64 once per triplet: one atomic_add on slot 0 each
+// (internal_functions.h:12-39), i.e. 2e8 serialised atomics on one address at C4.  A bulk append needs none: slot 0 is
+// only READ while the triplets are written at slot0 + k, and a one-thread kernel bumps it afterwards (stream order
+// separates the two).  Array order is kept, so a build from appended triplets is deterministic.
+template <typename SlotT, typename BitsT>
+__global__ void __launch_bounds__(CB_THREADS)
+append_coo_kernel(SlotT *__restrict__ buf, const int32_t *__restrict__ row, const int32_t *__restrict__ col,
+                  const BitsT *__restrict__ val, long long count, long long max_triplets, int negate) {
+  const long long start = static_cast<long long>(buf[0]);
+  if (start < 0 || start + count > max_triplets) return;  // overflow: nothing written, the bump makes build() fail
+  constexpr BitsT SIGN = BitsT(1) << (8 * sizeof(BitsT) - 1);
+  const long long stride = static_cast<long long>(gridDim.x) * CB_THREADS;
+  for (long long k = static_cast<long long>(blockIdx.x) * CB_THREADS + threadIdx.x; k < count; k += stride) {
+    SlotT *t = buf + 1 + 3 * (start + k);
+    BitsT bits = val[k];
+    if (negate) bits ^= SIGN;  // A[i, j] -= v inserts -v
+    t[0] = static_cast<SlotT>(row[k]);
+    t[1] = static_cast<SlotT>(col[k]);
+    t[2] = static_cast<SlotT>(bits);
+  }
+}
+
+// element e of k nodes contributes (nodes[e*k+a], nodes[e*k+b], mats[(e*k+a)*k+b]), a-major: one thread per triplet
+template <typename SlotT, typename BitsT>
+__global__ void __launch_bounds__(CB_THREADS)
+append_elements_kernel(SlotT *__restrict__ buf, const int32_t *__restrict__ nodes, const BitsT *__restrict__ mats,
+                       long long n_elems, int k, long long max_triplets) {
+  const long long kk = static_cast<long long>(k) * k;
+  const long long count = n_elems * kk;
+  const long long start = static_cast<long long>(buf[0]);
+  if (start < 0 || start + count > max_triplets) return;
+  const long long stride = static_cast<long long>(gridDim.x) * CB_THREADS;
+  for (long long t = static_cast<long long>(blockIdx.x) * CB_THREADS + threadIdx.x; t < count; t += stride) {
+    const long long e = t / kk;
+    const int ab = static_cast<int>(t - e * kk);
+    const int a = ab / k, b = ab - a * k;
+    SlotT *o = buf + 1 + 3 * (start + t);
+    o[0] = static_cast<SlotT>(nodes[e * k + a]);
+    o[1] = static_cast<SlotT>(nodes[e * k + b]);
+    o[2] = static_cast<SlotT>(mats[t]);
+  }
+}
+
+template <typename SlotT>
+__global__ void append_bump_kernel(SlotT *buf, long long count) {
+  buf[0] = static_cast<SlotT>(static_cast<long long>(buf[0]) + count);
+}
+
+static unsigned append_grid(int64_t count) {
+  return static_cast<unsigned>(std::min<int64_t>((count + CB_THREADS - 1) / CB_THREADS,
+                                                 static_cast<int64_t>(device_props().sm_count) * 16));
+}
+
+void Builder::append(const int32_t *row, const int32_t *col, const void *val, int64_t count, bool negate,
+                     cudaStream_t stream) {
+  QDSP_REQUIRE(count >= 0, QDSP_ERR_INVALID, "append: negative count");
+  if (count == 0) return;
+  QDSP_REQUIRE(row && col && val, QDSP_ERR_INVALID, "append: null pointer");
+  QDSP_REQUIRE(count <= max_triplets_, QDSP_ERR_INVALID,
+               "append: " + std::to_string(count) + " triplets exceed max_num_triplets " + std::to_string(max_triplets_));
+  if (dtype_ == QDSP_F64) {
+    append_coo_kernel<int64_t, uint64_t><<<append_grid(count), CB_THREADS, 0, stream>>>(
+        buf_.get<int64_t>(), row, col, static_cast<const uint64_t *>(val), count, max_triplets_, negate ? 1 : 0);
+    QDSP_LAUNCH_CHECK();
+    append_bump_kernel<int64_t><<<1, 1, 0, stream>>>(buf_.get<int64_t>(), count);
+  } else {
+    append_coo_kernel<int32_t, uint32_t><<<append_grid(count), CB_THREADS, 0, stream>>>(
+        buf_.get<int32_t>(), row, col, static_cast<const uint32_t *>(val), count, max_triplets_, negate ? 1 : 0);
+    QDSP_LAUNCH_CHECK();
+    append_bump_kernel<int32_t><<<1, 1, 0, stream>>>(buf_.get<int32_t>(), count);
+  }
+  QDSP_LAUNCH_CHECK();
+}
+
+void Builder::append_elements(const int32_t *nodes, const void *mats, int64_t n_elems, int k, cudaStream_t stream) {
+  QDSP_REQUIRE(n_elems >= 0 && k > 0 && k <= 64, QDSP_ERR_INVALID, "append_elements: bad element count or nodes per element");
+  if (n_elems == 0) return;
+  QDSP_REQUIRE(nodes && mats, QDSP_ERR_INVALID, "append_elements: null pointer");
+  const int64_t count = n_elems * k * k;
+  QDSP_REQUIRE(count <= max_triplets_, QDSP_ERR_INVALID,
+               "append_elements: " + std::to_string(count) + " triplets exceed max_num_triplets " +
+                   std::to_string(max_triplets_));
+  if (dtype_ == QDSP_F64) {
+    append_elements_kernel<int64_t, uint64_t><<<append_grid(count), CB_THREADS, 0, stream>>>(
+        buf_.get<int64_t>(), nodes, static_cast<const uint64_t *>(mats), n_elems, k, max_triplets_);
+    QDSP_LAUNCH_CHECK();
+    append_bump_kernel<int64_t><<<1, 1, 0, stream>>>(buf_.get<int64_t>(), count);
+  } else {
+    append_elements_kernel<int32_t, uint32_t><<<append_grid(count), CB_THREADS, 0, stream>>>(
+        buf_.get<int32_t>(), nodes, static_cast<const uint32_t *>(mats), n_elems, k, max_triplets_);
+    QDSP_LAUNCH_CHECK();
+    append_bump_kernel<int32_t><<<1, 1, 0, stream>>>(buf_.get<int32_t>(), count);
+  }
+  QDSP_LAUNCH_CHECK();
+}
+
 void Builder::clear(cudaStream_t stream) {
   built_ = false;
   QDSP_CUDA(cudaMemsetAsync(buf_.get(), 0, slot_bytes(), stream));

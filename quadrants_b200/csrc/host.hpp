@@ -18,6 +18,20 @@ void sort_pairs(void *keys, void *values, int64_t n, int key_kind, int value_byt
                 cudaStream_t stream);
 void sort_build_keys(void *keys, void *values, int64_t n, int key_bytes, int value_bytes, int key_bits, void *tmp,
                      cudaStream_t stream, void **keys_out, void **values_out);
+void sort_modern(void *keys, void *tmp_keys, void *values, void *tmp_values, int64_t capacity, const int32_t *n_dev,
+                 int key_elem, int value_bytes, int end_bit, void *scratch, size_t scratch_bytes, cudaStream_t stream);
+
+// ---- device-wide reduce / scan / select / reduce-by-key (device_algos.cu) ---------------------------------------------
+size_t algo_scratch_bytes(int algo, int64_t capacity, int elem_bytes);
+void device_reduce(const void *in, void *out, int64_t capacity, const int32_t *n_dev, int elem, int op, void *scratch,
+                   size_t scratch_bytes, cudaStream_t stream);
+void device_exclusive_scan(const void *in, void *out, int64_t capacity, const int32_t *n_dev, int elem, int op,
+                           void *scratch, size_t scratch_bytes, cudaStream_t stream);
+void device_select(const void *in, const int32_t *flags, void *out, int32_t *num_out, int64_t capacity,
+                   const int32_t *n_dev, int item_bytes, void *scratch, size_t scratch_bytes, cudaStream_t stream);
+void device_reduce_by_key_add(const void *keys_in, const void *values_in, void *keys_out, void *values_out,
+                              int32_t *num_runs, int64_t capacity, const int32_t *n_dev, int key_elem, int value_elem,
+                              void *scratch, size_t scratch_bytes, cudaStream_t stream);
 
 // ---- CuSparseMatrix (quadrants/program/sparse_matrix.h:206-299) -------------------------------------------------------
 // Owns csr_row_ptr_/csr_col_ind_/csr_val_ on the device.  Unlike the reference's shallow copy-ctor
@@ -73,6 +87,9 @@ class Builder {
   int64_t count(cudaStream_t stream) const;
   void fill_from_host(const void *triplets, int64_t count, cudaStream_t stream);
   void clear(cudaStream_t stream);
+  // bulk, atomic-free replacements of per-triplet insert_triplet_f32/f64; array order is kept
+  void append(const int32_t *row, const int32_t *col, const void *val, int64_t count, bool negate, cudaStream_t stream);
+  void append_elements(const int32_t *nodes, const void *mats, int64_t n_elems, int k, cudaStream_t stream);
   std::unique_ptr<CsrMatrix> build(cudaStream_t stream);
   void print_triplets() const;
   int rows() const { return rows_; }

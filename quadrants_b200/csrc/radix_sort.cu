@@ -33,6 +33,10 @@ __device__ __forceinline__ KeyT twiddle_in(KeyT k, int kind) {
   if constexpr (sizeof(KeyT) == 4) {
     if (kind == QDSP_KEY_I32) return k ^ 0x80000000u;
     if (kind == QDSP_KEY_F32) return (k & 0x80000000u) ? ~k : (k | 0x80000000u);
+  } else {
+    constexpr KeyT SIGN = KeyT(1) << 63;
+    if (kind == QDSP_KEY_I64) return k ^ SIGN;
+    if (kind == QDSP_KEY_F64) return (k & SIGN) ? ~k : (k | SIGN);
   }
   return k;
 }
@@ -41,16 +45,28 @@ __device__ __forceinline__ KeyT twiddle_out(KeyT k, int kind) {
   if constexpr (sizeof(KeyT) == 4) {
     if (kind == QDSP_KEY_I32) return k ^ 0x80000000u;
     if (kind == QDSP_KEY_F32) return (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+  } else {
+    constexpr KeyT SIGN = KeyT(1) << 63;
+    if (kind == QDSP_KEY_I64) return k ^ SIGN;
+    if (kind == QDSP_KEY_F64) return (k & SIGN) ? (k & ~SIGN) : ~k;
   }
   return k;
+}
+
+// live count: min(n, *n_dev) when the caller keeps the count on the device (qd.algorithms.sort's 0-d `n`)
+__device__ __forceinline__ long long rs_count(long long n, const int *n_dev) {
+  if (n_dev == nullptr) return n;
+  const long long m = *n_dev;
+  return m < 0 ? 0 : (m < n ? m : n);
 }
 
 // ---- pass 0: digit histograms of every pass in one read of the keys -----------------------------------------------
 template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS)
-rs_histogram_kernel(const KeyT *__restrict__ keys, long long n, int kind, int begin_bit, int end_bit, int passes,
-                    unsigned *__restrict__ hist /* passes x 256 */) {
+rs_histogram_kernel(const KeyT *__restrict__ keys, long long n, const int *__restrict__ n_dev, int kind, int begin_bit,
+                    int end_bit, int passes, unsigned *__restrict__ hist /* passes x 256 */) {
   extern __shared__ unsigned s_hist[];  // passes x 256
+  n = rs_count(n, n_dev);
   for (int i = threadIdx.x; i < passes * RS_RADIX; i += RS_THREADS) s_hist[i] = 0;
   __syncthreads();
   const long long stride = static_cast<long long>(gridDim.x) * RS_THREADS;
@@ -102,8 +118,8 @@ __host__ __device__ constexpr size_t rs_vals_offset() {
 template <typename KeyT, typename ValT, int ITEMS>
 __global__ void __launch_bounds__(RS_THREADS, 4)
 rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const ValT *__restrict__ vin,
-                   ValT *__restrict__ vout, long long n, int shift, int nbits, int kind, int tw_in, int tw_out,
-                   unsigned *__restrict__ ticket, unsigned *__restrict__ lookback /* tiles x 256 */,
+                   ValT *__restrict__ vout, long long n, const int *__restrict__ n_dev, int shift, int nbits, int kind,
+                   int tw_in, int tw_out, unsigned *__restrict__ ticket, unsigned *__restrict__ lookback /* tiles x 256 */,
                    const unsigned *__restrict__ bins /* exclusive-scanned histogram of this pass */) {
   constexpr bool HAS_VAL = !std::is_same<ValT, NoValue>::value;
   constexpr int TILE = RS_THREADS * ITEMS;
@@ -117,6 +133,8 @@ rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const 
   const unsigned tile = S.ticket;
   const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
   const long long tile_base = static_cast<long long>(tile) * TILE;
+  n = rs_count(n, n_dev);
+  if (tile_base >= n) return;  // device-resident count below the capacity: the grid is sized for the capacity
   const int valid_n = static_cast<int>(min(static_cast<long long>(TILE), n - tile_base));
   const unsigned dmask = (1u << nbits) - 1u;
 
@@ -248,8 +266,9 @@ static int rs_items(int kb, int vb) {
 }
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// aux = [tickets (8 passes) | histograms 8 x 256 | look-back words tiles x 256]
 struct RsLayout {
-  size_t hist_off, lookback_off, keys_off, vals_off, total;
+  size_t hist_off, lookback_off, aux_bytes, keys_off, vals_off, total;
   int64_t tiles;
 };
 static RsLayout rs_layout(int64_t n, int kb, int vb) {
@@ -258,36 +277,39 @@ static RsLayout rs_layout(int64_t n, int kb, int vb) {
   L.tiles = n > 0 ? (n + tile - 1) / tile : 1;
   L.hist_off = RS_HEADER_BYTES;
   L.lookback_off = align_up(L.hist_off + 8 * RS_RADIX * sizeof(unsigned), 256);
-  L.keys_off = align_up(L.lookback_off + static_cast<size_t>(L.tiles) * RS_RADIX * sizeof(unsigned), 256);
+  L.aux_bytes = align_up(L.lookback_off + static_cast<size_t>(L.tiles) * RS_RADIX * sizeof(unsigned), 256);
+  L.keys_off = L.aux_bytes;
   L.vals_off = align_up(L.keys_off + static_cast<size_t>(n) * kb, 256);
   L.total = align_up(L.vals_off + static_cast<size_t>(n) * vb, 256);
   return L;
 }
 
 size_t sort_tmp_bytes(int64_t n, int key_bytes, int value_bytes) { return rs_layout(n, key_bytes, value_bytes).total; }
+// aux only (the caller brings tmp_keys / tmp_values): sized for the smallest tile of this key width, any value width
+size_t sort_modern_scratch_bytes(int64_t capacity, int key_bytes) { return rs_layout(capacity, key_bytes, 8).aux_bytes; }
 
+// Runs the digit passes of bits [begin_bit, end_bit) ping-ponging between (keys, vals) and (kalt, valt); `n` sizes the
+// grids, the live count is min(n, *n_dev) when n_dev is given.  Returns where the sorted keys live.
 template <typename KeyT, typename ValT>
-static void *rs_run(KeyT *keys, ValT *vals, int64_t n, int kind, int begin_bit, int end_bit, void *tmp,
-                    cudaStream_t stream, void **vals_result) {
+static void *rs_run(KeyT *keys, ValT *vals, KeyT *kalt, ValT *valt, void *aux, int64_t n, const int *n_dev, int kind,
+                    int begin_bit, int end_bit, cudaStream_t stream, void **vals_result) {
   constexpr int KB = sizeof(KeyT);
   constexpr int VB = std::is_same<ValT, NoValue>::value ? 0 : sizeof(ValT);
   constexpr int ITEMS = RsItems<KB, VB>::value;
   constexpr int TILE = RS_THREADS * ITEMS;
   const RsLayout L = rs_layout(n, KB, VB);
   const int passes = (end_bit - begin_bit + 7) / 8;
-  char *base = static_cast<char *>(tmp);
+  char *base = static_cast<char *>(aux);
   unsigned *tickets = reinterpret_cast<unsigned *>(base);
   unsigned *hist = reinterpret_cast<unsigned *>(base + L.hist_off);
   unsigned *lookback = reinterpret_cast<unsigned *>(base + L.lookback_off);
-  KeyT *kalt = reinterpret_cast<KeyT *>(base + L.keys_off);
-  ValT *valt = reinterpret_cast<ValT *>(base + L.vals_off);
   const size_t lookback_bytes = static_cast<size_t>(L.tiles) * RS_RADIX * sizeof(unsigned);
 
   QDSP_CUDA(cudaMemsetAsync(base, 0, L.lookback_off, stream));  // tickets + histograms
   const int hist_grid = static_cast<int>(std::min<int64_t>((n + RS_THREADS - 1) / RS_THREADS,
                                                           static_cast<int64_t>(device_props().sm_count) * 8));
   rs_histogram_kernel<KeyT><<<hist_grid, RS_THREADS, passes * RS_RADIX * sizeof(unsigned), stream>>>(
-      keys, n, kind, begin_bit, end_bit, passes, hist);
+      keys, n, n_dev, kind, begin_bit, end_bit, passes, hist);
   QDSP_LAUNCH_CHECK();
   rs_scan_bins_kernel<<<passes, RS_RADIX, 0, stream>>>(hist);
   QDSP_LAUNCH_CHECK();
@@ -306,14 +328,27 @@ static void *rs_run(KeyT *keys, ValT *vals, int64_t n, int kind, int begin_bit, 
     const int nbits = std::min(8, end_bit - shift);
     QDSP_CUDA(cudaMemsetAsync(lookback, 0, lookback_bytes, stream));
     kernel<<<static_cast<unsigned>(L.tiles), RS_THREADS, smem, stream>>>(
-        kin, kout, vin, vout, n, shift, nbits, kind, p == 0, p == passes - 1, tickets + p, lookback,
+        kin, kout, vin, vout, n, n_dev, shift, nbits, kind, p == 0, p == passes - 1, tickets + p, lookback,
         hist + p * RS_RADIX);
     QDSP_LAUNCH_CHECK();
     std::swap(kin, kout);
     std::swap(vin, vout);
   }
   if (vals_result) *vals_result = vin;
-  return kin;  // where the sorted keys now live (caller buffer if `passes` is even)
+  return kin;  // the caller's buffer if `passes` is even
+}
+
+// old single-scratch form: the alternate buffers live behind the aux area of `tmp`
+template <typename KeyT, typename ValT>
+static void *rs_run_tmp(KeyT *keys, ValT *vals, int64_t n, int kind, int begin_bit, int end_bit, void *tmp,
+                        cudaStream_t stream, void **vals_result) {
+  constexpr int KB = sizeof(KeyT);
+  constexpr int VB = std::is_same<ValT, NoValue>::value ? 0 : sizeof(ValT);
+  const RsLayout L = rs_layout(n, KB, VB);
+  char *base = static_cast<char *>(tmp);
+  return rs_run<KeyT, ValT>(keys, vals, reinterpret_cast<KeyT *>(base + L.keys_off),
+                            reinterpret_cast<ValT *>(base + L.vals_off), tmp, n, nullptr, kind, begin_bit, end_bit,
+                            stream, vals_result);
 }
 
 // Sorts in place: if the pass count is odd the result is copied back from the scratch buffer.
@@ -321,7 +356,7 @@ template <typename KeyT, typename ValT>
 static void rs_sort_inplace(KeyT *keys, ValT *vals, int64_t n, int kind, int begin_bit, int end_bit, void *tmp,
                             cudaStream_t stream) {
   void *vres = nullptr;
-  void *kres = rs_run<KeyT, ValT>(keys, vals, n, kind, begin_bit, end_bit, tmp, stream, &vres);
+  void *kres = rs_run_tmp<KeyT, ValT>(keys, vals, n, kind, begin_bit, end_bit, tmp, stream, &vres);
   if (kres != keys) {
     QDSP_CUDA(cudaMemcpyAsync(keys, kres, static_cast<size_t>(n) * sizeof(KeyT), cudaMemcpyDeviceToDevice, stream));
     if constexpr (!std::is_same<ValT, NoValue>::value)
@@ -329,13 +364,13 @@ static void rs_sort_inplace(KeyT *keys, ValT *vals, int64_t n, int kind, int beg
   }
 }
 
-static int key_bytes_of(int kind) { return kind == QDSP_KEY_U64 ? 8 : 4; }
+static int key_bytes_of(int kind) { return kind >= QDSP_KEY_U64 ? 8 : 4; }
 
 // Public entry: in-place ascending stable sort of `keys` (and `values`).
 void sort_pairs(void *keys, void *values, int64_t n, int key_kind, int value_bytes, void *tmp, size_t tmp_bytes,
                 cudaStream_t stream) {
   QDSP_REQUIRE(n >= 0, QDSP_ERR_INVALID, "sort: negative length");
-  QDSP_REQUIRE(key_kind >= QDSP_KEY_U32 && key_kind <= QDSP_KEY_U64, QDSP_ERR_INVALID, "sort: bad key kind");
+  QDSP_REQUIRE(key_kind >= QDSP_KEY_U32 && key_kind <= QDSP_KEY_F64, QDSP_ERR_INVALID, "sort: bad key kind");
   QDSP_REQUIRE(value_bytes == 0 || value_bytes == 4 || value_bytes == 8, QDSP_ERR_INVALID,
                "sort: value_bytes must be 0, 4 or 8");
   QDSP_REQUIRE(n < (int64_t{1} << 30), QDSP_ERR_UNSUPPORTED, "sort: n must be below 2^30");
@@ -358,6 +393,48 @@ void sort_pairs(void *keys, void *values, int64_t n, int key_kind, int value_byt
   }
 }
 
+// qd.algorithms.sort (python/quadrants/algorithms/_radix_sort.py:277-344): caller-owned ping-pong buffers and scratch,
+// device-resident count, low `end_bit` bits, even pass count so the result lands in keys / values.
+void sort_modern(void *keys, void *tmp_keys, void *values, void *tmp_values, int64_t capacity, const int32_t *n_dev,
+                 int key_elem, int value_bytes, int end_bit, void *scratch, size_t scratch_bytes, cudaStream_t stream) {
+  static const int kind_of_elem[6] = {QDSP_KEY_I32, QDSP_KEY_U32, QDSP_KEY_F32, QDSP_KEY_I64, QDSP_KEY_U64, QDSP_KEY_F64};
+  QDSP_REQUIRE(key_elem >= 0 && key_elem < 6, QDSP_ERR_UNSUPPORTED, "sort: key dtype not supported");
+  QDSP_REQUIRE(capacity >= 0, QDSP_ERR_INVALID, "sort: negative capacity");
+  QDSP_REQUIRE(capacity < (int64_t{1} << 30), QDSP_ERR_UNSUPPORTED, "sort: capacity must be below 2^30");
+  QDSP_REQUIRE(value_bytes == 0 || value_bytes == 4 || value_bytes == 8, QDSP_ERR_INVALID,
+               "sort: value_bytes must be 0, 4 or 8");
+  const int kind = kind_of_elem[key_elem];
+  const int kb = key_bytes_of(kind);
+  QDSP_REQUIRE(end_bit > 0 && end_bit % 8 == 0 && end_bit <= kb * 8, QDSP_ERR_INVALID,
+               "sort: end_bit must be a positive multiple of 8 no larger than the key width");
+  QDSP_REQUIRE((end_bit / 8) % 2 == 0, QDSP_ERR_INVALID,
+               "sort: end_bit must give an even number of digit passes so the result lands back in keys");
+  if (capacity == 0) return;
+  QDSP_REQUIRE(keys && tmp_keys && scratch, QDSP_ERR_INVALID, "sort: null pointer");
+  QDSP_REQUIRE(keys != tmp_keys, QDSP_ERR_INVALID, "sort: keys and tmp_keys must be distinct buffers");
+  if (value_bytes) {
+    QDSP_REQUIRE(values && tmp_values, QDSP_ERR_INVALID, "sort: null values pointer");
+    QDSP_REQUIRE(values != tmp_values, QDSP_ERR_INVALID, "sort: values and tmp_values must be distinct buffers");
+  }
+  QDSP_REQUIRE(scratch_bytes >= sort_modern_scratch_bytes(capacity, kb), QDSP_ERR_INVALID, "sort: scratch too small");
+  QDSP_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 3u) == 0, QDSP_ERR_INVALID, "sort: scratch must be 4-byte aligned");
+  // an IEEE / two's-complement twiddle flips high bits: partial-width sorts are only meaningful for unsigned keys,
+  // exactly like the reference (it twiddles the whole key and sorts the low end_bit bits of the twiddled key)
+  void *kres = nullptr;
+  if (kb == 4) {
+    auto *k = static_cast<uint32_t *>(keys), *ka = static_cast<uint32_t *>(tmp_keys);
+    if (value_bytes == 0) kres = rs_run<uint32_t, NoValue>(k, nullptr, ka, nullptr, scratch, capacity, n_dev, kind, 0, end_bit, stream, nullptr);
+    else if (value_bytes == 4) kres = rs_run<uint32_t, uint32_t>(k, static_cast<uint32_t *>(values), ka, static_cast<uint32_t *>(tmp_values), scratch, capacity, n_dev, kind, 0, end_bit, stream, nullptr);
+    else kres = rs_run<uint32_t, uint64_t>(k, static_cast<uint64_t *>(values), ka, static_cast<uint64_t *>(tmp_values), scratch, capacity, n_dev, kind, 0, end_bit, stream, nullptr);
+  } else {
+    auto *k = static_cast<uint64_t *>(keys), *ka = static_cast<uint64_t *>(tmp_keys);
+    if (value_bytes == 0) kres = rs_run<uint64_t, NoValue>(k, nullptr, ka, nullptr, scratch, capacity, n_dev, kind, 0, end_bit, stream, nullptr);
+    else if (value_bytes == 4) kres = rs_run<uint64_t, uint32_t>(k, static_cast<uint32_t *>(values), ka, static_cast<uint32_t *>(tmp_values), scratch, capacity, n_dev, kind, 0, end_bit, stream, nullptr);
+    else kres = rs_run<uint64_t, uint64_t>(k, static_cast<uint64_t *>(values), ka, static_cast<uint64_t *>(tmp_values), scratch, capacity, n_dev, kind, 0, end_bit, stream, nullptr);
+  }
+  QDSP_REQUIRE(kres == keys, QDSP_ERR_STATE, "sort: internal error, result not in keys");
+}
+
 // Internal entry for the CSR build: sorts only bits [0, key_bits) and returns where the result lives (no copy back).
 void sort_build_keys(void *keys, void *values, int64_t n, int key_bytes, int value_bytes, int key_bits, void *tmp,
                      cudaStream_t stream, void **keys_out, void **values_out) {
@@ -365,11 +442,11 @@ void sort_build_keys(void *keys, void *values, int64_t n, int key_bytes, int val
   if (key_bits < 1) key_bits = 1;
   void *kr = nullptr, *vr = nullptr;
   if (key_bytes == 4) {
-    if (value_bytes == 4) kr = rs_run<uint32_t, uint32_t>(static_cast<uint32_t *>(keys), static_cast<uint32_t *>(values), n, QDSP_KEY_U32, 0, key_bits, tmp, stream, &vr);
-    else kr = rs_run<uint32_t, uint64_t>(static_cast<uint32_t *>(keys), static_cast<uint64_t *>(values), n, QDSP_KEY_U32, 0, key_bits, tmp, stream, &vr);
+    if (value_bytes == 4) kr = rs_run_tmp<uint32_t, uint32_t>(static_cast<uint32_t *>(keys), static_cast<uint32_t *>(values), n, QDSP_KEY_U32, 0, key_bits, tmp, stream, &vr);
+    else kr = rs_run_tmp<uint32_t, uint64_t>(static_cast<uint32_t *>(keys), static_cast<uint64_t *>(values), n, QDSP_KEY_U32, 0, key_bits, tmp, stream, &vr);
   } else {
-    if (value_bytes == 4) kr = rs_run<uint64_t, uint32_t>(static_cast<uint64_t *>(keys), static_cast<uint32_t *>(values), n, QDSP_KEY_U64, 0, key_bits, tmp, stream, &vr);
-    else kr = rs_run<uint64_t, uint64_t>(static_cast<uint64_t *>(keys), static_cast<uint64_t *>(values), n, QDSP_KEY_U64, 0, key_bits, tmp, stream, &vr);
+    if (value_bytes == 4) kr = rs_run_tmp<uint64_t, uint32_t>(static_cast<uint64_t *>(keys), static_cast<uint32_t *>(values), n, QDSP_KEY_U64, 0, key_bits, tmp, stream, &vr);
+    else kr = rs_run_tmp<uint64_t, uint64_t>(static_cast<uint64_t *>(keys), static_cast<uint64_t *>(values), n, QDSP_KEY_U64, 0, key_bits, tmp, stream, &vr);
   }
   *keys_out = kr;
   *values_out = vr;

@@ -15,8 +15,10 @@ class QuadrantsRuntimeError(RuntimeError):
 
 
 class DataType:
-    def __init__(self, name, np_dtype, torch_name):
+    def __init__(self, name, np_dtype, torch_name, storage_np=None):
         self.name, self.np_dtype, self._torch_name = name, np.dtype(np_dtype), torch_name
+        # dtype of the torch tensor that holds the bytes (u64 rides in an int64 tensor: same bits, full torch support)
+        self.storage_np = np.dtype(storage_np if storage_np is not None else np_dtype)
 
     @property
     def torch_dtype(self):
@@ -36,7 +38,8 @@ f64 = float64 = DataType("f64", np.float64, "float64")
 i32 = int32 = DataType("i32", np.int32, "int32")
 u32 = uint32 = DataType("u32", np.uint32, "uint32")
 i64 = int64 = DataType("i64", np.int64, "int64")
-_ALL = {t.name: t for t in (f32, f64, i32, u32, i64)}
+u64 = uint64 = DataType("u64", np.uint64, "int64", storage_np=np.int64)
+_ALL = {t.name: t for t in (f32, f64, i32, u32, i64, u64)}
 
 
 def to_dtype(x) -> DataType:
@@ -165,7 +168,7 @@ class Ndarray:
         return self.tensor.data_ptr()
 
     def to_numpy(self):
-        return self.tensor.detach().cpu().numpy().reshape(self.shape)
+        return self.tensor.detach().cpu().numpy().view(self.dtype.np_dtype).reshape(self.shape)
 
     def from_numpy(self, a):
         import torch
@@ -173,9 +176,11 @@ class Ndarray:
         a = np.ascontiguousarray(a, dtype=self.dtype.np_dtype).reshape(-1)
         if a.shape[0] != self.tensor.shape[0]:
             raise QuadrantsRuntimeError(f"from_numpy: shape mismatch {a.shape} vs {self.shape}")
-        self.tensor.copy_(torch.from_numpy(a))
+        self.tensor.copy_(torch.from_numpy(a.view(self.dtype.storage_np)))
 
     def fill(self, v):
+        if self.dtype.storage_np != self.dtype.np_dtype:
+            v = int(np.array([v], dtype=self.dtype.np_dtype).view(self.dtype.storage_np)[0])
         self.tensor.fill_(v)
 
     def _idx(self, i):

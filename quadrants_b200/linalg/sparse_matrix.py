@@ -162,6 +162,11 @@ class SparseMatrixBuilder:
         """Vectorised `A[rows[k], cols[k]] += vals[k]` (device-side append into the builder buffer)."""
         self.ptr.insert_triplets(rows, cols, vals)
 
+    def insert_elements(self, nodes, mats):
+        """Element-wise assembly: `A[nodes[e, a], nodes[e, b]] += mats[e, a, b]` for every element e (the FEM fill loop
+        of the reference's tests/python/test_implicit_fem.py:179-204 as one device-side append)."""
+        self.ptr.insert_elements(nodes, mats)
+
     def print_triplets(self):
         self.ptr.print_triplets_cuda()
 
