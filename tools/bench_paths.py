@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Secondary throughput harness (NOT the driver's bench line): the other BASELINE.json configs on one B200.
 
-    python tools/bench_paths.py [scan] [sort] [build] [fem]        # default: all, one JSON line per config
+    python tools/bench_paths.py [scan] [sort] [build] [fem] [algos]        # default: all, one JSON line per config
 
 C3  inclusive scan and key-value sort of 2^28 random i32                     (byte models of SURVEY 8(d))
 C4  triplet -> CSR build of 200 M random f32 triplets, ~30 % duplicates, rows = cols = 2^24
@@ -148,13 +148,77 @@ def bench_fem(lib, stream):
          success=bool(ok), rel_residual=cg.error, iters_per_s=round(cg.iterations / ms * 1e3, 1))
 
 
+def bench_algos(lib, stream):
+    """the modern device-wide ops at N = 2^26 (256 MB per 4-byte array, > L2) against the byte models
+    of DESIGN.md 3.7/3.8."""
+    A = qd.algorithms
+    n = 1 << 26
+    D = 4
+    g = torch.Generator(device="cuda").manual_seed(9)
+    cnt = qd.ndarray(qd.i32, 1); cnt.fill(n)
+    for dt, sb in ((qd.i32, 4), (qd.f32, 4), (qd.f64, 8)):
+        a, o, o1 = qd.ndarray(dt, n), qd.ndarray(dt, n), qd.ndarray(dt, 1)
+        if dt is qd.i32:
+            a.tensor.copy_(torch.randint(-1000, 1000, (n,), dtype=torch.int32, device="cuda", generator=g))
+        else:
+            a.tensor.uniform_(-1, 1, generator=g)
+        sc = qd.ndarray(qd.u32 if sb == 4 else qd.u64, A.exclusive_scan_scratch_slots(n, D))
+        run = lambda: A.reduce_add(a, o1, sc, cnt, dt, D)
+        run(); run()
+        emit(f"N1 reduce_add 2^26 {dt}", timed(run, 10), n * sb)
+        run = lambda: A.exclusive_scan_add(a, o, sc, cnt, dt, D)
+        run(); run()
+        emit(f"N1 exclusive_scan_add 2^26 {dt} (3-pass, fixed order)", timed(run, 10), 3 * n * sb, two_touch_bytes=2 * n * sb)
+        del a, o, o1, sc
+    a, o, fl, num = qd.ndarray(qd.i32, n), qd.ndarray(qd.i32, n), qd.ndarray(qd.i32, n), qd.ndarray(qd.i32, 1)
+    a.tensor.copy_(torch.arange(n, dtype=torch.int32, device="cuda"))
+    fl.tensor.copy_((torch.rand(n, device="cuda", generator=g) < 0.5).to(torch.int32))
+    sc = qd.ndarray(qd.u32, A.select_scratch_slots(n))
+    run = lambda: A.select(a, fl, o, num, sc, cnt, D)
+    run(); run()
+    k = int(num.to_numpy()[0])
+    emit("N1 select 2^26 i32, 50 % selected", timed(run, 10), n * 4 + 2 * n * 4 + k * 4, selected=k)
+    keys = qd.ndarray(qd.i32, n)
+    keys.tensor.copy_((torch.arange(n, device="cuda") // 8).to(torch.int32))
+    ko, vo = qd.ndarray(qd.i32, n), qd.ndarray(qd.f32, n)
+    vals = qd.ndarray(qd.f32, n); vals.tensor.uniform_(-1, 1, generator=g)
+    run = lambda: A.reduce_by_key_add(keys, vals, ko, vo, num, sc, cnt, qd.f32, D)
+    run(); run()
+    r = int(num.to_numpy()[0])
+    emit("N1 reduce_by_key_add 2^26 i32 keys / f32 values, runs of 8", timed(run, 10), 2 * n * 4 + n * 4 + r * 8, runs=r)
+    del fl, ko, vo, vals
+    src = torch.randint(-2**31, 2**31, (n,), dtype=torch.int64, device="cuda", generator=g).to(torch.int32)
+    tk, v, tv = qd.ndarray(qd.i32, n), qd.ndarray(qd.i32, n), qd.ndarray(qd.i32, n)
+    ssc = qd.ndarray(qd.u32, A.sort_scratch_slots(n, D))
+    n0 = qd.ndarray(qd.i32, ()); n0.fill(n)
+    def setup():
+        keys.tensor.copy_(src); v.tensor.copy_(a.tensor)
+    run = lambda: A.sort(keys, tk, v, tv, ssc, n0, qd.i32, True, 32, D)
+    setup(); run()
+    emit("N1 sort 2^26 i32 keys + i32 values (device count)", timed(run, 5, setup=setup), n * 4 + 4 * 2 * n * 8,
+         gpairs_per_s=round(n / timed(run, 3, setup=setup) / 1e6, 2))
+    del tk, v, tv, ssc, keys, src
+    t = 60_000_000
+    K = qd.linalg.SparseMatrixBuilder(1 << 24, 1 << 24, max_num_triplets=t, dtype=qd.f32)
+    r_ = torch.randint(0, 1 << 24, (t,), dtype=torch.int32, device="cuda", generator=g)
+    c_ = torch.randint(0, 1 << 24, (t,), dtype=torch.int32, device="cuda", generator=g)
+    v_ = torch.empty(t, dtype=torch.float32, device="cuda").uniform_(-1, 1, generator=g)
+    def reset():
+        K.ptr.buffer_tensor()[0] = 0
+        K.ptr._appended = 0
+    run = lambda: K.ptr.insert_triplets(r_, c_, v_)
+    reset(); run()
+    emit("N2 bulk append of 60 M f32 triplets (no atomics)", timed(run, 5, setup=reset), t * 12 + t * 12,
+         mtriplets_per_s=round(t / timed(run, 3, setup=reset) / 1e3, 1))
+
+
 def main():
     qd.init(arch=qd.cuda, device=0)
     lib = _lib.load()
     stream = torch.cuda.current_stream().cuda_stream
-    which = sys.argv[1:] or ["scan", "sort", "build", "fem"]
+    which = sys.argv[1:] or ["scan", "sort", "build", "fem", "algos"]
     for w in which:
-        {"scan": bench_scan, "sort": bench_sort, "build": bench_build, "fem": bench_fem}[w](lib, stream)
+        {"scan": bench_scan, "sort": bench_sort, "build": bench_build, "fem": bench_fem, "algos": bench_algos}[w](lib, stream)
         torch.cuda.empty_cache()
 
 
