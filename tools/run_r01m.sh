@@ -6,7 +6,7 @@ mkdir -p gpurun_out
 cd "$(dirname "$0")/.."
 T0=$SECONDS
 first=150
-for k in reduce exclusive_scan select reduce_by_key sort "builder or errors"; do
+for k in "reduce and not by_key" exclusive_scan select reduce_by_key sort "builder or errors"; do
   name=$(echo "$k" | tr ' ' '_')
   timeout $first python -m pytest tests/test_gpu_algorithms.py -q -x -k "$k" -p no:cacheprovider > gpurun_out/r01m_algos_$name.log 2>&1
   echo "[$((SECONDS-T0))s] algos -k '$k' exit $?" | tee -a gpurun_out/r01m_summary.txt
