@@ -16,6 +16,8 @@
 //      look back over the preceding tiles' descriptors for digit d, publish the inclusive prefix;
 //   4. scatter to shared memory in tile-sorted order, then write out so that consecutive threads store runs of
 //      consecutive global addresses.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace qdsp {
@@ -25,6 +27,8 @@ constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_RADIX = 256;
 constexpr size_t RS_HEADER_BYTES = 256;  // per-pass ticket counters (8 passes max)
 constexpr unsigned RS_FLAG_AGG = 1u << 30, RS_FLAG_PREFIX = 2u << 30, RS_FLAG_MASK = 3u << 30, RS_VAL_MASK = ~RS_FLAG_MASK;
+
+constexpr int RS_DEFAULT_RANK = 0;
 
 struct NoValue {};  // keys-only instantiation
 
@@ -115,7 +119,10 @@ __host__ __device__ constexpr size_t rs_vals_offset() {
   return (sizeof(RsSmem<KeyT, ValT, ITEMS>) + 15) / 16 * 16;
 }
 
-template <typename KeyT, typename ValT, int ITEMS>
+// RANK selects how the lanes that hold the same digit find each other: 0 = eight ballots per item interleaved with
+// the counter update, 1 = all ballots of all items first (independent, so their latencies overlap), then the serial
+// counter chain, 2 = like 1 with one match.any per item instead of eight ballots.
+template <typename KeyT, typename ValT, int ITEMS, int RANK>
 __global__ void __launch_bounds__(RS_THREADS, 4)
 rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const ValT *__restrict__ vin,
                    ValT *__restrict__ vout, long long n, const int *__restrict__ n_dev, int shift, int nbits, int kind,
@@ -155,28 +162,63 @@ rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const 
   }
   // 2. warp-private ranking
   unsigned rank[ITEMS];
+  if constexpr (RANK == 0) {
 #pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const bool ok = (wbase + i * 32) < valid_n;
-    const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
-    // lanes holding the same digit: one ballot per digit bit.  (match.any does this in one instruction, but its
-    // latency -- ~30 % of this kernel's stall samples in the ncu source view, profiles/r01e -- makes the 8 votes faster)
-    unsigned peers = __ballot_sync(FULL, ok);
+    for (int i = 0; i < ITEMS; ++i) {
+      const bool ok = (wbase + i * 32) < valid_n;
+      const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
+      // lanes holding the same digit: one ballot per digit bit.  (match.any does this in one instruction, but its
+      // latency -- ~30 % of this kernel's stall samples in the ncu source view, profiles/r01e -- makes the 8 votes faster)
+      unsigned peers = __ballot_sync(FULL, ok);
 #pragma unroll
-    for (int b = 0; b < 8; ++b) {
-      const bool bit = (d >> b) & 1u;
-      const unsigned m = __ballot_sync(FULL, bit);
-      peers &= bit ? m : ~m;
+      for (int b = 0; b < 8; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const unsigned m = __ballot_sync(FULL, bit);
+        peers &= bit ? m : ~m;
+      }
+      const unsigned leader = __ffs(peers) - 1;
+      unsigned old = 0;
+      if (lane == leader && ok) {
+        old = S.warp_hist[warp][d];
+        S.warp_hist[warp][d] = old + __popc(peers);
+      }
+      old = __shfl_sync(FULL, old, leader);
+      rank[i] = old + __popc(peers & lanemask_lt());
+      __syncwarp();
     }
-    const unsigned leader = __ffs(peers) - 1;
-    unsigned old = 0;
-    if (lane == leader && ok) {
-      old = S.warp_hist[warp][d];
-      S.warp_hist[warp][d] = old + __popc(peers);
+  } else {
+    unsigned peers[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const bool ok = (wbase + i * 32) < valid_n;
+      const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
+      unsigned p = __ballot_sync(FULL, ok);
+      if constexpr (RANK == 2) {
+        p &= __match_any_sync(FULL, d);
+      } else {
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+          const bool bit = (d >> b) & 1u;
+          const unsigned m = __ballot_sync(FULL, bit);
+          p &= bit ? m : ~m;
+        }
+      }
+      peers[i] = p;
     }
-    old = __shfl_sync(FULL, old, leader);
-    rank[i] = old + __popc(peers & lanemask_lt());
-    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const bool ok = (wbase + i * 32) < valid_n;
+      const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
+      const unsigned leader = __ffs(peers[i]) - 1;
+      unsigned old = 0;
+      if (lane == leader && ok) {
+        old = S.warp_hist[warp][d];
+        S.warp_hist[warp][d] = old + __popc(peers[i]);
+      }
+      old = __shfl_sync(FULL, old, leader);
+      rank[i] = old + __popc(peers[i] & lanemask_lt());
+      __syncwarp();
+    }
   }
   __syncthreads();
   // 3. thread d owns digit d
@@ -266,6 +308,13 @@ static int rs_items(int kb, int vb) {
 }
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// QDSP_RS_RANK=0|1|2 picks the ranking variant of the sweep kernel (measurement aid; read once)
+static int rs_rank_variant() {
+  const char *e = std::getenv("QDSP_RS_RANK");
+  const int v = e ? std::atoi(e) : RS_DEFAULT_RANK;
+  return v >= 0 && v <= 2 ? v : RS_DEFAULT_RANK;
+}
+
 // aux = [tickets (8 passes) | histograms 8 x 256 | look-back words tiles x 256]
 struct RsLayout {
   size_t hist_off, lookback_off, aux_bytes, keys_off, vals_off, total;
@@ -314,7 +363,11 @@ static void *rs_run(KeyT *keys, ValT *vals, KeyT *kalt, ValT *valt, void *aux, i
   rs_scan_bins_kernel<<<passes, RS_RADIX, 0, stream>>>(hist);
   QDSP_LAUNCH_CHECK();
 
-  auto kernel = rs_onesweep_kernel<KeyT, ValT, ITEMS>;
+  using Kernel = decltype(&rs_onesweep_kernel<KeyT, ValT, ITEMS, 0>);
+  static const int rank_variant = rs_rank_variant();
+  const Kernel kernel = rank_variant == 1   ? rs_onesweep_kernel<KeyT, ValT, ITEMS, 1>
+                        : rank_variant == 2 ? rs_onesweep_kernel<KeyT, ValT, ITEMS, 2>
+                                            : rs_onesweep_kernel<KeyT, ValT, ITEMS, 0>;
   const size_t smem = rs_vals_offset<KeyT, ValT, ITEMS>() + static_cast<size_t>(TILE) * (VB ? VB : 0);
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
