@@ -28,7 +28,7 @@ constexpr int RS_RADIX = 256;
 constexpr size_t RS_HEADER_BYTES = 256;  // per-pass ticket counters (8 passes max)
 constexpr unsigned RS_FLAG_AGG = 1u << 30, RS_FLAG_PREFIX = 2u << 30, RS_FLAG_MASK = 3u << 30, RS_VAL_MASK = ~RS_FLAG_MASK;
 
-constexpr int RS_DEFAULT_RANK = 0;
+constexpr int RS_DEFAULT_VARIANT = 0;
 
 struct NoValue {};  // keys-only instantiation
 
@@ -119,10 +119,7 @@ __host__ __device__ constexpr size_t rs_vals_offset() {
   return (sizeof(RsSmem<KeyT, ValT, ITEMS>) + 15) / 16 * 16;
 }
 
-// RANK selects how the lanes that hold the same digit find each other: 0 = eight ballots per item interleaved with
-// the counter update, 1 = all ballots of all items first (independent, so their latencies overlap), then the serial
-// counter chain, 2 = like 1 with one match.any per item instead of eight ballots.
-template <typename KeyT, typename ValT, int ITEMS, int RANK>
+template <typename KeyT, typename ValT, int ITEMS>
 __global__ void __launch_bounds__(RS_THREADS, 4)
 rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const ValT *__restrict__ vin,
                    ValT *__restrict__ vout, long long n, const int *__restrict__ n_dev, int shift, int nbits, int kind,
@@ -162,63 +159,29 @@ rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const 
   }
   // 2. warp-private ranking
   unsigned rank[ITEMS];
-  if constexpr (RANK == 0) {
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-      const bool ok = (wbase + i * 32) < valid_n;
-      const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
-      // lanes holding the same digit: one ballot per digit bit.  (match.any does this in one instruction, but its
-      // latency -- ~30 % of this kernel's stall samples in the ncu source view, profiles/r01e -- makes the 8 votes faster)
-      unsigned peers = __ballot_sync(FULL, ok);
+  for (int i = 0; i < ITEMS; ++i) {
+    const bool ok = (wbase + i * 32) < valid_n;
+    const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
+    // lanes holding the same digit: one ballot per digit bit.  (match.any does this in one instruction, but it is
+    // slower: 0.85 vs 0.59 ms per pass at 2^26 pairs even with all matches issued ahead of the counter chain,
+    // profiles/r01n_sort_variants.jsonl)
+    unsigned peers = __ballot_sync(FULL, ok);
 #pragma unroll
-      for (int b = 0; b < 8; ++b) {
-        const bool bit = (d >> b) & 1u;
-        const unsigned m = __ballot_sync(FULL, bit);
-        peers &= bit ? m : ~m;
-      }
-      const unsigned leader = __ffs(peers) - 1;
-      unsigned old = 0;
-      if (lane == leader && ok) {
-        old = S.warp_hist[warp][d];
-        S.warp_hist[warp][d] = old + __popc(peers);
-      }
-      old = __shfl_sync(FULL, old, leader);
-      rank[i] = old + __popc(peers & lanemask_lt());
-      __syncwarp();
+    for (int b = 0; b < 8; ++b) {
+      const bool bit = (d >> b) & 1u;
+      const unsigned m = __ballot_sync(FULL, bit);
+      peers &= bit ? m : ~m;
     }
-  } else {
-    unsigned peers[ITEMS];
-#pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-      const bool ok = (wbase + i * 32) < valid_n;
-      const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
-      unsigned p = __ballot_sync(FULL, ok);
-      if constexpr (RANK == 2) {
-        p &= __match_any_sync(FULL, d);
-      } else {
-#pragma unroll
-        for (int b = 0; b < 8; ++b) {
-          const bool bit = (d >> b) & 1u;
-          const unsigned m = __ballot_sync(FULL, bit);
-          p &= bit ? m : ~m;
-        }
-      }
-      peers[i] = p;
+    const unsigned leader = __ffs(peers) - 1;
+    unsigned old = 0;
+    if (lane == leader && ok) {
+      old = S.warp_hist[warp][d];
+      S.warp_hist[warp][d] = old + __popc(peers);
     }
-#pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-      const bool ok = (wbase + i * 32) < valid_n;
-      const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
-      const unsigned leader = __ffs(peers[i]) - 1;
-      unsigned old = 0;
-      if (lane == leader && ok) {
-        old = S.warp_hist[warp][d];
-        S.warp_hist[warp][d] = old + __popc(peers[i]);
-      }
-      old = __shfl_sync(FULL, old, leader);
-      rank[i] = old + __popc(peers[i] & lanemask_lt());
-      __syncwarp();
-    }
+    old = __shfl_sync(FULL, old, leader);
+    rank[i] = old + __popc(peers & lanemask_lt());
+    __syncwarp();
   }
   __syncthreads();
   // 3. thread d owns digit d
@@ -295,6 +258,181 @@ rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const 
   }
 }
 
+// peers &= (lanes whose digit bit B equals mine): and+setp -> one predicate-setting LOP3, one VOTE, one SEL, one LOP3
+// (the C++ form `peers &= bit ? m : ~m` compiles to six instructions per bit)
+template <int B>
+__device__ __forceinline__ void rs_peer_step(unsigned &peers, unsigned d) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b32 t, m, s;\n\t"
+      "and.b32 t, %1, %2;\n\t"
+      "setp.ne.u32 p, t, 0;\n\t"
+      "vote.sync.ballot.b32 m, p, 0xffffffff;\n\t"
+      "selp.b32 s, 0, 0xffffffff, p;\n\t"
+      "xor.b32 m, m, s;\n\t"
+      "and.b32 %0, %0, m;\n\t"
+      "}"
+      : "+r"(peers)
+      : "r"(d), "n"(1u << B));
+}
+
+// ---- the same sweep, instruction-trimmed (the kernel is issue-bound: ~150 thread instructions per key and 50 % issue
+// utilisation in profiles/r01n_kernel_onesweep.txt, DRAM at 21 %) --------------------------------------------------------
+//  * full tiles (all but the last) run a body without any per-item bounds test;
+//  * digit bits are tested in place (d & (1 << b)) instead of shift-mask-compare;
+//  * the global output index of each tile-sorted position is computed once and reused for the value.
+template <typename KeyT, typename ValT, int ITEMS, bool FULL_TILE>
+__device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT *s_vals, const KeyT *__restrict__ kin,
+                                              KeyT *__restrict__ kout, const ValT *__restrict__ vin,
+                                              ValT *__restrict__ vout, long long tile_base, int valid_n, int shift,
+                                              unsigned dmask, int kind, int tw_in, int tw_out, unsigned tile,
+                                              unsigned *__restrict__ lookback, const unsigned *__restrict__ bins) {
+  constexpr bool HAS_VAL = !std::is_same<ValT, NoValue>::value;
+  const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
+  KeyT key[ITEMS];
+  ValT val[ITEMS];
+  const int wbase = warp * 32 * ITEMS + lane;
+  const KeyT *kp = kin + tile_base + wbase;
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    if (FULL_TILE || wbase + i * 32 < valid_n) {
+      const KeyT k = kp[i * 32];
+      key[i] = tw_in ? twiddle_in(k, kind) : k;
+    } else {
+      key[i] = static_cast<KeyT>(~KeyT(0));
+    }
+  }
+  if constexpr (HAS_VAL) {
+    const ValT *vp = vin + tile_base + wbase;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i)
+      if (FULL_TILE || wbase + i * 32 < valid_n) val[i] = vp[i * 32];
+  }
+  unsigned *my_hist = &S.warp_hist[warp][0];
+  unsigned rank[ITEMS];
+  const unsigned lt = lanemask_lt();
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const bool ok = FULL_TILE || (wbase + i * 32 < valid_n);
+    const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
+    unsigned peers = FULL_TILE ? FULL : __ballot_sync(FULL, ok);
+    rs_peer_step<0>(peers, d);
+    rs_peer_step<1>(peers, d);
+    rs_peer_step<2>(peers, d);
+    rs_peer_step<3>(peers, d);
+    rs_peer_step<4>(peers, d);
+    rs_peer_step<5>(peers, d);
+    rs_peer_step<6>(peers, d);
+    rs_peer_step<7>(peers, d);
+    const unsigned leader = __ffs(peers) - 1;
+    unsigned old = 0;
+    if (lane == leader && ok) {
+      old = my_hist[d];
+      my_hist[d] = old + __popc(peers);
+    }
+    old = __shfl_sync(FULL, old, leader);
+    rank[i] = old + __popc(peers & lt);
+    __syncwarp();
+  }
+  __syncthreads();
+  {
+    const unsigned d = threadIdx.x;
+    unsigned sum = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w) {
+      const unsigned t = S.warp_hist[w][d];
+      S.warp_hist[w][d] = sum;
+      sum += t;
+    }
+    const unsigned count = sum;
+    unsigned *my = lookback + static_cast<size_t>(tile) * RS_RADIX + d;
+    unsigned exclusive = 0;
+    if (tile == 0) {
+      st_relaxed_u32(my, RS_FLAG_PREFIX | count);
+    } else {
+      st_relaxed_u32(my, RS_FLAG_AGG | count);
+      const unsigned *q = my - RS_RADIX;
+      while (true) {
+        unsigned v;
+        do { v = ld_relaxed_u32(q); } while ((v & RS_FLAG_MASK) == 0u);
+        exclusive += v & RS_VAL_MASK;
+        if ((v & RS_FLAG_MASK) == RS_FLAG_PREFIX) break;
+        q -= RS_RADIX;
+      }
+      st_relaxed_u32(my, RS_FLAG_PREFIX | ((exclusive + count) & RS_VAL_MASK));
+    }
+    const unsigned incl = warp_inclusive_scan(count);
+    if (lane == 31) S.warp_tot[warp] = incl;
+    __syncthreads();
+    unsigned wpre = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w)
+      if (w < (int)warp) wpre += S.warp_tot[w];
+    const unsigned start = wpre + incl - count;
+    S.digit_start[d] = start;
+    S.gbase[d] = bins[d] + exclusive - start;
+  }
+  __syncthreads();
+  unsigned pos[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
+    pos[i] = S.digit_start[d] + my_hist[d] + rank[i];
+    if (FULL_TILE || wbase + i * 32 < valid_n) S.keys[pos[i]] = key[i];
+  }
+  __syncthreads();
+  unsigned out_idx[ITEMS];  // global index of tile-sorted position threadIdx.x + i * 256
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const int p = threadIdx.x + i * RS_THREADS;
+    if (FULL_TILE || p < valid_n) {
+      const KeyT k = S.keys[p];
+      const unsigned d = static_cast<unsigned>(k >> shift) & dmask;
+      out_idx[i] = S.gbase[d] + p;
+      kout[out_idx[i]] = tw_out ? twiddle_out(k, kind) : k;
+    }
+  }
+  if constexpr (HAS_VAL) {
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i)
+      if (FULL_TILE || wbase + i * 32 < valid_n) s_vals[pos[i]] = val[i];
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int p = threadIdx.x + i * RS_THREADS;
+      if (FULL_TILE || p < valid_n) vout[out_idx[i]] = s_vals[p];
+    }
+  }
+}
+
+template <typename KeyT, typename ValT, int ITEMS>
+__global__ void __launch_bounds__(RS_THREADS, 4)
+rs_onesweep_v2_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const ValT *__restrict__ vin,
+                      ValT *__restrict__ vout, long long n, const int *__restrict__ n_dev, int shift, int nbits,
+                      int kind, int tw_in, int tw_out, unsigned *__restrict__ ticket,
+                      unsigned *__restrict__ lookback /* tiles x 256 */, const unsigned *__restrict__ bins) {
+  constexpr int TILE = RS_THREADS * ITEMS;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  auto &S = *reinterpret_cast<RsSmem<KeyT, ValT, ITEMS> *>(s_raw);
+  ValT *s_vals = reinterpret_cast<ValT *>(s_raw + rs_vals_offset<KeyT, ValT, ITEMS>());
+  if (threadIdx.x == 0) S.ticket = atomicAdd(ticket, 1u);
+  for (int i = threadIdx.x; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&S.warp_hist[0][0])[i] = 0;
+  __syncthreads();
+  const unsigned tile = S.ticket;
+  const long long tile_base = static_cast<long long>(tile) * TILE;
+  n = rs_count(n, n_dev);
+  if (tile_base >= n) return;
+  const int valid_n = static_cast<int>(min(static_cast<long long>(TILE), n - tile_base));
+  const unsigned dmask = (1u << nbits) - 1u;
+  if (valid_n == TILE)
+    rs_sweep_tile<KeyT, ValT, ITEMS, true>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind, tw_in,
+                                           tw_out, tile, lookback, bins);
+  else
+    rs_sweep_tile<KeyT, ValT, ITEMS, false>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind,
+                                            tw_in, tw_out, tile, lookback, bins);
+}
+
 // ---- host driver ---------------------------------------------------------------------------------------------------
 template <int KB, int VB> struct RsItems { static constexpr int value = 16; };
 template <> struct RsItems<4, 8> { static constexpr int value = 12; };
@@ -308,11 +446,11 @@ static int rs_items(int kb, int vb) {
 }
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-// QDSP_RS_RANK=0|1|2 picks the ranking variant of the sweep kernel (measurement aid; read once)
-static int rs_rank_variant() {
-  const char *e = std::getenv("QDSP_RS_RANK");
-  const int v = e ? std::atoi(e) : RS_DEFAULT_RANK;
-  return v >= 0 && v <= 2 ? v : RS_DEFAULT_RANK;
+// QDSP_RS_VARIANT=0|1 picks the sweep kernel (0 = rs_onesweep_kernel, 1 = the instruction-trimmed v2); read once
+static int rs_variant() {
+  const char *e = std::getenv("QDSP_RS_VARIANT");
+  const int v = e ? std::atoi(e) : RS_DEFAULT_VARIANT;
+  return v == 0 || v == 1 ? v : RS_DEFAULT_VARIANT;
 }
 
 // aux = [tickets (8 passes) | histograms 8 x 256 | look-back words tiles x 256]
@@ -363,11 +501,9 @@ static void *rs_run(KeyT *keys, ValT *vals, KeyT *kalt, ValT *valt, void *aux, i
   rs_scan_bins_kernel<<<passes, RS_RADIX, 0, stream>>>(hist);
   QDSP_LAUNCH_CHECK();
 
-  using Kernel = decltype(&rs_onesweep_kernel<KeyT, ValT, ITEMS, 0>);
-  static const int rank_variant = rs_rank_variant();
-  const Kernel kernel = rank_variant == 1   ? rs_onesweep_kernel<KeyT, ValT, ITEMS, 1>
-                        : rank_variant == 2 ? rs_onesweep_kernel<KeyT, ValT, ITEMS, 2>
-                                            : rs_onesweep_kernel<KeyT, ValT, ITEMS, 0>;
+  using Kernel = decltype(&rs_onesweep_kernel<KeyT, ValT, ITEMS>);
+  static const int variant = rs_variant();
+  const Kernel kernel = variant == 1 ? rs_onesweep_v2_kernel<KeyT, ValT, ITEMS> : rs_onesweep_kernel<KeyT, ValT, ITEMS>;
   const size_t smem = rs_vals_offset<KeyT, ValT, ITEMS>() + static_cast<size_t>(TILE) * (VB ? VB : 0);
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
