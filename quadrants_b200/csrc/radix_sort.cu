@@ -28,7 +28,7 @@ constexpr int RS_RADIX = 256;
 constexpr size_t RS_HEADER_BYTES = 256;  // per-pass ticket counters (8 passes max)
 constexpr unsigned RS_FLAG_AGG = 1u << 30, RS_FLAG_PREFIX = 2u << 30, RS_FLAG_MASK = 3u << 30, RS_VAL_MASK = ~RS_FLAG_MASK;
 
-constexpr int RS_DEFAULT_VARIANT = 0;
+constexpr int RS_DEFAULT_VARIANT = 1;  // +16 % (key-value) / +28 % (keys only) over variant 0, profiles/r01o
 
 struct NoValue {};  // keys-only instantiation
 
@@ -282,7 +282,56 @@ __device__ __forceinline__ void rs_peer_step(unsigned &peers, unsigned d) {
 //  * full tiles (all but the last) run a body without any per-item bounds test;
 //  * digit bits are tested in place (d & (1 << b)) instead of shift-mask-compare;
 //  * the global output index of each tile-sorted position is computed once and reused for the value.
-template <typename KeyT, typename ValT, int ITEMS, bool FULL_TILE>
+// look-back of one digit column: `my` = this tile's descriptor (aggregate already published).  Returns the exclusive
+// prefix and publishes the inclusive one.
+__device__ __forceinline__ unsigned rs_lookback_serial(unsigned *my, unsigned tile, unsigned count) {
+  if (tile == 0) return 0u;
+  unsigned exclusive = 0;
+  const unsigned *q = my - RS_RADIX;
+  while (true) {
+    unsigned v;
+    do { v = ld_relaxed_u32(q); } while ((v & RS_FLAG_MASK) == 0u);
+    exclusive += v & RS_VAL_MASK;
+    if ((v & RS_FLAG_MASK) == RS_FLAG_PREFIX) break;
+    q -= RS_RADIX;
+  }
+  st_relaxed_u32(my, RS_FLAG_PREFIX | ((exclusive + count) & RS_VAL_MASK));
+  return exclusive;
+}
+
+// Same walk, RS_LB_BATCH predecessors per round: the loads of a round are independent (one L2 latency for all of them);
+// a descriptor that is not published yet ends the round and is polled again at the head of the next one.
+constexpr int RS_LB_BATCH = 8;
+__device__ __forceinline__ unsigned rs_lookback_batched(unsigned *my, unsigned tile, unsigned count) {
+  if (tile == 0) return 0u;
+  unsigned exclusive = 0;
+  long long t = static_cast<long long>(tile) - 1;  // next predecessor to consume
+  const unsigned *col = my - static_cast<size_t>(tile) * RS_RADIX;  // descriptor of tile 0 for this digit
+  bool done = false;
+  while (!done) {
+    unsigned v[RS_LB_BATCH];
+#pragma unroll
+    for (int j = 0; j < RS_LB_BATCH; ++j)
+      v[j] = (t - j >= 0) ? ld_relaxed_u32(col + static_cast<size_t>(t - j) * RS_RADIX) : RS_FLAG_PREFIX;
+    int used = 0;
+#pragma unroll
+    for (int j = 0; j < RS_LB_BATCH; ++j) {
+      if (!done && used == j) {
+        const unsigned f = v[j] & RS_FLAG_MASK;
+        if (f != 0u) {
+          exclusive += v[j] & RS_VAL_MASK;
+          used = j + 1;
+          if (f == RS_FLAG_PREFIX) done = true;
+        }
+      }
+    }
+    t -= used;
+  }
+  st_relaxed_u32(my, RS_FLAG_PREFIX | ((exclusive + count) & RS_VAL_MASK));
+  return exclusive;
+}
+
+template <typename KeyT, typename ValT, int ITEMS, bool FULL_TILE, bool LATE_LB>
 __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT *s_vals, const KeyT *__restrict__ kin,
                                               KeyT *__restrict__ kout, const ValT *__restrict__ vin,
                                               ValT *__restrict__ vout, long long tile_base, int valid_n, int shift,
@@ -336,7 +385,10 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
     __syncwarp();
   }
   __syncthreads();
+  // thread d owns digit d: tile count, publication of the aggregate, tile-local digit offsets
   {
+    unsigned count, start, exclusive = 0;
+    unsigned *my = lookback + static_cast<size_t>(tile) * RS_RADIX + threadIdx.x;
     const unsigned d = threadIdx.x;
     unsigned sum = 0;
 #pragma unroll
@@ -345,23 +397,9 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
       S.warp_hist[w][d] = sum;
       sum += t;
     }
-    const unsigned count = sum;
-    unsigned *my = lookback + static_cast<size_t>(tile) * RS_RADIX + d;
-    unsigned exclusive = 0;
-    if (tile == 0) {
-      st_relaxed_u32(my, RS_FLAG_PREFIX | count);
-    } else {
-      st_relaxed_u32(my, RS_FLAG_AGG | count);
-      const unsigned *q = my - RS_RADIX;
-      while (true) {
-        unsigned v;
-        do { v = ld_relaxed_u32(q); } while ((v & RS_FLAG_MASK) == 0u);
-        exclusive += v & RS_VAL_MASK;
-        if ((v & RS_FLAG_MASK) == RS_FLAG_PREFIX) break;
-        q -= RS_RADIX;
-      }
-      st_relaxed_u32(my, RS_FLAG_PREFIX | ((exclusive + count) & RS_VAL_MASK));
-    }
+    count = sum;
+    st_relaxed_u32(my, (tile == 0 ? RS_FLAG_PREFIX : RS_FLAG_AGG) | count);
+    if constexpr (!LATE_LB) exclusive = rs_lookback_serial(my, tile, count);
     const unsigned incl = warp_inclusive_scan(count);
     if (lane == 31) S.warp_tot[warp] = incl;
     __syncthreads();
@@ -369,9 +407,10 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
 #pragma unroll
     for (int w = 0; w < RS_WARPS; ++w)
       if (w < (int)warp) wpre += S.warp_tot[w];
-    const unsigned start = wpre + incl - count;
+    start = wpre + incl - count;
     S.digit_start[d] = start;
-    S.gbase[d] = bins[d] + exclusive - start;
+    if constexpr (!LATE_LB) S.gbase[d] = bins[d] + exclusive - start;
+    else S.gbase[d] = count;  // parked in shared memory across the scatter (registers are at the 64 cap there)
   }
   __syncthreads();
   unsigned pos[ITEMS];
@@ -380,6 +419,19 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
     const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
     pos[i] = S.digit_start[d] + my_hist[d] + rank[i];
     if (FULL_TILE || wbase + i * 32 < valid_n) S.keys[pos[i]] = key[i];
+  }
+  if constexpr (HAS_VAL) {
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i)
+      if (FULL_TILE || wbase + i * 32 < valid_n) s_vals[pos[i]] = val[i];
+  }
+  if constexpr (LATE_LB) {
+    // the look-back runs only now: the predecessors had the whole shared-memory scatter to publish their counts, so
+    // far fewer polls are spent spinning (the spin loop was 22 % of the stall samples and 20 % of the executed
+    // instructions, profiles/r01n_kernel_onesweep.txt), and eight predecessors are fetched per round trip
+    const unsigned cnt = S.gbase[threadIdx.x];
+    const unsigned ex = rs_lookback_batched(lookback + static_cast<size_t>(tile) * RS_RADIX + threadIdx.x, tile, cnt);
+    S.gbase[threadIdx.x] = bins[threadIdx.x] + ex - S.digit_start[threadIdx.x];
   }
   __syncthreads();
   unsigned out_idx[ITEMS];  // global index of tile-sorted position threadIdx.x + i * 256
@@ -395,10 +447,6 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
   }
   if constexpr (HAS_VAL) {
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i)
-      if (FULL_TILE || wbase + i * 32 < valid_n) s_vals[pos[i]] = val[i];
-    __syncthreads();
-#pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
       const int p = threadIdx.x + i * RS_THREADS;
       if (FULL_TILE || p < valid_n) vout[out_idx[i]] = s_vals[p];
@@ -406,7 +454,7 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
   }
 }
 
-template <typename KeyT, typename ValT, int ITEMS>
+template <typename KeyT, typename ValT, int ITEMS, bool LATE_LB>
 __global__ void __launch_bounds__(RS_THREADS, 4)
 rs_onesweep_v2_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const ValT *__restrict__ vin,
                       ValT *__restrict__ vout, long long n, const int *__restrict__ n_dev, int shift, int nbits,
@@ -426,10 +474,10 @@ rs_onesweep_v2_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, con
   const int valid_n = static_cast<int>(min(static_cast<long long>(TILE), n - tile_base));
   const unsigned dmask = (1u << nbits) - 1u;
   if (valid_n == TILE)
-    rs_sweep_tile<KeyT, ValT, ITEMS, true>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind, tw_in,
+    rs_sweep_tile<KeyT, ValT, ITEMS, true, LATE_LB>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind, tw_in,
                                            tw_out, tile, lookback, bins);
   else
-    rs_sweep_tile<KeyT, ValT, ITEMS, false>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind,
+    rs_sweep_tile<KeyT, ValT, ITEMS, false, LATE_LB>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind,
                                             tw_in, tw_out, tile, lookback, bins);
 }
 
@@ -446,11 +494,12 @@ static int rs_items(int kb, int vb) {
 }
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-// QDSP_RS_VARIANT=0|1 picks the sweep kernel (0 = rs_onesweep_kernel, 1 = the instruction-trimmed v2); read once
+// QDSP_RS_VARIANT picks the sweep kernel: 0 = rs_onesweep_kernel, 1 = the instruction-trimmed v2, 2 = v2 with the
+// look-back after the shared-memory scatter, eight predecessors per round; read once
 static int rs_variant() {
   const char *e = std::getenv("QDSP_RS_VARIANT");
   const int v = e ? std::atoi(e) : RS_DEFAULT_VARIANT;
-  return v == 0 || v == 1 ? v : RS_DEFAULT_VARIANT;
+  return v >= 0 && v <= 2 ? v : RS_DEFAULT_VARIANT;
 }
 
 // aux = [tickets (8 passes) | histograms 8 x 256 | look-back words tiles x 256]
@@ -503,7 +552,9 @@ static void *rs_run(KeyT *keys, ValT *vals, KeyT *kalt, ValT *valt, void *aux, i
 
   using Kernel = decltype(&rs_onesweep_kernel<KeyT, ValT, ITEMS>);
   static const int variant = rs_variant();
-  const Kernel kernel = variant == 1 ? rs_onesweep_v2_kernel<KeyT, ValT, ITEMS> : rs_onesweep_kernel<KeyT, ValT, ITEMS>;
+  const Kernel kernel = variant == 1   ? rs_onesweep_v2_kernel<KeyT, ValT, ITEMS, false>
+                        : variant == 2 ? rs_onesweep_v2_kernel<KeyT, ValT, ITEMS, true>
+                                       : rs_onesweep_kernel<KeyT, ValT, ITEMS>;
   const size_t smem = rs_vals_offset<KeyT, ValT, ITEMS>() + static_cast<size_t>(TILE) * (VB ? VB : 0);
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
