@@ -28,8 +28,6 @@ constexpr int RS_RADIX = 256;
 constexpr size_t RS_HEADER_BYTES = 256;  // per-pass ticket counters (8 passes max)
 constexpr unsigned RS_FLAG_AGG = 1u << 30, RS_FLAG_PREFIX = 2u << 30, RS_FLAG_MASK = 3u << 30, RS_VAL_MASK = ~RS_FLAG_MASK;
 
-constexpr int RS_DEFAULT_VARIANT = 1;  // +16 % (key-value) / +28 % (keys only) over variant 0, profiles/r01o
-
 struct NoValue {};  // keys-only instantiation
 
 template <typename KeyT>
@@ -119,145 +117,6 @@ __host__ __device__ constexpr size_t rs_vals_offset() {
   return (sizeof(RsSmem<KeyT, ValT, ITEMS>) + 15) / 16 * 16;
 }
 
-template <typename KeyT, typename ValT, int ITEMS>
-__global__ void __launch_bounds__(RS_THREADS, 4)
-rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const ValT *__restrict__ vin,
-                   ValT *__restrict__ vout, long long n, const int *__restrict__ n_dev, int shift, int nbits, int kind,
-                   int tw_in, int tw_out, unsigned *__restrict__ ticket, unsigned *__restrict__ lookback /* tiles x 256 */,
-                   const unsigned *__restrict__ bins /* exclusive-scanned histogram of this pass */) {
-  constexpr bool HAS_VAL = !std::is_same<ValT, NoValue>::value;
-  constexpr int TILE = RS_THREADS * ITEMS;
-  extern __shared__ __align__(16) unsigned char s_raw[];
-  auto &S = *reinterpret_cast<RsSmem<KeyT, ValT, ITEMS> *>(s_raw);
-  ValT *s_vals = reinterpret_cast<ValT *>(s_raw + rs_vals_offset<KeyT, ValT, ITEMS>());
-
-  if (threadIdx.x == 0) S.ticket = atomicAdd(ticket, 1u);
-  for (int i = threadIdx.x; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&S.warp_hist[0][0])[i] = 0;
-  __syncthreads();
-  const unsigned tile = S.ticket;
-  const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
-  const long long tile_base = static_cast<long long>(tile) * TILE;
-  n = rs_count(n, n_dev);
-  if (tile_base >= n) return;  // device-resident count below the capacity: the grid is sized for the capacity
-  const int valid_n = static_cast<int>(min(static_cast<long long>(TILE), n - tile_base));
-  const unsigned dmask = (1u << nbits) - 1u;
-
-  // 1. loads: item i of lane l of warp w <-> tile position w*32*ITEMS + i*32 + l
-  KeyT key[ITEMS];
-  ValT val[ITEMS];
-  const int wbase = warp * 32 * ITEMS + lane;
-#pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const int p = wbase + i * 32;
-    if (p < valid_n) {
-      KeyT k = kin[tile_base + p];
-      key[i] = tw_in ? twiddle_in(k, kind) : k;
-      if constexpr (HAS_VAL) val[i] = vin[tile_base + p];
-    } else {
-      key[i] = static_cast<KeyT>(~KeyT(0));
-    }
-  }
-  // 2. warp-private ranking
-  unsigned rank[ITEMS];
-#pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const bool ok = (wbase + i * 32) < valid_n;
-    const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
-    // lanes holding the same digit: one ballot per digit bit.  (match.any does this in one instruction, but it is
-    // slower: 0.85 vs 0.59 ms per pass at 2^26 pairs even with all matches issued ahead of the counter chain,
-    // profiles/r01n_sort_variants.jsonl)
-    unsigned peers = __ballot_sync(FULL, ok);
-#pragma unroll
-    for (int b = 0; b < 8; ++b) {
-      const bool bit = (d >> b) & 1u;
-      const unsigned m = __ballot_sync(FULL, bit);
-      peers &= bit ? m : ~m;
-    }
-    const unsigned leader = __ffs(peers) - 1;
-    unsigned old = 0;
-    if (lane == leader && ok) {
-      old = S.warp_hist[warp][d];
-      S.warp_hist[warp][d] = old + __popc(peers);
-    }
-    old = __shfl_sync(FULL, old, leader);
-    rank[i] = old + __popc(peers & lanemask_lt());
-    __syncwarp();
-  }
-  __syncthreads();
-  // 3. thread d owns digit d
-  {
-    const unsigned d = threadIdx.x;
-    unsigned sum = 0;
-#pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w) {
-      const unsigned t = S.warp_hist[w][d];
-      S.warp_hist[w][d] = sum;  // exclusive offset of warp w inside digit d
-      sum += t;
-    }
-    const unsigned count = sum;
-    unsigned *my = lookback + static_cast<size_t>(tile) * RS_RADIX + d;
-    unsigned exclusive = 0;
-    if (tile == 0) {
-      st_relaxed_u32(my, RS_FLAG_PREFIX | count);
-    } else {
-      st_relaxed_u32(my, RS_FLAG_AGG | count);
-      const unsigned *q = my - RS_RADIX;
-      while (true) {
-        unsigned v;
-        do { v = ld_relaxed_u32(q); } while ((v & RS_FLAG_MASK) == 0u);
-        exclusive += v & RS_VAL_MASK;
-        if ((v & RS_FLAG_MASK) == RS_FLAG_PREFIX) break;
-        q -= RS_RADIX;
-      }
-      st_relaxed_u32(my, RS_FLAG_PREFIX | ((exclusive + count) & RS_VAL_MASK));
-    }
-    // block-exclusive scan of count over the 256 digits
-    const unsigned incl = warp_inclusive_scan(count);
-    if (lane == 31) S.warp_tot[warp] = incl;
-    __syncthreads();
-    unsigned wpre = 0;
-#pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w)
-      if (w < (int)warp) wpre += S.warp_tot[w];
-    const unsigned start = wpre + incl - count;
-    S.digit_start[d] = start;
-    S.gbase[d] = bins[d] + exclusive - start;
-  }
-  __syncthreads();
-  // 4. tile-sorted order in shared memory, then coalesced runs to global memory
-  unsigned pos[ITEMS];
-#pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const unsigned d = static_cast<unsigned>(key[i] >> shift) & dmask;
-    pos[i] = S.digit_start[d] + S.warp_hist[warp][d] + rank[i];
-    if ((wbase + i * 32) < valid_n) S.keys[pos[i]] = key[i];
-  }
-  __syncthreads();
-#pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const int p = threadIdx.x + i * RS_THREADS;
-    if (p < valid_n) {
-      const KeyT k = S.keys[p];
-      const unsigned d = static_cast<unsigned>(k >> shift) & dmask;
-      kout[S.gbase[d] + p] = tw_out ? twiddle_out(k, kind) : k;
-    }
-  }
-  if constexpr (HAS_VAL) {
-#pragma unroll
-    for (int i = 0; i < ITEMS; ++i)
-      if ((wbase + i * 32) < valid_n) s_vals[pos[i]] = val[i];
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-      const int p = threadIdx.x + i * RS_THREADS;
-      if (p < valid_n) {
-        const unsigned d = static_cast<unsigned>(S.keys[p] >> shift) & dmask;
-        vout[S.gbase[d] + p] = s_vals[p];
-      }
-    }
-  }
-}
-
 // peers &= (lanes whose digit bit B equals mine): and+setp -> one predicate-setting LOP3, one VOTE, one SEL, one LOP3
 // (the C++ form `peers &= bit ? m : ~m` compiles to six instructions per bit)
 template <int B>
@@ -282,24 +141,8 @@ __device__ __forceinline__ void rs_peer_step(unsigned &peers, unsigned d) {
 //  * full tiles (all but the last) run a body without any per-item bounds test;
 //  * digit bits are tested in place (d & (1 << b)) instead of shift-mask-compare;
 //  * the global output index of each tile-sorted position is computed once and reused for the value.
-// look-back of one digit column: `my` = this tile's descriptor (aggregate already published).  Returns the exclusive
-// prefix and publishes the inclusive one.
-__device__ __forceinline__ unsigned rs_lookback_serial(unsigned *my, unsigned tile, unsigned count) {
-  if (tile == 0) return 0u;
-  unsigned exclusive = 0;
-  const unsigned *q = my - RS_RADIX;
-  while (true) {
-    unsigned v;
-    do { v = ld_relaxed_u32(q); } while ((v & RS_FLAG_MASK) == 0u);
-    exclusive += v & RS_VAL_MASK;
-    if ((v & RS_FLAG_MASK) == RS_FLAG_PREFIX) break;
-    q -= RS_RADIX;
-  }
-  st_relaxed_u32(my, RS_FLAG_PREFIX | ((exclusive + count) & RS_VAL_MASK));
-  return exclusive;
-}
-
-// Same walk, RS_LB_BATCH predecessors per round: the loads of a round are independent (one L2 latency for all of them);
+// Look-back of one digit column: `my` = this tile's descriptor (aggregate already published); returns the exclusive
+// prefix and publishes the inclusive one.  RS_LB_BATCH predecessors per round: the loads of a round are independent (one L2 latency for all of them);
 // a descriptor that is not published yet ends the round and is polled again at the head of the next one.
 constexpr int RS_LB_BATCH = 8;
 __device__ __forceinline__ unsigned rs_lookback_batched(unsigned *my, unsigned tile, unsigned count) {
@@ -331,7 +174,7 @@ __device__ __forceinline__ unsigned rs_lookback_batched(unsigned *my, unsigned t
   return exclusive;
 }
 
-template <typename KeyT, typename ValT, int ITEMS, bool FULL_TILE, bool LATE_LB>
+template <typename KeyT, typename ValT, int ITEMS, bool FULL_TILE>
 __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT *s_vals, const KeyT *__restrict__ kin,
                                               KeyT *__restrict__ kout, const ValT *__restrict__ vin,
                                               ValT *__restrict__ vout, long long tile_base, int valid_n, int shift,
@@ -387,7 +230,7 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
   __syncthreads();
   // thread d owns digit d: tile count, publication of the aggregate, tile-local digit offsets
   {
-    unsigned count, start, exclusive = 0;
+    unsigned count, start;
     unsigned *my = lookback + static_cast<size_t>(tile) * RS_RADIX + threadIdx.x;
     const unsigned d = threadIdx.x;
     unsigned sum = 0;
@@ -399,7 +242,6 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
     }
     count = sum;
     st_relaxed_u32(my, (tile == 0 ? RS_FLAG_PREFIX : RS_FLAG_AGG) | count);
-    if constexpr (!LATE_LB) exclusive = rs_lookback_serial(my, tile, count);
     const unsigned incl = warp_inclusive_scan(count);
     if (lane == 31) S.warp_tot[warp] = incl;
     __syncthreads();
@@ -409,8 +251,7 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
       if (w < (int)warp) wpre += S.warp_tot[w];
     start = wpre + incl - count;
     S.digit_start[d] = start;
-    if constexpr (!LATE_LB) S.gbase[d] = bins[d] + exclusive - start;
-    else S.gbase[d] = count;  // parked in shared memory across the scatter (registers are at the 64 cap there)
+    S.gbase[d] = count;  // parked in shared memory across the scatter (registers are at their cap there)
   }
   __syncthreads();
   unsigned pos[ITEMS];
@@ -425,7 +266,7 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
     for (int i = 0; i < ITEMS; ++i)
       if (FULL_TILE || wbase + i * 32 < valid_n) s_vals[pos[i]] = val[i];
   }
-  if constexpr (LATE_LB) {
+  {
     // the look-back runs only now: the predecessors had the whole shared-memory scatter to publish their counts, so
     // far fewer polls are spent spinning (the spin loop was 22 % of the stall samples and 20 % of the executed
     // instructions, profiles/r01n_kernel_onesweep.txt), and eight predecessors are fetched per round trip
@@ -454,9 +295,9 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
   }
 }
 
-template <typename KeyT, typename ValT, int ITEMS, bool LATE_LB>
-__global__ void __launch_bounds__(RS_THREADS, 4)
-rs_onesweep_v2_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const ValT *__restrict__ vin,
+template <typename KeyT, typename ValT, int ITEMS, int MINB>
+__global__ void __launch_bounds__(RS_THREADS, MINB)
+rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const ValT *__restrict__ vin,
                       ValT *__restrict__ vout, long long n, const int *__restrict__ n_dev, int shift, int nbits,
                       int kind, int tw_in, int tw_out, unsigned *__restrict__ ticket,
                       unsigned *__restrict__ lookback /* tiles x 256 */, const unsigned *__restrict__ bins) {
@@ -474,33 +315,30 @@ rs_onesweep_v2_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, con
   const int valid_n = static_cast<int>(min(static_cast<long long>(TILE), n - tile_base));
   const unsigned dmask = (1u << nbits) - 1u;
   if (valid_n == TILE)
-    rs_sweep_tile<KeyT, ValT, ITEMS, true, LATE_LB>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind, tw_in,
+    rs_sweep_tile<KeyT, ValT, ITEMS, true>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind, tw_in,
                                            tw_out, tile, lookback, bins);
   else
-    rs_sweep_tile<KeyT, ValT, ITEMS, false, LATE_LB>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind,
+    rs_sweep_tile<KeyT, ValT, ITEMS, false>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind,
                                             tw_in, tw_out, tile, lookback, bins);
 }
 
 // ---- host driver ---------------------------------------------------------------------------------------------------
-template <int KB, int VB> struct RsItems { static constexpr int value = 16; };
-template <> struct RsItems<4, 8> { static constexpr int value = 12; };
-template <> struct RsItems<8, 0> { static constexpr int value = 12; };
-template <> struct RsItems<8, 4> { static constexpr int value = 12; };
-template <> struct RsItems<8, 8> { static constexpr int value = 8; };
-
+// Keys per thread (tile = 256 x ITEMS) and resident CTAs per SM the kernel is compiled for.  Wider items -> fewer
+// keys per thread so that key + value + rank registers stay under the cap.  QDSP_RS_ITEMS=8|12|16 overrides the choice
+// for 4-byte keys with 0/4-byte values (measurement aid; read once).
 static int rs_items(int kb, int vb) {
-  if (kb == 4) return vb == 8 ? 12 : 16;
+  static const int forced = [] {
+    const char *e = std::getenv("QDSP_RS_ITEMS");
+    const int v = e ? std::atoi(e) : 0;
+    return (v == 8 || v == 12 || v == 16) ? v : 0;
+  }();
+  if (kb == 4) {
+    if (vb == 8) return 12;
+    return forced ? forced : 16;
+  }
   return vb == 8 ? 8 : 12;
 }
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
-
-// QDSP_RS_VARIANT picks the sweep kernel: 0 = rs_onesweep_kernel, 1 = the instruction-trimmed v2, 2 = v2 with the
-// look-back after the shared-memory scatter, eight predecessors per round; read once
-static int rs_variant() {
-  const char *e = std::getenv("QDSP_RS_VARIANT");
-  const int v = e ? std::atoi(e) : RS_DEFAULT_VARIANT;
-  return v >= 0 && v <= 2 ? v : RS_DEFAULT_VARIANT;
-}
 
 // aux = [tickets (8 passes) | histograms 8 x 256 | look-back words tiles x 256]
 struct RsLayout {
@@ -526,12 +364,11 @@ size_t sort_modern_scratch_bytes(int64_t capacity, int key_bytes) { return rs_la
 
 // Runs the digit passes of bits [begin_bit, end_bit) ping-ponging between (keys, vals) and (kalt, valt); `n` sizes the
 // grids, the live count is min(n, *n_dev) when n_dev is given.  Returns where the sorted keys live.
-template <typename KeyT, typename ValT>
-static void *rs_run(KeyT *keys, ValT *vals, KeyT *kalt, ValT *valt, void *aux, int64_t n, const int *n_dev, int kind,
-                    int begin_bit, int end_bit, cudaStream_t stream, void **vals_result) {
+template <typename KeyT, typename ValT, int ITEMS, int MINB>
+static void *rs_run_items(KeyT *keys, ValT *vals, KeyT *kalt, ValT *valt, void *aux, int64_t n, const int *n_dev,
+                          int kind, int begin_bit, int end_bit, cudaStream_t stream, void **vals_result) {
   constexpr int KB = sizeof(KeyT);
   constexpr int VB = std::is_same<ValT, NoValue>::value ? 0 : sizeof(ValT);
-  constexpr int ITEMS = RsItems<KB, VB>::value;
   constexpr int TILE = RS_THREADS * ITEMS;
   const RsLayout L = rs_layout(n, KB, VB);
   const int passes = (end_bit - begin_bit + 7) / 8;
@@ -550,11 +387,7 @@ static void *rs_run(KeyT *keys, ValT *vals, KeyT *kalt, ValT *valt, void *aux, i
   rs_scan_bins_kernel<<<passes, RS_RADIX, 0, stream>>>(hist);
   QDSP_LAUNCH_CHECK();
 
-  using Kernel = decltype(&rs_onesweep_kernel<KeyT, ValT, ITEMS>);
-  static const int variant = rs_variant();
-  const Kernel kernel = variant == 1   ? rs_onesweep_v2_kernel<KeyT, ValT, ITEMS, false>
-                        : variant == 2 ? rs_onesweep_v2_kernel<KeyT, ValT, ITEMS, true>
-                                       : rs_onesweep_kernel<KeyT, ValT, ITEMS>;
+  auto kernel = rs_onesweep_kernel<KeyT, ValT, ITEMS, MINB>;
   const size_t smem = rs_vals_offset<KeyT, ValT, ITEMS>() + static_cast<size_t>(TILE) * (VB ? VB : 0);
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
@@ -576,6 +409,27 @@ static void *rs_run(KeyT *keys, ValT *vals, KeyT *kalt, ValT *valt, void *aux, i
   }
   if (vals_result) *vals_result = vin;
   return kin;  // the caller's buffer if `passes` is even
+}
+
+template <typename KeyT, typename ValT>
+static void *rs_run(KeyT *keys, ValT *vals, KeyT *kalt, ValT *valt, void *aux, int64_t n, const int *n_dev, int kind,
+                    int begin_bit, int end_bit, cudaStream_t stream, void **vals_result) {
+  constexpr int KB = sizeof(KeyT);
+  constexpr int VB = std::is_same<ValT, NoValue>::value ? 0 : sizeof(ValT);
+#define QDSP_RS_GO(ITEMS, MINB)                                                                                   \
+  return rs_run_items<KeyT, ValT, ITEMS, MINB>(keys, vals, kalt, valt, aux, n, n_dev, kind, begin_bit, end_bit, \
+                                               stream, vals_result)
+  const int items = rs_items(KB, VB);
+  if constexpr (KB == 4 && VB <= 4) {
+    if (items == 8) QDSP_RS_GO(8, 6);
+    if (items == 12) QDSP_RS_GO(12, 5);
+    QDSP_RS_GO(16, 4);
+  } else if constexpr (KB == 8 && VB == 8) {
+    QDSP_RS_GO(8, 4);
+  } else {
+    QDSP_RS_GO(12, 4);
+  }
+#undef QDSP_RS_GO
 }
 
 // old single-scratch form: the alternate buffers live behind the aux area of `tmp`
