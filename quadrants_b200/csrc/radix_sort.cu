@@ -169,7 +169,6 @@ __device__ __forceinline__ unsigned rs_lookback_batched(unsigned *my, unsigned t
       }
     }
     t -= used;
-    if (used == 0) __nanosleep(32);  // leave the issue slots to the CTAs this one is waiting for
   }
   st_relaxed_u32(my, RS_FLAG_PREFIX | ((exclusive + count) & RS_VAL_MASK));
   return exclusive;
@@ -202,47 +201,6 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
     for (int i = 0; i < ITEMS; ++i)
       if (FULL_TILE || wbase + i * 32 < valid_n) val[i] = vp[i * 32];
   }
-  // early counts ("match early counts" of Adinets & Merrill): the tile's digit histogram is taken BEFORE the ranking
-  // and published at once, so a successor's look-back never waits for this tile's ranking.  Without it the slowest
-  // in-flight tile holds up every later one (time was proportional to the NUMBER of tiles, profiles/r01q).
-  // Thread- and warp-uniform digits (sorted input, high digits of the CSR-build keys) collapse into one atomic.
-  {
-    const unsigned d0 = static_cast<unsigned>(key[0] >> shift) & dmask;
-    if constexpr (FULL_TILE) {
-      bool uni = true;
-#pragma unroll
-      for (int i = 1; i < ITEMS; ++i) uni &= (static_cast<unsigned>(key[i] >> shift) & dmask) == d0;
-      const bool warp_uni = __all_sync(FULL, uni && d0 == __shfl_sync(FULL, d0, 0));
-      if (warp_uni) {
-        if (lane == 0) atomicAdd(&S.digit_start[d0], 32u * ITEMS);
-      } else if (uni) {
-        atomicAdd(&S.digit_start[d0], static_cast<unsigned>(ITEMS));
-      } else {
-#pragma unroll
-        for (int i = 0; i < ITEMS; ++i) atomicAdd(&S.digit_start[static_cast<unsigned>(key[i] >> shift) & dmask], 1u);
-      }
-    } else {
-#pragma unroll
-      for (int i = 0; i < ITEMS; ++i)
-        if (wbase + i * 32 < valid_n) atomicAdd(&S.digit_start[static_cast<unsigned>(key[i] >> shift) & dmask], 1u);
-    }
-  }
-  __syncthreads();
-  {
-    // thread d owns digit d: publish the tile's count, tile-local exclusive scan over the digits
-    const unsigned count = S.digit_start[threadIdx.x];
-    st_relaxed_u32(lookback + static_cast<size_t>(tile) * RS_RADIX + threadIdx.x,
-                   (tile == 0 ? RS_FLAG_PREFIX : RS_FLAG_AGG) | count);
-    const unsigned incl = warp_inclusive_scan(count);
-    if (lane == 31) S.warp_tot[warp] = incl;
-    __syncthreads();
-    unsigned wpre = 0;
-#pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w)
-      if (w < (int)warp) wpre += S.warp_tot[w];
-    S.digit_start[threadIdx.x] = wpre + incl - count;  // read again only after the ranking's barrier
-    S.gbase[threadIdx.x] = count;                      // parked for the look-back
-  }
   unsigned *my_hist = &S.warp_hist[warp][0];
   unsigned rank[ITEMS];
   const unsigned lt = lanemask_lt();
@@ -270,8 +228,10 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
     __syncwarp();
   }
   __syncthreads();
+  // thread d owns digit d: tile count, publication of the aggregate, tile-local digit offsets
   {
-    // exclusive offset of each warp inside digit d
+    unsigned count, start;
+    unsigned *my = lookback + static_cast<size_t>(tile) * RS_RADIX + threadIdx.x;
     const unsigned d = threadIdx.x;
     unsigned sum = 0;
 #pragma unroll
@@ -280,6 +240,18 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
       S.warp_hist[w][d] = sum;
       sum += t;
     }
+    count = sum;
+    st_relaxed_u32(my, (tile == 0 ? RS_FLAG_PREFIX : RS_FLAG_AGG) | count);
+    const unsigned incl = warp_inclusive_scan(count);
+    if (lane == 31) S.warp_tot[warp] = incl;
+    __syncthreads();
+    unsigned wpre = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w)
+      if (w < (int)warp) wpre += S.warp_tot[w];
+    start = wpre + incl - count;
+    S.digit_start[d] = start;
+    S.gbase[d] = count;  // parked in shared memory across the scatter (registers are at their cap there)
   }
   __syncthreads();
   unsigned pos[ITEMS];
@@ -335,7 +307,6 @@ rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const 
   ValT *s_vals = reinterpret_cast<ValT *>(s_raw + rs_vals_offset<KeyT, ValT, ITEMS>());
   if (threadIdx.x == 0) S.ticket = atomicAdd(ticket, 1u);
   for (int i = threadIdx.x; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&S.warp_hist[0][0])[i] = 0;
-  S.digit_start[threadIdx.x] = 0;  // the tile histogram of the early counts
   __syncthreads();
   const unsigned tile = S.ticket;
   const long long tile_base = static_cast<long long>(tile) * TILE;
