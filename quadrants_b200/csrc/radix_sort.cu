@@ -7,15 +7,16 @@
 // cusparseXcoosortByRow + cusparseGather of CuSparseMatrix::build_csr_from_coo
 // (quadrants/program/sparse_matrix.cpp:358-368).
 //
-// HBM-bound: algorithmic traffic N*kb + P*2*N*(kb+vb) bytes for P digit passes.
+// Byte model (the roofline it is measured against): N*kb + P*2*N*(kb+vb) bytes for P digit passes.
 // Tile = 256 threads x ITEMS keys, warp-striped so that (warp, item, lane) order == input order:
 //   1. coalesced loads of keys (+values) into registers;
-//   2. per-warp ranking with match.any: peers holding the same digit elect a leader that bumps the warp's private
-//      digit counter in shared memory -> rank inside the warp, stable by construction;
-//   3. thread d (256 threads == 256 digits): scan of the 8 warp counters, publish the tile count of digit d,
-//      look back over the preceding tiles' descriptors for digit d, publish the inclusive prefix;
-//   4. scatter to shared memory in tile-sorted order, then write out so that consecutive threads store runs of
-//      consecutive global addresses.
+//   2. per-warp ranking: the lanes holding the same digit find each other with one ballot per digit bit and elect a
+//      leader that bumps the warp's private digit counter in shared memory -> rank inside the warp, stable by
+//      construction;
+//   3. thread d (256 threads == 256 digits): scan of the 8 warp counters, publish the tile count of digit d;
+//   4. scatter keys (+values) to shared memory in tile-sorted order;
+//   5. thread d looks back over the preceding tiles' descriptors for digit d, publishes the inclusive prefix;
+//   6. write out so that consecutive threads store runs of consecutive global addresses.
 #include <cstdlib>
 
 #include "common.cuh"
@@ -136,13 +137,17 @@ __device__ __forceinline__ void rs_peer_step(unsigned &peers, unsigned d) {
       : "r"(d), "n"(1u << B));
 }
 
-// ---- the same sweep, instruction-trimmed (the kernel is issue-bound: ~150 thread instructions per key and 50 % issue
-// utilisation in profiles/r01n_kernel_onesweep.txt, DRAM at 21 %) --------------------------------------------------------
+// ---- one digit pass ------------------------------------------------------------------------------------------------
+// The sweep is issue- and latency-bound, not DRAM-bound (profiles/r01n_kernel_onesweep.txt: ~150 thread instructions per
+// key at 50 % issue utilisation, DRAM at 21 %, a third of the stall samples in the look-back spin).  Hence:
 //  * full tiles (all but the last) run a body without any per-item bounds test;
-//  * digit bits are tested in place (d & (1 << b)) instead of shift-mask-compare;
+//  * the peer mask of a digit is built by rs_peer_step (3.5 SASS instructions per bit);
+//  * the look-back runs after the shared-memory scatter, eight predecessors per round trip;
 //  * the global output index of each tile-sorted position is computed once and reused for the value.
+// Measured steps: profiles/r01_sort_variants.jsonl.
+
 // Look-back of one digit column: `my` = this tile's descriptor (aggregate already published); returns the exclusive
-// prefix and publishes the inclusive one.  RS_LB_BATCH predecessors per round: the loads of a round are independent (one L2 latency for all of them);
+// prefix and publishes the inclusive one.  The RS_LB_BATCH loads of a round are independent (one L2 latency for all);
 // a descriptor that is not published yet ends the round and is polled again at the head of the next one.
 constexpr int RS_LB_BATCH = 8;
 __device__ __forceinline__ unsigned rs_lookback_batched(unsigned *my, unsigned tile, unsigned count) {
