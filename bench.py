@@ -184,6 +184,9 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; the best-effort Eigen variant is meant to use every host core
+    # (libgomp reads the variable when oracle/_ref is loaded, so set it first)
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     import oracle
 
     oracle.build()
