@@ -91,6 +91,20 @@ class Program:
 
         return torch.cuda.current_stream().cuda_stream
 
+    def create_sparse_matrix(self, n, m, dtype, storage_format="col_major"):
+        """export_lang.cpp:518-526 -> make_cu_sparse_matrix on arch=cuda (the storage format does not apply: CSR)."""
+        from . import _core
+
+        return _core.make_cu_sparse_matrix(n, m if m else n, dtype)
+
+    def make_sparse_matrix_from_ndarray(self, sm, ndarray):
+        """export_lang.cpp:527-532 / sparse_matrix.cpp:320-342: N x 3 float (row, col, value) triplets -> sm."""
+        import torch
+
+        trip = ndarray.tensor.reshape(-1).view(-1, 3)
+        sm.build_csr_from_coo(trip[:, 0].to(torch.int32).contiguous(), trip[:, 1].to(torch.int32).contiguous(),
+                              trip[:, 2].to(sm.get_data_type().torch_dtype).contiguous())
+
     def synchronize(self):
         import torch
 
