@@ -23,6 +23,11 @@ def parallel_sort(keys, values=None):
     The reference is a Batcher odd-even merge network (unstable, O(N log^2 N), one launch + sync() per stage); this is a
     stable LSD radix sort, so keys come out identical and ties keep their input order.  Unlike the reference it does
     not emit a DeprecationWarning-worthy amount of launches: 2 + 4 kernels for 32-bit keys."""
+    import warnings
+
+    warnings.warn(  # the reference's deprecation notice (_algorithms.py:33-40)
+        "qd.algorithms.parallel_sort is deprecated. Use qd.algorithms.sort (the @qd.func) instead. "
+        "See docs/source/user_guide/algorithms.md for migration.", DeprecationWarning, stacklevel=2)
     if not isinstance(keys, Ndarray):
         raise RuntimeError("parallel_sort expects 1-D qd fields / ndarrays")
     prog = _require_prog()
@@ -47,6 +52,11 @@ class PrefixSumExecutor:
     scratch buffer is allocated once."""
 
     def __init__(self, length):
+        import warnings
+
+        warnings.warn(  # the reference's deprecation notice (_algorithms.py:78-86)
+            "qd.algorithms.PrefixSumExecutor is deprecated. Use qd.algorithms.exclusive_scan_add (the @qd.func) "
+            "instead. See docs/source/user_guide/algorithms.md for migration.", DeprecationWarning, stacklevel=2)
         self.sorting_length = int(length)
         self._lib = _lib.load()
         _require_prog()

@@ -156,3 +156,17 @@ def test_abi_argument_validation_needs_no_device():
     assert b"scratch" in L.qdsp_last_error()
     assert L.qdsp_reduce(a, o, 64, None, 9, _lib.OP_ADD, s, C.sizeof(scratch), None) == 1
     assert L.qdsp_select(a, a, o, o, 64, None, 6, s, C.sizeof(scratch), None) == 1
+
+
+def test_legacy_entries_emit_the_reference_deprecation_warnings():
+    """tests/python/test_algorithms.py:748-759; the warning fires before anything touches the device."""
+    import quadrants_b200 as qd
+
+    with pytest.warns(DeprecationWarning, match="exclusive_scan_add"):
+        try:
+            qd.algorithms.PrefixSumExecutor(64)
+        except Exception:  # no CUDA device here: qd.init was never called
+            pass
+    with pytest.warns(DeprecationWarning, match="sort"):
+        with pytest.raises(RuntimeError):
+            qd.algorithms.parallel_sort("not a field")
