@@ -235,8 +235,9 @@ int qdsp_sort(void *keys, void *tmp_keys, void *values, void *tmp_values, int64_
  * slot 0 per triplet): appends `count` triplets (row[k], col[k], +-val[k]) behind the triplets already in the buffer,
  * in array order, with NO atomic -- every thread reads slot 0, writes its triplet at slot0 + k, and a second
  * one-thread kernel bumps slot 0, all stream-ordered.  row/col: device i32; val: device f32/f64 (the builder's
- * dtype).  Overflow beyond max_triplets is detected on the device: nothing is written, and qdsp_builder_count /
- * qdsp_builder_build report QDSP_ERR_INVALID. */
+ * dtype).  Overflow beyond max_triplets is detected on the device: nothing is written, slot 0 is still advanced (as the
+ * reference's insert_triplet does), so qdsp_builder_count then exceeds max_triplets and qdsp_builder_build reports
+ * QDSP_ERR_INVALID. */
 int qdsp_builder_append(qdsp_builder_t b, const int32_t *row, const int32_t *col, const void *val, int64_t count,
                         int negate, void *stream);
 /* Element-wise assembly (the FEM pattern of tests/python/test_implicit_fem.py:179-204): `n_elems` elements of `k`
