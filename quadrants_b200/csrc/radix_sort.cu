@@ -329,13 +329,13 @@ rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const 
 
 // ---- host driver ---------------------------------------------------------------------------------------------------
 // Keys per thread (tile = 256 x ITEMS) and resident CTAs per SM the kernel is compiled for.  Wider items -> fewer
-// keys per thread so that key + value + rank registers stay under the cap.  QDSP_RS_ITEMS=8|12|16 overrides the choice
+// keys per thread so that key + value + rank registers stay under the cap.  QDSP_RS_ITEMS=8|12|16|20|24 overrides the choice
 // for 4-byte keys with 0/4-byte values (measurement aid; read once).
 static int rs_items(int kb, int vb) {
   static const int forced = [] {
     const char *e = std::getenv("QDSP_RS_ITEMS");
     const int v = e ? std::atoi(e) : 0;
-    return (v == 8 || v == 12 || v == 16) ? v : 0;
+    return (v == 8 || v == 12 || v == 16 || v == 20 || v == 24) ? v : 0;
   }();
   if (kb == 4) {
     if (vb == 8) return 12;
@@ -428,6 +428,8 @@ static void *rs_run(KeyT *keys, ValT *vals, KeyT *kalt, ValT *valt, void *aux, i
   if constexpr (KB == 4 && VB <= 4) {
     if (items == 8) QDSP_RS_GO(8, 6);
     if (items == 12) QDSP_RS_GO(12, 5);
+    if (items == 20) QDSP_RS_GO(20, 3);  // larger tiles at 3 CTAs per SM: not measured yet (time rose when tiles
+    if (items == 24) QDSP_RS_GO(24, 3);  // shrank, profiles/r01_sort_variants.jsonl, so the other direction is open)
     QDSP_RS_GO(16, 4);
   } else if constexpr (KB == 8 && VB == 8) {
     QDSP_RS_GO(8, 4);

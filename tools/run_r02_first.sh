@@ -16,6 +16,10 @@ timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
 echo "[$((SECONDS-T0))s] bench + launch list exit $?"; cut -c1-300 gpurun_out/r02a_bench.json
 timeout 240 python tools/bench_paths.py > gpurun_out/r02a_paths.jsonl 2> gpurun_out/r02a_paths.err
 echo "[$((SECONDS-T0))s] bench_paths exit $?"; cut -c1-220 gpurun_out/r02a_paths.jsonl
+for it in 16 20 24; do   # larger tiles: the open direction of profiles/r01_sort_variants.jsonl
+  QDSP_RS_ITEMS=$it timeout 60 python tools/sort_probe.py 26 3 kv32,k32 | sed "s/\"default\"/\"items$it\"/" >> gpurun_out/r02a_sort_items.jsonl
+done
+cat gpurun_out/r02a_sort_items.jsonl
 timeout 60 python tools/sort_probe.py 25 1 kv32 > gpurun_out/r02a_sort_plain.log 2>&1 &&
 timeout 200 ncu --set full --clock-control none --import-source on -k regex:rs_onesweep -s 8 -c 1 -f -o gpurun_out/r02a_onesweep \
     python tools/sort_probe.py 25 1 kv32 > gpurun_out/r02a_ncu_sort.log 2>&1
