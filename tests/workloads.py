@@ -106,3 +106,20 @@ def spd_dense_10(seed: int = 0, dtype=np.float32):
     a = (m @ m.T).astype(dtype)
     i, j = np.meshgrid(np.arange(10), np.arange(10), indexing="ij")
     return i.ravel(), j.ravel(), a.ravel(), a, np.arange(1, 11).astype(dtype)
+
+
+def c2_spmv_x(n: int = 256 ** 3):
+    """x ~ U(-1, 1), seed 2, fp32."""
+    return np.random.default_rng(2).uniform(-1.0, 1.0, n).astype(np.float32)
+
+
+def c2_cg_xtrue(n: int = 256 ** 3):
+    """b = A x_true with x_true ~ U(-1, 1), seed 3, fp32."""
+    return np.random.default_rng(3).uniform(-1.0, 1.0, n).astype(np.float32)
+
+
+def row_abs_scale(indptr, indices, values, x):
+    """sum_j |a_ij x_j| per row in fp64: the scale of the per-row SpMV tolerance (BASELINE.json north_star)."""
+    prod = np.abs(values.astype(np.float64) * x[indices].astype(np.float64))
+    csum = np.concatenate([[0.0], np.cumsum(prod)])
+    return csum[indptr[1:]] - csum[indptr[:-1]]
