@@ -129,7 +129,8 @@ int qdsp_csr_destroy(qdsp_csr_t m);
 int qdsp_cg_create(qdsp_csr_t m, int max_iters, double tol, int mode, int verbose, qdsp_cg_t *out);
 /* solve (conjugate_gradient.h:36-49 / conjugate_gradient.cpp:19-83).  x, b: dense device vectors.  EIGEN_JACOBI
  * overwrites x from a zero start; CUCG starts from the x passed in.  iterations/error/success follow Eigen's
- * iterations()/error()/info()==Success; in CUCG mode error is r.r and success is r.r <= tol^2. */
+ * iterations()/error()/info()==Success; in CUCG mode error is r.r and success is r.r <= tol^2.
+ * x must be 16-byte aligned (the update kernels move it as 128-bit words); QDSP_ERR_INVALID otherwise. */
 int qdsp_cg_solve(qdsp_cg_t s, void *x, const void *b, void *stream, int *iterations, double *error, int *success);
 int qdsp_cg_solve_host(qdsp_cg_t s, void *x_host, const void *b_host, void *stream, int *iterations, double *error,
                        int *success);

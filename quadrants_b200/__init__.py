@@ -11,7 +11,7 @@ Same names, arguments and error behaviour as python/quadrants/linalg and python/
 behind them hand-written sm_100a CUDA reached through the C ABI of include/qdsp.h.  No CPU fallback.
 """
 from . import _lib  # noqa: F401
-from .lang import (Arch, Field, Ndarray, QuadrantsRuntimeError, ScalarNdarray, cpu, cuda, f32, f64, field, float32,  # noqa: F401
+from .lang import (Arch, Field, Ndarray, QuadrantsRuntimeError, ScalarNdarray, Vector, cpu, cuda, f32, f64, field, float32,  # noqa: F401
                    float64, get_runtime, gpu, i32, i64, init, int32, int64, ndarray, reset, sync, u32, u64, uint32,
                    uint64, x64)
 from . import _core  # noqa: F401,E402

@@ -942,6 +942,8 @@ CgSolver::~CgSolver() {
 
 void CgSolver::solve(void *x, const void *b, cudaStream_t stream, int *iterations, double *error, int *success) {
   QDSP_REQUIRE(x != nullptr && b != nullptr, QDSP_ERR_INVALID, "CG: null vector");
+  // the update kernels move x as 128-bit words (a misaligned view would fault: a sticky error for the whole process)
+  QDSP_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15u) == 0, QDSP_ERR_INVALID, "CG: x must be 16-byte aligned");
   if (impl_->A.dtype == QDSP_F32) solve_t<float>(*impl_, x, b, stream, iterations, error, success);
   else solve_t<double>(*impl_, x, b, stream, iterations, error, success);
 }
@@ -963,6 +965,7 @@ void CgSolver::solve_host(void *x_host, const void *b_host, cudaStream_t stream,
 
 void CgSolver::run_fixed(void *x, const void *b, int iters, cudaStream_t stream) {
   QDSP_REQUIRE(x != nullptr && b != nullptr && iters >= 0, QDSP_ERR_INVALID, "CG: bad arguments");
+  QDSP_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15u) == 0, QDSP_ERR_INVALID, "CG: x must be 16-byte aligned");
   if (impl_->A.dtype == QDSP_F32) run_fixed_t<float>(*impl_, x, b, iters, stream);
   else run_fixed_t<double>(*impl_, x, b, iters, stream);
 }

@@ -110,6 +110,15 @@ std::unique_ptr<CsrMatrix> CsrMatrix::transpose(cudaStream_t stream) const {
   return out;
 }
 
+// 64-bit total of the per-entry product counts (the i32 scan below wraps silently past 2^31)
+__global__ void sum_counts_kernel(int64_t n, const int *__restrict__ cnt, unsigned long long *__restrict__ total) {
+  unsigned long long t = 0;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n; i += static_cast<int64_t>(gridDim.x) * blockDim.x)
+    t += static_cast<unsigned long long>(cnt[i]);
+  t = warp_sum(t);
+  if (lane_id() == 0 && t) atomicAdd(total, t);
+}
+
 std::unique_ptr<CsrMatrix> CsrMatrix::matmul(const CsrMatrix &b, cudaStream_t stream) const {
   QDSP_REQUIRE(cols == b.rows, QDSP_ERR_INVALID, "sparse matrix product: dimension mismatch");
   QDSP_REQUIRE(dtype == b.dtype, QDSP_ERR_INVALID, "sparse matrix product: dtype mismatch");
@@ -121,11 +130,19 @@ std::unique_ptr<CsrMatrix> CsrMatrix::matmul(const CsrMatrix &b, cudaStream_t st
   expand_rows(*this, a_row.get<int>(), 0, stream);
   spgemm_count_kernel<<<grid_for(nnz), OP_THREADS, 0, stream>>>(nnz, indices.get<int>(), b.indptr.get<int>(), cnt.get<int>());
   QDSP_LAUNCH_CHECK();
-  inclusive_scan_i32(cnt.get<int>(), nnz, scan_tmp.get(), scan_tmp.bytes(), stream);
-  int total = 0;
-  QDSP_CUDA(cudaMemcpyAsync(&total, cnt.get<int>() + (nnz - 1), sizeof(int), cudaMemcpyDeviceToHost, stream));
+  DeviceBuffer total64(sizeof(unsigned long long));
+  QDSP_CUDA(cudaMemsetAsync(total64.get(), 0, sizeof(unsigned long long), stream));
+  sum_counts_kernel<<<std::min<int64_t>(grid_for(nnz), 1184), OP_THREADS, 0, stream>>>(nnz, cnt.get<int>(), total64.get<unsigned long long>());
+  QDSP_LAUNCH_CHECK();
+  unsigned long long total_ull = 0;
+  QDSP_CUDA(cudaMemcpyAsync(&total_ull, total64.get(), sizeof(total_ull), cudaMemcpyDeviceToHost, stream));
   QDSP_CUDA(cudaStreamSynchronize(stream));
-  QDSP_REQUIRE(total >= 0, QDSP_ERR_UNSUPPORTED, "sparse matrix product: intermediate size overflows int32");
+  // the expansion is sorted by the onesweep sort (< 2^30 items); the reference (cusparseSpGEMM) errors out as well when
+  // its work buffers do not fit
+  QDSP_REQUIRE(total_ull < (1ull << 30), QDSP_ERR_UNSUPPORTED,
+               "sparse matrix product: more than 2^30 partial products (intermediate does not fit one sort)");
+  const int total = static_cast<int>(total_ull);
+  inclusive_scan_i32(cnt.get<int>(), nnz, scan_tmp.get(), scan_tmp.bytes(), stream);
   const size_t vb = value_bytes();
   DeviceBuffer o_row(sizeof(int) * std::max(total, 1)), o_col(sizeof(int) * std::max(total, 1)), o_val(vb * std::max(total, 1));
   if (dtype == QDSP_F32)

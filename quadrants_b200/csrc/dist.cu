@@ -216,6 +216,45 @@ int DistContext::error_flag(cudaStream_t stream) const {
 }
 
 // ---- stand-alone distributed SpMV ---------------------------------------------------------------------------------------
+// Successive calls need a cross-rank rendezvous of their own (CG gets one from its all-reduces): the push of call k+1
+// stores into a neighbour's ghost segment, and that neighbour may still be inside the SpMV of call k reading it.  Every
+// consumer therefore reports "call k read" to the owners of its ghosts when its SpMV kernel has finished
+// (consumed flags, one per reader rank, in the owner's comm buffer), and an owner waits for consumed >= k from every
+// rank it sends to before it pushes call k+1.  counters[5] = stand-alone calls started on this rank -- a sequence number
+// of its own, because counters[1] (the push count that dist_halo_wait compares the halo flags with) also advances in CG.
+__device__ __forceinline__ unsigned long long *dist_flag_consumed(unsigned char *buf, int from_rank) {
+  return reinterpret_cast<unsigned long long *>(buf + DIST_FLAGS_OFF + 128) + from_rank;
+}
+
+__global__ void dist_wait_consumed_kernel(DistDev d) {
+  const unsigned calls = *reinterpret_cast<volatile unsigned *>(&d.counters[5]);
+  const int s = threadIdx.x;
+  if (s < d.n_send) {
+    const unsigned long long *f = dist_flag_consumed(d.self, d.send_peer[s]);
+    const long long t0 = clock64();
+    while (ld_acquire_sys_u64(f) < calls) {
+      if (clock64() - t0 > DIST_SPIN_LIMIT) {
+        atomicExch(d.error, 2);
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    d.counters[5] = calls + 1u;
+    // a rank that receives but sends nothing has no owner CTA to advance the push count its halo wait compares with
+    if (d.n_send == 0) d.counters[1] += 1u;
+  }
+}
+
+__global__ void dist_signal_consumed_kernel(DistDev d) {
+  const int r = threadIdx.x;
+  if (r >= d.n_recv) return;
+  const unsigned calls = *reinterpret_cast<volatile unsigned *>(&d.counters[5]);
+  // the SpMV kernel that read the ghosts ended before this kernel began (stream order)
+  st_release_sys_u64(dist_flag_consumed(d.peer[d.recv_peer[r]], d.rank), calls);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) dist_load_push_kernel(int n, const T *__restrict__ x, T *__restrict__ vec, DistDev d) {
   const int per = ((n + gridDim.x - 1) / gridDim.x + 1023) & ~1023;
@@ -230,12 +269,16 @@ void DistContext::spmv(const CsrMatrix &A, const void *x_loc, void *y_loc, cudaS
                "dist spmv: the matrix is not the one localized on this context");
   const int n = plan_.n_local;
   const int grid = std::max(1, std::min(ceil_div(n, 1024), device_props().sm_count * 4));
+  dist_wait_consumed_kernel<<<1, 32, 0, stream>>>(dev_);
+  QDSP_LAUNCH_CHECK();
   if (dtype_ == QDSP_F32)
     dist_load_push_kernel<float><<<grid, 256, 0, stream>>>(n, static_cast<const float *>(x_loc), static_cast<float *>(vector_ptr()), dev_);
   else
     dist_load_push_kernel<double><<<grid, 256, 0, stream>>>(n, static_cast<const double *>(x_loc), static_cast<double *>(vector_ptr()), dev_);
   QDSP_LAUNCH_CHECK();
   launch_spmv(A, vector_ptr(), y_loc, dev_, stream);
+  dist_signal_consumed_kernel<<<1, 32, 0, stream>>>(dev_);
+  QDSP_LAUNCH_CHECK();
   QDSP_REQUIRE(error_flag(stream) == 0, QDSP_ERR_COMM, "dist spmv: a peer rank did not answer (halo spin timed out)");
 }
 

@@ -9,6 +9,7 @@
 //   [0, 2048)      reduction slots   slots[2 parity][8 ranks][8 values][2 words]   8-byte words {payload32 | seq32}
 //   [2048, 2112)   halo flags        flags[8 ranks]                                 8-byte, monotone sequence numbers
 //   [2112, 2176)   z-halo flags      the same for the second halo channel (below)
+//   [2176, 2240)   consumed flags    stand-alone SpMV: flags[q] = calls whose ghosts rank q has finished reading (dist.cu)
 //   [4096, ...)    the operand vector of SpMV: n_loc owned entries, the ghost entries (from ghost_base), and from zbase a
 //                  second ghost-sized segment for the z channel
 // Protocol:
@@ -68,7 +69,7 @@ struct DistDev {
   const int *block_order = nullptr;
   int n_interior = 0;
   unsigned *counters = nullptr;                  // device, local: [0] reduction seq, [1] halo push count, [2] ticket,
-                                                 // [3] z push count, [4] z ticket
+                                                 // [3] z push count, [4] z ticket, [5] stand-alone SpMV calls
   int *error = nullptr;                          // device, local: != 0 after a timeout
 };
 

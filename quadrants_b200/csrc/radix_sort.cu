@@ -365,7 +365,15 @@ static RsLayout rs_layout(int64_t n, int kb, int vb) {
 
 size_t sort_tmp_bytes(int64_t n, int key_bytes, int value_bytes) { return rs_layout(n, key_bytes, value_bytes).total; }
 // aux only (the caller brings tmp_keys / tmp_values): sized for the smallest tile of this key width, any value width
-size_t sort_modern_scratch_bytes(int64_t capacity, int key_bytes) { return rs_layout(capacity, key_bytes, 8).aux_bytes; }
+// (8 keys per thread is the smallest tile ANY dispatch of rs_run can pick, QDSP_RS_ITEMS included, so the look-back area
+// checked against the caller's scratch never undercounts the tiles a sweep will use)
+size_t sort_modern_scratch_bytes(int64_t capacity, int key_bytes) {
+  (void)key_bytes;
+  const int64_t tile = RS_THREADS * 8;
+  const int64_t tiles = capacity > 0 ? (capacity + tile - 1) / tile : 1;
+  const size_t lookback_off = align_up(RS_HEADER_BYTES + 8 * RS_RADIX * sizeof(unsigned), 256);
+  return align_up(lookback_off + static_cast<size_t>(tiles) * RS_RADIX * sizeof(unsigned), 256);
+}
 
 // Runs the digit passes of bits [begin_bit, end_bit) ping-ponging between (keys, vals) and (kalt, valt); `n` sizes the
 // grids, the live count is min(n, *n_dev) when n_dev is given.  Returns where the sorted keys live.

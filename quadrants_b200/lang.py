@@ -182,14 +182,14 @@ class Ndarray:
         return self.tensor.data_ptr()
 
     def to_numpy(self):
-        return self.tensor.detach().cpu().numpy().view(self.dtype.np_dtype).reshape(self.shape)
+        return self.tensor.detach().cpu().numpy().view(self.dtype.np_dtype).reshape(self.shape + self.element_shape)
 
     def from_numpy(self, a):
         import torch
 
         a = np.ascontiguousarray(a, dtype=self.dtype.np_dtype).reshape(-1)
         if a.shape[0] != self.tensor.shape[0]:
-            raise QuadrantsRuntimeError(f"from_numpy: shape mismatch {a.shape} vs {self.shape}")
+            raise QuadrantsRuntimeError(f"from_numpy: shape mismatch {a.shape} vs {self.shape + self.element_shape}")
         self.tensor.copy_(torch.from_numpy(a.view(self.dtype.storage_np)))
 
     def fill(self, v):
@@ -206,9 +206,18 @@ class Ndarray:
         return j
 
     def __getitem__(self, i):
+        if self.element_shape:
+            k = self.element_shape[0]
+            return self.tensor[int(i) * k:(int(i) + 1) * k].tolist()
         return self.tensor[self._idx(i)].item()
 
     def __setitem__(self, i, v):
+        if self.element_shape:
+            import torch
+
+            k = self.element_shape[0]
+            self.tensor[int(i) * k:(int(i) + 1) * k] = torch.as_tensor(v, dtype=self.tensor.dtype)
+            return
         self.tensor[self._idx(i)] = v
 
     def __len__(self):
@@ -220,6 +229,22 @@ ScalarNdarray = Ndarray
 
 def ndarray(dtype, shape):
     return Ndarray(dtype, shape)
+
+
+class Vector:
+    """qd.Vector.ndarray(n, dtype, shape): a dense AOS array of n-vectors (python/quadrants/lang/matrix.py
+    Vector.ndarray) -- what `SparseMatrix.build_from_ndarray` takes (tests/python/test_sparse_matrix.py:70-85).  Storage is
+    one contiguous tensor of shape*n scalars; `a[i] = (..)` / `a[i]` address whole elements."""
+
+    @staticmethod
+    def ndarray(n, dtype, shape, layout=None):
+        if isinstance(shape, (int, np.integer)):
+            shape = (int(shape),)
+        total = int(np.prod(shape)) * int(n)
+        a = Ndarray(dtype, total)
+        a.shape = tuple(int(s) for s in shape)
+        a.element_shape = (int(n),)
+        return a
 
 
 def field(dtype, shape, offset=0):

@@ -1,0 +1,227 @@
+"""The BASELINE.json configs C2, C4 and C5 AT THEIR STATED SIZE against the reference's own Eigen, plus the two §8(a) rows
+that had no GPU test (A6 build_from_ndarray, A2 the atomic insert_triplet writer).  Needs a B200.
+
+The expected values are digests / strided samples that tests/golden/make_golden_full.py produced in the build container
+with oracle/_ref (the reference's vendored Eigen, compiled with the reference's flags) on the SAME seeded inputs, which
+tests/workloads.py regenerates here with numpy -- /root/reference does not exist on the GPU box.
+
+Bars (stated where they are enforced):
+  * CSR indptr / indices / values: sha256-identical to Eigen's row-major setFromTriplets (duplicates summed in buffer
+    order, explicit zeros kept).
+  * SpMV, C2 fp32 (one thread per row, Eigen's order): y sha256-identical, both storage orders.  C5 fp64 (stream path):
+    |y_i - y_ref_i| <= 1e-12 * sum_j |a_ij x_j| on every 64th row.
+  * CG, C2 fp32, tol 1e-6, budget 1000: same success flag, iteration count within +-3 of Eigen's (152; the fp64
+    trajectory needs 153), and ||x - x_ref|| / ||x_ref|| <= 3e-5 against BOTH Eigen's fp32 solution and its fp64 one.
+    The north star's 1e-5 is not attainable as worded: Eigen's own fp32 solve differs from its fp64 solve by 1.36e-5 on
+    this system (full_c2.json cg_f32.rel_err_vs_f64).
+  * CG, C5 fp64, tol 1e-10, budget 5000: success, iterations within 2 % of Eigen's 2244, x within 1e-7 relative.
+"""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import make_triplet_buffer
+from tests import workloads as W
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def sha(a) -> str:
+    return hashlib.sha256(np.ascontiguousarray(a).view(np.uint8).data).hexdigest()
+
+
+def gold(cfg):
+    meta = json.load(open(os.path.join(GOLD, f"full_{cfg}.json")))
+    return meta, np.load(os.path.join(GOLD, f"full_{cfg}.npz"))
+
+
+@pytest.fixture(scope="module")
+def qd():
+    import quadrants_b200 as qd
+
+    qd.init(arch=qd.cuda)
+    return qd
+
+
+def build_from_buffer(qd, buf, rows, cols, storage_format="col_major"):
+    dt = qd.f32 if buf.dtype == np.int32 else qd.f64
+    K = qd.linalg.SparseMatrixBuilder(rows, cols, max_num_triplets=max(int(buf[0]), 1), dtype=dt,
+                                      storage_format=storage_format)
+    K.ptr.fill_from_host(buf)
+    A = K.build()
+    del K
+    return A
+
+
+def to_nd(qd, a):
+    x = qd.ndarray({4: qd.f32, 8: qd.f64}[a.dtype.itemsize], a.shape[0])
+    x.from_numpy(a)
+    return x
+
+
+def assert_csr_digests(A, meta):
+    ip, ix, vals = A.matrix.to_scipy_arrays()
+    assert ix.shape[0] == meta["nnz"]
+    assert sha(ip) == meta["indptr_sha256"], "indptr differs from Eigen's outerIndexPtr"
+    assert sha(ix) == meta["indices_sha256"], "indices differ from Eigen's innerIndexPtr"
+    assert sha(vals) == meta["values_sha256"], "values differ from Eigen's valuePtr (duplicate sum order?)"
+    return ip, ix, vals
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# C2: 3-D Poisson 256^3 fp32 -- build, SpMV (both orders), CG to 1e-6
+# ---------------------------------------------------------------------------------------------------------------------
+def test_c2_full_size_build_spmv_cg_vs_eigen(qd):
+    meta, g = gold("c2")
+    n, N = 256, 256 ** 3
+    r, c, v = W.poisson3d_triplets(n, np.float32)
+    buf = make_triplet_buffer(r, c, v, np.float32)
+    del r, c, v
+    A = build_from_buffer(qd, buf, N, N, "col_major")
+    assert_csr_digests(A, meta)
+    x = to_nd(qd, W.c2_spmv_x())
+    y = (A @ x).to_numpy()
+    assert sha(y) == meta["y_colmajor_sha256"], "col-major SpMV is not bit-identical to Eigen's product"
+    assert np.array_equal(y[::meta["sample_stride"]].view(np.uint32), g["y_colmajor"].view(np.uint32))
+    Ar = build_from_buffer(qd, buf, N, N, "row_major")
+    del buf
+    yr = (Ar @ x).to_numpy()
+    assert sha(yr) == meta["y_rowmajor_sha256"], "row-major SpMV is not bit-identical to Eigen's product"
+    del Ar, x, y, yr
+    # CG: b = A x_true, exactly the bits Eigen's product gave
+    b = A @ to_nd(qd, W.c2_cg_xtrue())
+    assert sha(b.to_numpy()) == meta["b_sha256"]
+    ref = meta["cg_f32"]
+    cg = qd.linalg.SparseCG(A, b, max_iter=ref["budget"], atol=ref["tol"])
+    xs, ok = cg.solve()
+    xs = xs.to_numpy().astype(np.float64)
+    assert ok == ref["success"] and cg.error <= ref["tol"]
+    assert abs(cg.iterations - ref["iterations"]) <= 3, (cg.iterations, ref["iterations"], meta["cg_f64"]["iterations"])
+    s = xs[::meta["sample_stride"]]
+    x32, x64 = g["cg_f32_x"].astype(np.float64), g["cg_f64_x"]
+    e32 = np.linalg.norm(s - x32) / np.linalg.norm(x32)
+    e64 = np.linalg.norm(s - x64) / np.linalg.norm(x64)
+    eig = np.linalg.norm(x32 - x64) / np.linalg.norm(x64)
+    print(f"C2 CG: iterations {cg.iterations} (Eigen f32 {ref['iterations']}, f64 {meta['cg_f64']['iterations']}); "
+          f"|x-x_eigen32|/|x| {e32:.3e}, |x-x_eigen64|/|x| {e64:.3e}, Eigen f32 vs f64 {eig:.3e}")
+    assert e32 <= 3e-5 and e64 <= 3e-5, (e32, e64, eig)
+    assert abs(np.linalg.norm(xs) - meta["cg_f64"]["x_norm2"]) <= 1e-5 * meta["cg_f64"]["x_norm2"]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# C4: 200 M random triplets, 30 % repeats, 2^24 x 2^24 (and the f64 variant at 50 M)
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("cfg, dtype, nu, nd", [("c4", np.float32, 140_000_000, 60_000_000),
+                                                ("c4d", np.float64, 35_000_000, 15_000_000)])
+def test_c4_full_size_build_vs_eigen(qd, cfg, dtype, nu, nd):
+    meta, g = gold(cfg)
+    rows = cols = 1 << 24
+    r, c, v = W.random_triplets(rows, cols, nu, nd, seed=6, dtype=dtype)
+    buf = make_triplet_buffer(r, c, v, dtype)
+    del r, c, v
+    assert int(buf[0]) == meta["triplets"] and sha(buf) == meta["buffer_sha256"], "input generator drifted"
+    A = build_from_buffer(qd, buf, rows, cols)
+    del buf
+    ip, ix, vals = assert_csr_digests(A, meta)
+    assert np.array_equal(vals[::4096].view(np.uint8), g["values"].view(np.uint8))
+    assert np.array_equal(ix[::4096], g["indices"])
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# C5: FEM tets 2 M / 400 k, fp64 -- build, SpMV (stream path), Jacobi-PCG to 1e-10
+# ---------------------------------------------------------------------------------------------------------------------
+def test_c5_full_size_build_spmv_cg_vs_eigen(qd):
+    meta, g = gold("c5")
+    r, c, v, n = W.fem_tet_triplets(400_000, 2_000_000, seed=7, dtype=np.float64, compact=True)
+    buf = make_triplet_buffer(r, c, v, np.float64)
+    del r, c, v
+    assert n == meta["rows"] and sha(buf) == meta["buffer_sha256"], "input generator drifted"
+    A = build_from_buffer(qd, buf, n, n)
+    del buf
+    assert_csr_digests(A, meta)
+    st = meta["sample_stride"]
+    x = np.random.default_rng(8).uniform(-1, 1, n)
+    y = (A @ to_nd(qd, x)).to_numpy()
+    err = np.abs(y[::st] - g["y_colmajor"])
+    assert np.all(err <= 1e-12 * g["row_scale"] + 1e-300), float((err / (g["row_scale"] + 1e-300)).max())
+    ref = meta["cg_f64"]
+    cg = qd.linalg.SparseCG(A, to_nd(qd, x), max_iter=ref["budget"], atol=ref["tol"])   # b == x (seed 8)
+    xs, ok = cg.solve()
+    xs = xs.to_numpy()
+    assert ok == ref["success"] and cg.error <= ref["tol"]
+    assert abs(cg.iterations - ref["iterations"]) <= 0.02 * ref["iterations"], (cg.iterations, ref["iterations"])
+    rel = np.linalg.norm(xs[::st] - g["cg_x"]) / np.linalg.norm(g["cg_x"])
+    print(f"C5 CG: iterations {cg.iterations} (Eigen {ref['iterations']}), |x-x_eigen|/|x| {rel:.3e}")
+    assert rel <= 1e-7, rel
+    assert abs(np.linalg.norm(xs) - ref["x_norm2"]) <= 1e-7 * ref["x_norm2"]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# A6: SparseMatrix.build_from_ndarray (tests/python/test_sparse_matrix.py:60-85)
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype_name, storage_format", [("f32", "col_major"), ("f32", "row_major"),
+                                                        ("f64", "col_major"), ("f64", "row_major")])
+def test_build_sparse_matrix_from_ndarray(qd, dtype_name, storage_format):
+    n = 8
+    triplets = qd.Vector.ndarray(n=3, dtype=qd.f32, shape=n)
+    A = qd.linalg.SparseMatrix(n=10, m=10, dtype=qd.f32, storage_format=storage_format)
+    for i in range(n):          # the reference fills with a @qd.kernel; the data contract is the N x 3 float array
+        triplets[i] = [i, i, i]
+    A.build_from_ndarray(triplets)
+    for i in range(n):
+        assert A[i, i] == i
+    assert A[9, 9] == 0 and A[0, 1] == 0
+    # unsorted rows, duplicates (summed), a non-square target, through Program.make_sparse_matrix_from_ndarray
+    t2 = qd.Vector.ndarray(n=3, dtype=qd.f32, shape=5)
+    for k, trip in enumerate([(3, 1, 2.5), (0, 4, 1.0), (3, 1, 0.5), (2, 0, -1.0), (0, 0, 7.0)]):
+        t2[k] = trip
+    B = qd.linalg.SparseMatrix(n=4, m=5, dtype=qd.f32)
+    qd.get_runtime().prog.make_sparse_matrix_from_ndarray(B.matrix, t2.arr)
+    assert B[3, 1] == 3.0 and B[0, 4] == 1.0 and B[2, 0] == -1.0 and B[0, 0] == 7.0 and B[1, 1] == 0.0
+    with pytest.raises(qd.QuadrantsRuntimeError):
+        A.build_from_ndarray(qd.ndarray(qd.f32, 10))       # 10 scalars: not divisible by 3
+    with pytest.raises(qd.QuadrantsRuntimeError):
+        A.build_from_ndarray(np.zeros((3, 3), np.float32))  # not an ndarray
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# A2: the buffer contract under a CONCURRENT ATOMIC writer (internal_functions.h:12-39)
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_atomic_insert_triplet_writer(qd, oracle, dtype):
+    """A CUDA kernel appends triplets with `id = atomic_add(buf[0], 1)` exactly like the reference's JIT kernels; the
+    arrival order is the hardware's.  The buffer is then read back as it is and given to BOTH the oracle and build():
+    indptr / indices / values must match bit for bit (duplicates are summed in ARRIVAL order, which both sides read
+    from the same bytes)."""
+    import torch
+
+    from tests.atomic_writer import AtomicWriter
+
+    rows_n, cols_n, t = 3000, 2500, 200_000
+    rng = np.random.default_rng(11)
+    r = rng.integers(0, rows_n, t).astype(np.int32)
+    c = rng.integers(0, 40, t).astype(np.int32) * 61 % cols_n        # few columns per row -> many duplicates
+    v = rng.uniform(-1, 1, t).astype(dtype)
+    K = qd.linalg.SparseMatrixBuilder(rows_n, cols_n, max_num_triplets=t + 10, dtype=qd.f32 if dtype == np.float32 else qd.f64)
+    w = AtomicWriter()
+    w.insert(K._get_ndarray_addr(), torch.from_numpy(r).cuda(), torch.from_numpy(c).cuda(), torch.from_numpy(v).cuda())
+    torch.cuda.synchronize()
+    assert K.ptr.num_triplets() == t
+    buf = K.ptr.buffer_tensor().cpu().numpy().copy()
+    assert int(buf[0]) == t
+    body = buf[1:1 + 3 * t].reshape(t, 3)
+    # same multiset of triplets, some other order
+    got = np.lexsort((body[:, 2], body[:, 1], body[:, 0]))
+    slot = np.int32 if dtype == np.float32 else np.int64
+    want = np.lexsort((v.view(slot), c, r))
+    assert np.array_equal(body[got][:, 0], r[want]) and np.array_equal(body[got][:, 2], v.view(slot)[want])
+    A = K.build()
+    ip, ix, vals = A.matrix.to_scipy_arrays()
+    oo, oi, ov = oracle.build_matrix(buf, rows_n, cols_n, True)
+    assert np.array_equal(ip, oo) and np.array_equal(ix, oi)
+    assert np.array_equal(vals.view(np.uint8), ov.view(np.uint8))
+    assert K.ptr.num_triplets() == 0        # build() resets slot 0, the builder is reusable
