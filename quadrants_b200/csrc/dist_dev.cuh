@@ -166,13 +166,21 @@ __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_re
 // the signal leaves as soon as the halo rows are done instead of at the end of the kernel (measured at 8 ranks: the
 // direction kernel took 25 us with an all-CTA ticket against 10 us without any push, profiles/r01h_8gpu_trace.txt).
 // Z = false: channel p, pushes vec[i].  Z = true: channel z, pushes vec[i] * mul[i] (r and D^-1).
-template <typename T, bool Z>
+// NT = 0: called by every thread of the CTA.  NT > 0: called by threads [0, NT) only (the consumer warps of the persistent
+// CG kernel; the producer warp is elsewhere) -- they synchronise on named barrier 1 and stride by NT.
+template <int NT>
+__device__ __forceinline__ void dist_push_bar() {
+  if constexpr (NT == 0) __syncthreads();
+  else asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+}
+template <typename T, bool Z, int NT = 0>
 __device__ __forceinline__ void dist_halo_push_impl(const DistDev &d, const T *vec, const T *mul, int lo, int hi, int per) {
   if (d.world <= 1) return;
+  const int nthreads = NT == 0 ? static_cast<int>(blockDim.x) : NT;
   bool mine = false;
   for (int s = 0; s < d.n_send; ++s) mine = mine || (lo < hi && hi > d.send_first[s] && lo <= d.send_last[s]);
   if (!mine) return;
-  __syncthreads();  // the CTA's own writes of vec[lo, hi) are visible to all its threads
+  dist_push_bar<NT>();  // the CTA's own writes of vec[lo, hi) are visible to all its threads
   for (int s = 0; s < d.n_send; ++s) {
     if (hi <= d.send_first[s] || lo > d.send_last[s]) continue;
     const int *list = d.send_list[s];
@@ -187,11 +195,11 @@ __device__ __forceinline__ void dist_halo_push_impl(const DistDev &d, const T *v
         const int nv = (jhi - jlo) / V;
         const int4 *src4 = reinterpret_cast<const int4 *>(vec + first + jlo);
         int4 *dst4 = reinterpret_cast<int4 *>(dst + jlo);
-        for (int j = threadIdx.x; j < nv; j += blockDim.x) dst4[j] = src4[j];
-        for (int j = jlo + nv * V + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = vec[first + j];
+        for (int j = threadIdx.x; j < nv; j += nthreads) dst4[j] = src4[j];
+        for (int j = jlo + nv * V + threadIdx.x; j < jhi; j += nthreads) dst[j] = vec[first + j];
       } else if (vec_ok && ((reinterpret_cast<uintptr_t>(mul + first + jlo) & 15u) == 0)) {
         const int nv = (jhi - jlo) / V;
-        for (int j = threadIdx.x; j < nv; j += blockDim.x) {
+        for (int j = threadIdx.x; j < nv; j += nthreads) {
           T a[V], m[V];
           *reinterpret_cast<int4 *>(a) = reinterpret_cast<const int4 *>(vec + first + jlo)[j];
           *reinterpret_cast<int4 *>(m) = reinterpret_cast<const int4 *>(mul + first + jlo)[j];
@@ -199,9 +207,9 @@ __device__ __forceinline__ void dist_halo_push_impl(const DistDev &d, const T *v
           for (int e = 0; e < V; ++e) a[e] = m[e] * a[e];
           reinterpret_cast<int4 *>(dst + jlo)[j] = *reinterpret_cast<int4 *>(a);
         }
-        for (int j = jlo + nv * V + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = mul[first + j] * vec[first + j];
+        for (int j = jlo + nv * V + threadIdx.x; j < jhi; j += nthreads) dst[j] = mul[first + j] * vec[first + j];
       } else {
-        for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = Z ? mul[first + j] * vec[first + j] : vec[first + j];
+        for (int j = jlo + threadIdx.x; j < jhi; j += nthreads) dst[j] = Z ? mul[first + j] * vec[first + j] : vec[first + j];
       }
     } else {
       int a = 0, b = cnt;
@@ -210,10 +218,10 @@ __device__ __forceinline__ void dist_halo_push_impl(const DistDev &d, const T *v
       b = cnt;
       while (a < b) { const int m = (a + b) >> 1; if (list[m] < hi) a = m + 1; else b = m; }
       const int jhi = a;
-      for (int j = jlo + threadIdx.x; j < jhi; j += blockDim.x) dst[j] = Z ? mul[list[j]] * vec[list[j]] : vec[list[j]];
+      for (int j = jlo + threadIdx.x; j < jhi; j += nthreads) dst[j] = Z ? mul[list[j]] * vec[list[j]] : vec[list[j]];
     }
   }
-  __syncthreads();
+  dist_push_bar<NT>();
   if (threadIdx.x == 0) {
     // number of CTAs that own a halo row: chunks [c * per, (c + 1) * per) meeting any [send_first, send_last]
     int owners = 0, covered_to = -1;  // send ranges are visited in ascending order of their first row
@@ -242,9 +250,9 @@ __device__ __forceinline__ void dist_halo_push_impl(const DistDev &d, const T *v
   }
 }
 
-template <typename T>
+template <typename T, int NT = 0>
 __device__ __forceinline__ void dist_halo_push_signal(const DistDev &d, const T *vec, int lo, int hi, int per) {
-  dist_halo_push_impl<T, false>(d, vec, nullptr, lo, hi, per);
+  dist_halo_push_impl<T, false, NT>(d, vec, nullptr, lo, hi, per);
 }
 // z channel: pushes D^-1[i] * r[i] of the halo rows in [lo, hi)
 template <typename T>

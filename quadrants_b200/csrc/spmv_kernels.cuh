@@ -90,6 +90,35 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
       "}\n" ::"r"(smem_u32(bar)), "r"(parity)
       : "memory");
 }
+// one probe of the barrier phase; true when the phase with this parity has completed
+__device__ __forceinline__ bool mbar_try_wait(unsigned long long *bar, unsigned parity) {
+  unsigned ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// BOUNDED (persistent CG kernel): gives up after ~4 s of clock64 and returns false, so that a failed peer / a bug ends the
+// kernel instead of hanging the GPU
+template <bool BOUNDED>
+__device__ __forceinline__ bool mbar_wait_b(unsigned long long *bar, unsigned parity) {
+  if constexpr (!BOUNDED) {
+    mbar_wait(bar, parity);
+    return true;
+  } else {
+    if (mbar_try_wait(bar, parity)) return true;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity))
+      if (clock64() - t0 > 8000000000LL) return false;
+    return true;
+  }
+}
 __device__ __forceinline__ unsigned long long l2_evict_first_policy() {
   unsigned long long pol;
   asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
@@ -107,6 +136,29 @@ __device__ __forceinline__ void tma_bulk_g2s(void *dst, const void *src, unsigne
 template <typename T>
 __host__ __device__ constexpr size_t spmv_stream_smem_bytes() {
   return SPMV_STREAM_STAGES * spmv_stage_bytes<T>() + 2 * SPMV_STREAM_STAGES * sizeof(unsigned long long) + 128;
+}
+
+// The operand gather.  Stand-alone kernels read x through the read-only (non-coherent) path.  Inside the persistent CG
+// kernel (cg.cu, cg_fused_kernel) the operand is REWRITTEN between two products of the same launch, by other CTAs and,
+// multi-GPU, by peer ranks: there the gather is a plain weak load (ld.global.ca), which the acquire of the grid barrier /
+// halo wait orders after those writes (the acquire invalidates the SM's L1); .nc loads are outside the memory model.
+template <bool COHERENT, typename T>
+__device__ __forceinline__ T ld_x(const T *p) {
+  if constexpr (COHERENT) return __ldca(p);
+  else return __ldg(p);
+}
+
+// mbarrier ring of a persistent SpMV: `full` (1 arrival + tx bytes) and `empty` (one arrival per consumer warp) per stage
+template <int STAGES>
+__device__ __forceinline__ void spmv_ring_init(unsigned long long *full, unsigned long long *empty) {
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], SPMV_CONSUMERS / 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
 }
 
 template <typename T>
@@ -154,16 +206,17 @@ struct NoSink {
   template <typename T> __device__ __forceinline__ void segment(int, T) {}
 };
 // sum_i w[i] * y[i] in double (CG: p.Ap)
-template <typename T>
+// (COHERENT: w is rewritten between two products of the same launch -- see ld_x)
+template <typename T, bool COHERENT = false>
 struct DotSink {
-  const T *__restrict__ w;
+  const T *w;
   double acc = 0.0;
   static constexpr int AUX = 0;
   static constexpr int CAP = SPMV_CAP;
   struct Pre { T w; };
-  __device__ __forceinline__ Pre pre(int i, const T *, int) const { return Pre{w[i]}; }
+  __device__ __forceinline__ Pre pre(int i, const T *, int) const { return Pre{ld_x<COHERENT>(w + i)}; }
   __device__ __forceinline__ void row(int, T y, Pre q) { acc += static_cast<double>(q.w * y); }
-  __device__ __forceinline__ void segment(int i, T part) { acc += static_cast<double>(w[i] * part); }
+  __device__ __forceinline__ void segment(int i, T part) { acc += static_cast<double>(ld_x<COHERENT>(w + i) * part); }
 };
 // The seven inner products of the one-reduction CG iteration (cg.cu), t = A p, z = D^-1 r:
 //   v0 = p.t  v1 = t.z  v2 = t.D^-1 t  v3 = r.t  v4 = t.t  v5 = r.z  v6 = r.r      (all accumulated in double)
@@ -194,11 +247,14 @@ struct MergedSink {
 // such block to the consumers (its acquire reaches them through the stage's mbarrier) and interior blocks start at
 // once.  The ghost segment begins on a 128-byte boundary, so no L1 line holds both owned and ghost entries.
 // `indptr`, `indices`, `values` must be readable 16 bytes past their ends (the matrices of this library carry 64).
-template <typename T, int LPR, bool ROW_MAJOR_ORDER, typename Sink>
+// FUSED (the persistent CG kernel): the caller initialised the ring once (spmv_ring_init) and calls this function once
+// per CG iteration `iter` from the producer thread and from the consumers INDEPENDENTLY (the producer streams the constant
+// matrix arrays and may run ahead of the consumers by the depth of the ring); ring positions continue across calls;
+// nothing here synchronises the whole CTA; the halo wait moves to the consumers; x is read coherently (ld_x).
+template <typename T, int LPR, bool ROW_MAJOR_ORDER, typename Sink, bool FUSED = false>
 __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int rows, const int *__restrict__ indptr,
                                                 const int *__restrict__ indices, const T *__restrict__ values,
-                                                const T *__restrict__ x, T *__restrict__ y, Sink &sink,
-                                                const DistDev &dist) {
+                                                const T *x, T *y, Sink &sink, const DistDev &dist, int iter = 0) {
   constexpr int R = SPMV_CONSUMERS / LPR;  // rows per block
   constexpr int AUX = Sink::AUX;
   constexpr int CAP = Sink::CAP;
@@ -206,19 +262,14 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
   auto *full = reinterpret_cast<unsigned long long *>(base + SPMV_STAGES * spmv_stage_bytes<T, AUX, CAP>());
   auto *empty = full + SPMV_STAGES;
   const int t = threadIdx.x;
-  if (t == 0) {
-    for (int s = 0; s < SPMV_STAGES; ++s) {
-      mbar_init(&full[s], 1);
-      mbar_init(&empty[s], SPMV_CONSUMERS / 32);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
+  if constexpr (!FUSED) spmv_ring_init<SPMV_STAGES>(full, empty);
   // no per-block ghost map for this block size: every CTA waits for the halo before its first gather
   const bool lazy_halo = dist.world > 1 && dist.ghost_blocks != nullptr && dist.ghost_block_rows == R;
-  if (dist.world > 1 && !lazy_halo) {
-    if (t == 0) dist_halo_wait(dist);
-    __syncthreads();
+  if constexpr (!FUSED) {
+    if (dist.world > 1 && !lazy_halo) {
+      if (t == 0) dist_halo_wait(dist);
+      __syncthreads();
+    }
   }
 
   const int nblk = (rows + R - 1) / R;
@@ -232,12 +283,13 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
   const int n_ghost_blk = ordered ? nblk - n_first : 0;
   const int n_tail = n_ghost_blk > static_cast<int>(blockIdx.x) ? (n_ghost_blk - 1 - blockIdx.x) / gridDim.x + 1 : 0;
   const int n_items = n_run + n_tail;
+  const int ring0 = FUSED ? iter * n_items : 0;  // ring position of this call's first item
 
   if (t >= SPMV_CONSUMERS) {
     // ---- producer: one thread ----
     if (t == SPMV_CONSUMERS && n_items > 0) {
       const unsigned long long pol = l2_evict_first_policy();
-      bool halo_pending = lazy_halo;
+      bool halo_pending = lazy_halo && !FUSED;
       int s_next = 0, blk_prev = -2;
       for (int it = 0; it < n_items; ++it) {
         int blk = blk0 + it;
@@ -246,15 +298,15 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
           dist_halo_wait(dist);
           halo_pending = false;
         }
-        const int stage = it % SPMV_STAGES;
-        const unsigned phase = (it / SPMV_STAGES) & 1;
+        const int stage = (ring0 + it) % SPMV_STAGES;
+        const unsigned phase = ((ring0 + it) / SPMV_STAGES) & 1;
         const int r0 = blk * R;
         const int nr = min(R, rows - r0);
         const int s = (blk == blk_prev + 1) ? s_next : indptr[r0];  // consecutive blocks: one indptr load per block
         const int e = indptr[r0 + nr];
         s_next = e;
         blk_prev = blk;
-        mbar_wait(&empty[stage], phase ^ 1u);
+        if (!mbar_wait_b<FUSED>(&empty[stage], phase ^ 1u)) return;
         const SpmvStage<T> st = spmv_stage<T, AUX, CAP>(base, stage);
         if (ordered) st.ptr[SPMV_DESC_SLOT] = blk;  // published by the arrive below (release)
         const int a0 = s & ~3;
@@ -284,12 +336,21 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
     // ---- consumers ----
     const int lane = t & 31, warp = t >> 5;
     const int row_in_blk = t / LPR, q = t % LPR;
+    bool halo_pending = FUSED && dist.world > 1;
     for (int it = 0; it < n_items; ++it) {
-      const int stage = it % SPMV_STAGES;
-      const unsigned phase = (it / SPMV_STAGES) & 1;
+      const int stage = (ring0 + it) % SPMV_STAGES;
+      const unsigned phase = ((ring0 + it) / SPMV_STAGES) & 1;
       const SpmvStage<T> st = spmv_stage<T, AUX, CAP>(base, stage);
-      mbar_wait(&full[stage], phase);
+      if (!mbar_wait_b<FUSED>(&full[stage], phase)) return;
       const int blk = ordered ? st.ptr[SPMV_DESC_SLOT] : blk0 + it;
+      if constexpr (FUSED) {
+        // (uniform over the consumers: every thread evaluates the same block)
+        if (halo_pending && (!lazy_halo || (ordered ? it >= n_run : dist.ghost_blocks[blk] != 0))) {
+          if (t == 0) dist_halo_wait(dist);
+          consumer_bar();
+          halo_pending = false;
+        }
+      }
       const int r0 = blk * R;
       const int nr = min(R, rows - r0);
       const int s = st.ptr[0], e = st.ptr[nr];
@@ -309,7 +370,7 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
                 const bool ok = k + j < hi;
                 const int c = ok ? st.idx[k + j] : 0;
                 v[j] = ok ? st.val[k + j] : T(0);
-                xv[j] = ok ? __ldg(x + c) : T(0);
+                xv[j] = ok ? ld_x<FUSED>(x + c) : T(0);
               }
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
@@ -337,7 +398,7 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
                 const bool ok = k + j * LPR < hi;
                 const int c = ok ? st.idx[k + j * LPR] : 0;
                 v[j] = ok ? st.val[k + j * LPR] : T(0);
-                xv[j] = ok ? __ldg(x + c) : T(0);
+                xv[j] = ok ? ld_x<FUSED>(x + c) : T(0);
               }
 #pragma unroll
               for (int j = 0; j < 4; ++j) acc = fma_t(v[j], xv[j], acc);
@@ -358,7 +419,7 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
         for (int r = warp; r < nr; r += SPMV_CONSUMERS / 32) {
           const int a = st.ptr[r], b = st.ptr[r + 1];
           T acc = T(0);
-          for (int k = a + lane; k < b; k += 32) acc = fma_t(values[k], __ldg(x + indices[k]), acc);
+          for (int k = a + lane; k < b; k += 32) acc = fma_t(values[k], ld_x<FUSED>(x + indices[k]), acc);
           acc = warp_sum(acc);
           if (lane == 0) {
             y[r0 + r] = acc;
@@ -378,31 +439,34 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
 // consumer-only barrier the rows of the block are summed from shared memory, one row per thread (many short rows) or
 // one row per warp (few long rows); a SEGMENT block reduces to one partial sum.  Not bit-identical to Eigen's order
 // (held to the 1e-5 / 1e-12 per-row tolerance).
-template <typename T, typename Sink>
+// FUSED: as for spmv_persistent (ring initialised by the caller, producer and consumers call independently once per CG
+// iteration `iter`, halo wait on the consumer side, coherent gather).
+template <typename T, typename Sink, bool FUSED = false>
 __device__ __forceinline__ void spmv_stream(unsigned char *smem_raw, const int *__restrict__ indptr,
                                             const int *__restrict__ indices, const T *__restrict__ values,
-                                            const T *__restrict__ x, T *__restrict__ y, Sink &sink,
-                                            const SpmvPlanDev &plan, const DistDev &dist) {
+                                            const T *x, T *y, Sink &sink, const SpmvPlanDev &plan, const DistDev &dist,
+                                            int iter = 0) {
   unsigned char *base = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
   auto *full = reinterpret_cast<unsigned long long *>(base + SPMV_STREAM_STAGES * spmv_stage_bytes<T>());
   auto *empty = full + SPMV_STREAM_STAGES;
   __shared__ unsigned s_last;
   const int t = threadIdx.x;
-  if (t == 0) {
-    for (int s = 0; s < SPMV_STREAM_STAGES; ++s) {
-      mbar_init(&full[s], 1);
-      mbar_init(&empty[s], SPMV_CONSUMERS / 32);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
+  if constexpr (!FUSED) spmv_ring_init<SPMV_STREAM_STAGES>(full, empty);
   if (dist.world > 1) {  // no per-block ghost map on this path: wait for the halo before the first gather
-    if (t == 0) dist_halo_wait(dist);
-    __syncthreads();
+    if constexpr (FUSED) {
+      if (t < SPMV_CONSUMERS) {
+        if (t == 0) dist_halo_wait(dist);
+        consumer_bar();
+      }
+    } else {
+      if (t == 0) dist_halo_wait(dist);
+      __syncthreads();
+    }
   }
   const int per_cta = (plan.nblk + gridDim.x - 1) / gridDim.x;
-  const int blk0 = blockIdx.x * per_cta;
+  const int blk0 = min(plan.nblk, static_cast<int>(blockIdx.x) * per_cta);
   const int blk1 = min(plan.nblk, blk0 + per_cta);
+  const int ring0 = FUSED ? iter * (blk1 - blk0) : 0;  // ring position of this call's first block
 
   if (t >= SPMV_CONSUMERS) {
     if (t == SPMV_CONSUMERS && blk0 < blk1) {
@@ -411,9 +475,9 @@ __device__ __forceinline__ void spmv_stream(unsigned char *smem_raw, const int *
       for (int blk = blk0, it = 0; blk < blk1; ++blk, ++it) {
         const int4 d = next;
         if (blk + 1 < blk1) next = plan.blocks[blk + 1];
-        const int stage = it % SPMV_STREAM_STAGES;
-        const unsigned phase = (it / SPMV_STREAM_STAGES) & 1;
-        mbar_wait(&empty[stage], phase ^ 1u);
+        const int stage = (ring0 + it) % SPMV_STREAM_STAGES;
+        const unsigned phase = ((ring0 + it) / SPMV_STREAM_STAGES) & 1;
+        if (!mbar_wait_b<FUSED>(&empty[stage], phase ^ 1u)) return;
         const SpmvStage<T> st = spmv_stage<T>(base, stage);
         *reinterpret_cast<int4 *>(st.ptr + SPMV_DESC_SLOT) = d;  // published by the arrive below (release)
         const int a0 = d.z & ~3;
@@ -440,10 +504,10 @@ __device__ __forceinline__ void spmv_stream(unsigned char *smem_raw, const int *
   } else {
     const int lane = t & 31, warp = t >> 5;
     for (int blk = blk0, it = 0; blk < blk1; ++blk, ++it) {
-      const int stage = it % SPMV_STREAM_STAGES;
-      const unsigned phase = (it / SPMV_STREAM_STAGES) & 1;
+      const int stage = (ring0 + it) % SPMV_STREAM_STAGES;
+      const unsigned phase = ((ring0 + it) / SPMV_STREAM_STAGES) & 1;
       const SpmvStage<T> st = spmv_stage<T>(base, stage);
-      mbar_wait(&full[stage], phase);
+      if (!mbar_wait_b<FUSED>(&full[stage], phase)) return;
       const int4 d = *reinterpret_cast<const int4 *>(st.ptr + SPMV_DESC_SLOT);
       const int a0 = d.z & ~3;
       const int lo = d.z - a0, cnt = d.w - a0;
@@ -454,7 +518,7 @@ __device__ __forceinline__ void spmv_stream(unsigned char *smem_raw, const int *
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const int kk = k + j * SPMV_CONSUMERS;
-          xv[j] = kk < cnt ? __ldg(x + st.idx[kk]) : T(0);
+          xv[j] = kk < cnt ? ld_x<FUSED>(x + st.idx[kk]) : T(0);
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {

@@ -25,6 +25,7 @@ import oracle as O  # noqa: E402
 from tests import workloads as W  # noqa: E402
 
 STRIDE = 4096
+C2_STRIDE = 4099   # prime: a power-of-two stride on the 256^3 grid would sample the k = 0 boundary plane only
 
 
 def sha(a) -> str:
@@ -63,7 +64,7 @@ def c2(ref):
     mc = ref.matrix_from_compressed(outer, inner, vals, N, N, False)   # symmetric: CSC arrays == CSR arrays
     yc = mc.spmv(x)
     meta["y_colmajor_sha256"] = sha(yc)
-    arrays = {"y_rowmajor": y[::STRIDE].copy(), "y_colmajor": yc[::STRIDE].copy()}
+    arrays = {"y_rowmajor": y[::C2_STRIDE].copy(), "y_colmajor": yc[::C2_STRIDE].copy()}
     xt = W.c2_cg_xtrue()
     b = mc.spmv(xt)
     meta["b_sha256"] = sha(b)
@@ -73,7 +74,7 @@ def c2(ref):
     meta["cg_f32"] = {"success": bool(ok), "iterations": int(it), "error": float(err), "tol": 1e-6, "budget": 1000,
                       "x_norm2": float(np.linalg.norm(xs.astype(np.float64))),
                       "rel_err_vs_xtrue": float(np.linalg.norm(xs.astype(np.float64) - xt) / np.linalg.norm(xt.astype(np.float64)))}
-    arrays["cg_f32_x"] = xs[::STRIDE].copy()
+    arrays["cg_f32_x"] = xs[::C2_STRIDE].copy()
     del mc
     md = ref.matrix_from_compressed(outer, inner, vals.astype(np.float64), N, N, False)
     t1 = time.time()
@@ -83,8 +84,8 @@ def c2(ref):
                       "x_norm2": float(np.linalg.norm(xd)),
                       "rel_err_vs_xtrue": float(np.linalg.norm(xd - xt) / np.linalg.norm(xt.astype(np.float64)))}
     meta["cg_f32"]["rel_err_vs_f64"] = float(np.linalg.norm(xs.astype(np.float64) - xd) / np.linalg.norm(xd))
-    arrays["cg_f64_x"] = xd[::STRIDE].copy()
-    meta["sample_stride"] = STRIDE
+    arrays["cg_f64_x"] = xd[::C2_STRIDE].copy()
+    meta["sample_stride"] = C2_STRIDE
     save("c2", meta, arrays)
 
 

@@ -86,7 +86,7 @@ def test_c2_full_size_build_spmv_cg_vs_eigen(qd):
     x = to_nd(qd, W.c2_spmv_x())
     y = (A @ x).to_numpy()
     assert sha(y) == meta["y_colmajor_sha256"], "col-major SpMV is not bit-identical to Eigen's product"
-    assert np.array_equal(y[::meta["sample_stride"]].view(np.uint32), g["y_colmajor"].view(np.uint32))
+    assert np.array_equal(np.ascontiguousarray(y[::meta["sample_stride"]]).view(np.uint32), g["y_colmajor"].view(np.uint32))
     Ar = build_from_buffer(qd, buf, N, N, "row_major")
     del buf
     yr = (Ar @ x).to_numpy()
@@ -127,7 +127,7 @@ def test_c4_full_size_build_vs_eigen(qd, cfg, dtype, nu, nd):
     A = build_from_buffer(qd, buf, rows, cols)
     del buf
     ip, ix, vals = assert_csr_digests(A, meta)
-    assert np.array_equal(vals[::4096].view(np.uint8), g["values"].view(np.uint8))
+    assert np.array_equal(np.ascontiguousarray(vals[::4096]).view(np.uint8), g["values"].view(np.uint8))
     assert np.array_equal(ix[::4096], g["indices"])
 
 

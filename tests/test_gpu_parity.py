@@ -643,3 +643,48 @@ def test_error_behaviour(qd):
         qd.algorithms.PrefixSumExecutor(8).run(qd.ndarray(qd.f32, 8))
     with pytest.raises(RuntimeError):
         qd.linalg.SparseMatrixBuilder(4, 4, max_num_triplets=4, storage_format="diag")
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# persistent (fused) CG kernel vs the three-kernel iteration
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", ["poisson2d_f32", "poisson2d_f64", "fem_f64", "fem_f32", "rowmajor_f32"])
+def test_cg_fused_kernel_matches_three_kernel_form(qd, oracle, monkeypatch, case):
+    """The default solver runs the whole loop in ONE cooperative persistent kernel (cg.cu, cg_fused_kernel); QDSP_CG_FUSED=0
+    selects the three-kernel iteration it replaces.  Same recurrence, same scalar roundings, same stopping rule: the two
+    must stop within a few iterations of each other (only the grouping of the dot-product partials differs) and agree
+    with the oracle like every other CG test; a fixed-budget run must give the same x to rounding."""
+    f64 = case.endswith("f64")
+    dtype = np.float64 if f64 else np.float32
+    if case.startswith("fem"):
+        r, c, v, n = W.fem_tet_triplets(20000, 120000, seed=7, dtype=dtype, compact=True)   # stream path
+        b = np.random.default_rng(9).uniform(-1, 1, n).astype(dtype)
+        tol, budget = (1e-10 if f64 else 1e-5), 5000
+    else:
+        r, c, v = W.poisson2d_triplets(200, dtype=dtype)
+        n = 200 * 200
+        b = np.ones(n, dtype)
+        tol, budget = 1e-6, 2000
+    buf = make_triplet_buffer(r, c, v, dtype)
+    A = build_from_buffer(qd, buf, n, n, "row_major" if case.startswith("rowmajor") else "col_major")
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("QDSP_CG_FUSED", mode)
+        cg = qd.linalg.SparseCG(A, to_nd(qd, b), max_iter=budget, atol=tol)
+        x, ok = cg.solve()
+        xa, ita = x.to_numpy().copy(), cg.iterations
+        x2, ok2 = cg.solve()                       # a second solve on the same solver object: state fully reset, and
+        assert ok and ok2 and cg.iterations == ita  # the fixed-order reductions make it reproducible bit for bit
+        assert np.array_equal(bits(xa), bits(x2.to_numpy()))
+        xf = qd.ndarray(qd.f64 if f64 else qd.f32, n)
+        cg.cg_solver.run_fixed(xf, to_nd(qd, b), 25)
+        out[mode] = (cg.iterations, x.to_numpy().astype(np.float64), xf.to_numpy().astype(np.float64), cg.error)
+    (it1, x1, f1, e1), (it0, x0, f0, e0) = out["1"], out["0"]
+    assert abs(it1 - it0) <= max(2, 0.02 * it0), (it1, it0)
+    assert e1 <= tol and e0 <= tol
+    assert np.linalg.norm(f1 - f0) / np.linalg.norm(f0) < (1e-12 if f64 else 2e-5)
+    co, ci, cv = oracle.build_matrix(buf, n, n, False)
+    xo, oko, ito, _ = oracle.cg(co, ci, cv, b, budget, tol)
+    assert oko and abs(it1 - ito) <= (max(3, 0.02 * ito) if f64 else 0.25 * ito), (it1, ito)
+    rel = np.linalg.norm(x1 - xo) / np.linalg.norm(xo)
+    assert rel < (1e-8 if f64 else 2e-2), rel
