@@ -343,7 +343,7 @@ __device__ __forceinline__ void cg_residual_body(const T *__restrict__ tmp, cons
     s_rr = fma_t(r4.z, r4.z, s_rr); s_rz = fma_t(r4.z, d4.z * r4.z, s_rz);
     s_rr = fma_t(r4.w, r4.w, s_rr); s_rz = fma_t(r4.w, d4.w * r4.w, s_rz);
   }
-  for (int i = (hi4 << 2) + threadIdx.x; i < hi; i += blockDim.x) {
+  for (int i = max(lo, hi4 << 2) + threadIdx.x; i < hi; i += blockDim.x) {
     const T ri = fma_t(-alpha, tmp[i], r[i]);
     r[i] = ri;
     s_rr = fma_t(ri, ri, s_rr);
@@ -428,7 +428,7 @@ __device__ __forceinline__ void cg_direction_body(const T *r, const T *__restric
       reinterpret_cast<V *>(p)[i] = p4;
     }
   }
-  for (int i = (hi4 << 2) + threadIdx.x; i < hi; i += nthreads) {
+  for (int i = max(lo, hi4 << 2) + threadIdx.x; i < hi; i += nthreads) {
     const T pi = p[i];
     if (with_x) x[i] = fma_t(alpha, pi, x[i]);
     if (update_p) p[i] = fma_t(beta, pi, dinv[i] * r[i]);
@@ -527,7 +527,7 @@ cg_update_merged_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ 
       reinterpret_cast<V *>(p)[i] = p4;
     }
   }
-  for (int i = (hi4 << 2) + threadIdx.x; i < hi; i += blockDim.x) {
+  for (int i = max(lo, hi4 << 2) + threadIdx.x; i < hi; i += blockDim.x) {
     const T ri = fma_t(-alpha, tmp[i], r[i]);
     const T pi = p[i];
     r[i] = ri;
@@ -704,16 +704,37 @@ cg_fused_kernel(int rows, const int *__restrict__ indptr, const int *__restrict_
     hi = min(rows, lo + per);
   }
   using V = typename Vec4T<T>::type;
+  // (a CTA past the end has lo == hi == rows: an EMPTY chunk; the scalar tails below start at max(lo, hi4 << 2) so that such
+  // a CTA does not redo the rows % 4 last elements -- that was a real bug: x[n-1] updated once per idle CTA)
   const int lo4 = lo >> 2, hi4 = hi >> 2;
+  // The vector phases: plain pointers (the arrays are rewritten within this launch, so no __restrict__ / read-only path),
+  // which also forbids the compiler to hoist the loads of the next element group above the stores of this one.  The
+  // loops are therefore batched by hand: U 128-bit groups per thread are loaded first, then updated and stored.
+  constexpr int U = sizeof(T) == 4 ? 2 : 1;  // (register budget: 56 / 72 per thread, see fused_min_blocks)
   auto update_x = [&](T alpha) {
-    for (int i = lo4 + t; i < hi4; i += SPMV_CONSUMERS) {
+    int i = lo4 + t;
+    for (; i + (U - 1) * SPMV_CONSUMERS < hi4; i += U * SPMV_CONSUMERS) {
+      V p4[U], x4[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        p4[u] = reinterpret_cast<const V *>(p)[i + u * SPMV_CONSUMERS];
+        x4[u] = reinterpret_cast<const V *>(x)[i + u * SPMV_CONSUMERS];
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        x4[u].x = fma_t(alpha, p4[u].x, x4[u].x); x4[u].y = fma_t(alpha, p4[u].y, x4[u].y);
+        x4[u].z = fma_t(alpha, p4[u].z, x4[u].z); x4[u].w = fma_t(alpha, p4[u].w, x4[u].w);
+        reinterpret_cast<V *>(x)[i + u * SPMV_CONSUMERS] = x4[u];
+      }
+    }
+    for (; i < hi4; i += SPMV_CONSUMERS) {
       const V p4 = reinterpret_cast<const V *>(p)[i];
       V x4 = reinterpret_cast<V *>(x)[i];
       x4.x = fma_t(alpha, p4.x, x4.x); x4.y = fma_t(alpha, p4.y, x4.y);
       x4.z = fma_t(alpha, p4.z, x4.z); x4.w = fma_t(alpha, p4.w, x4.w);
       reinterpret_cast<V *>(x)[i] = x4;
     }
-    for (int i = (hi4 << 2) + t; i < hi; i += SPMV_CONSUMERS) x[i] = fma_t(alpha, p[i], x[i]);
+    for (int k = max(lo, hi4 << 2) + t; k < hi; k += SPMV_CONSUMERS) x[k] = fma_t(alpha, p[k], x[k]);
   };
   for (int it = 0; it < iters; ++it) {
     // ---- A: tmp = A p, p.tmp ----
@@ -730,10 +751,7 @@ cg_fused_kernel(int rows, const int *__restrict__ indptr, const int *__restrict_
     // ---- B: r -= alpha tmp, |r|^2, r.D^-1 r ----
     {
       T s_rr = T(0), s_rz = T(0);
-      for (int i = lo4 + t; i < hi4; i += SPMV_CONSUMERS) {
-        const V t4 = reinterpret_cast<const V *>(tmp)[i];
-        const V d4 = reinterpret_cast<const V *>(dinv)[i];
-        V r4 = reinterpret_cast<V *>(r)[i];
+      auto one = [&](const V &t4, const V &d4, V r4, int i) {
         r4.x = fma_t(-alpha, t4.x, r4.x); r4.y = fma_t(-alpha, t4.y, r4.y);
         r4.z = fma_t(-alpha, t4.z, r4.z); r4.w = fma_t(-alpha, t4.w, r4.w);
         reinterpret_cast<V *>(r)[i] = r4;
@@ -741,12 +759,26 @@ cg_fused_kernel(int rows, const int *__restrict__ indptr, const int *__restrict_
         s_rr = fma_t(r4.y, r4.y, s_rr); s_rz = fma_t(r4.y, d4.y * r4.y, s_rz);
         s_rr = fma_t(r4.z, r4.z, s_rr); s_rz = fma_t(r4.z, d4.z * r4.z, s_rz);
         s_rr = fma_t(r4.w, r4.w, s_rr); s_rz = fma_t(r4.w, d4.w * r4.w, s_rz);
+      };
+      int i = lo4 + t;
+      for (; i + (U - 1) * SPMV_CONSUMERS < hi4; i += U * SPMV_CONSUMERS) {
+        V t4[U], d4[U], r4[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          t4[u] = reinterpret_cast<const V *>(tmp)[i + u * SPMV_CONSUMERS];
+          d4[u] = reinterpret_cast<const V *>(dinv)[i + u * SPMV_CONSUMERS];
+          r4[u] = reinterpret_cast<const V *>(r)[i + u * SPMV_CONSUMERS];
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) one(t4[u], d4[u], r4[u], i + u * SPMV_CONSUMERS);
       }
-      for (int i = (hi4 << 2) + t; i < hi; i += SPMV_CONSUMERS) {
-        const T ri = fma_t(-alpha, tmp[i], r[i]);
-        r[i] = ri;
+      for (; i < hi4; i += SPMV_CONSUMERS)
+        one(reinterpret_cast<const V *>(tmp)[i], reinterpret_cast<const V *>(dinv)[i], reinterpret_cast<const V *>(r)[i], i);
+      for (int k = max(lo, hi4 << 2) + t; k < hi; k += SPMV_CONSUMERS) {
+        const T ri = fma_t(-alpha, tmp[k], r[k]);
+        r[k] = ri;
         s_rr = fma_t(ri, ri, s_rr);
-        s_rz = fma_t(ri, dinv[i] * ri, s_rz);
+        s_rz = fma_t(ri, dinv[k] * ri, s_rz);
       }
       double v[2] = {static_cast<double>(s_rr), static_cast<double>(s_rz)};
       fused_arrive<2>(B, v, partials, s_red, d, [&](const double (&s)[2]) { cg_finish_B<T>(sc, s[0], s[1]); });
@@ -761,8 +793,40 @@ cg_fused_kernel(int rows, const int *__restrict__ indptr, const int *__restrict_
     }
     if (t == 0) *reinterpret_cast<volatile int *>(&s_go) = it + 2;  // iteration it + 1 will run: let the producer start it
     // ---- C: p = D^-1 r + beta p (and the deferred x += alpha p), halo ----
-    cg_direction_body<T>(r, dinv, p, x, overlap_x ? T(0) : alpha, static_cast<T>(__ldcg(&sc->beta)), true, lo, hi,
-                         SPMV_CONSUMERS, !overlap_x);
+    {
+      const T beta = static_cast<T>(__ldcg(&sc->beta));
+      const bool with_x = !overlap_x;
+      auto one = [&](V p4, const V &r4, const V &d4, int i) {
+        if (with_x) {
+          V x4 = reinterpret_cast<const V *>(x)[i];
+          x4.x = fma_t(alpha, p4.x, x4.x); x4.y = fma_t(alpha, p4.y, x4.y);
+          x4.z = fma_t(alpha, p4.z, x4.z); x4.w = fma_t(alpha, p4.w, x4.w);
+          reinterpret_cast<V *>(x)[i] = x4;
+        }
+        p4.x = fma_t(beta, p4.x, d4.x * r4.x); p4.y = fma_t(beta, p4.y, d4.y * r4.y);
+        p4.z = fma_t(beta, p4.z, d4.z * r4.z); p4.w = fma_t(beta, p4.w, d4.w * r4.w);
+        reinterpret_cast<V *>(p)[i] = p4;
+      };
+      int i = lo4 + t;
+      for (; i + (U - 1) * SPMV_CONSUMERS < hi4; i += U * SPMV_CONSUMERS) {
+        V p4[U], r4[U], d4[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          p4[u] = reinterpret_cast<const V *>(p)[i + u * SPMV_CONSUMERS];
+          r4[u] = reinterpret_cast<const V *>(r)[i + u * SPMV_CONSUMERS];
+          d4[u] = reinterpret_cast<const V *>(dinv)[i + u * SPMV_CONSUMERS];
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) one(p4[u], r4[u], d4[u], i + u * SPMV_CONSUMERS);
+      }
+      for (; i < hi4; i += SPMV_CONSUMERS)
+        one(reinterpret_cast<const V *>(p)[i], reinterpret_cast<const V *>(r)[i], reinterpret_cast<const V *>(dinv)[i], i);
+      for (int k = max(lo, hi4 << 2) + t; k < hi; k += SPMV_CONSUMERS) {
+        const T pk = p[k];
+        if (with_x) x[k] = fma_t(alpha, pk, x[k]);
+        p[k] = fma_t(beta, pk, dinv[k] * r[k]);
+      }
+    }
     dist_halo_push_signal<T, SPMV_CONSUMERS>(d, p, lo, hi, per);
     {
       double none[1];

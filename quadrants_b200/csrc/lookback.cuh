@@ -25,14 +25,16 @@ __device__ __forceinline__ unsigned take_ticket(unsigned *counter, unsigned *sme
 // 32 at a time and returns (to every lane) the exclusive prefix of the tile; finally publishes the inclusive prefix.
 // Values are summed modulo 2^62 (callers truncate to their width, so i32 wrap-around is preserved).
 __device__ __forceinline__ unsigned long long lookback_exclusive(unsigned long long *desc, unsigned tile,
-                                                                 unsigned long long aggregate) {
+                                                                 unsigned long long aggregate, int shift = 0,
+                                                                 unsigned backoff_ns = 0) {
+  // shift: descriptors are 8 << shift bytes apart (padding spreads the hot descriptors over more L2 slices)
   const unsigned lane = lane_id();
   aggregate &= LB_VALUE_MASK;
   if (tile == 0) {
     if (lane == 0) st_relaxed_u64(&desc[0], LB_PREFIX | aggregate);
     return 0ull;
   }
-  if (lane == 0) st_relaxed_u64(&desc[tile], LB_AGGREGATE | aggregate);
+  if (lane == 0) st_relaxed_u64(&desc[static_cast<size_t>(tile) << shift], LB_AGGREGATE | aggregate);
   unsigned long long exclusive = 0ull;
   long long idx = static_cast<long long>(tile) - 1;
   while (true) {
@@ -43,11 +45,12 @@ __device__ __forceinline__ unsigned long long lookback_exclusive(unsigned long l
     unsigned long long d;
     unsigned pmask;
     while (true) {
-      d = (t >= 0) ? ld_relaxed_u64(&desc[t]) : LB_PREFIX;  // before tile 0: a prefix of zero
+      d = (t >= 0) ? ld_relaxed_u64(&desc[static_cast<size_t>(t) << shift]) : LB_PREFIX;  // before tile 0: a prefix of zero
       const unsigned inv = __ballot_sync(FULL, (d & LB_STATUS_MASK) == LB_INVALID);
       pmask = __ballot_sync(FULL, (d & LB_STATUS_MASK) == LB_PREFIX);
       const unsigned nearer = pmask ? ((1u << (__ffs(pmask) - 1)) - 1u) : FULL;
       if ((inv & nearer) == 0u) break;
+      if (backoff_ns) __nanosleep(backoff_ns);
     }
     unsigned long long v = d & LB_VALUE_MASK;
     if (pmask) {
@@ -60,9 +63,10 @@ __device__ __forceinline__ unsigned long long lookback_exclusive(unsigned long l
     idx -= 32;
   }
   exclusive &= LB_VALUE_MASK;
-  if (lane == 0) st_relaxed_u64(&desc[tile], LB_PREFIX | ((exclusive + aggregate) & LB_VALUE_MASK));
+  if (lane == 0) st_relaxed_u64(&desc[static_cast<size_t>(tile) << shift], LB_PREFIX | ((exclusive + aggregate) & LB_VALUE_MASK));
   return exclusive;
 }
+
 #endif
 
 }  // namespace qdsp

@@ -25,6 +25,7 @@
 #pragma once
 #include "common.cuh"
 #include "dist_dev.cuh"
+#include "tma.cuh"
 
 namespace qdsp {
 
@@ -65,72 +66,6 @@ __host__ __device__ constexpr size_t spmv_stage_bytes() {
 template <typename T, int AUX = 0, int CAP = SPMV_CAP>
 __host__ __device__ constexpr size_t spmv_smem_bytes() {
   return SPMV_STAGES * spmv_stage_bytes<T, AUX, CAP>() + 2 * SPMV_STAGES * sizeof(unsigned long long) + 128 /*alignment slack*/;
-}
-
-// ---- mbarrier / TMA bulk-copy primitives (sm_90+; SASS: SYNCS.*, UBLKCP) -------------------------------------------
-__device__ __forceinline__ unsigned smem_u32(const void *p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
-__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\n"
-      "bra WAIT_%=;\n"
-      "DONE_%=:\n"
-      "}\n" ::"r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-}
-// one probe of the barrier phase; true when the phase with this parity has completed
-__device__ __forceinline__ bool mbar_try_wait(unsigned long long *bar, unsigned parity) {
-  unsigned ok;
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-      "selp.u32 %0, 1, 0, p;\n"
-      "}\n"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-// BOUNDED (persistent CG kernel): gives up after ~4 s of clock64 and returns false, so that a failed peer / a bug ends the
-// kernel instead of hanging the GPU
-template <bool BOUNDED>
-__device__ __forceinline__ bool mbar_wait_b(unsigned long long *bar, unsigned parity) {
-  if constexpr (!BOUNDED) {
-    mbar_wait(bar, parity);
-    return true;
-  } else {
-    if (mbar_try_wait(bar, parity)) return true;
-    const long long t0 = clock64();
-    while (!mbar_try_wait(bar, parity))
-      if (clock64() - t0 > 8000000000LL) return false;
-    return true;
-  }
-}
-__device__ __forceinline__ unsigned long long l2_evict_first_policy() {
-  unsigned long long pol;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-// global -> shared bulk copy; dst/src 16-byte aligned, bytes a multiple of 16; completes on `bar`
-__device__ __forceinline__ void tma_bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *bar,
-                                             unsigned long long policy) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-      ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
-      : "memory");
 }
 
 template <typename T>

@@ -685,6 +685,33 @@ def test_cg_fused_kernel_matches_three_kernel_form(qd, oracle, monkeypatch, case
     assert np.linalg.norm(f1 - f0) / np.linalg.norm(f0) < (1e-12 if f64 else 2e-5)
     co, ci, cv = oracle.build_matrix(buf, n, n, False)
     xo, oko, ito, _ = oracle.cg(co, ci, cv, b, budget, tol)
-    assert oko and abs(it1 - ito) <= (max(3, 0.02 * ito) if f64 else 0.25 * ito), (it1, ito)
+    # fp32: Eigen's sequential float dot products lose orthogonality and need MORE iterations than the GPU's double-
+    # accumulated ones (test_cg_c1_poisson512 documents the same effect): never slower than the reference is the bar
+    assert oko and (abs(it1 - ito) <= max(3, 0.02 * ito) if f64 else it1 <= 1.05 * ito), (it1, ito)
     rel = np.linalg.norm(x1 - xo) / np.linalg.norm(xo)
     assert rel < (1e-8 if f64 else 2e-2), rel
+
+
+@pytest.mark.parametrize("shift", [1, 2, 3])
+@pytest.mark.parametrize("n", [1, 5, 8191, 8192, 8193, 100003])
+def test_scan_unaligned_pointer(qd, oracle, shift, n):
+    """the reference scans whatever i32 field it is given; a pointer that is only 4-byte aligned must
+    work (tile 0 skips the 1-3 foreign slots in front of it) and must not touch its neighbours."""
+    import ctypes as C
+
+    import torch
+
+    from quadrants_b200 import _lib
+
+    lib = _lib.load()
+    rng = np.random.default_rng(n + shift)
+    a = rng.integers(-2**31, 2**31, n + shift + 5, dtype=np.int64).astype(np.int32)
+    t = torch.from_numpy(a).cuda()
+    tmp = torch.empty(lib.qdsp_scan_tmp_bytes(n), dtype=torch.uint8, device="cuda")
+    view = t[shift:shift + n]
+    assert view.data_ptr() % 16 == 4 * shift
+    _lib.check(lib.qdsp_inclusive_scan_i32(view.data_ptr(), n, tmp.data_ptr(), tmp.numel(),
+                                           torch.cuda.current_stream().cuda_stream))
+    out = t.cpu().numpy()
+    assert np.array_equal(out[shift:shift + n], oracle.inclusive_scan(a[shift:shift + n]))
+    assert np.array_equal(out[:shift], a[:shift]) and np.array_equal(out[shift + n:], a[shift + n:])
