@@ -62,6 +62,10 @@ struct CgScalars {
   unsigned ticket[4];
   unsigned gen;          // generation of the grid barrier of the persistent kernel (cg_fused_kernel)
   unsigned bar_ticket;   // its arrival counter
+  // QDSP_CG_TRACE=2: nanoseconds CTA 0 ([0..6)) and the last CTA ([6..12)) spent in {A, barrier 1, B, barrier 2, C,
+  // barrier 3} of the persistent kernel, summed over the iterations of one launch (a debugging aid)
+  unsigned long long tprof[12];
+  int trace;
 };
 
 // ---- block / grid reductions ----------------------------------------------------------------------------------------
@@ -282,7 +286,7 @@ template <typename T, int LPR, bool ROW_MAJOR_ORDER>
 __global__ void __launch_bounds__(SPMV_THREADS)
 cg_spmv_dot_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ indices,
                    const T *__restrict__ values, const T *__restrict__ p, T *__restrict__ tmp,
-                   CgScalars *__restrict__ sc, double *__restrict__ partials, DistDev d, int use_nccl) {
+                   CgScalars *__restrict__ sc, double *__restrict__ partials, DistDev d, int use_nccl, SpmvSched sched) {
   extern __shared__ unsigned char smem_raw[];
   __shared__ double s_red[16];
   __shared__ unsigned s_flag;
@@ -294,7 +298,7 @@ cg_spmv_dot_kernel(int rows, const int *__restrict__ indptr, const int *__restri
     return;
   }
   DotSink<T> sink{p};
-  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, sink, d);
+  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, sink, d, 0, sched);
   double v[1] = {sink.acc};
   if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag))
     cg_reduce_and_finish<1>(v, d, use_nccl, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
@@ -566,6 +570,12 @@ __device__ __forceinline__ void st_release_gpu_u32(unsigned *p, unsigned v) {
   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 // block sum over the 256 consumer threads (named barrier 1; the producer warp is elsewhere)
 template <int NV>
 __device__ __forceinline__ void consumer_block_sum(double (&v)[NV], double *s_red /* NV * 8 */) {
@@ -640,13 +650,18 @@ __device__ __forceinline__ void fused_arrive(FusedBar &B, double (&v)[NV == 0 ? 
 // Waiting half: returns when the barrier whose arrival was the last fused_arrive has opened.
 __device__ __forceinline__ void fused_wait(FusedBar &B) {
   if (threadIdx.x == 0) {
+    // Poll with RELAXED loads and acquire once at the end: an acquire load invalidates the SM's L1 every time it is
+    // issued, and a CTA spinning on acquires wipes the x lines that the other three CTAs of the SM are still gathering
+    // from (measured: the first version of this kernel ran 13 % slower than the three-kernel iteration for this reason)
     const long long t0 = clock64();
-    while (static_cast<int>(ld_acquire_gpu_u32(&B.sc->gen) - B.gen) < 0) {
+    while (static_cast<int>(ld_relaxed_u32(&B.sc->gen) - B.gen) < 0) {
+      __nanosleep(40);
       if (clock64() - t0 > DIST_SPIN_LIMIT) {
         *B.s_flag = 2u;
         break;
       }
     }
+    (void)ld_acquire_gpu_u32(&B.sc->gen);
   }
   consumer_bar();
   if (*B.s_flag == 2u) B.failed = 1;
@@ -736,6 +751,16 @@ cg_fused_kernel(int rows, const int *__restrict__ indptr, const int *__restrict_
     }
     for (int k = max(lo, hi4 << 2) + t; k < hi; k += SPMV_CONSUMERS) x[k] = fma_t(alpha, p[k], x[k]);
   };
+  const bool prof = sc->trace != 0 && t == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1);
+  unsigned long long *tp = sc->tprof + (blockIdx.x == 0 ? 0 : 6);
+  unsigned long long tq = prof ? globaltimer_ns() : 0ull;
+  auto mark = [&](int k) {
+    if (prof) {
+      const unsigned long long now = globaltimer_ns();
+      tp[k] += now - tq;
+      tq = now;
+    }
+  };
   for (int it = 0; it < iters; ++it) {
     // ---- A: tmp = A p, p.tmp ----
     DotSink<T, true> sink{p};
@@ -743,8 +768,10 @@ cg_fused_kernel(int rows, const int *__restrict__ indptr, const int *__restrict_
     else spmv_persistent<T, LPR, ROW_MAJOR_ORDER, DotSink<T, true>, true>(smem_raw, rows, indptr, indices, values, p, tmp, sink, d, it);
     {
       double v[1] = {sink.acc};
+      mark(0);
       fused_arrive<1>(B, v, partials, s_red, d, [&](const double (&s)[1]) { cg_finish_A<T>(sc, s[0]); });
       fused_wait(B);
+      mark(1);
     }
     if (B.failed || __ldcg(&sc->done) == 3) break;
     const T alpha = static_cast<T>(__ldcg(&sc->alpha));
@@ -781,9 +808,11 @@ cg_fused_kernel(int rows, const int *__restrict__ indptr, const int *__restrict_
         s_rz = fma_t(ri, dinv[k] * ri, s_rz);
       }
       double v[2] = {static_cast<double>(s_rr), static_cast<double>(s_rz)};
+      mark(2);
       fused_arrive<2>(B, v, partials, s_red, d, [&](const double (&s)[2]) { cg_finish_B<T>(sc, s[0], s[1]); });
       if (overlap_x) update_x(alpha);  // needs alpha only: runs while the reduction crosses NVLink
       fused_wait(B);
+      mark(3);
     }
     const int done = __ldcg(&sc->done);
     if (B.failed || done != 0 || it + 1 == iters) {
@@ -828,11 +857,13 @@ cg_fused_kernel(int rows, const int *__restrict__ indptr, const int *__restrict_
       }
     }
     dist_halo_push_signal<T, SPMV_CONSUMERS>(d, p, lo, hi, per);
+    mark(4);
     {
       double none[1];
       fused_arrive<0>(B, none, partials, s_red, d, [](const double (&)[1]) {});
       fused_wait(B);
     }
+    mark(5);
     if (B.failed) break;
   }
   if (t == 0) {
@@ -850,7 +881,7 @@ struct CgSolver::Impl {
   bool verbose;
   DistContext *dist;
   bool use_nccl = false;
-  DeviceBuffer r, p_own, tmp, dinv, partials, scalars, xstage, bstage;
+  DeviceBuffer r, p_own, tmp, dinv, partials, scalars, xstage, bstage, sched;  // sched: this solver's SpMV work counters
   void *p = nullptr;          // operand vector of the SpMV: p_own, or the comm buffer's vector when distributed
   CgScalars *h_sc = nullptr;  // pinned mirror
   cudaStream_t stream = nullptr;
@@ -899,12 +930,13 @@ void launch_spmv_dot(CgSolver::Impl &I) {
   const CsrMatrix &A = I.A;
   auto *sc = I.scalars.get<CgScalars>();
   const size_t smem = spmv_smem_bytes<T>();
+  const SpmvSched sched = spmv_sched_for(ceil_div(I.n, SPMV_CONSUMERS / LPR), I.spmv_grid, I.sched.get<unsigned>());
   if (A.row_major_order && LPR == 1)
     launch_pdl(cg_spmv_dot_kernel<T, LPR, true>, I.spmv_grid, SPMV_THREADS, smem, I.stream, I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
-        sc, I.partials.get<double>(), I.dev(), I.use_nccl);
+        sc, I.partials.get<double>(), I.dev(), I.use_nccl, sched);
   else
     launch_pdl(cg_spmv_dot_kernel<T, LPR, false>, I.spmv_grid, SPMV_THREADS, smem, I.stream, I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
-        sc, I.partials.get<double>(), I.dev(), I.use_nccl);
+        sc, I.partials.get<double>(), I.dev(), I.use_nccl, sched);
 }
 
 template <typename T>
@@ -1091,6 +1123,10 @@ void start(CgSolver::Impl &I, T *x, const T *b, int max_iters, double tol, bool 
   init.stop_le = (I.mode == QDSP_CG_CUCG) ? 1 : 0;
   init.relative = I.mode == QDSP_CG_EIGEN_JACOBI;
   init.tol = never_converge ? -1.0 : tol;
+  {
+    const char *tr = std::getenv("QDSP_CG_TRACE");
+    init.trace = (tr && tr[0] == '2') ? 1 : 0;
+  }
   QDSP_CUDA(cudaMemcpyAsync(sc, &init, sizeof(init), cudaMemcpyHostToDevice, I.stream));
   const T *tmp = nullptr;
   if (I.mode == QDSP_CG_EIGEN_JACOBI) {
@@ -1214,6 +1250,23 @@ void run_fixed_t(CgSolver::Impl &I, void *x, const void *b, int iters, cudaStrea
     run_traced<T>(I, static_cast<T *>(x), iters);
   } else if (I.fused) {
     if (iters > 0) fused_dispatch<T>(I, static_cast<T *>(x), iters);
+    if (trace && trace[0] == '2') {
+      CgScalars &h = *I.h_sc;
+      QDSP_CUDA(cudaMemcpyAsync(&h, I.scalars.get(), sizeof(CgScalars), cudaMemcpyDeviceToHost, I.stream));
+      QDSP_CUDA(cudaStreamSynchronize(I.stream));
+      const char *names[6] = {"A spmv", "bar1", "B resid", "bar2", "C direc", "bar3"};
+      for (int who = 0; who < 2; ++who) {
+        std::fprintf(stderr, "[qdsp fused trace rank %d, %s CTA] us per iteration over %d:", I.dist ? I.dist->rank() : 0,
+                     who == 0 ? "first" : "last", iters);
+        double tot = 0;
+        for (int k = 0; k < 6; ++k) {
+          const double us = 1e-3 * static_cast<double>(h.tprof[who * 6 + k]) / iters;
+          tot += us;
+          std::fprintf(stderr, " %s %.2f", names[k], us);
+        }
+        std::fprintf(stderr, " | total %.2f\n", tot);
+      }
+    }
   } else {
     ensure_graph<T>(I, static_cast<T *>(x), batch);
     int left = iters;
@@ -1262,7 +1315,14 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
     const int R = SPMV_CONSUMERS / I.lpr;
     I.spmv_grid = std::max(1, std::min(ceil_div(A.rows, R), device_props().sm_count * occ));
   }
-  I.vec_grid = std::max(1, std::min(ceil_div(A.rows, 1024), device_props().sm_count * 8));
+  // CTAs of the vector kernels: up to 8 per SM; QDSP_CG_VEC_CTAS=k caps it at k per SM (fewer CTAs = a shorter last-block
+  // ticket chain, which matters when a rank's vectors are small)
+  int vec_per_sm = 8;
+  if (const char *e = std::getenv("QDSP_CG_VEC_CTAS")) vec_per_sm = std::max(1, std::min(8, std::atoi(e)));
+  // ... and at least 8192 elements per CTA: with 2.1 M rows per rank (C2 on 8 GPUs) 1184 CTAs of 1771 elements spent more
+  // time in the last-block ticket than in the update (measured at 8 ranks: 56.3 us per iteration with 2 CTAs per SM against
+  // 60.5 with 8, profiles/r02r_8gpu_knobs.txt)
+  I.vec_grid = std::max(1, std::min(std::min(ceil_div(A.rows, 1024), ceil_div(A.rows, 8192) + 1), device_props().sm_count * vec_per_sm));
   // variant: "classic" (Eigen's two reductions per iteration) unless QDSP_CG_VARIANT=merged asks for the one-reduction
   // form.  Measured (profiles/r01h_8gpu_trace.txt): the merged SpMV kernel needs 72 registers -> 3 CTAs per SM and is
   // 25 % slower than the classic one, which costs more than the saved all-reduce even at 8 ranks; kept as an option.
@@ -1280,14 +1340,17 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
       I.spmv_grid = std::max(1, std::min(ceil_div(A.rows, R), device_props().sm_count * mocc));
     }
   }
-  // persistent variant (default): needs co-residency by contract -> cooperative launch; QDSP_CG_FUSED=0 restores the
-  // three-kernel iteration (also used for QDSP_ALLREDUCE=nccl, the merged variant, verbose solves and traced runs)
+  // persistent variant: opt-in with QDSP_CG_FUSED=1 (needs co-residency by contract -> cooperative launch).  Measured on
+  // B200 it LOSES to the three-kernel iteration at every rank count (C2: 2715 vs 3172 it/s on 1 GPU, 5080 vs 6257 on 2,
+  // 14102 vs 17031 on 8; profiles/r02q_*): a grid barrier over 592 CTAs costs 5-17 us (ticket atomics + the fence that
+  // drains each CTA's stores + load imbalance that a kernel boundary hides equally), and the vector phases run on the
+  // SpMV's 4 x 256 threads per SM at 56 registers.  Kept for the record and for small, launch-bound systems.
   {
     const char *e = std::getenv("QDSP_CG_FUSED");
     int coop = 0, dev = 0;
     QDSP_CUDA(cudaGetDevice(&dev));
     QDSP_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
-    I.fused = !(e && e[0] == '0') && coop && !I.use_nccl && !I.merged && !verbose && A.rows > 0;
+    I.fused = (e && e[0] == '1') && coop && !I.use_nccl && !I.merged && !verbose && A.rows > 0;
     if (I.fused) {
       const int focc = (A.dtype == QDSP_F32) ? fused_dispatch<float>(I, nullptr, 0) : fused_dispatch<double>(I, nullptr, 0);
       if (focc < 1) I.fused = false;
@@ -1300,6 +1363,8 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
   I.partials.alloc(sizeof(double) * 8 * static_cast<size_t>(std::max(std::max(I.spmv_grid, I.vec_grid), I.fused_grid)));
   I.scalars.alloc(sizeof(CgScalars));
   QDSP_CUDA(cudaMemset(I.scalars.get(), 0, sizeof(CgScalars)));
+  I.sched.alloc(2 * sizeof(unsigned));
+  QDSP_CUDA(cudaMemset(I.sched.get(), 0, 2 * sizeof(unsigned)));
   QDSP_CUDA(cudaHostAlloc(reinterpret_cast<void **>(&I.h_sc), sizeof(CgScalars), cudaHostAllocDefault));
   QDSP_CUDA(cudaStreamCreateWithFlags(&I.stream, cudaStreamNonBlocking));
   QDSP_CUDA(cudaEventCreateWithFlags(&I.ev_in, cudaEventDisableTiming));

@@ -266,14 +266,17 @@ __device__ __forceinline__ void dist_halo_wait(const DistDev &d) {
   const unsigned want = *reinterpret_cast<volatile unsigned *>(&d.counters[1]);
   const long long t0 = clock64();
   for (int r = 0; r < d.n_recv; ++r) {
+    // (relaxed polls, ONE acquire at the end: every acquire load invalidates the SM's L1, which the other CTAs of the SM are
+    // gathering x through)
     const unsigned long long *f = dist_flag(d.self, d.recv_peer[r]);
-    while (ld_acquire_sys_u64(f) < want) {
+    while (ld_sys_u64(f) < want) {
       if (clock64() - t0 > DIST_SPIN_LIMIT) {
         atomicExch(d.error, 2);
         break;
       }
     }
   }
+  if (d.n_recv > 0) (void)ld_acquire_sys_u64(dist_flag(d.self, d.recv_peer[0]));
 }
 // The same for the z channel (thread 0 of a CTA, before its first read of a z-ghost; follow with __syncthreads()).
 __device__ __forceinline__ void dist_halo_wait_z(const DistDev &d) {
@@ -282,13 +285,14 @@ __device__ __forceinline__ void dist_halo_wait_z(const DistDev &d) {
   const long long t0 = clock64();
   for (int r = 0; r < d.n_recv; ++r) {
     const unsigned long long *f = dist_flag_z(d.self, d.recv_peer[r]);
-    while (ld_acquire_sys_u64(f) < want) {
+    while (ld_sys_u64(f) < want) {
       if (clock64() - t0 > DIST_SPIN_LIMIT) {
         atomicExch(d.error, 2);
         break;
       }
     }
   }
+  if (d.n_recv > 0) (void)ld_acquire_sys_u64(dist_flag_z(d.self, d.recv_peer[0]));
 }
 #endif  // __CUDACC__
 

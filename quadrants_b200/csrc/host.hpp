@@ -55,6 +55,10 @@ class CsrMatrix {
   mutable int spmv_max_block_nnz = 0;  // largest stage footprint of a uniform row block (spmv_prepare)
   mutable DeviceBuffer spmv_plan_blocks, spmv_plan_long, spmv_plan_partials, spmv_plan_ticket;
   mutable int spmv_plan_nblk = 0, spmv_plan_nlong = 0;
+  // work counters of the dynamically scheduled tail of the uniform path (spmv_kernels.cuh SpmvSched): 16 slots used
+  // round-robin, so up to 16 products of one matrix may be in flight on different streams
+  mutable DeviceBuffer spmv_sched_buf;
+  mutable unsigned spmv_sched_next = 0;
 
   size_t value_bytes() const { return dtype == QDSP_F64 ? 8 : 4; }
   void allocate(int rows_, int cols_, int64_t nnz_, int dtype_);
@@ -109,6 +113,9 @@ class Builder {
 // Chooses the SpMV path of A (mode, lanes per row, plan blocks); idempotent.  Synchronises `stream` the first time.
 void spmv_prepare(const CsrMatrix &A, cudaStream_t stream);
 struct SpmvPlanDev;
+struct SpmvSched;
+// scheduling of a uniform-path launch of `grid` CTAs over `nblk` row blocks; counters = 2 zeroed unsigned words (or nullptr)
+SpmvSched spmv_sched_for(int nblk, int grid, unsigned *counters);
 // pure host: the stream-path work partition (blocks {row0, nrows | -(segment+1), nz0, nz1}; long_rows {row, first segment})
 void spmv_plan_host(const int32_t *indptr, int rows, std::vector<int4> &blocks, std::vector<int2> &long_rows,
                     int &n_segments);

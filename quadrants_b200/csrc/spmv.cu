@@ -34,10 +34,23 @@ const DeviceProps &device_props() {
 template <typename T, int LPR, bool ROW_MAJOR_ORDER>
 __global__ void __launch_bounds__(SPMV_THREADS)
 spmv_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ indices, const T *__restrict__ values,
-            const T *__restrict__ x, T *__restrict__ y, DistDev d) {
+            const T *__restrict__ x, T *__restrict__ y, DistDev d, SpmvSched sched) {
   extern __shared__ unsigned char smem_raw[];
   NoSink sink;
-  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, x, y, sink, d);
+  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, x, y, sink, d, 0, sched);
+}
+
+// Static run per CTA = 3/4 of an even share; the rest is handed out two blocks at a time.  Small launches (< 8 blocks per
+// CTA) stay static: nothing to balance.  QDSP_SPMV_DYNAMIC=0 switches the dynamic tail off (measurement aid).
+SpmvSched spmv_sched_for(int nblk, int grid, unsigned *counters) {
+  SpmvSched s;
+  static const bool on = [] { const char *e = std::getenv("QDSP_SPMV_DYNAMIC"); return !(e && e[0] == '0'); }();
+  if (!on || counters == nullptr || grid <= 0 || nblk < 8 * grid) return s;
+  s.work = counters;
+  s.done = counters + 1;
+  s.static_blocks = static_cast<int>((static_cast<int64_t>(nblk) / grid) * 3 / 4);
+  s.chunk = 2;
+  return s;
 }
 
 template <typename T>
@@ -121,6 +134,9 @@ void spmv_prepare(const CsrMatrix &A, cudaStream_t stream) {
   const bool uniform = force ? std::string(force) != "stream" : stats[1] <= SPMV_CAP;
   A.spmv_lpr = L;
   if (uniform) {
+    A.spmv_sched_buf.alloc(16 * 2 * sizeof(unsigned));
+    QDSP_CUDA(cudaMemsetAsync(A.spmv_sched_buf.get(), 0, A.spmv_sched_buf.bytes(), stream));
+    QDSP_CUDA(cudaStreamSynchronize(stream));
     A.spmv_mode = 1;
     return;
   }
@@ -194,10 +210,13 @@ void launch_spmv_t(const CsrMatrix &A, const T *x, T *y, const DistDev &d, cudaS
   const int grid = std::max(1, std::min(ceil_div(A.rows, R), device_props().sm_count * spmv_ctas_per_sm<T, LPR>()));
   const size_t smem = spmv_smem_bytes<T>();
   const int *ip = A.indptr.get<int>(), *ix = A.indices.get<int>();
+  unsigned *counters = A.spmv_sched_buf.get<unsigned>();
+  if (counters) counters += 2 * (A.spmv_sched_next++ % 16);
+  const SpmvSched sched = spmv_sched_for(ceil_div(A.rows, R), grid, counters);
   if (A.row_major_order && LPR == 1)
-    spmv_kernel<T, LPR, true><<<grid, SPMV_THREADS, smem, stream>>>(A.rows, ip, ix, A.values.get<T>(), x, y, d);
+    spmv_kernel<T, LPR, true><<<grid, SPMV_THREADS, smem, stream>>>(A.rows, ip, ix, A.values.get<T>(), x, y, d, sched);
   else
-    spmv_kernel<T, LPR, false><<<grid, SPMV_THREADS, smem, stream>>>(A.rows, ip, ix, A.values.get<T>(), x, y, d);
+    spmv_kernel<T, LPR, false><<<grid, SPMV_THREADS, smem, stream>>>(A.rows, ip, ix, A.values.get<T>(), x, y, d, sched);
   QDSP_LAUNCH_CHECK();
 }
 

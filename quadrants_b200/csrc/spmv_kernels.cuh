@@ -127,6 +127,19 @@ struct SpmvPlanDev {
   unsigned *ticket = nullptr;
 };
 
+// Work distribution of the uniform path.  work == nullptr: every CTA owns a contiguous run of ceil(nblk / grid) row blocks.
+// Otherwise CTA c owns the contiguous run [c * static_blocks, (c + 1) * static_blocks) and the blocks from
+// grid * static_blocks on are handed out in chunks of `chunk` through the device counter *work -- the CTAs of an SM do not
+// get equal shares of HBM bandwidth (measured: the first CTA of a static partition was done after 176 us of a 229 us
+// product), so the last quarter of the matrix goes to whoever is free.  The kernel resets both counters itself (the last
+// producer thread to run out of work), so consecutive launches need no memset.
+struct SpmvSched {
+  unsigned *work = nullptr;  // next dynamic block offset
+  unsigned *done = nullptr;  // producers that have finished
+  int static_blocks = 0;
+  int chunk = 2;
+};
+
 __device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(SPMV_CONSUMERS) : "memory"); }
 
 // ---- row sinks: what a kernel does with each finished y[row] besides storing it ----------------------------------------
@@ -189,7 +202,8 @@ struct MergedSink {
 template <typename T, int LPR, bool ROW_MAJOR_ORDER, typename Sink, bool FUSED = false>
 __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int rows, const int *__restrict__ indptr,
                                                 const int *__restrict__ indices, const T *__restrict__ values,
-                                                const T *x, T *y, Sink &sink, const DistDev &dist, int iter = 0) {
+                                                const T *x, T *y, Sink &sink, const DistDev &dist, int iter = 0,
+                                                const SpmvSched sched = SpmvSched{}) {
   constexpr int R = SPMV_CONSUMERS / LPR;  // rows per block
   constexpr int AUX = Sink::AUX;
   constexpr int CAP = Sink::CAP;
@@ -211,24 +225,46 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
   // work items of this CTA.  Plain: a contiguous run of blocks.  Ordered (multi-GPU): a contiguous run of the interior
   // blocks, then every gridDim.x-th ghost block; the producer leaves the block id in the stage for the consumers.
   const bool ordered = lazy_halo && dist.block_order != nullptr;
+  const bool dyn = !FUSED && !ordered && sched.work != nullptr;  // static run, then chunks from the shared counter
   const int n_first = ordered ? dist.n_interior : nblk;
-  const int per_cta = (n_first + gridDim.x - 1) / gridDim.x;
+  const int per_cta = dyn ? sched.static_blocks : (n_first + gridDim.x - 1) / gridDim.x;
   const int blk0 = min(n_first, static_cast<int>(blockIdx.x) * per_cta);
   const int n_run = min(n_first, blk0 + per_cta) - blk0;
   const int n_ghost_blk = ordered ? nblk - n_first : 0;
   const int n_tail = n_ghost_blk > static_cast<int>(blockIdx.x) ? (n_ghost_blk - 1 - blockIdx.x) / gridDim.x + 1 : 0;
-  const int n_items = n_run + n_tail;
+  const int n_items = n_run + n_tail;  // (dyn: only the static run; the dynamic part ends with a sentinel)
   const int ring0 = FUSED ? iter * n_items : 0;  // ring position of this call's first item
+  const int dyn_base = dyn ? min(nblk, static_cast<int>(gridDim.x) * per_cta) : nblk;
 
   if (t >= SPMV_CONSUMERS) {
     // ---- producer: one thread ----
-    if (t == SPMV_CONSUMERS && n_items > 0) {
+    if (t == SPMV_CONSUMERS && (n_items > 0 || dyn)) {
       const unsigned long long pol = l2_evict_first_policy();
       bool halo_pending = lazy_halo && !FUSED;
       int s_next = 0, blk_prev = -2;
-      for (int it = 0; it < n_items; ++it) {
+      int dyn_next = 0, dyn_end = 0;  // current chunk of the dynamic part
+      for (int it = 0; dyn || it < n_items; ++it) {
         int blk = blk0 + it;
         if (ordered) blk = dist.block_order[it < n_run ? blk0 + it : n_first + blockIdx.x + (it - n_run) * gridDim.x];
+        if (dyn && it >= n_items) {
+          if (dyn_next == dyn_end) {
+            dyn_next = dyn_base + static_cast<int>(atomicAdd(sched.work, static_cast<unsigned>(sched.chunk)));
+            dyn_end = min(nblk, dyn_next + sched.chunk);
+          }
+          if (dyn_next >= nblk) {
+            // out of work: sentinel for the consumers, then the completion ticket (the last producer re-arms the counters)
+            const int stage = it % SPMV_STAGES;
+            mbar_wait(&empty[stage], ((it / SPMV_STAGES) & 1) ^ 1u);
+            spmv_stage<T, AUX, CAP>(base, stage).ptr[SPMV_DESC_SLOT] = -1;
+            mbar_arrive(&full[stage]);
+            if (atomicAdd(sched.done, 1u) == gridDim.x - 1) {
+              *sched.work = 0u;
+              *sched.done = 0u;
+            }
+            break;
+          }
+          blk = dyn_next++;
+        }
         if (halo_pending && (ordered ? it >= n_run : dist.ghost_blocks[blk] != 0)) {
           dist_halo_wait(dist);
           halo_pending = false;
@@ -243,7 +279,7 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
         blk_prev = blk;
         if (!mbar_wait_b<FUSED>(&empty[stage], phase ^ 1u)) return;
         const SpmvStage<T> st = spmv_stage<T, AUX, CAP>(base, stage);
-        if (ordered) st.ptr[SPMV_DESC_SLOT] = blk;  // published by the arrive below (release)
+        if (ordered || dyn) st.ptr[SPMV_DESC_SLOT] = blk;  // published by the arrive below (release)
         const int a0 = s & ~3;
         const int cnt = e - a0;
         const unsigned ptr_bytes = static_cast<unsigned>(((nr + 1) * 4 + 15) & ~15);
@@ -272,12 +308,13 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
     const int lane = t & 31, warp = t >> 5;
     const int row_in_blk = t / LPR, q = t % LPR;
     bool halo_pending = FUSED && dist.world > 1;
-    for (int it = 0; it < n_items; ++it) {
+    for (int it = 0; dyn || it < n_items; ++it) {
       const int stage = (ring0 + it) % SPMV_STAGES;
       const unsigned phase = ((ring0 + it) / SPMV_STAGES) & 1;
       const SpmvStage<T> st = spmv_stage<T, AUX, CAP>(base, stage);
       if (!mbar_wait_b<FUSED>(&full[stage], phase)) return;
-      const int blk = ordered ? st.ptr[SPMV_DESC_SLOT] : blk0 + it;
+      const int blk = (ordered || dyn) ? st.ptr[SPMV_DESC_SLOT] : blk0 + it;
+      if (dyn && blk < 0) break;  // the producer's sentinel
       if constexpr (FUSED) {
         // (uniform over the consumers: every thread evaluates the same block)
         if (halo_pending && (!lazy_halo || (ordered ? it >= n_run : dist.ghost_blocks[blk] != 0))) {

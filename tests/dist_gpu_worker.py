@@ -203,6 +203,7 @@ def main():
             assert np.isfinite(xs.to_numpy()).all()
             del solver, ctx
             dist.barrier()
+    os.environ["QDSP_ALLREDUCE"] = "p2p"
     changing_x_case(rank, world, dev, n)
     one_way_ghost_case(rank, world, dev)
     fem_case(rank, world, dev)

@@ -650,8 +650,8 @@ def test_error_behaviour(qd):
 # ---------------------------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("case", ["poisson2d_f32", "poisson2d_f64", "fem_f64", "fem_f32", "rowmajor_f32"])
 def test_cg_fused_kernel_matches_three_kernel_form(qd, oracle, monkeypatch, case):
-    """The default solver runs the whole loop in ONE cooperative persistent kernel (cg.cu, cg_fused_kernel); QDSP_CG_FUSED=0
-    selects the three-kernel iteration it replaces.  Same recurrence, same scalar roundings, same stopping rule: the two
+    """QDSP_CG_FUSED=1 runs the whole loop in ONE cooperative persistent kernel (cg.cu, cg_fused_kernel); the default
+    (QDSP_CG_FUSED unset / 0) is the three-kernel iteration.  Same recurrence, same scalar roundings, same stopping rule: the two
     must stop within a few iterations of each other (only the grouping of the dot-product partials differs) and agree
     with the oracle like every other CG test; a fixed-budget run must give the same x to rounding."""
     f64 = case.endswith("f64")
