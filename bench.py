@@ -53,6 +53,87 @@ def poisson3d_triplets_device(n, lo, hi, device):
     return torch.cat(rows), torch.cat(cols), torch.cat(vals)
 
 
+def stencil_probe(n, lo, hi, device):
+    """Parity probe for the assembled operator: x(g) = small integers keyed on the global row id g, and y = A x for the
+    z-planes [lo, hi) in closed form from the stencil (6 x - the in-bounds neighbours).  Every partial sum is a small
+    integer, so the fp32 product is exact whatever the summation order: the GPU result must be bit-equal."""
+    import torch
+
+    i = torch.arange(lo, hi, device=device, dtype=torch.int64).view(-1, 1, 1)
+    j = torch.arange(n, device=device, dtype=torch.int64).view(1, -1, 1)
+    k = torch.arange(n, device=device, dtype=torch.int64).view(1, 1, -1)
+
+    def xval(ii, jj, kk):
+        g = (ii * n + jj) * n + kk
+        return ((g * 40503) % 17 - 8).to(torch.float32)
+
+    x = xval(i, j, k)
+    y = 6.0 * x
+    for di, dj, dk in ((-1, 0, 0), (1, 0, 0), (0, -1, 0), (0, 1, 0), (0, 0, -1), (0, 0, 1)):
+        ii, jj, kk = i + di, j + dj, k + dk
+        ok = (ii >= 0) & (ii < n) & (jj >= 0) & (jj < n) & (kk >= 0) & (kk < n)
+        y = y - torch.where(ok, xval(ii.clamp(0, n - 1), jj.clamp(0, n - 1), kk.clamp(0, n - 1)), torch.zeros((), device=device))
+    return x.reshape(-1).contiguous(), y.reshape(-1).contiguous()
+
+
+def live_spmv_traffic(n, timeout_s=240):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE spmv_kernel launch, captured now, on this box, by running
+    `bench.py --spmv-once` under ncu in a child process (after the timed regions; nothing timed runs under the profiler).
+    -> (bytes, source string) or (None, why)."""
+    import shutil
+
+    ncu = shutil.which("ncu") or "/usr/local/cuda/bin/ncu"
+    if not os.path.exists(ncu):
+        return None, "ncu not on this box"
+    cmd = [ncu, "--metrics", "dram__bytes_read.sum,dram__bytes_write.sum", "--clock-control", "none", "--print-units",
+           "base", "-k", "regex:spmv_kernel", "--launch-skip", "2", "--launch-count", "1", "--csv", sys.executable,
+           os.path.join(ROOT, "bench.py"), "--spmv-once", "--grid", str(n)]
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    try:
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout_s, env=env, cwd=ROOT)
+    except (OSError, subprocess.TimeoutExpired) as e:
+        return None, f"ncu child failed: {type(e).__name__}"
+    total, seen = 0.0, 0
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    import csv
+
+    for row in csv.reader(out.stdout.splitlines()):
+        if len(row) < 3:
+            continue
+        for pos, cell in enumerate(row):
+            if cell in ("dram__bytes_read.sum", "dram__bytes_write.sum") and pos + 2 < len(row):
+                try:
+                    total += float(row[pos + 2].replace(",", "")) * scale.get(row[pos + 1], 1.0)
+                    seen += 1
+                except ValueError:
+                    pass
+    if seen != 2:
+        return None, f"ncu child rc={out.returncode}, no dram metrics parsed"
+    return total, "live: ncu dram__bytes_read.sum + dram__bytes_write.sum of one spmv_kernel launch, child process of this run"
+
+
+def spmv_once(args):
+    """Child of live_spmv_traffic: assemble the workload matrix and launch the SpMV kernel four times."""
+    import torch
+
+    import quadrants_b200 as qd
+
+    qd.init(arch=qd.cuda, device=0)
+    n = args.grid
+    dev = torch.device("cuda", 0)
+    r, c, v = poisson3d_triplets_device(n, 0, n, dev)
+    K = qd.linalg.SparseMatrixBuilder(n ** 3, n ** 3, max_num_triplets=int(r.shape[0]), dtype=qd.f32)
+    K.ptr.insert_triplets(r, c, v)
+    A = K.build()
+    x = qd.ndarray(qd.f32, n ** 3)
+    x.tensor.uniform_(-1.0, 1.0)
+    y = qd.ndarray(qd.f32, n ** 3)
+    for _ in range(4):
+        A.matrix.spmv(None, x, y)
+    torch.cuda.synchronize()
+    return 0
+
+
 def spmv_bytes(n, m, nnz, sv):
     """Algorithmic bytes of one SpMV: every array once."""
     return nnz * (sv + 4) + (n + 1) * 4 + m * sv + n * sv
@@ -234,6 +315,11 @@ def run_gpu(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries the ONE JSON line and nothing else: whatever the libraries print (NCCL's version banner ...) goes
+    # to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
     qd.init(arch=qd.cuda, device=local)
@@ -333,67 +419,119 @@ def run_gpu(args):
     ms_per_step = ms_total / args.steps
     value = ips * args.steps / (ms_total * 1e-3)
 
+    n_loc = (hi - lo) if world > 1 else n_rows
+    plane_lo, plane_hi = (lo // (n * n), hi // (n * n)) if world > 1 else (0, n)
+
+    def spmv_call(x, y):
+        if world > 1:
+            ctx.spmv(x, y)
+        else:
+            A.matrix.spmv(None, x, y)
+
+    def all_ranks(obj):
+        if world == 1:
+            return [obj]
+        box = [None] * world
+        dist.all_gather_object(box, obj)
+        return box
+
+    # ---- parity gate 1 (before any rate is reported): the assembled (and, for N > 1, partitioned + halo-exchanged)
+    # operator against the closed-form stencil, bit for bit, on every rank ---------------------------------------------
+    xp_t, yp_t = stencil_probe(n, plane_lo, plane_hi, dev)
+    xs = qd.ndarray(qd.f32, n_loc)
+    ys = qd.ndarray(qd.f32, n_loc)
+    xs.tensor.copy_(xp_t)
+    ys.tensor.fill_(float("nan"))
+    spmv_call(xs, ys)
+    torch.cuda.synchronize()
+    spmv_exact = bool(torch.equal(ys.tensor, yp_t))
+    del xp_t, yp_t
+    if not all(all_ranks(spmv_exact)):
+        raise SystemExit(f"PARITY FAILURE rank {rank}: SpMV differs from the closed-form stencil; no rate reported")
+
     # ---- roofline of the dominant kernel: SpMV (the same CTA code the CG's A.p kernel runs) ---------------------------
-    roofline, spmv_gbs = None, None
-    if world == 1:
-        xs = qd.ndarray(qd.f32, n_rows)
-        xs.tensor.uniform_(-1.0, 1.0, generator=torch.Generator(device=dev).manual_seed(2))
-        ys = qd.ndarray(qd.f32, n_rows)
-        for _ in range(5):
-            A.matrix.spmv(None, xs, ys)
-        reps = 50
-        torch.cuda.synchronize()
-        e0.record(stream)
-        for _ in range(reps):
-            A.matrix.spmv(None, xs, ys)
-        e1.record(stream)
-        torch.cuda.synchronize()
-        spmv_ms = e0.elapsed_time(e1) / reps
-        alg = spmv_bytes(n_rows, n_rows, nnz_total, sv)
-        spmv_gbs = alg / (spmv_ms * 1e-3) / 1e9
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except OSError:
-            pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
-        traffic = None
-        try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "spmv_traffic.json"))).get("dram_bytes_per_launch")
-        except (OSError, ValueError):
-            pass
-        roofline = {"bound": "hbm", "kernel": "spmv_kernel<float> (== cg_spmv_dot_kernel body)", "achieved": spmv_gbs,
-                    "peak": peak, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
-                    "unit": "GB/s", "frac": spmv_gbs / peak, "frac_of_nominal_8000": spmv_gbs / 8000.0,
-                    "algorithmic_bytes_per_launch": alg, "ms_per_launch": spmv_ms, "traffic": traffic}
-        del xs, ys
+    xs.tensor.uniform_(-1.0, 1.0, generator=torch.Generator(device=dev).manual_seed(2 + rank))
+    for _ in range(5):
+        spmv_call(xs, ys)
+    reps = 50
+    barrier()
+    e0.record(stream)
+    for _ in range(reps):
+        spmv_call(xs, ys)
+    e1.record(stream)
+    barrier()
+    spmv_ms = e0.elapsed_time(e1) / reps
+    nnz_loc = A.matrix.nnz()
+    n_cols_loc = n_loc + (ctx.n_ghost if world > 1 else 0)
+    alg = spmv_bytes(n_loc, n_cols_loc, nnz_loc, sv)
+    per_rank = all_ranks({"rank": rank, "ms_per_launch": spmv_ms, "algorithmic_bytes_per_launch": alg,
+                          "achieved": alg / (spmv_ms * 1e-3) / 1e9})
+    spmv_gbs = sum(p["achieved"] for p in per_rank)          # whole job
+    per_gpu = min(p["achieved"] for p in per_rank)           # the slowest rank is the one the roofline is about
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    roofline = {"bound": "hbm",
+                "kernel": "spmv_kernel<float> (== cg_spmv_dot_kernel body)" if world == 1 else
+                          "qdsp_dist_spmv per rank: halo push by peer stores + spmv_kernel<float> + consumed signal",
+                "achieved": per_gpu, "peak": peak,
+                "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
+                "unit": "GB/s", "frac": per_gpu / peak, "frac_of_nominal_8000": per_gpu / 8000.0,
+                "algorithmic_bytes_per_launch": alg, "ms_per_launch": max(p["ms_per_launch"] for p in per_rank),
+                "traffic": None}
+    if world > 1:
+        roofline["per_rank"] = per_rank
+        roofline["note"] = "achieved/frac = the slowest rank's per-GPU figure; spmv_gbs on the line = sum over ranks"
+    del xs, ys
 
-    # ---- e2e: the host-buffer C-ABI call (qdsp_cg_solve_host): b H2D + x D2H inside the timed region -------------------
-    e2e = None
-    if world == 1:
-        bh = torch.ones(n_rows, dtype=torch.float32).pin_memory()
-        xh = torch.zeros(n_rows, dtype=torch.float32).pin_memory()
-        it, err, ok = C.c_int(), C.c_double(), C.c_int()
-        h = cg.cg_solver._h
+    # ---- e2e: the host-buffer C-ABI call (qdsp_cg_solve_host): b H2D + x D2H inside the timed region; for N > 1 every
+    # rank moves its own slice of b and x (pinned), the region is barrier-bracketed and the max over ranks is taken --------
+    bh = torch.ones(n_loc, dtype=torch.float32).pin_memory()
+    xh = torch.zeros(n_loc, dtype=torch.float32).pin_memory()
+    it, err, ok = C.c_int(), C.c_double(), C.c_int()
+    h = cg.cg_solver._h
 
-        def step_host():
-            _lib.check(lib.qdsp_cg_solve_host(h, xh.data_ptr(), bh.data_ptr(), stream.cuda_stream, C.byref(it),
-                                              C.byref(err), C.byref(ok)))
+    def step_host():
+        _lib.check(lib.qdsp_cg_solve_host(h, xh.data_ptr(), bh.data_ptr(), stream.cuda_stream, C.byref(it),
+                                          C.byref(err), C.byref(ok)))
 
-        for _ in range(max(1, args.warmup)):
-            step_host()
-        torch.cuda.synchronize()
-        e0.record(stream)
-        done_iters = 0
-        for _ in range(args.steps):
-            step_host()
-            done_iters += it.value
-        e1.record(stream)
-        torch.cuda.synchronize()
-        e2e_ms = e0.elapsed_time(e1)
-        e2e = {"value": done_iters / (e2e_ms * 1e-3), "unit": "iters/s", "h2d_bytes_per_step": n_rows * sv,
-               "d2h_bytes_per_step": n_rows * sv, "call": "qdsp_cg_solve_host", "iters_per_step": done_iters // args.steps,
-               "final_rel_residual": err.value}
+    for _ in range(max(1, args.warmup)):
+        step_host()
+    barrier()
+    e0.record(stream)
+    done_iters = 0
+    for _ in range(args.steps):
+        step_host()
+        done_iters += it.value
+    e1.record(stream)
+    barrier()
+    e2e_ms = max_over_ranks(e0.elapsed_time(e1))
+    e2e = {"value": done_iters / (e2e_ms * 1e-3), "unit": "iters/s", "h2d_bytes_per_step": n_rows * sv,
+           "d2h_bytes_per_step": n_rows * sv, "call": "qdsp_cg_solve_host" + (" on every rank's slice" if world > 1 else ""),
+           "iters_per_step": done_iters // args.steps, "final_rel_residual": err.value}
+
+    # ---- parity gate 2: the solve that was just timed.  Every rank must have run the same number of iterations and hold
+    # the same residual estimate, and the TRUE residual |b - A x| / |b| recomputed from the returned x must agree with the
+    # recurrence's ------------------------------------------------------------------------------------------------------
+    seen = all_ranks((done_iters, err.value))
+    xd = qd.ndarray(qd.f32, n_loc)
+    xd.tensor.copy_(xh, non_blocking=False)
+    rd = qd.ndarray(qd.f32, n_loc)
+    spmv_call(xd, rd)
+    rr = torch.stack([((1.0 - rd.tensor.double()) ** 2).sum(), torch.tensor(float(n_loc), device=dev, dtype=torch.float64)])
+    if world > 1:
+        dist.all_reduce(rr)
+    true_rel = float(torch.sqrt(rr[0] / rr[1]).item())
+    cg_ok = (len(set(seen)) == 1 and np.isfinite(true_rel) and abs(true_rel - err.value) <= 2e-2 * err.value + 1e-7)
+    if not cg_ok:
+        raise SystemExit(f"PARITY FAILURE rank {rank}: per-rank (iterations, error) {seen}; true residual {true_rel} vs "
+                         f"reported {err.value}; no rate reported")
+    parity = {"spmv_vs_closed_form_stencil": "bit-exact on every rank", "cg_iterations_equal_across_ranks": True,
+              "cg_true_rel_residual": true_rel, "cg_reported_rel_residual": err.value}
+    del xd, rd
 
     # ---- CPU baseline on a bounded sample (rank 0, N = 1 only) ----------------------------------------------------------
     cpu = None
@@ -403,6 +541,33 @@ def run_gpu(args):
         oracle.build()
         ip, ix, vv = A.matrix.to_scipy_arrays()
         cpu = CpuCg((ip, ix, vv), n_rows).baseline(args.cpu_iters)
+        del ip, ix, vv
+
+    # ---- the kernel to beat: the reference's own cuSPARSE / cuBLAS calls on this GPU, this matrix (N = 1) ---------------
+    if world == 1 and not args.no_kernel_to_beat:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import bench_cusparse
+
+            ktb = bench_cusparse.measure(*A.matrix.csr_tensors(), n_rows, n_rows)
+            roofline["kernel_to_beat_ms"] = ktb["spmv_csr_alg1_hoisted_ms"]
+            roofline["kernel_to_beat"] = ktb
+        except Exception as e:  # the bench line must survive a missing library
+            roofline["kernel_to_beat_ms"] = None
+            roofline["kernel_to_beat"] = {"unavailable": f"{type(e).__name__}: {e}"}
+
+    # ---- DRAM traffic of the dominant kernel, captured now by a child process under ncu (rank 0) ------------------------
+    if rank == 0:
+        traffic, src = (None, "disabled (--no-live-traffic)") if args.no_live_traffic else live_spmv_traffic(n)
+        if traffic is None:
+            try:
+                rec = json.load(open(os.path.join(ROOT, "profiles", "spmv_traffic.json")))
+                traffic, src = rec.get("dram_bytes_per_launch"), f"committed capture profiles/spmv_traffic.json ({src})"
+            except (OSError, ValueError):
+                pass
+        roofline["traffic"], roofline["traffic_source"] = traffic, src
+        if world > 1:
+            roofline["traffic_note"] = "single-GPU launch over the whole matrix; a rank streams 1/N of it"
 
     if rank == 0:
         iter_bytes = cg_iter_bytes(n_rows, nnz_total, sv)
@@ -419,13 +584,13 @@ def run_gpu(args):
                            "csr_build_ms": build_ms},
                 "cg_gbs": value * iter_bytes / 1e9, "cg_algorithmic_bytes_per_iter": iter_bytes,
                 "spmv_gbs": spmv_gbs, "gpu_launches": int(launches), "clocks": clocks}
-        if roofline:
-            line["roofline"] = roofline
-        if e2e:
-            line["e2e"] = e2e
+        line["roofline"] = roofline
+        line["e2e"] = e2e
+        line["parity_checked"] = True
+        line["parity"] = parity
         if cpu:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line))
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         # tear the solver and the peer mappings down while every rank is still alive
         torch.cuda.synchronize()
@@ -447,12 +612,17 @@ def main():
     ap.add_argument("--iters-per-step", type=int, default=100)
     ap.add_argument("--cpu-iters", type=int, default=12, help="CG iterations of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-kernel-to-beat", action="store_true", help="skip the cuSPARSE/cuBLAS reference-path timing")
+    ap.add_argument("--no-live-traffic", action="store_true", help="skip the ncu child that measures DRAM traffic")
+    ap.add_argument("--spmv-once", action="store_true", help=argparse.SUPPRESS)
     args = ap.parse_args()
     if os.environ.get("QDSP_DEBUG_HANG"):
         import faulthandler
         faulthandler.dump_traceback_later(float(os.environ["QDSP_DEBUG_HANG"]), exit=True)
     if args.warmup < 3:
         args.warmup = 3
+    if args.spmv_once:
+        return spmv_once(args)
     if args.impl == "reference":
         return run_reference(args)
     return run_gpu(args)

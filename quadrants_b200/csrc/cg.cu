@@ -39,15 +39,14 @@ namespace qdsp {
 
 constexpr int CG_THREADS = 256;
 
-// Programmatic dependent launch: every kernel of the iteration loop is launched with
-// cudaLaunchAttributeProgrammaticStreamSerialization, lets its successor be scheduled as soon as all of its own CTAs
-// are running (launch_dependents) and waits for its predecessor's completion + memory flush before touching anything
-// (wait).  The successor's launch latency and prologue then overlap this kernel's tail; ordering is unchanged.
+// Programmatic dependent launch (QDSP_PDL=1): every kernel of the iteration loop is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization.  A kernel waits for its predecessor's completion + memory flush
+// before touching anything (pdl_wait, its first statement) and lets its successor be scheduled once every one of its
+// own CTAs has finished its share of the streaming work (pdl_trigger, in front of the grid reduction): the successor's
+// launch latency then overlaps the reduction / all-reduce tail of this kernel; ordering is unchanged.
 // Both instructions are no-ops in a kernel launched without the attribute.
-__device__ __forceinline__ void pdl_wait_then_release() {
-  asm volatile("griddepcontrol.wait;" ::: "memory");
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 struct CgScalars {
   double pAp, abs_new, abs_old, res2, rhs2, thr;
@@ -65,8 +64,39 @@ struct CgScalars {
   // QDSP_CG_TRACE=2: nanoseconds CTA 0 ([0..6)) and the last CTA ([6..12)) spent in {A, barrier 1, B, barrier 2, C,
   // barrier 3} of the persistent kernel, summed over the iterations of one launch (a debugging aid)
   unsigned long long tprof[12];
+  // QDSP_CG_TRACE=3: in-graph timeline of the three-kernel iteration, from %globaltimer.  tl_acc[2k] = idle time in
+  // front of kernel k (end of the previous kernel's last CTA -> start of CTA 0), tl_acc[2k+1] = duration of kernel k,
+  // tl_acc[6], [7] = time the last CTA of kernels A, B spent in the cross-rank all-reduce
+  unsigned long long tl_acc[8];
+  unsigned long long tl_start, tl_end;
+  int tl_prev;
   int trace;
 };
+
+// ---- QDSP_CG_TRACE=3 timeline (see CgScalars::tl_acc) -------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long cg_now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// first statement of iteration kernel k (0 = A.p + dot, 1 = residual, 2 = direction); CTA 0 closes the books of the
+// previous kernel and opens this one's
+__device__ __forceinline__ void cg_tl_begin(CgScalars *sc, int k) {
+  if (sc->trace != 3 || blockIdx.x != 0 || threadIdx.x != 0) return;
+  const unsigned long long now = cg_now_ns();
+  const unsigned long long end = *reinterpret_cast<volatile unsigned long long *>(&sc->tl_end);
+  if (end != 0ull) {
+    sc->tl_acc[2 * sc->tl_prev + 1] += end - sc->tl_start;
+    sc->tl_acc[2 * k] += now - end;
+  }
+  sc->tl_start = now;
+  sc->tl_prev = k;
+}
+// last statement of every CTA of an iteration kernel
+__device__ __forceinline__ void cg_tl_end(CgScalars *sc) {
+  if (sc->trace != 3 || threadIdx.x != 0) return;
+  atomicMax(&sc->tl_end, cg_now_ns());
+}
 
 // ---- block / grid reductions ----------------------------------------------------------------------------------------
 template <int NV>
@@ -209,7 +239,10 @@ __device__ __forceinline__ void cg_reduce_and_finish(double (&v)[NV], const Dist
     return;
   }
   if (threadIdx.x < 32) {
+    const bool tl = sc->trace == 3 && threadIdx.x == 0 && (NV == 1 || NV == 2);
+    const unsigned long long t0 = tl ? cg_now_ns() : 0ull;
     dist_allreduce<NV>(d, v);
+    if (tl) sc->tl_acc[5 + NV] += cg_now_ns() - t0;
     if (threadIdx.x == 0) {
       if (d.world > 1 && *reinterpret_cast<volatile int *>(d.error)) sc->done = 3;
       else fin(v);
@@ -242,6 +275,21 @@ cg_invdiag_kernel(int n, const int *__restrict__ indptr, const int *__restrict__
 __device__ __forceinline__ void cta_chunk(int n, int &lo, int &hi, int &per) {
   per = ((n + gridDim.x - 1) / gridDim.x + 1023) & ~1023;
   lo = min(n, static_cast<int>(blockIdx.x) * per);
+  hi = min(n, lo + per);
+}
+
+// The same partition with the chunks dealt from both ends: CTA 0 -> chunk 0, CTA 1 -> chunk G-1, CTA 2 -> chunk 1, ...
+// A row-block rank's halo rows are the first and the last rows it owns, and the CTAs that own them still have a peer
+// push + system-scope fence (~4 us) to do after the sweep.  The block scheduler starts CTAs in index order, so with the
+// plain order the upper boundary sat in the CTAs that finish LAST -- one of them was usually the ticket-last block, which
+// then ran all-reduce and push back to back (measured at 2 ranks, QDSP_CG_TRACE=3: the residual kernel of the rank with
+// an upper neighbour took 33.2 us against 27.8 us on the rank with a lower neighbour, and the other rank idled 5.4 us in
+// the next all-reduce).  Dealt from both ends, both boundaries belong to the earliest CTAs.
+__device__ __forceinline__ void cta_chunk_ends(int n, int &lo, int &hi, int &per) {
+  per = ((n + gridDim.x - 1) / gridDim.x + 1023) & ~1023;
+  const int b = static_cast<int>(blockIdx.x);
+  const int c = (b & 1) ? static_cast<int>(gridDim.x) - 1 - (b >> 1) : (b >> 1);
+  lo = min(n, c * per);
   hi = min(n, lo + per);
 }
 
@@ -290,18 +338,21 @@ cg_spmv_dot_kernel(int rows, const int *__restrict__ indptr, const int *__restri
   extern __shared__ unsigned char smem_raw[];
   __shared__ double s_red[16];
   __shared__ unsigned s_flag;
-  pdl_wait_then_release();
+  pdl_wait();
   if (sc->done) {
     // the deferred x += alpha p of the final iteration has been applied by the direction kernel before this launch:
     // retire alpha so that a replayed direction kernel is a no-op
     if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;
     return;
   }
+  cg_tl_begin(sc, 0);
   DotSink<T> sink{p};
   spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, sink, d, 0, sched);
+  pdl_trigger();
   double v[1] = {sink.acc};
   if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag))
     cg_reduce_and_finish<1>(v, d, use_nccl, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
+  cg_tl_end(sc);
 }
 
 // the same for an irregular matrix (stream path of spmv_kernels.cuh)
@@ -313,16 +364,19 @@ cg_spmv_dot_stream_kernel(const int *__restrict__ indptr, const int *__restrict_
   extern __shared__ unsigned char smem_raw[];
   __shared__ double s_red[16];
   __shared__ unsigned s_flag;
-  pdl_wait_then_release();
+  pdl_wait();
   if (sc->done) {
     if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;
     return;
   }
+  cg_tl_begin(sc, 0);
   DotSink<T> sink{p};
   spmv_stream<T>(smem_raw, indptr, indices, values, p, tmp, sink, plan, d);
+  pdl_trigger();
   double v[1] = {sink.acc};
   if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag))
     cg_reduce_and_finish<1>(v, d, use_nccl, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
+  cg_tl_end(sc);
 }
 
 template <typename T> struct Vec4T;
@@ -390,16 +444,18 @@ cg_residual_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv,
                    CgScalars *__restrict__ sc, double *__restrict__ partials, DistDev d, int use_nccl) {
   __shared__ double s_red[2 * 16];
   __shared__ unsigned s_flag;
-  pdl_wait_then_release();
+  pdl_wait();
   if (sc->done) return;
+  cg_tl_begin(sc, 1);
   T s_rr = T(0), s_rz = T(0);
   int lo = 0, hi = 0, per = 1024;
   if (d.zmode) {
-    cta_chunk(n, lo, hi, per);
+    cta_chunk_ends(n, lo, hi, per);
     cg_residual_body<T>(tmp, dinv, r, static_cast<T>(sc->alpha), lo, hi, s_rr, s_rz);
   } else {
     cg_residual_body_strided<T>(n, tmp, dinv, r, static_cast<T>(sc->alpha), s_rr, s_rz);
   }
+  pdl_trigger();
   double v[2] = {static_cast<double>(s_rr), static_cast<double>(s_rz)};
   if (grid_sum_last_block<2>(v, partials, &sc->ticket[2], s_red, &s_flag))
     cg_reduce_and_finish<2>(v, d, use_nccl, sc, [&](const double (&t)[2]) { cg_finish_B<T>(sc, t[0], t[1]); });
@@ -407,6 +463,7 @@ cg_residual_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv,
   // wait for the NVLink acknowledgements runs beside the grid reduction and its all-reduce, not in front of them
   // (pushing first cost ~9 us per iteration at 2 ranks)
   if (d.zmode) dist_halo_push_signal_z<T>(d, r, dinv, lo, hi, per);
+  cg_tl_end(sc);
 }
 
 // x += alpha p and (update_p) p = D^-1 r + beta p on this CTA's chunk [lo, hi)
@@ -442,16 +499,18 @@ __device__ __forceinline__ void cg_direction_body(const T *r, const T *__restric
 template <typename T>
 __global__ void __launch_bounds__(CG_THREADS)
 cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, T *__restrict__ p, T *__restrict__ x,
-                    const CgScalars *__restrict__ sc, DistDev d) {
-  pdl_wait_then_release();
+                    CgScalars *__restrict__ sc, DistDev d) {
+  pdl_wait();
   const int done = sc->done;
   if (done == 3) return;
   if (done != 0 && sc->alpha == 0.0) return;  // replayed after the end of the solve: x already has its last update
+  cg_tl_begin(sc, 2);
   int lo, hi, per;
   cta_chunk(n, lo, hi, per);
   // converged (done == 1): only the deferred x += alpha p is still owed; p is dead.  done == 2: Eigen still updates p
   const T beta = static_cast<T>(sc->beta);
   cg_direction_body<T>(r, dinv, p, x, static_cast<T>(sc->alpha), beta, done != 1, lo, hi, CG_THREADS, true);
+  pdl_trigger();
   if (d.world > 1 && done == 0) {
     if (d.zmode) {
       // ghost copies of p, updated here from the z' the owners pushed a kernel ago: p_g = fma(beta, p_g, z_g) is the
@@ -469,6 +528,7 @@ cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, 
       dist_halo_push_signal<T>(d, p, lo, hi, per);
     }
   }
+  cg_tl_end(sc);
 }
 
 // ---- variant "merged": two kernels and ONE reduction per iteration -----------------------------------------------------
@@ -485,7 +545,7 @@ cg_spmv_merged_kernel(int rows, const int *__restrict__ indptr, const int *__res
   extern __shared__ unsigned char smem_raw[];
   __shared__ double s_red[7 * 16];
   __shared__ unsigned s_flag;
-  pdl_wait_then_release();
+  pdl_wait();
   if (sc->done) {
     if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;  // see cg_spmv_dot_kernel
     return;
@@ -503,7 +563,7 @@ template <typename T>
 __global__ void __launch_bounds__(CG_THREADS)
 cg_update_merged_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv, T *__restrict__ r,
                         T *__restrict__ p, T *__restrict__ x, const CgScalars *__restrict__ sc, DistDev d) {
-  pdl_wait_then_release();
+  pdl_wait();
   const int done = sc->done;
   if (done == 3) return;
   if (done != 0 && sc->alpha == 0.0) return;  // replayed after the end of the solve
@@ -902,7 +962,7 @@ struct CgSolver::Impl {
 
 namespace {
 
-// Launch with the programmatic-stream-serialization attribute (see pdl_wait_then_release) when QDSP_PDL=1.  Off by
+// Launch with the programmatic-stream-serialization attribute (see pdl_wait) when QDSP_PDL=1.  Off by
 // default: measured on B200 it is neutral on small systems and 7 % SLOWER at 256^3 (337 vs 315 us per iteration) --
 // the early-scheduled successor competes with the tail of the running kernel.
 bool pdl_enabled() {
@@ -1125,7 +1185,7 @@ void start(CgSolver::Impl &I, T *x, const T *b, int max_iters, double tol, bool 
   init.tol = never_converge ? -1.0 : tol;
   {
     const char *tr = std::getenv("QDSP_CG_TRACE");
-    init.trace = (tr && tr[0] == '2') ? 1 : 0;
+    init.trace = (tr && tr[0] == '2') ? 1 : (tr && tr[0] == '3') ? 3 : 0;
   }
   QDSP_CUDA(cudaMemcpyAsync(sc, &init, sizeof(init), cudaMemcpyHostToDevice, I.stream));
   const T *tmp = nullptr;
@@ -1276,6 +1336,17 @@ void run_fixed_t(CgSolver::Impl &I, void *x, const void *b, int iters, cudaStrea
       left -= batch;
     }
     for (; left > 0; --left) launch_iteration<T>(I, static_cast<T *>(x));
+    if (trace && trace[0] == '3' && iters > 0) {
+      // in-graph timeline (a debugging aid: the solve is synchronised here; never used for a reported number)
+      CgScalars &h = *I.h_sc;
+      QDSP_CUDA(cudaMemcpyAsync(&h, I.scalars.get(), sizeof(CgScalars), cudaMemcpyDeviceToHost, I.stream));
+      QDSP_CUDA(cudaStreamSynchronize(I.stream));
+      const double k = 1e-3 / iters;
+      std::fprintf(stderr, "[qdsp timeline rank %d] us per iteration over %d: idle %.2f | A.p+dot %.2f (all-reduce %.2f) | idle %.2f | "
+                   "residual %.2f (all-reduce %.2f) | idle %.2f | direction %.2f | sum %.2f\n", I.dist ? I.dist->rank() : 0, iters,
+                   k * h.tl_acc[0], k * h.tl_acc[1], k * h.tl_acc[6], k * h.tl_acc[2], k * h.tl_acc[3], k * h.tl_acc[7], k * h.tl_acc[4],
+                   k * h.tl_acc[5], k * (h.tl_acc[0] + h.tl_acc[1] + h.tl_acc[2] + h.tl_acc[3] + h.tl_acc[4] + h.tl_acc[5]));
+    }
   }
   QDSP_CUDA(cudaEventRecord(I.ev_out, I.stream));
   QDSP_CUDA(cudaStreamWaitEvent(stream, I.ev_out, 0));

@@ -179,16 +179,13 @@ __device__ __forceinline__ unsigned rs_lookback_batched(unsigned *my, unsigned t
   return exclusive;
 }
 
+// keys (+values) of one tile into registers, warp-striped, straight from global memory
 template <typename KeyT, typename ValT, int ITEMS, bool FULL_TILE>
-__device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT *s_vals, const KeyT *__restrict__ kin,
-                                              KeyT *__restrict__ kout, const ValT *__restrict__ vin,
-                                              ValT *__restrict__ vout, long long tile_base, int valid_n, int shift,
-                                              unsigned dmask, int kind, int tw_in, int tw_out, unsigned tile,
-                                              unsigned *__restrict__ lookback, const unsigned *__restrict__ bins) {
+__device__ __forceinline__ void rs_load_tile(KeyT (&key)[ITEMS], ValT (&val)[ITEMS], const KeyT *__restrict__ kin,
+                                             const ValT *__restrict__ vin, long long tile_base, int valid_n, int kind,
+                                             int tw_in) {
   constexpr bool HAS_VAL = !std::is_same<ValT, NoValue>::value;
   const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
-  KeyT key[ITEMS];
-  ValT val[ITEMS];
   const int wbase = warp * 32 * ITEMS + lane;
   const KeyT *kp = kin + tile_base + wbase;
 #pragma unroll
@@ -206,6 +203,18 @@ __device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT
     for (int i = 0; i < ITEMS; ++i)
       if (FULL_TILE || wbase + i * 32 < valid_n) val[i] = vp[i * 32];
   }
+}
+
+// everything after the load: ranking, digit offsets, shared-memory scatter, look-back, coalesced write-out
+template <typename KeyT, typename ValT, int ITEMS, bool FULL_TILE>
+__device__ __forceinline__ void rs_sweep_tile(RsSmem<KeyT, ValT, ITEMS> &S, ValT *s_vals, KeyT (&key)[ITEMS],
+                                              ValT (&val)[ITEMS], KeyT *__restrict__ kout, ValT *__restrict__ vout,
+                                              int valid_n, int shift, unsigned dmask, int kind, int tw_out,
+                                              unsigned tile, unsigned *__restrict__ lookback,
+                                              const unsigned *__restrict__ bins) {
+  constexpr bool HAS_VAL = !std::is_same<ValT, NoValue>::value;
+  const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
+  const int wbase = warp * 32 * ITEMS + lane;
   unsigned *my_hist = &S.warp_hist[warp][0];
   unsigned rank[ITEMS];
   const unsigned lt = lanemask_lt();
@@ -319,13 +328,25 @@ rs_onesweep_kernel(const KeyT *__restrict__ kin, KeyT *__restrict__ kout, const 
   if (tile_base >= n) return;
   const int valid_n = static_cast<int>(min(static_cast<long long>(TILE), n - tile_base));
   const unsigned dmask = (1u << nbits) - 1u;
-  if (valid_n == TILE)
-    rs_sweep_tile<KeyT, ValT, ITEMS, true>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind, tw_in,
-                                           tw_out, tile, lookback, bins);
-  else
-    rs_sweep_tile<KeyT, ValT, ITEMS, false>(S, s_vals, kin, kout, vin, vout, tile_base, valid_n, shift, dmask, kind,
-                                            tw_in, tw_out, tile, lookback, bins);
+  KeyT key[ITEMS];
+  ValT val[ITEMS];
+  if (valid_n == TILE) {
+    rs_load_tile<KeyT, ValT, ITEMS, true>(key, val, kin, vin, tile_base, valid_n, kind, tw_in);
+    rs_sweep_tile<KeyT, ValT, ITEMS, true>(S, s_vals, key, val, kout, vout, valid_n, shift, dmask, kind, tw_out, tile,
+                                           lookback, bins);
+  } else {
+    rs_load_tile<KeyT, ValT, ITEMS, false>(key, val, kin, vin, tile_base, valid_n, kind, tw_in);
+    rs_sweep_tile<KeyT, ValT, ITEMS, false>(S, s_vals, key, val, kout, vout, valid_n, shift, dmask, kind, tw_out, tile,
+                                            lookback, bins);
+  }
 }
+
+// A persistent form of this kernel (each CTA loops over tiles; the next tile's keys and values arrive by TMA bulk copy
+// into a landing buffer while the current one is ranked and scattered) was built and measured in round 2 and REMOVED:
+// with a static b, b+G, ... tile assignment all G tiles of a round reach their look-back together and walk ~G
+// predecessors (2^28 pairs 7.77 ms, keys only 7.07 ms against 7.20 / 5.72 ms for this kernel); with tiles handed out by
+// ticket one ahead it was 7.59 / 8.01 ms.  The landing buffer costs a CTA per SM for pairs, and the extra shared-memory
+// round trip + barrier per tile outweigh the hidden load latency, which the four resident CTAs already overlap.
 
 // ---- host driver ---------------------------------------------------------------------------------------------------
 // Keys per thread (tile = 256 x ITEMS) and resident CTAs per SM the kernel is compiled for.  Wider items -> fewer

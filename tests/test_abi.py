@@ -95,3 +95,19 @@ def test_product_does_not_touch_the_oracle():
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
                 assert "qd_oracle" not in text and "eigen_ref" not in text, f
+
+
+def test_product_does_not_call_vendor_sparse_libraries(lib_path):
+    """cuSPARSE / cuBLAS are the reference's path (the kernel to beat, tools/bench_cusparse.py); the product neither
+    links nor loads them."""
+    import subprocess
+
+    needed = subprocess.run(["readelf", "-d", lib_path], capture_output=True, text=True).stdout
+    assert "cusparse" not in needed and "cublas" not in needed
+    pkg = os.path.join(ROOT, "quadrants_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".hpp", ".h")) and f != "build.py":
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert not re.search(r"#include\s*<(cusparse|cublas)", text), f
+                assert "libcusparse" not in text and "libcublas" not in text, f

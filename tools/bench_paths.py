@@ -1,8 +1,9 @@
 #!/usr/bin/env python
 """Secondary throughput harness (NOT the driver's bench line): the other BASELINE.json configs on one B200.
 
-    python tools/bench_paths.py [scan] [sort] [build] [fem] [algos]        # default: all, one JSON line per config
+    python tools/bench_paths.py [c1] [scan] [sort] [build] [fem] [algos]        # default: all, one JSON line per config
 
+C1  2-D Poisson 512 x 512 fp32: build, SpMV, SparseCG to 1e-6 (the reference's CPU-runnable case)
 C3  inclusive scan and key-value sort of 2^28 random i32                     (byte models of SURVEY 8(d))
 C4  triplet -> CSR build of 200 M random f32 triplets, ~30 % duplicates, rows = cols = 2^24
 C5  fp64 SpMV + Jacobi-PCG on an irregular FEM-like matrix (power-law row lengths)
@@ -47,6 +48,43 @@ def emit(name, ms, nbytes, **extra):
     print(json.dumps({"config": name, "ms": round(ms, 4), "algorithmic_bytes": int(nbytes), "gbs": round(gbs, 1),
                       "frac_of_measured_peak": round(gbs / PEAK, 4), "frac_of_nominal_8000": round(gbs / 8000, 4),
                       **extra}), flush=True)
+
+
+def bench_c1(lib, stream):
+    """C1 (BASELINE configs[0], the reference's own CPU-runnable case): 2-D 5-point Poisson 512 x 512, build + SpMV +
+    SparseCG to 1e-6, fp32.  Everything fits in L2 (16 MB), so this line is launch/latency-bound, not HBM-bound."""
+    from tests import workloads as W
+    r, c, v = W.poisson2d_triplets(512)
+    n = 512 * 512
+    rt, ct, vt = torch.from_numpy(r.astype(np.int32)).cuda(), torch.from_numpy(c.astype(np.int32)).cuda(), torch.from_numpy(v).cuda()
+    K = qd.linalg.SparseMatrixBuilder(n, n, max_num_triplets=int(r.shape[0]), dtype=qd.f32)
+    out = []
+    def setup():
+        K.ptr.buffer_tensor()[0] = 0
+        K.ptr._appended = 0
+        K.ptr.insert_triplets(rt, ct, vt)
+        out.clear()
+    def run():
+        out.append(K.build())
+    setup(); run()
+    ms_build = timed(run, 5, setup=setup)
+    A = out[0]
+    nnz = A.matrix.nnz()
+    x = qd.ndarray(qd.f32, n); x.tensor.uniform_(-1, 1)
+    y = qd.ndarray(qd.f32, n)
+    spmv = lambda: A.matrix.spmv(None, x, y)
+    for _ in range(5):
+        spmv()
+    reps = 500
+    ms = timed(lambda: [spmv() for _ in range(reps)], 3) / reps
+    emit("C1 2-D Poisson 512x512 fp32 SpMV (L2-resident)", ms, nnz * 8 + (n + 1) * 4 + 2 * n * 4, rows=n, nnz=int(nnz),
+         build_ms=round(ms_build, 3))
+    b = qd.ndarray(qd.f32, n); b.fill(1.0)
+    cg = qd.linalg.SparseCG(A, b, max_iter=5000, atol=1e-6)
+    cg.solve(); torch.cuda.synchronize()
+    ms = timed(lambda: cg.solve(), 5)
+    emit("C1 2-D Poisson 512x512 fp32 Jacobi-PCG to 1e-6", ms, cg.iterations * (nnz * 8 + (n + 1) * 4 + 13 * n * 4),
+         iterations=cg.iterations, rel_residual=cg.error, iters_per_s=round(cg.iterations / ms * 1e3, 1))
 
 
 def bench_scan(lib, stream):
@@ -216,9 +254,9 @@ def main():
     qd.init(arch=qd.cuda, device=0)
     lib = _lib.load()
     stream = torch.cuda.current_stream().cuda_stream
-    which = sys.argv[1:] or ["scan", "sort", "build", "fem", "algos"]
+    which = sys.argv[1:] or ["c1", "scan", "sort", "build", "fem", "algos"]
     for w in which:
-        {"scan": bench_scan, "sort": bench_sort, "build": bench_build, "fem": bench_fem, "algos": bench_algos}[w](lib, stream)
+        {"c1": bench_c1, "scan": bench_scan, "sort": bench_sort, "build": bench_build, "fem": bench_fem, "algos": bench_algos}[w](lib, stream)
         torch.cuda.empty_cache()
 
 
