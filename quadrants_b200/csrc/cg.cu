@@ -48,6 +48,24 @@ constexpr int CG_THREADS = 256;
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// Chained launch (experimental, QDSP_CG_CHAIN=1; see chain_enabled for the measurements).  The residual and the direction kernel are launched with the
+// programmatic-serialization attribute but do NOT execute griddepcontrol.wait: their CTAs become resident as soon as every
+// CTA of the predecessor has passed its pdl_trigger (i.e. finished streaming), and thread 0 of each polls a flag that
+// the predecessor's last CTA raises after the grid reduction + cross-rank all-reduce + scalar update.  Everything the
+// successor reads (the vectors the predecessor's CTAs wrote before their reduction tickets, the scalars) is ordered before
+// the flag by the ticket chain (fence + atomic per CTA, acquire in the last CTA, release on the flag), so the kernel
+// boundary -- ~2 us of drain + launch, and in the residual kernel the 4-7 us tail in which the halo CTAs wait for their
+// NVLink acknowledgements (QDSP_CG_TRACE=3) -- leaves the critical path.  The A.p kernel that follows is launched
+// normally, i.e. after BOTH predecessors have completed, and lowers the flags again.
+__device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu_u32(unsigned *p, unsigned v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 struct CgScalars {
   double pAp, abs_new, abs_old, res2, rhs2, thr;
   double alpha, beta;
@@ -67,11 +85,35 @@ struct CgScalars {
   // QDSP_CG_TRACE=3: in-graph timeline of the three-kernel iteration, from %globaltimer.  tl_acc[2k] = idle time in
   // front of kernel k (end of the previous kernel's last CTA -> start of CTA 0), tl_acc[2k+1] = duration of kernel k,
   // tl_acc[6], [7] = time the last CTA of kernels A, B spent in the cross-rank all-reduce
-  unsigned long long tl_acc[8];
+  unsigned long long tl_acc[10];  // [8], [9]: start of kernel A, B -> its last CTA reaches the reduction
   unsigned long long tl_start, tl_end;
   int tl_prev;
   int trace;
+  // chained launch (see cg_chain_wait): 1 = the residual / direction kernels start early and wait for these flags
+  int chain;
+  unsigned push_seq;  // amode: halo pushes of this rank completed before the current A.p kernel (DistDev::want_ptr)
+  unsigned flag_A, flag_B;  // raised by the last CTA of the A.p / residual kernel once its scalars are final
 };
+
+// all threads of the CTA; returns once `flag` is up (bounded: a lost predecessor ends the solve with done = 3)
+__device__ __forceinline__ void cg_chain_wait(unsigned *flag, CgScalars *sc) {
+  if (threadIdx.x == 0) {
+    const long long t0 = clock64();
+    while (ld_relaxed_u32(flag) == 0u) {
+      __nanosleep(32);
+      if (clock64() - t0 > 4000000000LL) {
+        sc->done = 3;
+        break;
+      }
+    }
+    (void)ld_acquire_gpu_u32(flag);
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void cg_chain_raise(unsigned *flag) {
+  __threadfence();
+  st_release_gpu_u32(flag, 1u);
+}
 
 // ---- QDSP_CG_TRACE=3 timeline (see CgScalars::tl_acc) -------------------------------------------------------------------
 __device__ __forceinline__ unsigned long long cg_now_ns() {
@@ -241,6 +283,7 @@ __device__ __forceinline__ void cg_reduce_and_finish(double (&v)[NV], const Dist
   if (threadIdx.x < 32) {
     const bool tl = sc->trace == 3 && threadIdx.x == 0 && (NV == 1 || NV == 2);
     const unsigned long long t0 = tl ? cg_now_ns() : 0ull;
+    if (tl) sc->tl_acc[7 + NV] += t0 - sc->tl_start;
     dist_allreduce<NV>(d, v);
     if (tl) sc->tl_acc[5 + NV] += cg_now_ns() - t0;
     if (threadIdx.x == 0) {
@@ -248,6 +291,13 @@ __device__ __forceinline__ void cg_reduce_and_finish(double (&v)[NV], const Dist
       else fin(v);
     }
   }
+}
+
+// one warp: sum of `mine` over the ranks (CgSolver construction: do all ranks qualify for amode?)
+__global__ void cg_agree_kernel(DistDev d, double mine, double *out) {
+  double v[1] = {mine};
+  dist_allreduce<1>(d, v);
+  if (threadIdx.x == 0) *out = v[0];
 }
 
 // ---- setup kernels ----------------------------------------------------------------------------------------------------
@@ -285,6 +335,8 @@ __device__ __forceinline__ void cta_chunk(int n, int &lo, int &hi, int &per) {
 // then ran all-reduce and push back to back (measured at 2 ranks, QDSP_CG_TRACE=3: the residual kernel of the rank with
 // an upper neighbour took 33.2 us against 27.8 us on the rank with a lower neighbour, and the other rank idled 5.4 us in
 // the next all-reduce).  Dealt from both ends, both boundaries belong to the earliest CTAs.
+// (Also tried, and slower: dedicated halo CTAs with 2048-row slices so that the push overlaps the interior sweep --
+// 2 ranks x 2.1 M rows 54.1 -> 57.2 us per iteration, 2 x 8.4 M rows 158 -> 176 us; profiles/r02x_chain.txt.)
 __device__ __forceinline__ void cta_chunk_ends(int n, int &lo, int &hi, int &per) {
   per = ((n + gridDim.x - 1) / gridDim.x + 1023) & ~1023;
   const int b = static_cast<int>(blockIdx.x);
@@ -316,7 +368,10 @@ cg_init_kernel(int n, const T *__restrict__ b, const T *__restrict__ tmp, const 
   }
   double v[3] = {static_cast<double>(s0), static_cast<double>(s1), static_cast<double>(s2)};
   if (grid_sum_last_block<3>(v, partials, &sc->ticket[0], s_red, &s_flag))
-    cg_reduce_and_finish<3>(v, d, use_nccl, sc, [&](const double (&t)[3]) { cg_finish_init<T>(sc, t); });
+    cg_reduce_and_finish<3>(v, d, use_nccl, sc, [&](const double (&t)[3]) {
+      cg_finish_init<T>(sc, t);
+      if (d.world > 1) sc->push_seq = *reinterpret_cast<volatile unsigned *>(&d.counters[1]);
+    });
 }
 
 // Multi-GPU: the halo of the first direction, sent by its own kernel AFTER cg_init_kernel.  The all-reduce that ends
@@ -339,19 +394,26 @@ cg_spmv_dot_kernel(int rows, const int *__restrict__ indptr, const int *__restri
   __shared__ double s_red[16];
   __shared__ unsigned s_flag;
   pdl_wait();
+  const int chain = sc->chain;
   if (sc->done) {
     // the deferred x += alpha p of the final iteration has been applied by the direction kernel before this launch:
     // retire alpha so that a replayed direction kernel is a no-op
-    if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      sc->alpha = 0.0;
+      if (chain) cg_chain_raise(&sc->flag_A);
+    }
     return;
   }
+  if (chain && blockIdx.x == 0 && threadIdx.x == 0) sc->flag_A = sc->flag_B = 0u;  // ordered before the raise by CTA 0's ticket
   cg_tl_begin(sc, 0);
   DotSink<T> sink{p};
   spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, sink, d, 0, sched);
   pdl_trigger();
   double v[1] = {sink.acc};
-  if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag))
+  if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag)) {
     cg_reduce_and_finish<1>(v, d, use_nccl, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
+    if (chain && threadIdx.x == 0) cg_chain_raise(&sc->flag_A);
+  }
   cg_tl_end(sc);
 }
 
@@ -365,17 +427,24 @@ cg_spmv_dot_stream_kernel(const int *__restrict__ indptr, const int *__restrict_
   __shared__ double s_red[16];
   __shared__ unsigned s_flag;
   pdl_wait();
+  const int chain = sc->chain;
   if (sc->done) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) sc->alpha = 0.0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      sc->alpha = 0.0;
+      if (chain) cg_chain_raise(&sc->flag_A);
+    }
     return;
   }
+  if (chain && blockIdx.x == 0 && threadIdx.x == 0) sc->flag_A = sc->flag_B = 0u;
   cg_tl_begin(sc, 0);
   DotSink<T> sink{p};
   spmv_stream<T>(smem_raw, indptr, indices, values, p, tmp, sink, plan, d);
   pdl_trigger();
   double v[1] = {sink.acc};
-  if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag))
+  if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag)) {
     cg_reduce_and_finish<1>(v, d, use_nccl, sc, [&](const double (&t)[1]) { cg_finish_A<T>(sc, t[0]); });
+    if (chain && threadIdx.x == 0) cg_chain_raise(&sc->flag_A);
+  }
   cg_tl_end(sc);
 }
 
@@ -388,7 +457,15 @@ template <typename T>
 __device__ __forceinline__ void cg_residual_body(const T *__restrict__ tmp, const T *__restrict__ dinv,
                                                  T *__restrict__ r, T alpha, int lo, int hi, T &s_rr, T &s_rz) {
   using V = typename Vec4T<T>::type;
-  const int lo4 = lo >> 2, hi4 = hi >> 2;  // chunks are multiples of 1024 except the last one's end
+  // [lo, hi) may start and end anywhere: scalar head up to the next multiple of 4, 128-bit body, scalar tail
+  const int lo_al = min(hi, (lo + 3) & ~3);
+  for (int i = lo + threadIdx.x; i < lo_al; i += blockDim.x) {
+    const T ri = fma_t(-alpha, tmp[i], r[i]);
+    r[i] = ri;
+    s_rr = fma_t(ri, ri, s_rr);
+    s_rz = fma_t(ri, dinv[i] * ri, s_rz);
+  }
+  const int lo4 = lo_al >> 2, hi4 = max(hi >> 2, lo4);
   for (int i = lo4 + threadIdx.x; i < hi4; i += blockDim.x) {
     const V t4 = reinterpret_cast<const V *>(tmp)[i];
     const V d4 = reinterpret_cast<const V *>(dinv)[i];
@@ -401,7 +478,7 @@ __device__ __forceinline__ void cg_residual_body(const T *__restrict__ tmp, cons
     s_rr = fma_t(r4.z, r4.z, s_rr); s_rz = fma_t(r4.z, d4.z * r4.z, s_rz);
     s_rr = fma_t(r4.w, r4.w, s_rr); s_rz = fma_t(r4.w, d4.w * r4.w, s_rz);
   }
-  for (int i = max(lo, hi4 << 2) + threadIdx.x; i < hi; i += blockDim.x) {
+  for (int i = max(lo_al, hi4 << 2) + threadIdx.x; i < hi; i += blockDim.x) {
     const T ri = fma_t(-alpha, tmp[i], r[i]);
     r[i] = ri;
     s_rr = fma_t(ri, ri, s_rr);
@@ -444,21 +521,33 @@ cg_residual_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ dinv,
                    CgScalars *__restrict__ sc, double *__restrict__ partials, DistDev d, int use_nccl) {
   __shared__ double s_red[2 * 16];
   __shared__ unsigned s_flag;
-  pdl_wait();
-  if (sc->done) return;
+  const int chain = sc->chain;
+  if (chain) cg_chain_wait(&sc->flag_A, sc);
+  else pdl_wait();
+  if (sc->done) {
+    if (chain && blockIdx.x == 0 && threadIdx.x == 0) cg_chain_raise(&sc->flag_B);
+    return;
+  }
   cg_tl_begin(sc, 1);
   T s_rr = T(0), s_rz = T(0);
   int lo = 0, hi = 0, per = 1024;
+  const T alpha = static_cast<T>(sc->alpha);
   if (d.zmode) {
     cta_chunk_ends(n, lo, hi, per);
-    cg_residual_body<T>(tmp, dinv, r, static_cast<T>(sc->alpha), lo, hi, s_rr, s_rz);
+    cg_residual_body<T>(tmp, dinv, r, alpha, lo, hi, s_rr, s_rz);
   } else {
-    cg_residual_body_strided<T>(n, tmp, dinv, r, static_cast<T>(sc->alpha), s_rr, s_rz);
+    cg_residual_body_strided<T>(n, tmp, dinv, r, alpha, s_rr, s_rz);
   }
   pdl_trigger();
   double v[2] = {static_cast<double>(s_rr), static_cast<double>(s_rz)};
-  if (grid_sum_last_block<2>(v, partials, &sc->ticket[2], s_red, &s_flag))
-    cg_reduce_and_finish<2>(v, d, use_nccl, sc, [&](const double (&t)[2]) { cg_finish_B<T>(sc, t[0], t[1]); });
+  if (grid_sum_last_block<2>(v, partials, &sc->ticket[2], s_red, &s_flag)) {
+    cg_reduce_and_finish<2>(v, d, use_nccl, sc, [&](const double (&t)[2]) {
+      cg_finish_B<T>(sc, t[0], t[1]);
+      // (the A.p kernel of this iteration is complete: its push is counted)
+      if (d.world > 1) sc->push_seq = *reinterpret_cast<volatile unsigned *>(&d.counters[1]);
+    });
+    if (chain && threadIdx.x == 0) cg_chain_raise(&sc->flag_B);
+  }
   // multi-GPU: z' = D^-1 r' of the halo rows leaves now -- AFTER this CTA has handed in its partial sums, so that the
   // wait for the NVLink acknowledgements runs beside the grid reduction and its all-reduce, not in front of them
   // (pushing first cost ~9 us per iteration at 2 ranks)
@@ -500,7 +589,8 @@ template <typename T>
 __global__ void __launch_bounds__(CG_THREADS)
 cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, T *__restrict__ p, T *__restrict__ x,
                     CgScalars *__restrict__ sc, DistDev d) {
-  pdl_wait();
+  if (sc->chain) cg_chain_wait(&sc->flag_B, sc);
+  else pdl_wait();
   const int done = sc->done;
   if (done == 3) return;
   if (done != 0 && sc->alpha == 0.0) return;  // replayed after the end of the solve: x already has its last update
@@ -511,7 +601,7 @@ cg_direction_kernel(int n, const T *__restrict__ r, const T *__restrict__ dinv, 
   const T beta = static_cast<T>(sc->beta);
   cg_direction_body<T>(r, dinv, p, x, static_cast<T>(sc->alpha), beta, done != 1, lo, hi, CG_THREADS, true);
   pdl_trigger();
-  if (d.world > 1 && done == 0) {
+  if (d.world > 1 && done == 0 && !d.amode) {
     if (d.zmode) {
       // ghost copies of p, updated here from the z' the owners pushed a kernel ago: p_g = fma(beta, p_g, z_g) is the
       // owners' own operation on the same operands, so owner and copy stay bit-identical and nothing is sent now
@@ -621,14 +711,6 @@ cg_update_merged_kernel(int n, const T *__restrict__ tmp, const T *__restrict__ 
 // generation word (release / acquire at gpu scope); the acquire also invalidates L1, which is what makes the plain
 // loads of tmp / r / p -- written by other CTAs within the same launch -- and the coherent x gather (ld_x) correct.
 // Every spin is bounded (~4 s of clock64): a bug cannot hang the GPU.
-__device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned *p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_gpu_u32(unsigned *p, unsigned v) {
-  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
@@ -950,6 +1032,8 @@ struct CgSolver::Impl {
   void *graph_x = nullptr;
   int graph_iters = 0;
   int vec_grid = 0, spmv_grid = 0, lpr = 1;
+  size_t vec_smem = 0;  // chained launch: dynamic shared memory that caps the vector kernels at their fair share of CTAs per SM
+  bool chain = false;   // residual / direction kernels launched early, ordered by device flags (cg_chain_wait)
   bool merged = false;  // one-reduction variant (cg_spmv_merged_kernel + cg_update_merged_kernel)
   bool fused = false;   // persistent cooperative kernel for the whole iteration loop (cg_fused_kernel)
   int fused_grid = 0;
@@ -957,7 +1041,18 @@ struct CgSolver::Impl {
 
   Impl(const CsrMatrix &A_, int mi, double t, int m, bool v, DistContext *d)
       : A(A_), max_iters(mi), tol(t), mode(m), verbose(v), dist(d) {}
-  DistDev dev() const { return dist ? dist->dev() : DistDev{}; }
+  bool amode = false;  // the A.p kernel sends the halo of p itself (DistDev::amode); agreed on by all ranks at construction
+  DistDev dev() const {
+    if (!dist) return DistDev{};
+    DistDev d = dist->dev();
+    if (amode) {
+      d.amode = 1;
+      d.zmode = 0;
+      d.block_order = d.block_order_all;
+      d.want_ptr = reinterpret_cast<const unsigned *>(scalars.get<char>() + offsetof(CgScalars, push_seq));
+    }
+    return d;
+  }
 };
 
 namespace {
@@ -969,6 +1064,16 @@ bool pdl_enabled() {
   static const bool on = [] { const char *e = std::getenv("QDSP_PDL"); return e && e[0] == '1'; }();
   return on;
 }
+// chained launch of the residual / direction kernels (cg_chain_wait): QDSP_CG_CHAIN=1.  Off by default -- measured on
+// B200 (profiles/r02x_chain.txt): the two launch gaps shrink from 1.8 to 0.3-0.7 us and, multi-GPU, the halo tail of the
+// residual kernel is hidden (2 ranks x 2.1 M rows: 55.5 -> 52.7 us per iteration), but the shared-memory request that
+// keeps the early CTAs evenly spread leaves the vector kernels too little L1 at 8 CTAs per SM (256^3: 287 -> 313 us on
+// one GPU, 159 -> 175 us on two), and one multi-GPU parity case failed under it.  Kept for experiments only.
+bool chain_enabled() {
+  static const bool on = [] { const char *e = std::getenv("QDSP_CG_CHAIN"); return e && e[0] == '1'; }();
+  return on && !pdl_enabled();
+}
+thread_local bool g_launch_early = false;  // set around the launches that may start before their predecessor has drained
 template <typename... KArgs, typename... Args>
 void launch_pdl(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t stream, Args &&...args) {
   cudaLaunchConfig_t cfg = {};
@@ -980,7 +1085,7 @@ void launch_pdl(void (*kernel)(KArgs...), int grid, int block, size_t smem, cuda
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = (pdl_enabled() || g_launch_early) ? 1 : 0;
   QDSP_CUDA(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(std::forward<Args>(args))...));
   count_launch();
 }
@@ -1143,9 +1248,16 @@ void launch_iteration(CgSolver::Impl &I, T *x) {
   }
   launch_spmv_dot_any<T>(I);
   if (I.use_nccl) nccl_reduce_then<T>(I, 1, 1);
-  launch_pdl(cg_residual_kernel<T>, I.vec_grid, CG_THREADS, 0, I.stream, n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(), sc, part, I.dev(), I.use_nccl);
-  if (I.use_nccl) nccl_reduce_then<T>(I, 2, 2);
-  launch_pdl(cg_direction_kernel<T>, I.vec_grid, CG_THREADS, 0, I.stream, n, I.r.get<T>(), I.dinv.get<T>(), static_cast<T *>(I.p), x, sc, I.dev());
+  g_launch_early = I.chain;
+  try {
+    launch_pdl(cg_residual_kernel<T>, I.vec_grid, CG_THREADS, I.vec_smem, I.stream, n, I.tmp.get<T>(), I.dinv.get<T>(), I.r.get<T>(), sc, part, I.dev(), I.use_nccl);
+    if (I.use_nccl) nccl_reduce_then<T>(I, 2, 2);
+    launch_pdl(cg_direction_kernel<T>, I.vec_grid, CG_THREADS, I.vec_smem, I.stream, n, I.r.get<T>(), I.dinv.get<T>(), static_cast<T *>(I.p), x, sc, I.dev());
+  } catch (...) {
+    g_launch_early = false;
+    throw;
+  }
+  g_launch_early = false;
 }
 
 int kernels_per_iteration(const CgSolver::Impl &I) { return I.merged ? (I.use_nccl ? 3 : 2) : (I.use_nccl ? 5 : 3); }
@@ -1186,6 +1298,7 @@ void start(CgSolver::Impl &I, T *x, const T *b, int max_iters, double tol, bool 
   {
     const char *tr = std::getenv("QDSP_CG_TRACE");
     init.trace = (tr && tr[0] == '2') ? 1 : (tr && tr[0] == '3') ? 3 : 0;
+    init.chain = (I.chain && !(tr && tr[0] == '1')) ? 1 : 0;
   }
   QDSP_CUDA(cudaMemcpyAsync(sc, &init, sizeof(init), cudaMemcpyHostToDevice, I.stream));
   const T *tmp = nullptr;
@@ -1201,7 +1314,7 @@ void start(CgSolver::Impl &I, T *x, const T *b, int max_iters, double tol, bool 
                                                              I.partials.get<double>(), I.dev(), I.use_nccl);
   QDSP_LAUNCH_CHECK();
   if (I.use_nccl) nccl_reduce_then<T>(I, 3, 0);
-  if (I.dist && I.dist->world() > 1) {
+  if (I.dist && I.dist->world() > 1 && !I.amode) {
     cg_push_direction_kernel<T><<<I.vec_grid, CG_THREADS, 0, I.stream>>>(n, static_cast<const T *>(I.p), I.dev());
     QDSP_LAUNCH_CHECK();
   }
@@ -1343,9 +1456,10 @@ void run_fixed_t(CgSolver::Impl &I, void *x, const void *b, int iters, cudaStrea
       QDSP_CUDA(cudaStreamSynchronize(I.stream));
       const double k = 1e-3 / iters;
       std::fprintf(stderr, "[qdsp timeline rank %d] us per iteration over %d: idle %.2f | A.p+dot %.2f (all-reduce %.2f) | idle %.2f | "
-                   "residual %.2f (all-reduce %.2f) | idle %.2f | direction %.2f | sum %.2f\n", I.dist ? I.dist->rank() : 0, iters,
+                   "residual %.2f (all-reduce %.2f) | idle %.2f | direction %.2f | sum %.2f | last CTA reaches the reduction after %.2f (A), %.2f (B)\n", I.dist ? I.dist->rank() : 0, iters,
                    k * h.tl_acc[0], k * h.tl_acc[1], k * h.tl_acc[6], k * h.tl_acc[2], k * h.tl_acc[3], k * h.tl_acc[7], k * h.tl_acc[4],
-                   k * h.tl_acc[5], k * (h.tl_acc[0] + h.tl_acc[1] + h.tl_acc[2] + h.tl_acc[3] + h.tl_acc[4] + h.tl_acc[5]));
+                   k * h.tl_acc[5], k * (h.tl_acc[0] + h.tl_acc[1] + h.tl_acc[2] + h.tl_acc[3] + h.tl_acc[4] + h.tl_acc[5]),
+                   k * h.tl_acc[8], k * h.tl_acc[9]);
     }
   }
   QDSP_CUDA(cudaEventRecord(I.ev_out, I.stream));
@@ -1393,7 +1507,11 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
   // ... and at least 8192 elements per CTA: with 2.1 M rows per rank (C2 on 8 GPUs) 1184 CTAs of 1771 elements spent more
   // time in the last-block ticket than in the update (measured at 8 ranks: 56.3 us per iteration with 2 CTAs per SM against
   // 60.5 with 8, profiles/r02r_8gpu_knobs.txt)
-  I.vec_grid = std::max(1, std::min(std::min(ceil_div(A.rows, 1024), ceil_div(A.rows, 8192) + 1), device_props().sm_count * vec_per_sm));
+  // (multi-GPU: the direction kernel also updates the ghost copies of p, and a rank may own far fewer rows than it has
+  // ghosts -- the hub rows of an nnz-balanced FEM partition: 26 k owned rows against 373 k ghosts meant 4 CTAs and an
+  // 85 us direction kernel; the grid is sized for whichever is larger, CTAs without an owned chunk idle through the rest)
+  const int vec_n = std::max(A.rows, dist ? dist->n_ghost() : 0);
+  I.vec_grid = std::max(1, std::min(std::min(ceil_div(vec_n, 1024), ceil_div(vec_n, 8192) + 1), device_props().sm_count * vec_per_sm));
   // variant: "classic" (Eigen's two reductions per iteration) unless QDSP_CG_VARIANT=merged asks for the one-reduction
   // form.  Measured (profiles/r01h_8gpu_trace.txt): the merged SpMV kernel needs 72 registers -> 3 CTAs per SM and is
   // 25 % slower than the classic one, which costs more than the saved all-reduce even at 8 ranks; kept as an option.
@@ -1431,6 +1549,25 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
       }
     }
   }
+  // the early-launched vector kernels spin on device flags: every one of their CTAs must be resident next to the tail
+  // of the predecessor, which the vector grid (<= 2 CTAs per SM of 256 threads) always is
+  I.chain = chain_enabled() && !I.use_nccl && !I.merged && !I.fused && A.rows > 0;
+  if (I.chain) {
+    // CTAs of an early-launched kernel go wherever the predecessor frees room first; unchecked, the SMs whose A.p CTAs
+    // finish first take 8 vector CTAs each and the others none (measured: the residual kernel ran 16 us instead of 9.7).
+    // A dummy shared-memory request caps every SM at its fair share.
+    const int per_sm = ceil_div(I.vec_grid, device_props().sm_count);
+    const size_t budget = 227 * 1024 / static_cast<size_t>(per_sm);
+    I.vec_smem = budget > 4096 ? budget - 2048 : 0;
+    const int bytes = static_cast<int>(I.vec_smem);
+    if (A.dtype == QDSP_F32) {
+      QDSP_CUDA(cudaFuncSetAttribute(cg_residual_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+      QDSP_CUDA(cudaFuncSetAttribute(cg_direction_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    } else {
+      QDSP_CUDA(cudaFuncSetAttribute(cg_residual_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+      QDSP_CUDA(cudaFuncSetAttribute(cg_direction_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    }
+  }
   I.partials.alloc(sizeof(double) * 8 * static_cast<size_t>(std::max(std::max(I.spmv_grid, I.vec_grid), I.fused_grid)));
   I.scalars.alloc(sizeof(CgScalars));
   QDSP_CUDA(cudaMemset(I.scalars.get(), 0, sizeof(CgScalars)));
@@ -1448,6 +1585,22 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
     cg_invdiag_kernel<double><<<g, CG_THREADS, 0, I.stream>>>(A.rows, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<double>(), identity, I.dinv.get<double>());
   QDSP_LAUNCH_CHECK();
   QDSP_CUDA(cudaStreamSynchronize(I.stream));
+  // amode: the A.p kernel pushes the halo of p itself (spmv_kernels.cuh) and the vector kernels carry no communication
+  // at all.  Every rank must run the same protocol, so the choice is all-reduced: it holds only if it holds everywhere.
+  if (dist && dist->world() > 1 && !I.use_nccl) {
+    const DistDev d = dist->dev();
+    const char *e = std::getenv("QDSP_CG_AMODE");
+    const bool mine = !(e && e[0] == '0') && !I.merged && !I.fused && A.spmv_mode == 1 && d.ghost_blocks != nullptr &&
+                      d.ghost_block_rows == SPMV_CONSUMERS / I.lpr && d.block_order_all != nullptr && d.n_send > 0 &&
+                      d.n_send == d.n_recv;
+    double *out = I.partials.get<double>();
+    cg_agree_kernel<<<1, 32, 0, I.stream>>>(d, mine ? 1.0 : 0.0, out);
+    QDSP_LAUNCH_CHECK();
+    double votes = 0.0;
+    QDSP_CUDA(cudaMemcpyAsync(&votes, out, sizeof(double), cudaMemcpyDeviceToHost, I.stream));
+    QDSP_CUDA(cudaStreamSynchronize(I.stream));
+    I.amode = votes > dist->world() - 0.5;
+  }
 }
 
 CgSolver::~CgSolver() {

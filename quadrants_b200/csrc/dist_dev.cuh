@@ -68,6 +68,13 @@ struct DistDev {
   // NVLink latency of the halo hides behind interior work.
   const int *block_order = nullptr;
   int n_interior = 0;
+  const int *block_order_all = nullptr;          // the same list, always there (block_order is set only when it is to be used)
+  // amode (the CG's A.p kernel, cg.cu): the kernel that READS the operand also sends its halo -- the CTAs that own a halo
+  // row push it before their first block, everybody reads the interior blocks first.  Then the number of pushes the
+  // flags must show is *want_ptr + 1 (want_ptr: a device word holding the push count at the start of the kernel;
+  // counters[1] itself advances while the kernel runs).
+  int amode = 0;
+  const unsigned *want_ptr = nullptr;
   unsigned *counters = nullptr;                  // device, local: [0] reduction seq, [1] halo push count, [2] ticket,
                                                  // [3] z push count, [4] z ticket, [5] stand-alone SpMV calls
   int *error = nullptr;                          // device, local: != 0 after a timeout
@@ -173,8 +180,10 @@ __device__ __forceinline__ void dist_push_bar() {
   if constexpr (NT == 0) __syncthreads();
   else asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
 }
+// owners_override > 0: the caller's CTAs are not the uniform cta-chunk partition; that many CTAs own a halo row.
 template <typename T, bool Z, int NT = 0>
-__device__ __forceinline__ void dist_halo_push_impl(const DistDev &d, const T *vec, const T *mul, int lo, int hi, int per) {
+__device__ __forceinline__ void dist_halo_push_impl(const DistDev &d, const T *vec, const T *mul, int lo, int hi, int per,
+                                                    int owners_override = 0) {
   if (d.world <= 1) return;
   const int nthreads = NT == 0 ? static_cast<int>(blockDim.x) : NT;
   bool mine = false;
@@ -224,17 +233,19 @@ __device__ __forceinline__ void dist_halo_push_impl(const DistDev &d, const T *v
   dist_push_bar<NT>();
   if (threadIdx.x == 0) {
     // number of CTAs that own a halo row: chunks [c * per, (c + 1) * per) meeting any [send_first, send_last]
-    int owners = 0, covered_to = -1;  // send ranges are visited in ascending order of their first row
-    int order[DIST_MAX_RANKS];
-    for (int s = 0; s < d.n_send; ++s) order[s] = s;
-    for (int i = 1; i < d.n_send; ++i)
-      for (int j = i; j > 0 && d.send_first[order[j]] < d.send_first[order[j - 1]]; --j) {
-        const int t = order[j]; order[j] = order[j - 1]; order[j - 1] = t;
+    int owners = owners_override, covered_to = -1;  // send ranges are visited in ascending order of their first row
+    if (owners_override <= 0) {
+      int order[DIST_MAX_RANKS];
+      for (int s = 0; s < d.n_send; ++s) order[s] = s;
+      for (int i = 1; i < d.n_send; ++i)
+        for (int j = i; j > 0 && d.send_first[order[j]] < d.send_first[order[j - 1]]; --j) {
+          const int t = order[j]; order[j] = order[j - 1]; order[j - 1] = t;
+        }
+      for (int i = 0; i < d.n_send; ++i) {
+        const int s = order[i];
+        const int c0 = max(d.send_first[s] / per, covered_to + 1), c1 = d.send_last[s] / per;
+        if (c1 >= c0) { owners += c1 - c0 + 1; covered_to = c1; }
       }
-    for (int i = 0; i < d.n_send; ++i) {
-      const int s = order[i];
-      const int c0 = max(d.send_first[s] / per, covered_to + 1), c1 = d.send_last[s] / per;
-      if (c1 >= c0) { owners += c1 - c0 + 1; covered_to = c1; }
     }
     fence_acq_rel_sys();  // my peer stores (and, cumulatively, the CTA's) are performed before the ticket is visible
     const unsigned t = atomicAdd(&d.counters[Z ? 4 : 2], 1u);
@@ -256,14 +267,16 @@ __device__ __forceinline__ void dist_halo_push_signal(const DistDev &d, const T 
 }
 // z channel: pushes D^-1[i] * r[i] of the halo rows in [lo, hi)
 template <typename T>
-__device__ __forceinline__ void dist_halo_push_signal_z(const DistDev &d, const T *r, const T *dinv, int lo, int hi, int per) {
-  dist_halo_push_impl<T, true>(d, r, dinv, lo, hi, per);
+__device__ __forceinline__ void dist_halo_push_signal_z(const DistDev &d, const T *r, const T *dinv, int lo, int hi, int per,
+                                                        int owners_override = 0) {
+  dist_halo_push_impl<T, true>(d, r, dinv, lo, hi, per, owners_override);
 }
 
 // Called by thread 0 of a CTA before the CTA's first read of a ghost entry; follow with __syncthreads().
 __device__ __forceinline__ void dist_halo_wait(const DistDev &d) {
   if (d.world <= 1) return;
-  const unsigned want = *reinterpret_cast<volatile unsigned *>(&d.counters[1]);
+  const unsigned want = d.want_ptr ? *reinterpret_cast<const volatile unsigned *>(d.want_ptr) + 1u
+                                   : *reinterpret_cast<volatile unsigned *>(&d.counters[1]);
   const long long t0 = clock64();
   for (int r = 0; r < d.n_recv; ++r) {
     // (relaxed polls, ONE acquire at the end: every acquire load invalidates the SM's L1, which the other CTAs of the SM are

@@ -224,13 +224,15 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
   const int nblk = (rows + R - 1) / R;
   // work items of this CTA.  Plain: a contiguous run of blocks.  Ordered (multi-GPU): a contiguous run of the interior
   // blocks, then every gridDim.x-th ghost block; the producer leaves the block id in the stage for the consumers.
+  // Ordered AND dynamic: the CTAs take their static runs and the dynamic chunks from the same interior-first list.
   const bool ordered = lazy_halo && dist.block_order != nullptr;
-  const bool dyn = !FUSED && !ordered && sched.work != nullptr;  // static run, then chunks from the shared counter
-  const int n_first = ordered ? dist.n_interior : nblk;
+  const bool dyn = !FUSED && sched.work != nullptr;  // static run, then chunks from the shared counter
+  const bool split = ordered && !dyn;                // interior run + strided ghost tail (the static multi-GPU order)
+  const int n_first = split ? dist.n_interior : nblk;
   const int per_cta = dyn ? sched.static_blocks : (n_first + gridDim.x - 1) / gridDim.x;
   const int blk0 = min(n_first, static_cast<int>(blockIdx.x) * per_cta);
   const int n_run = min(n_first, blk0 + per_cta) - blk0;
-  const int n_ghost_blk = ordered ? nblk - n_first : 0;
+  const int n_ghost_blk = split ? nblk - n_first : 0;
   const int n_tail = n_ghost_blk > static_cast<int>(blockIdx.x) ? (n_ghost_blk - 1 - blockIdx.x) / gridDim.x + 1 : 0;
   const int n_items = n_run + n_tail;  // (dyn: only the static run; the dynamic part ends with a sentinel)
   const int ring0 = FUSED ? iter * n_items : 0;  // ring position of this call's first item
@@ -245,7 +247,7 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
       int dyn_next = 0, dyn_end = 0;  // current chunk of the dynamic part
       for (int it = 0; dyn || it < n_items; ++it) {
         int blk = blk0 + it;
-        if (ordered) blk = dist.block_order[it < n_run ? blk0 + it : n_first + blockIdx.x + (it - n_run) * gridDim.x];
+        if (split) blk = dist.block_order[it < n_run ? blk0 + it : n_first + blockIdx.x + (it - n_run) * gridDim.x];
         if (dyn && it >= n_items) {
           if (dyn_next == dyn_end) {
             dyn_next = dyn_base + static_cast<int>(atomicAdd(sched.work, static_cast<unsigned>(sched.chunk)));
@@ -265,7 +267,8 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
           }
           blk = dyn_next++;
         }
-        if (halo_pending && (ordered ? it >= n_run : dist.ghost_blocks[blk] != 0)) {
+        if (ordered && dyn) blk = dist.block_order[blk];  // position in the interior-first list -> block
+        if (halo_pending && (split ? it >= n_run : dist.ghost_blocks[blk] != 0)) {
           dist_halo_wait(dist);
           halo_pending = false;
         }
@@ -307,6 +310,15 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
     // ---- consumers ----
     const int lane = t & 31, warp = t >> 5;
     const int row_in_blk = t / LPR, q = t % LPR;
+    if constexpr (!FUSED) {
+      if (dist.amode) {
+        // this kernel sends the halo of its own operand: the CTAs whose chunk of x holds a halo row store it into the
+        // neighbours' ghost segments now; the NVLink round trip runs beside the interior blocks of every rank
+        const int per = ((rows + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x) + 1023) & ~1023;
+        const int lo = min(rows, static_cast<int>(blockIdx.x) * per);
+        dist_halo_push_impl<T, false, SPMV_CONSUMERS>(dist, x, nullptr, lo, min(rows, lo + per), per);
+      }
+    }
     bool halo_pending = FUSED && dist.world > 1;
     for (int it = 0; dyn || it < n_items; ++it) {
       const int stage = (ring0 + it) % SPMV_STAGES;

@@ -40,7 +40,8 @@ def plan_host(rank: int, world: int, row_offsets, indices_global: np.ndarray, gh
     lib = _lib.load()
     ro = np.ascontiguousarray(row_offsets, dtype=np.int64)
     idx = np.ascontiguousarray(indices_global, dtype=np.int32).copy()
-    ghosts = np.empty(max(1, idx.shape[0]), np.int32)
+    # (a dense owner contributes all of its rows, at most twice the ghosts actually referenced)
+    ghosts = np.empty(max(1, min(2 * idx.shape[0], int(ro[-1]))), np.int32)
     n_ghost = C.c_int64()
     owner = np.zeros(world + 1, np.int32)
     _lib.check(lib.qdsp_dist_plan_host(rank, world, ro.ctypes.data, idx.ctypes.data, idx.shape[0], int(ghost_base),

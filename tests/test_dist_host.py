@@ -137,3 +137,16 @@ def test_exchange_protocol_gloo(tmp_path, world):
     env = dict(os.environ, OMP_NUM_THREADS="1")
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=240, env=env, cwd=ROOT)
     assert r.returncode == 0 and f"DIST_HOST_OK {world}" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+def test_plan_host_dense_owner():
+    """A rank that reads at least half of an owner's rows takes the whole slice (one contiguous send run for the
+    owner); a sparsely read owner keeps its exact ghost list."""
+    ro = np.array([0, 4, 12, 20])
+    # rank 0 reads columns 5, 6, 8, 11 of rank 1 (4 of 8 rows: dense) and column 13 of rank 2 (1 of 8: sparse)
+    cols = np.array([0, 5, 6, 2, 8, 11, 13, 3], np.int32)
+    idx, ghosts, owner = qdist.plan_host(0, 3, ro, cols)
+    assert ghosts.tolist() == list(range(4, 12)) + [13]
+    assert owner.tolist() == [0, 0, 8, 9]
+    back = np.where(idx < 4, idx, ghosts[np.maximum(idx - 4, 0)])
+    assert back.tolist() == cols.tolist()
