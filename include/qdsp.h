@@ -247,6 +247,43 @@ int qdsp_builder_append(qdsp_builder_t b, const int32_t *row, const int32_t *col
 int qdsp_builder_append_elements(qdsp_builder_t b, const int32_t *nodes, const void *mats, int64_t n_elems, int k,
                                  void *stream);
 
+/* ---- SparseSolver (quadrants/program/sparse_solver.h:22-136) ---------------------------------------------------------
+ * make_cusparse_solver (sparse_solver.cpp:548-558) + CuSparseSolver.  solver_type: 0 "LLT", 1 "LDLT", 2 "LU";
+ * ordering: 0 "AMD", 1 "COLAMD" -- both select the same symmetric minimum-degree ordering of A + A^T, as the reference's
+ * arch=cuda path does (it ignores the argument and calls csrsymamdHost, sparse_solver.cpp:200).  dtype: f32 or f64 (the
+ * reference's cuSOLVER path is f32 only).  LLT / LDLT read the lower triangle of the matrix (Eigen::Lower,
+ * sparse_solver.h:9-13); LU factorises without row exchanges on the symmetrised pattern (the reference pivots). */
+typedef struct qdsp_solver_s *qdsp_solver_t;
+int qdsp_solver_create(int dtype, int solver_type, int ordering, qdsp_solver_t *out);
+/* analyze_pattern (sparse_solver.cpp:233-288): ordering + symbolic factorisation on the host, like the reference's
+ * reorder() (:169-231); uploads the factor pattern.  Synchronises `stream`. */
+int qdsp_solver_analyze_pattern(qdsp_solver_t s, qdsp_csr_t m, void *stream);
+/* factorize (sparse_solver.cpp:290-364): numeric factorisation on the device in one launch.  *success = 0 when a pivot
+ * is zero (LLT: not positive) -- the reference asserts singularity == -1 (:326-327, :359-360); *zero_pivot then holds the
+ * first failing pivot in the permuted numbering (the csrcholZeroPivot convention), else -1.  Synchronises `stream`. */
+int qdsp_solver_factorize(qdsp_solver_t s, qdsp_csr_t m, void *stream, int *success, int *zero_pivot);
+/* solve_rf (sparse_solver.cpp:366-476): x = A^-1 b, device vectors of n elements (permutation, both triangular solves
+ * and the inverse permutation on the device; the reference's LU branch round-trips through the host). */
+int qdsp_solver_solve(qdsp_solver_t s, const void *b, void *x, void *stream);
+/* The same through host buffers: EigenSparseSolver::solve(b) as the Python layer calls it with numpy arrays
+ * (python/quadrants/linalg/sparse_solver.py:103-106). */
+int qdsp_solver_solve_host(qdsp_solver_t s, const void *b_host, void *x_host, void *stream);
+/* info (sparse_solver.cpp:120-123): 1 after a successful factorisation.  (QD_NOT_IMPLEMENTED on the reference's
+ * arch=cuda path, sparse_solver.h:120-122.) */
+int qdsp_solver_info(qdsp_solver_t s, int *success);
+/* Size of the analysed factor: entries of L including the diagonal, height of the elimination tree (the length of the
+ * dependency chain the device kernels walk), and sum over columns of (column length)^2 ~ multiply-adds of the
+ * factorisation. */
+int qdsp_solver_stats(qdsp_solver_t s, int64_t *factor_nnz, int *etree_height, double *flops);
+int qdsp_solver_destroy(qdsp_solver_t s);
+/* Pure host helper (no CUDA needed) behind qdsp_solver_analyze_pattern, exposed so that the ordering and the symbolic
+ * factorisation are testable without a GPU.  perm_out[new] = old (n); parent_out: elimination tree (n, -1 = root);
+ * colptr_out (n + 1) / rowidx_out (up to rowidx_capacity, may be NULL): the factor pattern by columns, rows ascending,
+ * diagonal first.  natural_order != 0 skips the ordering (identity permutation). */
+int qdsp_solver_analyze_host(int n, const int32_t *indptr, const int32_t *indices, int natural_order, int32_t *perm_out,
+                             int32_t *parent_out, int32_t *colptr_out, int32_t *rowidx_out, int64_t rowidx_capacity,
+                             int64_t *factor_nnz, int *etree_height);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -80,6 +80,22 @@ class Oracle:
         L.qdo_stable_sort_u64.argtypes = [_VOIDP, _VOIDP, C.c_int64]
         L.qdo_inclusive_scan_i32.restype = None
         L.qdo_inclusive_scan_i32.argtypes = [_VOIDP, C.c_int64]
+        for name in ("f32", "f64"):
+            getattr(L, f"qdo_direct_{name}").restype = C.c_int
+            getattr(L, f"qdo_direct_{name}").argtypes = [C.c_int, _VOIDP, _VOIDP, _VOIDP, C.c_int, _VOIDP, _VOIDP]
+
+    # -- A16 ------------------------------------------------------------------------------------------------------
+    def direct_solve(self, indptr, indices, vals, b, ldlt=False):
+        """Simplicial LLT / LDLT of the LOWER triangle of a CSR matrix + solve (small systems: dense workspace).
+        Returns (x, ok)."""
+        indptr, indices = (np.ascontiguousarray(a, dtype=np.int32) for a in (indptr, indices))
+        vals = np.ascontiguousarray(vals)
+        name = "f64" if vals.dtype == np.float64 else "f32"
+        b = np.ascontiguousarray(b, dtype=vals.dtype)
+        x = np.zeros_like(b)
+        rc = getattr(self.lib, f"qdo_direct_{name}")(indptr.shape[0] - 1, indptr.ctypes.data, indices.ctypes.data,
+                                                     vals.ctypes.data, int(ldlt), b.ctypes.data, x.ctypes.data)
+        return x, rc == 0
 
     # -- A3 -------------------------------------------------------------------------------------------------------
     def build_matrix(self, buf: np.ndarray, rows: int, cols: int, row_major: bool = True):
@@ -289,6 +305,9 @@ class EigenRef:
         L.ref_cg_solve.restype = C.c_int
         L.ref_cg_solve.argtypes = [_VOIDP, _VOIDP, _VOIDP, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_int),
                                    C.POINTER(C.c_double)]
+        if hasattr(L, "ref_direct_solve"):
+            L.ref_direct_solve.restype = C.c_int
+            L.ref_direct_solve.argtypes = [_VOIDP, C.c_int, C.c_int, _VOIDP, _VOIDP]
         L.ref_num_threads.restype = C.c_int
         L.ref_set_num_threads.argtypes = [C.c_int]
         L.ref_eigen_version.restype = C.c_char_p
@@ -350,6 +369,16 @@ class EigenRef:
             if info < 0:
                 raise RuntimeError("SparseCG accepts col_major matrices only (conjugate_gradient.h:40)")
             return x, info == 0, it.value, err.value
+
+        def direct_solve(self, b, solver_type="LLT", ordering="AMD"):
+            """EigenSparseSolver analyze_pattern + factorize + solve (sparse_solver.cpp:86-107).  Returns (x, ok)."""
+            b = np.ascontiguousarray(b, dtype=self.dtype)
+            x = np.zeros(self.cols, self.dtype)
+            info = self.ref.lib.ref_direct_solve(self.h, {"LLT": 0, "LDLT": 1, "LU": 2}[solver_type],
+                                                 {"AMD": 0, "COLAMD": 1}[ordering], b.ctypes.data, x.ctypes.data)
+            if info == -1:
+                raise RuntimeError("the direct solvers are declared on col_major matrices (sparse_solver.h:9-20)")
+            return x, info == 0
 
     def matrix(self, buf, rows, cols, row_major=True):
         return EigenRef.Matrix(self, buf, rows, cols, row_major)

@@ -12,6 +12,9 @@
 //   cg    : CG<EigenT,DT>::solve     (quadrants/program/conjugate_gradient.h:36-49)
 //           Eigen::ConjugateGradient<SparseMatrix<DT>, Lower|Upper>, setMaxIterations, setTolerance,
 //           compute, solve, iterations(), error(), info()
+//   direct: EigenSparseSolver<...>::analyze_pattern / factorize / solve / info  (quadrants/program/sparse_solver.cpp:74-123)
+//           with the twelve solver types of sparse_solver.h:9-20,60-71: Simplicial{LLT,LDLT}<SparseMatrix<dt>, Lower,
+//           {AMD,COLAMD}Ordering<int>> and SparseLU<SparseMatrix<dt>, {AMD,COLAMD}Ordering<int>>
 // The full Quadrants package cannot be built here (LLVM 22, nanobind, spdlog,
 // dlpack, SPIRV-Cross are absent), which is why the calls are restated rather
 // than linked.  Built by oracle/Makefile into oracle/_ref/ (git-ignored) with
@@ -26,6 +29,9 @@
 
 #include "Eigen/Sparse"
 #include "Eigen/IterativeLinearSolvers"
+#include "Eigen/SparseCholesky"
+#include "Eigen/SparseLU"
+#include "Eigen/OrderingMethods"
 
 #define REF_API extern "C" __attribute__((visibility("default")))
 
@@ -180,6 +186,48 @@ REF_API int ref_cg_solve(void *h, const void *b, void *x, int max_iters, double 
     std::memcpy(x, x_.data(), sizeof(double) * m->cols);
   }
   return info;
+}
+
+namespace {
+// analyzePattern + factorize + solve + info, exactly the member calls of EigenSparseSolver (sparse_solver.cpp:86-123)
+template <typename Solver, typename M, typename V>
+int direct_solve(const M &mat, const V &b, V &x, double *factor_ms) {
+  Solver solver;
+  solver.analyzePattern(mat);
+  solver.factorize(mat);
+  if (solver.info() != Eigen::Success) return static_cast<int>(solver.info());
+  x = solver.solve(b);
+  (void)factor_ms;
+  return static_cast<int>(solver.info());
+}
+template <typename T>
+int direct_dispatch(const Eigen::SparseMatrix<T> &mat, int type, int ordering, const T *b, T *x, int n) {
+  using M = Eigen::SparseMatrix<T>;
+  using V = Eigen::Matrix<T, Eigen::Dynamic, 1>;
+  V bv = Eigen::Map<const V>(b, n), xv;
+  int info = -1;
+  const int key = type * 2 + ordering;
+  switch (key) {
+    case 0: info = direct_solve<Eigen::SimplicialLLT<M, Eigen::Lower, Eigen::AMDOrdering<int>>>(mat, bv, xv, nullptr); break;
+    case 1: info = direct_solve<Eigen::SimplicialLLT<M, Eigen::Lower, Eigen::COLAMDOrdering<int>>>(mat, bv, xv, nullptr); break;
+    case 2: info = direct_solve<Eigen::SimplicialLDLT<M, Eigen::Lower, Eigen::AMDOrdering<int>>>(mat, bv, xv, nullptr); break;
+    case 3: info = direct_solve<Eigen::SimplicialLDLT<M, Eigen::Lower, Eigen::COLAMDOrdering<int>>>(mat, bv, xv, nullptr); break;
+    case 4: info = direct_solve<Eigen::SparseLU<M, Eigen::AMDOrdering<int>>>(mat, bv, xv, nullptr); break;
+    case 5: info = direct_solve<Eigen::SparseLU<M, Eigen::COLAMDOrdering<int>>>(mat, bv, xv, nullptr); break;
+    default: return -2;
+  }
+  if (info == 0) std::memcpy(x, xv.data(), sizeof(T) * n);
+  return info;
+}
+}  // namespace
+
+// type: 0 LLT, 1 LDLT, 2 LU; ordering: 0 AMD, 1 COLAMD.  The matrix must be col-major (the solvers are declared on
+// Eigen::SparseMatrix<dt>, sparse_solver.h:9-20).  Returns Eigen's info() (0 = Success), -1 for a row-major handle.
+REF_API int ref_direct_solve(void *h, int type, int ordering, const void *b, void *x) {
+  auto *m = static_cast<RefMatrix *>(h);
+  if (m->row_major) return -1;
+  if (!m->f64) return direct_dispatch<float>(m->fc, type, ordering, static_cast<const float *>(b), static_cast<float *>(x), m->rows);
+  return direct_dispatch<double>(m->dc, type, ordering, static_cast<const double *>(b), static_cast<double *>(x), m->rows);
 }
 
 REF_API int ref_num_threads(void) { return Eigen::nbThreads(); }

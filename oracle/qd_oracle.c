@@ -487,3 +487,69 @@ QDO_API double qdo_csr_get_f32(const int32_t *outer, const int32_t *inner, const
     if (inner[k] == c) return vals[k];
   return 0.0;
 }
+
+/* ------------------------------------------------------------------------- */
+/* Direct solve.  Restates Eigen's simplicial Cholesky, the  */
+/* solver behind EigenSparseSolver<SimplicialLLT/LDLT<.., Lower, ..>>          */
+/* (quadrants/program/sparse_solver.h:9-13, sparse_solver.cpp:86-107;          */
+/* Eigen/src/SparseCholesky/SimplicialCholesky_impl.h:284-383): elimination    */
+/* tree, then row-by-row ("up-looking") factorisation -- row k of L is the     */
+/* solution of a sparse triangular system whose pattern is the tree paths from */
+/* the entries of A(0:k, k) -- followed by L y = b, D, L^T x = y.  Only the     */
+/* LOWER triangle of A (given in CSR) is read.  Natural ordering: the fill-     */
+/* reducing permutation changes rounding, not the solution, and the GPU path    */
+/* is compared with a tolerance.  ldlt != 0: unit L and D; else L L^T.         */
+/* Returns 0, or 1 + k when pivot k is zero (LDLT) / not positive (LLT).        */
+/* Dense O(n^2) workspace: small systems only (test infrastructure).           */
+/* ------------------------------------------------------------------------- */
+#define QDO_DIRECT(NAME, VAL_T, SQRT)                                                              \
+  QDO_API int NAME(int n, const int32_t *outer, const int32_t *inner, const VAL_T *vals, int ldlt, \
+                   const VAL_T *b, VAL_T *x) {                                                     \
+    VAL_T *L = (VAL_T *)calloc((size_t)n * n, sizeof(VAL_T)); /* row-major dense lower factor */   \
+    VAL_T *D = (VAL_T *)calloc((size_t)n, sizeof(VAL_T));                                          \
+    VAL_T *y = (VAL_T *)calloc((size_t)n, sizeof(VAL_T));                                          \
+    int rc = 0;                                                                                    \
+    for (int k = 0; k < n && rc == 0; ++k) {                                                       \
+      /* scatter row k of the lower triangle (== column k of the upper one) */                     \
+      for (int i = 0; i <= k; ++i) y[i] = (VAL_T)0;                                                \
+      for (int32_t p = outer[k]; p < outer[k + 1]; ++p)                                            \
+        if (inner[p] <= k) y[inner[p]] += vals[p];                                                 \
+      VAL_T d = y[k];                                                                              \
+      /* ascending i is a topological order of the row subtree */                                  \
+      for (int i = 0; i < k; ++i) {                                                                \
+        VAL_T yi = y[i];                                                                           \
+        VAL_T lki;                                                                                 \
+        if (ldlt) lki = yi / D[i];                                                                 \
+        else { lki = yi / L[(size_t)i * n + i]; yi = lki; }                                        \
+        for (int r = i + 1; r < k; ++r) y[r] -= L[(size_t)r * n + i] * yi;                         \
+        d -= lki * yi;                                                                             \
+        L[(size_t)k * n + i] = lki;                                                                \
+      }                                                                                            \
+      if (ldlt) {                                                                                  \
+        D[k] = d;                                                                                  \
+        L[(size_t)k * n + k] = (VAL_T)1;                                                           \
+        if (d == (VAL_T)0) rc = 1 + k;                                                             \
+      } else {                                                                                     \
+        if (!(d > (VAL_T)0)) rc = 1 + k;                                                           \
+        else L[(size_t)k * n + k] = SQRT(d);                                                       \
+      }                                                                                            \
+    }                                                                                              \
+    if (rc == 0) {                                                                                 \
+      for (int i = 0; i < n; ++i) {                                                                \
+        VAL_T s = b[i];                                                                            \
+        for (int j = 0; j < i; ++j) s -= L[(size_t)i * n + j] * x[j];                              \
+        x[i] = s / L[(size_t)i * n + i];                                                           \
+      }                                                                                            \
+      if (ldlt)                                                                                    \
+        for (int i = 0; i < n; ++i) x[i] /= D[i];                                                  \
+      for (int i = n - 1; i >= 0; --i) {                                                           \
+        VAL_T s = x[i];                                                                            \
+        for (int j = i + 1; j < n; ++j) s -= L[(size_t)j * n + i] * x[j];                          \
+        x[i] = s / L[(size_t)i * n + i];                                                           \
+      }                                                                                            \
+    }                                                                                              \
+    free(L); free(D); free(y);                                                                     \
+    return rc;                                                                                     \
+  }
+QDO_DIRECT(qdo_direct_f32, float, sqrtf)
+QDO_DIRECT(qdo_direct_f64, double, sqrt)

@@ -384,3 +384,90 @@ def make_double_cg_solver(A, max_iters, tol, verbose):
 
 def make_cu_sparse_matrix(rows, cols, dt):
     return CuSparseMatrix(rows, cols, dt)
+
+
+class CuSparseSolver:
+    """CuSparseSolver (export_lang.cpp make_cusparse_solver; quadrants/program/sparse_solver.h:81-136) over solver.cu:
+    host minimum-degree ordering + symbolic analysis, numeric factorisation and both triangular solves on the device."""
+
+    def __init__(self, dt, solver_type, ordering):
+        if solver_type not in _lib.SOLVER_TYPES:
+            raise QuadrantsRuntimeError(f"Not supported sparse solver type: {solver_type}")
+        self._lib = _lib.load()
+        self._dt = to_dtype(dt)
+        self._h = C.c_void_p()
+        self._A = None
+        _lib.check(self._lib.qdsp_solver_create(_dt(dt), _lib.SOLVER_TYPES[solver_type],
+                                                _lib.SOLVER_ORDERINGS.get(ordering, 0), C.byref(self._h)))
+
+    def __del__(self):
+        try:
+            if self._h.value:
+                self._lib.qdsp_solver_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    def analyze_pattern(self, sm):
+        self._A = sm
+        _lib.check(self._lib.qdsp_solver_analyze_pattern(self._h, sm._need(), _stream()))
+
+    def factorize(self, sm):
+        ok, piv = C.c_int(), C.c_int()
+        _lib.check(self._lib.qdsp_solver_factorize(self._h, sm._need(), _stream(), C.byref(ok), C.byref(piv)))
+        if not ok.value:
+            # the reference: QD_ASSERT(singularity == -1) after csrcholZeroPivot / csrluZeroPivotHost
+            # (sparse_solver.cpp:326-327, 359-360)
+            raise QuadrantsRuntimeError(f"SparseSolver factorisation failed: zero pivot at (permuted) index {piv.value}")
+
+    def compute(self, sm):
+        self.analyze_pattern(sm)
+        self.factorize(sm)
+        return self.info()
+
+    def solve_rf(self, prog, sm, b, x):
+        _lib.check(self._lib.qdsp_solver_solve(self._h, b.data_ptr(), x.data_ptr(), _stream(prog)))
+
+    def solve(self, b: np.ndarray) -> np.ndarray:
+        """EigenSparseSolver::solve(b) with a numpy right-hand side (export_lang.cpp solve overloads)."""
+        npdt = np.float64 if self._dt is f64 else np.float32
+        bb = np.ascontiguousarray(b, dtype=npdt)
+        x = np.empty_like(bb)
+        _lib.check(self._lib.qdsp_solver_solve_host(self._h, bb.ctypes.data, x.ctypes.data, _stream()))
+        return x
+
+    def info(self) -> bool:
+        ok = C.c_int()
+        _lib.check(self._lib.qdsp_solver_info(self._h, C.byref(ok)))
+        return bool(ok.value)
+
+    def stats(self):
+        nnz, h, fl = C.c_int64(), C.c_int(), C.c_double()
+        _lib.check(self._lib.qdsp_solver_stats(self._h, C.byref(nnz), C.byref(h), C.byref(fl)))
+        return {"factor_nnz": nnz.value, "etree_height": h.value, "flops": fl.value}
+
+
+def make_cusparse_solver(dt, solver_type, ordering):
+    return CuSparseSolver(dt, solver_type, ordering)
+
+
+make_sparse_solver = make_cusparse_solver  # the arch=x64 factory name; there is one (device) implementation here
+
+
+def solver_analyze_host(indptr, indices, natural_order=False):
+    """Pure host: ordering + symbolic factorisation of a square CSR pattern (no GPU needed).  Returns a dict with perm
+    (new -> old), parent (elimination tree), colptr / rowidx (factor pattern by columns) and etree_height."""
+    lib = _lib.load()
+    ip = np.ascontiguousarray(indptr, dtype=np.int32)
+    ix = np.ascontiguousarray(indices, dtype=np.int32)
+    n = ip.shape[0] - 1
+    perm, parent, colptr = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(n + 1, np.int32)
+    nnz, h = C.c_int64(), C.c_int()
+    _lib.check(lib.qdsp_solver_analyze_host(n, ip.ctypes.data, ix.ctypes.data, int(natural_order), perm.ctypes.data,
+                                            parent.ctypes.data, colptr.ctypes.data, None, 0, C.byref(nnz), C.byref(h)))
+    rowidx = np.empty(nnz.value, np.int32)
+    _lib.check(lib.qdsp_solver_analyze_host(n, ip.ctypes.data, ix.ctypes.data, int(natural_order), perm.ctypes.data,
+                                            parent.ctypes.data, colptr.ctypes.data, rowidx.ctypes.data, nnz.value,
+                                            C.byref(nnz), C.byref(h)))
+    return {"perm": perm, "parent": parent, "colptr": colptr, "rowidx": rowidx, "factor_nnz": nnz.value,
+            "etree_height": h.value}

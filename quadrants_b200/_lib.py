@@ -19,6 +19,8 @@ ELEM_I32, ELEM_U32, ELEM_F32, ELEM_I64, ELEM_U64, ELEM_F64 = 0, 1, 2, 3, 4, 5  #
 OP_ADD, OP_MIN, OP_MAX = 0, 1, 2  # qdsp_reduce_op
 ALGO_REDUCE, ALGO_SCAN, ALGO_SELECT, ALGO_REDUCE_BY_KEY, ALGO_SORT = 0, 1, 2, 3, 4  # qdsp_algo
 CG_EIGEN_JACOBI, CG_CUCG = 0, 1
+SOLVER_TYPES = {"LLT": 0, "LDLT": 1, "LU": 2}
+SOLVER_ORDERINGS = {"AMD": 0, "COLAMD": 1}
 
 _vp, _i, _i64, _sz, _d = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_double
 _P = C.POINTER
@@ -81,6 +83,15 @@ SIGNATURES = {
     "qdsp_sort": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "qdsp_builder_append": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
     "qdsp_builder_append_elements": (_i, [_vp, _vp, _vp, _i64, _i, _vp]),
+    "qdsp_solver_create": (_i, [_i, _i, _i, _P(_vp)]),
+    "qdsp_solver_analyze_pattern": (_i, [_vp, _vp, _vp]),
+    "qdsp_solver_factorize": (_i, [_vp, _vp, _vp, _P(_i), _P(_i)]),
+    "qdsp_solver_solve": (_i, [_vp, _vp, _vp, _vp]),
+    "qdsp_solver_solve_host": (_i, [_vp, _vp, _vp, _vp]),
+    "qdsp_solver_info": (_i, [_vp, _P(_i)]),
+    "qdsp_solver_stats": (_i, [_vp, _P(_i64), _P(_i), _P(_d)]),
+    "qdsp_solver_destroy": (_i, [_vp]),
+    "qdsp_solver_analyze_host": (_i, [_i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i64, _P(_i64), _P(_i)]),
 }
 
 _lib = None

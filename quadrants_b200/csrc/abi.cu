@@ -6,6 +6,7 @@
 
 #include "dist.hpp"
 #include "host.hpp"
+#include "solver.hpp"
 
 using namespace qdsp;
 
@@ -13,6 +14,7 @@ struct qdsp_builder_s { std::unique_ptr<Builder> impl; };
 struct qdsp_csr_s { std::unique_ptr<CsrMatrix> impl; };
 struct qdsp_cg_s { std::unique_ptr<CgSolver> impl; qdsp_csr_s *matrix; };
 struct qdsp_dist_s { std::unique_ptr<DistContext> impl; };
+struct qdsp_solver_s { std::unique_ptr<DirectSolver> impl; };
 
 namespace {
 thread_local std::string g_last_error;
@@ -370,6 +372,76 @@ int qdsp_builder_append(qdsp_builder_t b, const int32_t *row, const int32_t *col
 int qdsp_builder_append_elements(qdsp_builder_t b, const int32_t *nodes, const void *mats, int64_t n_elems, int k,
                                  void *stream) {
   return guarded([&] { NOT_NULL(b); b->impl->append_elements(nodes, mats, n_elems, k, S(stream)); });
+}
+
+// ---- SparseSolver (solver.cu) ---------------------------------------------------------------------------------------------------
+int qdsp_solver_create(int dtype, int solver_type, int ordering, qdsp_solver_t *out) {
+  return guarded([&] {
+    NOT_NULL(out);
+    auto *h = new qdsp_solver_s();
+    try {
+      h->impl = std::make_unique<DirectSolver>(dtype, solver_type, ordering);
+    } catch (...) {
+      delete h;
+      throw;
+    }
+    *out = h;
+  });
+}
+int qdsp_solver_analyze_pattern(qdsp_solver_t s, qdsp_csr_t m, void *stream) {
+  return guarded([&] { NOT_NULL(s); NOT_NULL(m); s->impl->analyze_pattern(*m->impl, S(stream)); });
+}
+int qdsp_solver_factorize(qdsp_solver_t s, qdsp_csr_t m, void *stream, int *success, int *zero_pivot) {
+  return guarded([&] {
+    NOT_NULL(s); NOT_NULL(m);
+    s->impl->factorize(*m->impl, S(stream));
+    if (success) *success = s->impl->info() ? 1 : 0;
+    if (zero_pivot) *zero_pivot = s->impl->zero_pivot();
+  });
+}
+int qdsp_solver_solve(qdsp_solver_t s, const void *b, void *x, void *stream) {
+  return guarded([&] { NOT_NULL(s); s->impl->solve(b, x, S(stream)); });
+}
+int qdsp_solver_solve_host(qdsp_solver_t s, const void *b_host, void *x_host, void *stream) {
+  return guarded([&] { NOT_NULL(s); s->impl->solve_host(b_host, x_host, S(stream)); });
+}
+int qdsp_solver_info(qdsp_solver_t s, int *success) {
+  return guarded([&] { NOT_NULL(s); NOT_NULL(success); *success = s->impl->info() ? 1 : 0; });
+}
+int qdsp_solver_stats(qdsp_solver_t s, int64_t *factor_nnz, int *etree_height, double *flops) {
+  return guarded([&] {
+    NOT_NULL(s);
+    const SymbolicFactor &f = s->impl->symbolic();
+    if (factor_nnz) *factor_nnz = f.factor_nnz;
+    if (etree_height) *etree_height = f.height;
+    if (flops) *flops = f.flops;
+  });
+}
+int qdsp_solver_destroy(qdsp_solver_t s) {
+  return guarded([&] { delete s; });
+}
+int qdsp_solver_analyze_host(int n, const int32_t *indptr, const int32_t *indices, int natural_order, int32_t *perm_out,
+                             int32_t *parent_out, int32_t *colptr_out, int32_t *rowidx_out, int64_t rowidx_capacity,
+                             int64_t *factor_nnz, int *etree_height) {
+  return guarded([&] {
+    NOT_NULL(indptr);
+    QDSP_REQUIRE(n >= 0, QDSP_ERR_INVALID, "solver analyse: negative size");
+    QDSP_REQUIRE(indices != nullptr || indptr[n] == 0, QDSP_ERR_INVALID, "solver analyse: null indices");
+    std::vector<int32_t> perm(n);
+    if (natural_order) for (int i = 0; i < n; ++i) perm[i] = i;
+    else solver_order_host(n, indptr, indices, perm);
+    SymbolicFactor f;
+    solver_symbolic_host(n, indptr, indices, perm, f);
+    if (perm_out) std::memcpy(perm_out, f.perm.data(), sizeof(int32_t) * n);
+    if (parent_out) std::memcpy(parent_out, f.parent.data(), sizeof(int32_t) * n);
+    if (colptr_out) std::memcpy(colptr_out, f.colptr.data(), sizeof(int32_t) * (n + 1));
+    if (rowidx_out) {
+      QDSP_REQUIRE(rowidx_capacity >= f.factor_nnz, QDSP_ERR_INVALID, "solver analyse: rowidx_capacity too small");
+      std::memcpy(rowidx_out, f.rowidx.data(), sizeof(int32_t) * f.factor_nnz);
+    }
+    if (factor_nnz) *factor_nnz = f.factor_nnz;
+    if (etree_height) *etree_height = f.height;
+  });
 }
 
 }  // extern "C"

@@ -1,0 +1,644 @@
+// solver.cu -- sparse direct solver on the device: LLT / LDLT / LU behind qd.linalg.SparseSolver.
+//
+// Replaces CuSparseSolver (quadrants/program/sparse_solver.cpp:149-476).  The reference's arch=cuda path is: D2H the CSR,
+// csrsymamdHost + csrpermHost on the host (:169-231), then cuSOLVER's low-level csrchol{Analysis,Factor,Solve} on the
+// device for LLT/LDLT (:245-265, :302-331, :379-430) -- and for LU everything on the HOST (csrlu*Host, :267-288,
+// :333-364, :432-476), fp32 only.  Here:
+//
+//   analyze_pattern  host: approximate-minimum-degree ordering of A + A^T, elimination tree, factor pattern in CSC with a
+//                    row index on top (SymbolicFactor); device: the pattern and the A -> factor slot map.
+//   factorize        device, ONE launch: left-looking, one warp per column, columns claimed in ascending order from an
+//                    atomic counter.  A column waits (ld.acquire on a per-column flag) for each column it depends on in
+//                    ascending order, subtracts that column's contribution, then scales and publishes itself
+//                    (st.release).  Ascending claims make the wait deadlock-free: the lowest unfinished column never
+//                    waits, and only running warps hold claims.  The dependency order is fixed, so the factor is
+//                    bit-reproducible run to run (no atomics on values).
+//                    Where the tail of a dependency column has the same pattern as the target column (chains of the
+//                    elimination tree / supernodes -- most of the arithmetic), slots map 1:1 and the update is a
+//                    coalesced axpy; otherwise a binary search in the target's sorted rows.
+//                    LU: static (diagonal) pivoting on the symmetrised pattern, L unit-lower by columns, U by rows in the
+//                    same slots -- no partial pivoting (the reference's Eigen SparseLU and csrluHost pivot; a zero pivot
+//                    here is reported through info()).  Enough for the SPD / diagonally dominant systems the reference
+//                    tests (tests/python/test_sparse_linear_solver.py:17-177).
+//   solve            device, two launches: synchronisation-free triangular solves, one warp per row, the same flag
+//                    protocol (forward ascending, backward descending), permutation folded into the first load and the
+//                    last store.  Fixed summation order.
+// Bound: latency of the dependency chain (elimination-tree height x one flag round trip), not HBM; the factor lives in L2
+// for every size a direct solver is used at.  No cuSOLVER / cuSPARSE.
+#include <algorithm>
+#include <climits>
+#include <cstring>
+#include <numeric>
+
+#include "solver.hpp"
+
+namespace qdsp {
+
+// =====================================================================================================================
+// host analysis
+// =====================================================================================================================
+namespace {
+
+// adjacency of A + A^T without the diagonal, sorted, duplicates removed
+void symmetric_adjacency(int n, const int32_t *ip, const int32_t *ix, std::vector<int32_t> &ptr, std::vector<int32_t> &adj) {
+  std::vector<int64_t> cnt(n + 1, 0);
+  for (int r = 0; r < n; ++r)
+    for (int q = ip[r]; q < ip[r + 1]; ++q) {
+      const int c = ix[q];
+      QDSP_REQUIRE(c >= 0 && c < n, QDSP_ERR_INVALID, "solver: column index out of range");
+      if (c != r) { ++cnt[r + 1]; ++cnt[c + 1]; }
+    }
+  for (int i = 0; i < n; ++i) cnt[i + 1] += cnt[i];
+  QDSP_REQUIRE(cnt[n] < INT_MAX, QDSP_ERR_INVALID, "solver: pattern too large");
+  std::vector<int32_t> tmp(static_cast<size_t>(cnt[n]));
+  std::vector<int64_t> next(cnt.begin(), cnt.end() - 1);
+  for (int r = 0; r < n; ++r)
+    for (int q = ip[r]; q < ip[r + 1]; ++q) {
+      const int c = ix[q];
+      if (c != r) { tmp[next[r]++] = c; tmp[next[c]++] = r; }
+    }
+  ptr.assign(n + 1, 0);
+  adj.clear();
+  adj.reserve(tmp.size());
+  for (int i = 0; i < n; ++i) {
+    auto b = tmp.begin() + cnt[i], e = tmp.begin() + cnt[i + 1];
+    std::sort(b, e);
+    e = std::unique(b, e);
+    adj.insert(adj.end(), b, e);
+    ptr[i + 1] = static_cast<int32_t>(adj.size());
+  }
+}
+
+// degree buckets: doubly linked lists
+struct Buckets {
+  std::vector<int32_t> head, next, prev;
+  explicit Buckets(int n) : head(n + 1, -1), next(n, -1), prev(n, -1) {}
+  void insert(int i, int d) {
+    next[i] = head[d];
+    prev[i] = -1;
+    if (head[d] >= 0) prev[head[d]] = i;
+    head[d] = i;
+  }
+  void remove(int i, int d) {
+    if (prev[i] >= 0) next[prev[i]] = next[i];
+    else head[d] = next[i];
+    if (next[i] >= 0) prev[next[i]] = prev[i];
+  }
+};
+
+}  // namespace
+
+void solver_order_host(int n, const int32_t *indptr, const int32_t *indices, std::vector<int32_t> &perm) {
+  perm.assign(n, 0);
+  if (n == 0) return;
+  std::vector<int32_t> aptr, aadj;
+  symmetric_adjacency(n, indptr, indices, aptr, aadj);
+  // quotient graph: a live variable i has variable neighbours adjv[i] and element neighbours adje[i]; an element e (named
+  // by its pivot) has the variable list elem[e].  state: 0 variable, 1 live element, 2 absorbed element.
+  std::vector<std::vector<int32_t>> adjv(n), adje(n), elem(n);
+  std::vector<int32_t> deg(n), mark(n, -1);
+  std::vector<uint8_t> state(n, 0);
+  std::vector<int64_t> w(n, 0);
+  int64_t wflg = 1;
+  Buckets bk(n);
+  for (int i = 0; i < n; ++i) {
+    adjv[i].assign(aadj.begin() + aptr[i], aadj.begin() + aptr[i + 1]);
+    deg[i] = static_cast<int32_t>(adjv[i].size());
+  }
+  for (int i = n - 1; i >= 0; --i) bk.insert(i, deg[i]);  // ties: lowest index first
+  std::vector<int32_t>().swap(aadj);
+  int mindeg = 0;
+  std::vector<int32_t> lp, keep;
+  for (int step = 0; step < n; ++step) {
+    while (bk.head[mindeg] < 0) ++mindeg;
+    const int p = bk.head[mindeg];
+    bk.remove(p, mindeg);
+    perm[step] = p;
+    // the new element: L_p = (A_p u U_{e in E_p} L_e) \ {p}
+    lp.clear();
+    mark[p] = step;
+    for (int v : adjv[p])
+      if (state[v] == 0 && mark[v] != step) { mark[v] = step; lp.push_back(v); }
+    for (int e : adje[p])
+      if (state[e] == 1) {
+        for (int v : elem[e])
+          if (state[v] == 0 && mark[v] != step) { mark[v] = step; lp.push_back(v); }
+        state[e] = 2;
+        std::vector<int32_t>().swap(elem[e]);
+      }
+    state[p] = 1;
+    std::vector<int32_t>().swap(adjv[p]);
+    std::vector<int32_t>().swap(adje[p]);
+    // w[e] - wflg = |L_e \ L_p| for every live element e that touches L_p
+    for (int i : lp)
+      for (int e : adje[i])
+        if (state[e] == 1) {
+          if (w[e] < wflg) w[e] = wflg + static_cast<int64_t>(elem[e].size());
+          --w[e];
+        }
+    const int lpn = static_cast<int>(lp.size());
+    for (int i : lp) {
+      int64_t sum = 0;
+      keep.clear();
+      for (int e : adje[i])
+        if (state[e] == 1) {
+          const int64_t ext = w[e] - wflg;
+          if (ext > 0) { sum += ext; keep.push_back(e); }
+          else { state[e] = 2; std::vector<int32_t>().swap(elem[e]); }  // aggressive absorption: L_e is inside L_p
+        }
+      keep.push_back(p);
+      adje[i].assign(keep.begin(), keep.end());
+      keep.clear();
+      for (int v : adjv[i])
+        if (state[v] == 0 && mark[v] != step) keep.push_back(v);
+      adjv[i].assign(keep.begin(), keep.end());
+      const int64_t d = std::min<int64_t>(std::min<int64_t>(n - step - 1, static_cast<int64_t>(deg[i]) + lpn - 1),
+                                          static_cast<int64_t>(adjv[i].size()) + lpn - 1 + sum);
+      bk.remove(i, deg[i]);
+      deg[i] = static_cast<int32_t>(std::max<int64_t>(d, 0));
+      bk.insert(i, deg[i]);
+      if (deg[i] < mindeg) mindeg = deg[i];
+    }
+    elem[p] = lp;
+    wflg += n + 1;
+  }
+}
+
+void solver_symbolic_host(int n, const int32_t *indptr, const int32_t *indices, const std::vector<int32_t> &perm,
+                          SymbolicFactor &out) {
+  out = SymbolicFactor();
+  out.n = n;
+  out.perm = perm;
+  out.pinv.assign(n, -1);
+  for (int i = 0; i < n; ++i) {
+    QDSP_REQUIRE(perm[i] >= 0 && perm[i] < n && out.pinv[perm[i]] < 0, QDSP_ERR_INVALID, "solver: not a permutation");
+    out.pinv[perm[i]] = i;
+  }
+  // strictly-lower adjacency of the permuted symmetric pattern: low[i] = {k < i : B(i,k) != 0}
+  std::vector<int32_t> aptr, aadj;
+  symmetric_adjacency(n, indptr, indices, aptr, aadj);
+  std::vector<int32_t> lptr(n + 1, 0), low;
+  for (int i = 0; i < n; ++i) {
+    const int o = perm[i];
+    int c = 0;
+    for (int q = aptr[o]; q < aptr[o + 1]; ++q) c += out.pinv[aadj[q]] < i;
+    lptr[i + 1] = lptr[i] + c;
+  }
+  low.resize(lptr[n]);
+  for (int i = 0; i < n; ++i) {
+    const int o = perm[i];
+    int at = lptr[i];
+    for (int q = aptr[o]; q < aptr[o + 1]; ++q) {
+      const int k = out.pinv[aadj[q]];
+      if (k < i) low[at++] = k;
+    }
+  }
+  // elimination tree (Liu, path compression)
+  out.parent.assign(n, -1);
+  {
+    std::vector<int32_t> anc(n, -1);
+    for (int i = 0; i < n; ++i)
+      for (int q = lptr[i]; q < lptr[i + 1]; ++q) {
+        int r = low[q];
+        while (r != -1 && r < i) {
+          const int nx = anc[r];
+          anc[r] = i;
+          if (nx == -1) out.parent[r] = i;
+          r = nx;
+        }
+      }
+  }
+  // row patterns by walking the tree from each B(i,k) up to the first marked node (row subtree)
+  std::vector<int32_t> mark(n, -1), colcount(n, 1);
+  out.rowptr.assign(n + 1, 0);
+  std::vector<int32_t> &rowcol = out.rowcol;
+  rowcol.clear();
+  int64_t total = n;
+  for (int i = 0; i < n; ++i) {
+    mark[i] = i;
+    const size_t start = rowcol.size();
+    for (int q = lptr[i]; q < lptr[i + 1]; ++q)
+      for (int r = low[q]; mark[r] != i; r = out.parent[r]) {
+        mark[r] = i;
+        rowcol.push_back(r);
+        ++colcount[r];
+      }
+    std::sort(rowcol.begin() + start, rowcol.end());
+    total += static_cast<int64_t>(rowcol.size() - start);
+    QDSP_REQUIRE(total < INT_MAX, QDSP_ERR_INVALID, "solver: the factor has more than 2^31 entries");
+    out.rowptr[i + 1] = static_cast<int32_t>(rowcol.size());
+  }
+  out.factor_nnz = total;
+  out.colptr.assign(n + 1, 0);
+  for (int j = 0; j < n; ++j) out.colptr[j + 1] = out.colptr[j] + colcount[j];
+  out.rowidx.assign(static_cast<size_t>(total), 0);
+  out.rowpos.assign(rowcol.size(), 0);
+  std::vector<int32_t> next(n);
+  for (int j = 0; j < n; ++j) {
+    out.rowidx[out.colptr[j]] = j;  // the diagonal leads its column
+    next[j] = out.colptr[j] + 1;
+    out.flops += static_cast<double>(colcount[j]) * colcount[j];
+  }
+  for (int i = 0; i < n; ++i)
+    for (int q = out.rowptr[i]; q < out.rowptr[i + 1]; ++q) {
+      const int k = rowcol[q];
+      out.rowpos[q] = next[k];
+      out.rowidx[next[k]++] = i;
+    }
+  std::vector<int32_t> depth(n, 1);
+  for (int j = 0; j < n; ++j) {  // parents have larger indices
+    out.height = std::max(out.height, depth[j]);
+    if (out.parent[j] >= 0) depth[out.parent[j]] = std::max(depth[out.parent[j]], depth[j] + 1);
+  }
+}
+
+// =====================================================================================================================
+// device
+// =====================================================================================================================
+namespace {
+
+constexpr int SOLVER_THREADS = 256;
+constexpr int SOLVER_WARPS = SOLVER_THREADS / 32;
+// flag block: [0, n) per-column flags, then the control words
+constexpr int CTL_COUNTER = 0, CTL_ERROR = 1, CTL_ABORT = 2, CTL_WORDS = 4;
+constexpr unsigned long long WAIT_TIMEOUT_NS = 3000000000ull;
+
+struct FactorDev {
+  int n;
+  const int *colptr, *rowidx, *rowptr, *rowcol, *rowpos, *perm;
+  int *flags;  // n + CTL_WORDS
+  void *lx, *ux;
+};
+
+__device__ __forceinline__ int ld_acquire_s32(const int *p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_s32(int *p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Spins until flags[k] is set.  A wait that lasts longer than WAIT_TIMEOUT_NS (it cannot, unless the GPU is shared with a
+// kernel that starves the claimed columns' warps) raises the abort word, after which every wait returns at once.
+__device__ __forceinline__ void wait_flag(const int *flags, int n, int k) {
+  if (ld_acquire_s32(flags + k) != 0) return;
+  unsigned long long t0 = 0;
+  for (unsigned spin = 1;; ++spin) {
+    if (ld_acquire_s32(flags + k) != 0) return;
+    if ((spin & 1023u) == 0) {
+      if (ld_acquire_s32(flags + n + CTL_ABORT) != 0) return;
+      const unsigned long long t = global_ns();
+      if (t0 == 0) t0 = t;
+      else if (t - t0 > WAIT_TIMEOUT_NS) {
+        atomicExch(const_cast<int *>(flags) + n + CTL_ABORT, 1);
+        return;
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ int lower_bound_dev(const int *a, int len, int key) {
+  int lo = 0, hi = len;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(a + mid) < key) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+
+// A's values into the factor slots (amap: >= 0 slot of lx, <= -2 slot -2-v of ux, -1 not used by this factorisation)
+template <typename T>
+__global__ void solver_scatter_kernel(const T *__restrict__ aval, const int *__restrict__ amap, int64_t nnz, T *lx, T *ux) {
+  for (int64_t q = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < nnz;
+       q += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int s = amap[q];
+    if (s >= 0) lx[s] = aval[q];
+    else if (s <= -2) ux[-2 - s] = aval[q];
+  }
+}
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(SOLVER_THREADS) solver_factor_kernel(FactorDev f) {
+  const int lane = threadIdx.x & 31;
+  const int n = f.n;
+  T *lx = static_cast<T *>(f.lx);
+  T *ux = static_cast<T *>(f.ux);
+  int *flags = f.flags;
+  for (;;) {
+    int j = 0;
+    if (lane == 0) j = atomicAdd(flags + n + CTL_COUNTER, 1);
+    j = __shfl_sync(FULL, j, 0);
+    if (j >= n) return;
+    const int cj = __ldg(f.colptr + j), lenj = __ldg(f.colptr + j + 1) - cj;
+    const int r0 = __ldg(f.rowptr + j), cnt = __ldg(f.rowptr + j + 1) - r0;
+    for (int m = 0; m < cnt; ++m) {
+      const int k = __ldg(f.rowcol + r0 + m);
+      const int pjk = __ldg(f.rowpos + r0 + m);  // slot of (j, k) in column k
+      if (lane == 0) wait_flag(flags, n, k);
+      __syncwarp();
+      const int ck = __ldg(f.colptr + k), ek = __ldg(f.colptr + k + 1);
+      // the multiplier of column k in column j.  Own-column slots are only touched by this warp; other columns' values
+      // were published before their flag, and are read through L2 (ld.cg) so that no stale L1 line is seen.
+      T u;
+      if (MODE == SOLVER_LU) u = __ldcg(ux + pjk);
+      else {
+        u = __ldcg(lx + pjk);
+        if (MODE == SOLVER_LDLT) u *= __ldcg(lx + ck);
+      }
+      // rows >= j of column k  ->  column j
+      const int tail = ek - pjk;
+      if (tail == lenj) {
+        for (int t = lane; t < lenj; t += 32) __stcg(lx + cj + t, __ldcg(lx + cj + t) - __ldcg(lx + pjk + t) * u);
+      } else {
+        for (int t = lane; t < tail; t += 32) {
+          const int pos = lower_bound_dev(f.rowidx + cj, lenj, __ldg(f.rowidx + pjk + t));
+          __stcg(lx + cj + pos, __ldcg(lx + cj + pos) - __ldcg(lx + pjk + t) * u);
+        }
+      }
+      if (MODE == SOLVER_LU) {
+        // rows strictly between k and j of column k  ->  U(i, j), i.e. the slots of the later entries of row j
+        const int nup = pjk - ck - 1, rest = cnt - 1 - m;
+        if (nup == rest) {
+          for (int t = lane; t < nup; t += 32) {
+            const int s = __ldg(f.rowpos + r0 + m + 1 + t);
+            __stcg(ux + s, __ldcg(ux + s) - __ldcg(lx + ck + 1 + t) * u);
+          }
+        } else {
+          for (int t = lane; t < nup; t += 32) {
+            const int mm = lower_bound_dev(f.rowcol + r0 + m + 1, rest, __ldg(f.rowidx + ck + 1 + t));
+            const int s = __ldg(f.rowpos + r0 + m + 1 + mm);
+            __stcg(ux + s, __ldcg(ux + s) - __ldcg(lx + ck + 1 + t) * u);
+          }
+        }
+      }
+      __syncwarp();
+    }
+    // pivot and scaling
+    T d = __ldcg(lx + cj);
+    bool bad;
+    if (MODE == SOLVER_LLT) bad = !(d > T(0));
+    else bad = !(d != T(0)) || d != d;
+    if (bad) {
+      if (lane == 0) atomicMin(flags + n + CTL_ERROR, j);
+      d = T(1);
+    }
+    if (MODE == SOLVER_LLT) {
+      d = sqrt(d);
+      if (lane == 0) __stcg(lx + cj, d);
+    }
+    for (int t = 1 + lane; t < lenj; t += 32) __stcg(lx + cj + t, __ldcg(lx + cj + t) / d);
+    __syncwarp();
+    if (lane == 0) {
+      __threadfence();
+      st_release_s32(flags + j, 1);
+    }
+  }
+}
+
+// forward substitution  L y = P b  (LLT: L;  LDLT, LU: unit L), one warp per row, rows claimed ascending
+template <typename T, int MODE>
+__global__ void __launch_bounds__(SOLVER_THREADS) solver_forward_kernel(FactorDev f, const T *__restrict__ b, T *y) {
+  const int lane = threadIdx.x & 31;
+  const int n = f.n;
+  const T *lx = static_cast<const T *>(f.lx);
+  int *flags = f.flags;
+  for (;;) {
+    int j = 0;
+    if (lane == 0) j = atomicAdd(flags + n + CTL_COUNTER, 1);
+    j = __shfl_sync(FULL, j, 0);
+    if (j >= n) return;
+    const int r0 = __ldg(f.rowptr + j), cnt = __ldg(f.rowptr + j + 1) - r0;
+    T acc = T(0);
+    for (int m = lane; m < cnt; m += 32) {
+      const int k = __ldg(f.rowcol + r0 + m);
+      wait_flag(flags, n, k);
+      acc += __ldcg(lx + __ldg(f.rowpos + r0 + m)) * __ldcg(y + k);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) {
+      T v = b[__ldg(f.perm + j)] - acc;
+      if (MODE == SOLVER_LLT) v /= __ldcg(lx + __ldg(f.colptr + j));
+      __stcg(y + j, v);
+      __threadfence();
+      st_release_s32(flags + j, 1);
+    }
+  }
+}
+
+// backward substitution, rows claimed descending; x is written in the caller's (unpermuted) numbering as well
+template <typename T, int MODE>
+__global__ void __launch_bounds__(SOLVER_THREADS) solver_backward_kernel(FactorDev f, T *y, T *x) {
+  const int lane = threadIdx.x & 31;
+  const int n = f.n;
+  const T *lx = static_cast<const T *>(f.lx);
+  const T *vx = MODE == SOLVER_LU ? static_cast<const T *>(f.ux) : lx;
+  int *flags = f.flags;
+  for (;;) {
+    int c = 0;
+    if (lane == 0) c = atomicAdd(flags + n + CTL_COUNTER, 1);
+    c = __shfl_sync(FULL, c, 0);
+    if (c >= n) return;
+    const int j = n - 1 - c;
+    const int cj = __ldg(f.colptr + j), lenj = __ldg(f.colptr + j + 1) - cj;
+    T acc = T(0);
+    for (int t = 1 + lane; t < lenj; t += 32) {
+      const int i = __ldg(f.rowidx + cj + t);
+      wait_flag(flags, n, i);
+      acc += __ldcg(vx + cj + t) * __ldcg(y + i);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) {
+      const T d = __ldcg(lx + cj);
+      T v = __ldcg(y + j);
+      if (MODE == SOLVER_LDLT) v = v / d - acc;
+      else v = (v - acc) / d;
+      __stcg(y + j, v);
+      x[__ldg(f.perm + j)] = v;
+      __threadfence();
+      st_release_s32(flags + j, 1);
+    }
+  }
+}
+
+template <typename K>
+int solver_grid(K kernel, int n) {
+  int occ = 0;
+  QDSP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, SOLVER_THREADS, 0));
+  const int cap = std::max(1, occ) * device_props().sm_count;
+  return std::max(1, std::min(cap, ceil_div(n, SOLVER_WARPS)));
+}
+
+}  // namespace
+
+DirectSolver::DirectSolver(int dtype, int solver_type, int ordering) : dtype_(dtype), type_(solver_type), ordering_(ordering) {
+  QDSP_REQUIRE(dtype == QDSP_F32 || dtype == QDSP_F64, QDSP_ERR_INVALID, "Not supported sparse solver data type");
+  QDSP_REQUIRE(solver_type >= SOLVER_LLT && solver_type <= SOLVER_LU, QDSP_ERR_INVALID, "Not supported sparse solver type");
+  QDSP_REQUIRE(ordering == 0 || ordering == 1, QDSP_ERR_INVALID, "Not supported sparse solver ordering");
+}
+DirectSolver::~DirectSolver() = default;
+
+void DirectSolver::analyze_pattern(const CsrMatrix &A, cudaStream_t stream) {
+  QDSP_REQUIRE(A.rows == A.cols, QDSP_ERR_INVALID, "solver: the matrix must be square");
+  QDSP_REQUIRE(A.dtype == dtype_, QDSP_ERR_INVALID, "solver: dtype of the matrix differs from the solver's");
+  const int n = A.rows;
+  std::vector<int32_t> ip(n + 1), ix(static_cast<size_t>(A.nnz));
+  QDSP_CUDA(cudaMemcpyAsync(ip.data(), A.indptr.get(), sizeof(int32_t) * (n + 1), cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaMemcpyAsync(ix.data(), A.indices.get(), sizeof(int32_t) * A.nnz, cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+  std::vector<int32_t> perm;
+  // both ordering names select the same symmetric minimum-degree ordering, like the reference's arch=cuda path, which
+  // ignores the argument and calls csrsymamdHost (make_cusparse_solver, sparse_solver.cpp:548-558)
+  solver_order_host(n, ip.data(), ix.data(), perm);
+  solver_symbolic_host(n, ip.data(), ix.data(), perm, sym_);
+  // where each entry of A lands.  LLT / LDLT read the LOWER triangle of A only (Eigen::Lower, sparse_solver.h:9-13).
+  std::vector<int32_t> amap(static_cast<size_t>(A.nnz), -1);
+  for (int r = 0; r < n; ++r)
+    for (int q = ip[r]; q < ip[r + 1]; ++q) {
+      const int c = ix[q];
+      if (type_ != SOLVER_LU && c > r) continue;
+      const int pr = sym_.pinv[r], pc = sym_.pinv[c];
+      int hi = pr, lo = pc;
+      bool upper = false;
+      if (pr < pc) { hi = pc; lo = pr; upper = type_ == SOLVER_LU; }
+      const int32_t *b = sym_.rowidx.data() + sym_.colptr[lo], *e = sym_.rowidx.data() + sym_.colptr[lo + 1];
+      const int32_t *it = std::lower_bound(b, e, hi);
+      QDSP_REQUIRE(it != e && *it == hi, QDSP_ERR_INVALID, "solver: entry outside the analysed pattern");
+      const int slot = static_cast<int>(it - sym_.rowidx.data());
+      amap[q] = upper ? -2 - slot : slot;
+    }
+  auto up = [&](DeviceBuffer &d, const std::vector<int32_t> &h) {
+    d.alloc(std::max<size_t>(h.size(), 1) * sizeof(int32_t));
+    if (!h.empty()) QDSP_CUDA(cudaMemcpyAsync(d.get(), h.data(), h.size() * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+  };
+  up(d_colptr_, sym_.colptr);
+  up(d_rowidx_, sym_.rowidx);
+  up(d_rowptr_, sym_.rowptr);
+  up(d_rowcol_, sym_.rowcol);
+  up(d_rowpos_, sym_.rowpos);
+  up(d_perm_, sym_.perm);
+  up(d_amap_, amap);
+  const size_t vb = dtype_ == QDSP_F64 ? 8 : 4;
+  d_lx_.alloc(static_cast<size_t>(sym_.factor_nnz) * vb);
+  if (type_ == SOLVER_LU) d_ux_.alloc(static_cast<size_t>(sym_.factor_nnz) * vb);
+  d_flags_.alloc(static_cast<size_t>(n + CTL_WORDS) * sizeof(int));
+  d_work_.alloc(static_cast<size_t>(std::max(n, 1)) * vb);
+  QDSP_CUDA(cudaStreamSynchronize(stream));  // the host vectors above go out of scope
+  nnz_a_ = A.nnz;
+  analyzed_ = true;
+  factorized_ = false;
+  zero_pivot_ = -1;
+}
+
+namespace {
+void reset_flags(int *flags, int n, cudaStream_t stream) {
+  QDSP_CUDA(cudaMemsetAsync(flags, 0, static_cast<size_t>(n + CTL_WORDS) * sizeof(int), stream));
+  const int big = INT_MAX;
+  QDSP_CUDA(cudaMemcpyAsync(flags + n + CTL_ERROR, &big, sizeof(int), cudaMemcpyHostToDevice, stream));
+}
+void read_ctl(const int *flags, int n, cudaStream_t stream, int *ctl) {
+  QDSP_CUDA(cudaMemcpyAsync(ctl, flags + n, CTL_WORDS * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+  QDSP_REQUIRE(ctl[CTL_ABORT] == 0, QDSP_ERR_CUDA, "solver: a dependency wait timed out on the device");
+}
+}  // namespace
+
+template <typename T, int MODE>
+static void factor_launch(const FactorDev &f, cudaStream_t stream) {
+  const int grid = solver_grid(solver_factor_kernel<T, MODE>, f.n);
+  solver_factor_kernel<T, MODE><<<grid, SOLVER_THREADS, 0, stream>>>(f);
+  QDSP_LAUNCH_CHECK();
+}
+template <typename T, int MODE>
+static void solve_launch(const FactorDev &f, const T *b, T *y, T *x, cudaStream_t stream) {
+  reset_flags(f.flags, f.n, stream);
+  solver_forward_kernel<T, MODE><<<solver_grid(solver_forward_kernel<T, MODE>, f.n), SOLVER_THREADS, 0, stream>>>(f, b, y);
+  QDSP_LAUNCH_CHECK();
+  reset_flags(f.flags, f.n, stream);
+  solver_backward_kernel<T, MODE><<<solver_grid(solver_backward_kernel<T, MODE>, f.n), SOLVER_THREADS, 0, stream>>>(f, y, x);
+  QDSP_LAUNCH_CHECK();
+}
+
+#define SOLVER_DISPATCH(FN, ...)                                                             \
+  do {                                                                                       \
+    if (dtype_ == QDSP_F64) {                                                                \
+      if (type_ == SOLVER_LLT) FN<double, SOLVER_LLT>(__VA_ARGS__);                          \
+      else if (type_ == SOLVER_LDLT) FN<double, SOLVER_LDLT>(__VA_ARGS__);                   \
+      else FN<double, SOLVER_LU>(__VA_ARGS__);                                               \
+    } else {                                                                                 \
+      if (type_ == SOLVER_LLT) FN<float, SOLVER_LLT>(__VA_ARGS__);                           \
+      else if (type_ == SOLVER_LDLT) FN<float, SOLVER_LDLT>(__VA_ARGS__);                    \
+      else FN<float, SOLVER_LU>(__VA_ARGS__);                                                \
+    }                                                                                        \
+  } while (0)
+
+void DirectSolver::factorize(const CsrMatrix &A, cudaStream_t stream) {
+  QDSP_REQUIRE(analyzed_, QDSP_ERR_STATE, "solver: analyze_pattern() must be called before factorize()");
+  QDSP_REQUIRE(A.rows == sym_.n && A.cols == sym_.n && A.nnz == nnz_a_ && A.dtype == dtype_, QDSP_ERR_INVALID,
+               "solver: the matrix does not match the analysed pattern");
+  const int n = sym_.n;
+  factorized_ = false;
+  zero_pivot_ = -1;
+  if (n == 0) { factorized_ = true; return; }
+  const size_t vb = dtype_ == QDSP_F64 ? 8 : 4;
+  QDSP_CUDA(cudaMemsetAsync(d_lx_.get(), 0, static_cast<size_t>(sym_.factor_nnz) * vb, stream));
+  if (type_ == SOLVER_LU) QDSP_CUDA(cudaMemsetAsync(d_ux_.get(), 0, static_cast<size_t>(sym_.factor_nnz) * vb, stream));
+  const int sgrid = std::max(1, std::min(device_props().sm_count * 8, ceil_div(A.nnz, 256)));
+  if (dtype_ == QDSP_F64)
+    solver_scatter_kernel<double><<<sgrid, 256, 0, stream>>>(A.values.get<double>(), d_amap_.get<int>(), A.nnz,
+                                                              d_lx_.get<double>(), d_ux_.get<double>());
+  else
+    solver_scatter_kernel<float><<<sgrid, 256, 0, stream>>>(A.values.get<float>(), d_amap_.get<int>(), A.nnz,
+                                                             d_lx_.get<float>(), d_ux_.get<float>());
+  QDSP_LAUNCH_CHECK();
+  reset_flags(d_flags_.get<int>(), n, stream);
+  FactorDev f{n, d_colptr_.get<int>(), d_rowidx_.get<int>(), d_rowptr_.get<int>(), d_rowcol_.get<int>(),
+              d_rowpos_.get<int>(), d_perm_.get<int>(), d_flags_.get<int>(), d_lx_.get(), d_ux_.get()};
+  SOLVER_DISPATCH(factor_launch, f, stream);
+  int ctl[CTL_WORDS];
+  read_ctl(d_flags_.get<int>(), n, stream, ctl);
+  zero_pivot_ = ctl[CTL_ERROR] == INT_MAX ? -1 : ctl[CTL_ERROR];
+  factorized_ = true;
+}
+
+void DirectSolver::solve(const void *b, void *x, cudaStream_t stream) {
+  QDSP_REQUIRE(factorized_, QDSP_ERR_STATE, "solver: factorize() must be called before solve()");
+  QDSP_REQUIRE(b != nullptr && x != nullptr, QDSP_ERR_INVALID, "solver: null vector");
+  const int n = sym_.n;
+  if (n == 0) return;
+  FactorDev f{n, d_colptr_.get<int>(), d_rowidx_.get<int>(), d_rowptr_.get<int>(), d_rowcol_.get<int>(),
+              d_rowpos_.get<int>(), d_perm_.get<int>(), d_flags_.get<int>(), d_lx_.get(), d_ux_.get()};
+  if (dtype_ == QDSP_F64) {
+    const double *bb = static_cast<const double *>(b);
+    double *yy = d_work_.get<double>(), *xx = static_cast<double *>(x);
+    if (type_ == SOLVER_LLT) solve_launch<double, SOLVER_LLT>(f, bb, yy, xx, stream);
+    else if (type_ == SOLVER_LDLT) solve_launch<double, SOLVER_LDLT>(f, bb, yy, xx, stream);
+    else solve_launch<double, SOLVER_LU>(f, bb, yy, xx, stream);
+  } else {
+    const float *bb = static_cast<const float *>(b);
+    float *yy = d_work_.get<float>(), *xx = static_cast<float *>(x);
+    if (type_ == SOLVER_LLT) solve_launch<float, SOLVER_LLT>(f, bb, yy, xx, stream);
+    else if (type_ == SOLVER_LDLT) solve_launch<float, SOLVER_LDLT>(f, bb, yy, xx, stream);
+    else solve_launch<float, SOLVER_LU>(f, bb, yy, xx, stream);
+  }
+  int ctl[CTL_WORDS];
+  read_ctl(d_flags_.get<int>(), n, stream, ctl);
+}
+
+void DirectSolver::solve_host(const void *b_host, void *x_host, cudaStream_t stream) {
+  QDSP_REQUIRE(b_host != nullptr && x_host != nullptr, QDSP_ERR_INVALID, "solver: null vector");
+  const size_t bytes = static_cast<size_t>(sym_.n) * (dtype_ == QDSP_F64 ? 8 : 4);
+  DeviceBuffer db(bytes), dx(bytes);
+  QDSP_CUDA(cudaMemcpyAsync(db.get(), b_host, bytes, cudaMemcpyHostToDevice, stream));
+  solve(db.get(), dx.get(), stream);
+  QDSP_CUDA(cudaMemcpyAsync(x_host, dx.get(), bytes, cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+}
+
+}  // namespace qdsp

@@ -251,7 +251,10 @@ def field(dtype, shape, offset=0):
     """1-D dense field; enough of qd.field for parallel_sort / PrefixSumExecutor callers."""
     if isinstance(offset, (tuple, list)):
         offset = offset[0]
-    return Ndarray(dtype, shape, offset=offset)
+    return Field(dtype, shape, offset=offset)
 
 
-Field = Ndarray
+class Field(Ndarray):
+    """qd.field(...) result.  Same dense device storage as Ndarray; a distinct type because the reference's Python layer
+    dispatches on it (e.g. SparseSolver.solve: Field -> numpy result, Ndarray -> Ndarray result,
+    python/quadrants/linalg/sparse_solver.py:103-110)."""

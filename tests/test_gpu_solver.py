@@ -1,0 +1,196 @@
+"""A16 / N4: qd.linalg.SparseSolver on the device (quadrants_b200/csrc/solver.cu) through the public API -> C ABI.
+
+Ports of the reference's tests/python/test_sparse_linear_solver.py (same matrices, same checks), the golden solutions of
+the reference's own Eigen solvers (tests/golden/solver_golden.npz), a mid-size 2-D Poisson system, and the failure and
+reproducibility behaviour.  Needs a B200.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import make_triplet_buffer
+from tests import workloads as W
+from tests.test_solver_host import check_solution, dense_of
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "solver_golden.npz")
+
+
+@pytest.fixture(scope="module")
+def qd():
+    import quadrants_b200 as qd
+
+    qd.init(arch=qd.cuda)
+    return qd
+
+
+def build(qd, r, c, v, n, dt):
+    buf = make_triplet_buffer(r, c, v.astype(dt), dt)
+    K = qd.linalg.SparseMatrixBuilder(n, n, max_num_triplets=max(int(buf[0]), 1),
+                                      dtype=qd.f32 if dt == np.float32 else qd.f64)
+    K.ptr.fill_from_host(buf)
+    return K.build()
+
+
+def psd10(seed, dt):
+    a = np.random.default_rng(seed).random((10, 10))
+    return (a @ a.T + np.eye(10)).astype(dt)
+
+
+def fill_dense(qd, a, dt):
+    n = a.shape[0]
+    i, j = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    return build(qd, i.ravel(), j.ravel(), a.ravel(), n, dt)
+
+
+# ---- ports of the reference's tests ----------------------------------------------------------------------------------
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+@pytest.mark.parametrize("solver_type", ["LLT", "LDLT", "LU"])
+@pytest.mark.parametrize("ordering", ["AMD", "COLAMD"])
+def test_sparse_LLT_solver(qd, dt, solver_type, ordering):
+    """test_sparse_linear_solver.py:17-53 (field right-hand side -> numpy result)."""
+    qdt = qd.f32 if dt == np.float32 else qd.f64
+    a = psd10(1, dt)
+    A = fill_dense(qd, a, dt)
+    b = qd.field(dtype=qdt, shape=10)
+    b.from_numpy(np.arange(1, 11).astype(dt))
+    solver = qd.linalg.SparseSolver(dtype=qdt, solver_type=solver_type, ordering=ordering)
+    solver.analyze_pattern(A)
+    solver.factorize(A)
+    x = solver.solve(b)
+    assert isinstance(x, np.ndarray) and solver.info()
+    res = np.linalg.solve(a.astype(np.float64), b.to_numpy().astype(np.float64))
+    assert np.allclose(x, res, rtol=5e-3 if dt == np.float32 else 1e-9)
+
+
+@pytest.mark.parametrize("solver_type", ["LLT", "LDLT", "LU"])
+@pytest.mark.parametrize("ordering", ["AMD", "COLAMD"])
+def test_sparse_solver_ndarray_vector(qd, solver_type, ordering):
+    """test_sparse_linear_solver.py:56-92 (ndarray right-hand side -> ndarray result on the device)."""
+    a = psd10(2, np.float32)
+    A = fill_dense(qd, a, np.float32)
+    b = qd.ndarray(qd.f32, shape=10)
+    b.from_numpy(np.arange(1, 11).astype(np.float32))
+    solver = qd.linalg.SparseSolver(dtype=qd.f32, solver_type=solver_type, ordering=ordering)
+    solver.analyze_pattern(A)
+    solver.factorize(A)
+    x = solver.solve(b)
+    assert isinstance(x, qd.Ndarray)
+    res = np.linalg.solve(a.astype(np.float64), b.to_numpy().astype(np.float64))
+    assert np.allclose(x.to_numpy(), res, rtol=5e-3)
+
+
+def test_gpu_sparse_solver(qd):
+    """test_sparse_linear_solver.py:95-150: analyze + factorize, then compute(); rtol 5e-3."""
+    a = psd10(3, np.float32)
+    A = fill_dense(qd, a, np.float32)
+    b = qd.ndarray(shape=10, dtype=qd.f32)
+    b.from_numpy((1.0 + np.arange(10) / 10).astype(np.float32))
+    x_np = np.linalg.solve(a, b.to_numpy())
+    solver = qd.linalg.SparseSolver(dtype=qd.f32)
+    solver.analyze_pattern(A)
+    solver.factorize(A)
+    assert np.allclose(solver.solve(b).to_numpy(), x_np, rtol=5.0e-3)
+    solver = qd.linalg.SparseSolver(dtype=qd.f32)
+    solver.compute(A)
+    assert np.allclose(solver.solve(b).to_numpy(), x_np, rtol=5.0e-3)
+
+
+# ---- against the reference's Eigen solvers --------------------------------------------------------------------------------
+@pytest.mark.parametrize("tag,dt", [("f32", np.float32), ("f64", np.float64)])
+def test_solver_matches_reference_eigen_golden(qd, tag, dt):
+    gold = np.load(GOLD)
+    qdt = qd.f32 if dt == np.float32 else qd.f64
+    for name, n, r, c, v, b, sym in W.solver_cases():
+        A = build(qd, r, c, v, n, dt)
+        a = dense_of(n, r, c, v, dt)
+        for st in (("LLT", "LDLT", "LU") if sym else ("LU",)):
+            solver = qd.linalg.SparseSolver(dtype=qdt, solver_type=st)
+            solver.compute(A)
+            assert solver.info()
+            x = solver.solve(b.astype(dt))
+            check_solution(name, tag, x, gold[f"{name}/{tag}/{st}/AMD"], a, b.astype(dt).astype(np.float64))
+
+
+def test_solver_reads_the_lower_triangle_only(qd):
+    """Eigen::Lower (sparse_solver.h:9-13): garbage in the strict upper triangle does not change an LLT / LDLT solve."""
+    a = psd10(4, np.float64)
+    junk = a + np.triu(np.random.default_rng(0).random((10, 10)), 1)
+    b = np.arange(1, 11, dtype=np.float64)
+    for st in ("LLT", "LDLT"):
+        s = qd.linalg.SparseSolver(dtype=qd.f64, solver_type=st)
+        s.compute(fill_dense(qd, junk, np.float64))
+        assert np.allclose(s.solve(b), np.linalg.solve(a, b), rtol=1e-10)
+
+
+@pytest.mark.parametrize("solver_type", ["LLT", "LDLT", "LU"])
+def test_solver_poisson2d_mid_size_and_reproducible(qd, solver_type):
+    """2-D Poisson 192^2 (36 864 rows): long dependency chains, supernode fast path and searched updates, fp64."""
+    nx = 192
+    n = nx * nx
+    r, c, v = W.poisson2d_triplets(nx, dtype=np.float64)
+    A = build(qd, r, c, v, n, np.float64)
+    xt = np.random.default_rng(5).uniform(-1, 1, n)
+    xd = qd.ndarray(qd.f64, n)
+    xd.from_numpy(xt)
+    b = A @ xd
+    s = qd.linalg.SparseSolver(dtype=qd.f64, solver_type=solver_type)
+    s.compute(A)
+    st = s.solver.stats()
+    assert st["factor_nnz"] > A.matrix.nnz() and st["etree_height"] < n
+    x1 = s.solve(b).to_numpy()
+    assert np.linalg.norm(x1 - xt) <= 1e-9 * np.linalg.norm(xt)
+    s.factorize(A)  # refactorisation with the same pattern (the "rf" of solve_rf)
+    x2 = s.solve(b).to_numpy()
+    assert np.array_equal(x1.view(np.uint64), x2.view(np.uint64)), "fixed dependency order => bit-identical"
+
+
+def test_solver_unsymmetric_lu_larger(qd):
+    rng = np.random.default_rng(9)
+    n = 3000
+    r = rng.integers(0, n, 20000)
+    c = np.clip(r + rng.integers(-40, 41, 20000), 0, n - 1)
+    keep = r != c
+    r, c = r[keep], c[keep]
+    v = rng.uniform(-1, 1, r.shape[0])
+    a = np.zeros((n, n))
+    np.add.at(a, (r, c), v)
+    d = 1.0 + np.maximum(np.abs(a).sum(0), np.abs(a).sum(1))
+    a[np.arange(n), np.arange(n)] = d
+    A = build(qd, np.concatenate([r, np.arange(n)]), np.concatenate([c, np.arange(n)]), np.concatenate([v, d]), n,
+              np.float64)
+    b = np.cos(np.arange(n) * 0.01)
+    s = qd.linalg.SparseSolver(dtype=qd.f64, solver_type="LU")
+    s.compute(A)
+    x = s.solve(b)
+    assert np.linalg.norm(a @ x - b) <= 1e-12 * np.linalg.norm(b)
+
+
+# ---- failure behaviour ---------------------------------------------------------------------------------------------------
+def test_solver_failures(qd):
+    indef = np.array([[1.0, 2.0], [2.0, 1.0]])
+    A = fill_dense(qd, indef, np.float64)
+    s = qd.linalg.SparseSolver(dtype=qd.f64, solver_type="LLT")
+    s.analyze_pattern(A)
+    with pytest.raises(qd.QuadrantsRuntimeError):  # QD_ASSERT(singularity == -1), sparse_solver.cpp:326-327
+        s.factorize(A)
+    assert not s.info()
+    s = qd.linalg.SparseSolver(dtype=qd.f64, solver_type="LDLT")  # indefinite is fine for LDLT
+    s.compute(A)
+    assert np.allclose(indef @ s.solve(np.ones(2)), np.ones(2))
+    sing = np.array([[1.0, 1.0], [1.0, 1.0]])
+    s = qd.linalg.SparseSolver(dtype=qd.f64, solver_type="LU")
+    with pytest.raises(qd.QuadrantsRuntimeError):
+        s.compute(fill_dense(qd, sing, np.float64))
+    with pytest.raises(qd.QuadrantsRuntimeError, match="compute"):
+        qd.linalg.SparseSolver(dtype=qd.f64).solve(np.ones(2))
+    with pytest.raises(qd.QuadrantsRuntimeError, match="not consistent"):
+        qd.linalg.SparseSolver(dtype=qd.f32).analyze_pattern(A)
+    with pytest.raises(qd.QuadrantsRuntimeError, match="not supported in linear solvers"):
+        qd.linalg.SparseSolver(dtype=qd.f64).compute(np.eye(2))
+    from quadrants_b200 import _lib
+
+    s = qd.linalg.SparseSolver(dtype=qd.f64)
+    with pytest.raises(_lib.QdspError):  # factorize before analyze_pattern
+        s.factorize(A)

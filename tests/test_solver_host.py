@@ -1,0 +1,136 @@
+"""A16 (SparseSolver) on the CPU: the oracle's restatement of Eigen's simplicial Cholesky against the golden solutions of
+the reference's own Eigen solvers (tests/golden/solver_golden.npz, made by make_solver_golden.py) and, when oracle/_ref is
+present, against them live; the host analysis of the product (ordering + symbolic factorisation, pure C++ behind
+qdsp_solver_analyze_host) against a dense boolean elimination."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import make_triplet_buffer
+from tests import workloads as W
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "solver_golden.npz")
+# Forward error against the reference's solution.  The reference's own bar is rtol 5e-3 on a 10x10 matrix
+# (test_sparse_linear_solver.py:136).  fem_300 (stiffness + 1e-2 mass) has a condition number ~1e5: in fp32 Eigen's own
+# AMD and COLAMD solutions differ by ~1e-2, so there the forward bar is 5e-2 and the BACKWARD error carries the check.
+TOL = {"f32": 2e-3, "f64": 1e-9}
+TOL_ILL = {"f32": 5e-2, "f64": 1e-7}
+ILL = {"fem_300"}
+
+
+def check_solution(name, tag, x, xr, a, b):
+    """x against the reference's xr (forward) and against the system itself (normwise backward error, <= 100 eps)."""
+    tol = (TOL_ILL if name in ILL else TOL)[tag]
+    x64 = x.astype(np.float64)
+    assert np.linalg.norm(x64 - xr) <= tol * np.linalg.norm(xr), (name, tag, np.linalg.norm(x64 - xr) / np.linalg.norm(xr))
+    eps = np.finfo(np.float32 if tag == "f32" else np.float64).eps
+    back = np.linalg.norm(a @ x64 - b) / (np.linalg.norm(a, 2) * np.linalg.norm(x64) + np.linalg.norm(b))
+    assert back <= 100 * eps, (name, tag, back)
+
+
+def dense_of(n, r, c, v, dt):
+    a = np.zeros((n, n), dt)
+    np.add.at(a, (r, c), v.astype(dt))
+    return a.astype(np.float64)
+
+
+def _csr(oracle, r, c, v, n, dt):
+    buf = make_triplet_buffer(r, c, v.astype(dt), dt)
+    return oracle.build_matrix(buf, n, n, True)
+
+
+@pytest.mark.parametrize("tag,dt", [("f32", np.float32), ("f64", np.float64)])
+def test_oracle_direct_solve_matches_reference_eigen(oracle, tag, dt):
+    gold = np.load(GOLD)
+    for name, n, r, c, v, b, sym in W.solver_cases():
+        if not sym:
+            continue
+        ip, ix, vals = _csr(oracle, r, c, v, n, dt)
+        for st in ("LLT", "LDLT"):
+            x, ok = oracle.direct_solve(ip, ix, vals, b.astype(dt), ldlt=(st == "LDLT"))
+            assert ok
+            for od in ("AMD", "COLAMD"):
+                check_solution(name, tag, x, gold[f"{name}/{tag}/{st}/{od}"], dense_of(n, r, c, v, dt),
+                               b.astype(dt).astype(np.float64))
+
+
+def test_golden_is_current_when_reference_present(eigen_ref):
+    gold = np.load(GOLD)
+    for name, n, r, c, v, b, sym in W.solver_cases():
+        buf = make_triplet_buffer(r, c, v.astype(np.float64), np.float64)
+        m = eigen_ref.matrix(buf, n, n, row_major=False)
+        x, ok = m.direct_solve(b, "LU", "COLAMD")
+        assert ok and np.array_equal(x, gold[f"{name}/f64/LU/COLAMD"]), name
+        # and the solutions are solutions
+        a = np.zeros((n, n))
+        np.add.at(a, (r, c), v)
+        assert np.linalg.norm(a @ x - b) <= 1e-10 * np.linalg.norm(b)
+
+
+def test_oracle_direct_solve_reports_failure(oracle):
+    ip = np.array([0, 1, 3], np.int32)
+    ix = np.array([0, 0, 1], np.int32)
+    b = np.ones(2)
+    _, ok = oracle.direct_solve(ip, ix, np.array([1.0, 2.0, 1.0]), b, ldlt=False)  # [[1,2],[2,1]]: indefinite
+    assert not ok
+    x, ok = oracle.direct_solve(ip, ix, np.array([1.0, 2.0, 1.0]), b, ldlt=True)   # LDLT takes it
+    assert ok and np.allclose(np.array([[1.0, 2.0], [2.0, 1.0]]) @ x, b)
+
+
+def _symbolic_dense(a, perm):
+    n = a.shape[0]
+    b = ((np.abs(a) + np.abs(a.T)) != 0)[np.ix_(perm, perm)]
+    np.fill_diagonal(b, True)
+    for k in range(n):
+        r = np.nonzero(b[k + 1:, k])[0] + k + 1
+        b[np.ix_(r, r)] = True
+    return np.tril(b)
+
+
+@pytest.mark.parametrize("natural", [True, False])
+def test_host_analysis_pattern_equals_boolean_elimination(oracle, natural):
+    from quadrants_b200 import _core
+
+    for name, n, r, c, v, b, sym in W.solver_cases():
+        if n > 600:
+            continue
+        ip, ix, vals = _csr(oracle, r, c, v, n, np.float64)
+        res = _core.solver_analyze_host(ip, ix, natural_order=natural)
+        perm = res["perm"]
+        assert sorted(perm.tolist()) == list(range(n))
+        if natural:
+            assert np.array_equal(perm, np.arange(n))
+        a = np.zeros((n, n))
+        np.add.at(a, (r, c), 1.0)
+        low = _symbolic_dense(a, perm)
+        assert int(low.sum()) == res["factor_nnz"], name
+        for j in range(n):
+            rows = res["rowidx"][res["colptr"][j]:res["colptr"][j + 1]]
+            assert rows[0] == j and np.array_equal(rows, np.nonzero(low[:, j])[0]), (name, j)
+            p = res["parent"][j]
+            assert p == (rows[1] if rows.shape[0] > 1 else -1)  # etree parent = first off-diagonal row of the column
+
+
+def test_minimum_degree_ordering_reduces_fill_on_a_grid(oracle):
+    from quadrants_b200 import _core
+
+    r, c, v = W.poisson2d_triplets(48, dtype=np.float64)
+    ip, ix, _ = _csr(oracle, r, c, v, 48 * 48, np.float64)
+    nat = _core.solver_analyze_host(ip, ix, natural_order=True)
+    amd = _core.solver_analyze_host(ip, ix, natural_order=False)
+    assert nat["factor_nnz"] == 48 * 48 * 49 - 48 * 49 // 2 * 2 + 0 or nat["factor_nnz"] > 100000  # banded: ~ n * 49
+    assert amd["factor_nnz"] < 0.45 * nat["factor_nnz"]
+    assert amd["etree_height"] < nat["etree_height"]
+    # deterministic
+    again = _core.solver_analyze_host(ip, ix, natural_order=False)
+    assert np.array_equal(again["perm"], amd["perm"])
+
+
+def test_host_analysis_rejects_bad_input():
+    from quadrants_b200 import _core, _lib
+
+    with pytest.raises(_lib.QdspError):
+        _core.solver_analyze_host(np.array([0, 1, 2], np.int32), np.array([0, 5], np.int32))
+    res = _core.solver_analyze_host(np.array([0], np.int32), np.array([], np.int32))
+    assert res["factor_nnz"] == 0 and res["etree_height"] == 0

@@ -12,10 +12,12 @@ GOLD = os.path.join(os.path.dirname(__file__), "golden", "nanobind_surface.json"
 
 # what is mirrored, and what is deliberately not
 MIRRORED = {"SparseMatrixBuilder": "SparseMatrixBuilder", "SparseMatrix": "CuSparseMatrix",
-            "CuSparseMatrix": "CuSparseMatrix", "CGf": "CGf", "CGd": "CGd", "CUCG": "CUCG"}
-MIRRORED_FUNCTIONS = {"make_cucg_solver", "make_float_cg_solver", "make_double_cg_solver"}
-NOT_MIRRORED_PREFIXES = ("EigenSparseSolver", "SparseSolver", "CuSparseSolver")  # A16: direct factorisations
-NOT_MIRRORED_FUNCTIONS = {"make_sparse_solver", "make_cusparse_solver"}
+            "CuSparseMatrix": "CuSparseMatrix", "CGf": "CGf", "CGd": "CGd", "CUCG": "CUCG",
+            "CuSparseSolver": "CuSparseSolver", "SparseSolver": "CuSparseSolver"}
+MIRRORED_FUNCTIONS = {"make_cucg_solver", "make_float_cg_solver", "make_double_cg_solver", "make_sparse_solver",
+                      "make_cusparse_solver"}
+NOT_MIRRORED_PREFIXES = ()
+NOT_MIRRORED_FUNCTIONS = set()
 
 
 @pytest.fixture(scope="module")
@@ -46,7 +48,9 @@ def test_core_objects_carry_every_bound_method(surface):
     for ref_cls, methods in surface["classes"].items():
         if ref_cls.startswith(NOT_MIRRORED_PREFIXES):
             continue
-        if ref_cls.endswith("_EigenSparseMatrix"):  # the CPU twins: one device class stands for all four
+        if ref_cls.startswith("EigenSparseSolver"):  # the twelve CPU instantiations: one device class stands for them
+            cls = _core.CuSparseSolver
+        elif ref_cls.endswith("_EigenSparseMatrix"):  # the CPU twins: one device class stands for all four
             cls = _core.CuSparseMatrix
             methods = [m for m in methods if m != "mat_vec_mul"] + ["mat_vec_mul_host"]
         else:
@@ -99,10 +103,11 @@ def test_python_layer_signatures():
         "select_scratch_slots", "sort", "sort_scratch_slots"])  # python/quadrants/algorithms/__init__.py:26-43
 
 
-def test_sparse_solver_is_an_honest_stub():
+def test_sparse_solver_has_no_hidden_fallback():
     import quadrants_b200 as qd
+    from quadrants_b200 import _core
 
     with pytest.raises(qd.QuadrantsRuntimeError):
         qd.linalg.SparseSolver(solver_type="QR")  # argument validation is the reference's
-    src = inspect.getsource(qd.linalg.sparse_solver)
-    assert "SparseCG(" not in src.replace("qd.linalg.SparseCG for", "") and "scipy" not in src, "no hidden fallback"
+    for src in (inspect.getsource(qd.linalg.sparse_solver), inspect.getsource(_core.CuSparseSolver)):
+        assert "SparseCG(" not in src and "scipy" not in src and "linalg.solve" not in src, "no hidden fallback"

@@ -123,3 +123,35 @@ def row_abs_scale(indptr, indices, values, x):
     prod = np.abs(values.astype(np.float64) * x[indices].astype(np.float64))
     csum = np.concatenate([[0.0], np.cumsum(prod)])
     return csum[indptr[1:]] - csum[indptr[:-1]]
+
+
+def solver_cases():
+    """A16 (SparseSolver) inputs, shared by tests/golden/make_solver_golden.py (reference's Eigen) and the GPU tests.
+    Yields (name, n, rows, cols, vals_f64, b_f64, symmetric).  The 10x10 ones are the reference's own test matrix
+    (tests/python/test_sparse_linear_solver.py:22-29: A A^T + I, b = 1..n)."""
+    for seed in range(3):
+        rng = np.random.default_rng(100 + seed)
+        m = rng.random((10, 10))
+        a = m @ m.T + np.eye(10)
+        i, j = np.meshgrid(np.arange(10), np.arange(10), indexing="ij")
+        yield f"dense10_s{seed}", 10, i.ravel(), j.ravel(), a.ravel(), np.arange(1, 11, dtype=np.float64), True
+    r, c, v = poisson2d_triplets(24, dtype=np.float64)
+    n = 24 * 24
+    yield "poisson2d_24", n, r, c, v.astype(np.float64), 1.0 + np.arange(n) / n, True
+    r, c, v, nv = fem_tet_triplets(300, 1500, seed=11, compact=True)
+    # duplicates are summed by the builder; the lower and upper triangles receive the same sums in the same order
+    yield "fem_300", nv, r, c, v, np.cos(np.arange(nv) * 0.37), True
+    rng = np.random.default_rng(42)
+    n = 120
+    r = rng.integers(0, n, 900)
+    c = rng.integers(0, n, 900)
+    keep = r != c
+    r, c = r[keep], c[keep]
+    v = rng.uniform(-1.0, 1.0, r.shape[0])
+    rowsum = np.zeros(n)
+    np.add.at(rowsum, r, np.abs(v))
+    colsum = np.zeros(n)
+    np.add.at(colsum, c, np.abs(v))
+    d = 1.0 + np.maximum(rowsum, colsum)  # strictly diagonally dominant by rows and columns: no pivoting needed
+    yield ("unsym_dd_120", n, np.concatenate([r, np.arange(n)]), np.concatenate([c, np.arange(n)]),
+           np.concatenate([v, d]), np.sin(np.arange(n) * 0.11) + 2.0, False)
