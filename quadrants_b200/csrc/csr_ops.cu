@@ -3,6 +3,9 @@
 // BASELINE config: each one is expressed as "emit COO triplets on the device, then run the same
 // sort + collapse pipeline as the builder", so they inherit its kernels and its determinism (duplicates summed in a
 // fixed order).
+#include <cstdlib>
+#include <vector>
+
 #include "host.hpp"
 
 namespace qdsp {
@@ -110,15 +113,40 @@ std::unique_ptr<CsrMatrix> CsrMatrix::transpose(cudaStream_t stream) const {
   return out;
 }
 
-// 64-bit total of the per-entry product counts (the i32 scan below wraps silently past 2^31)
-__global__ void sum_counts_kernel(int64_t n, const int *__restrict__ cnt, unsigned long long *__restrict__ total) {
-  unsigned long long t = 0;
-  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n; i += static_cast<int64_t>(gridDim.x) * blockDim.x)
-    t += static_cast<unsigned long long>(cnt[i]);
+// partial products of every row of A*B in 64 bits (the i32 scans below work on one bounded chunk at a time)
+__global__ void __launch_bounds__(OP_THREADS)
+spgemm_row_products_kernel(int rows, const int *__restrict__ a_ptr, const int *__restrict__ a_idx,
+                           const int *__restrict__ b_ptr, long long *__restrict__ out) {
+  const int warp = (blockIdx.x * OP_THREADS + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  long long t = 0;
+  for (int k = a_ptr[warp] + lane; k < a_ptr[warp + 1]; k += 32) t += b_ptr[a_idx[k] + 1] - b_ptr[a_idx[k]];
   t = warp_sum(t);
-  if (lane_id() == 0 && t) atomicAdd(total, t);
+  if (lane == 0) out[warp] = t;
 }
 
+// dst[i] = src[i] + add  (row pointers of one chunk into the final indptr)
+__global__ void __launch_bounds__(OP_THREADS)
+offset_copy_kernel(long long n, const int *__restrict__ src, int add, int *__restrict__ dst) {
+  const long long i = static_cast<long long>(blockIdx.x) * OP_THREADS + threadIdx.x;
+  if (i < n) dst[i] = src[i] + add;
+}
+
+// Partial products one chunk of rows may expand to.  Bounds the intermediate of A*B (16-20 bytes per product plus the
+// sort's ping-pong buffers): 2^26 products ~ 2.5 GB.  QDSP_SPGEMM_CHUNK overrides (tests force several chunks with it).
+static long long spgemm_chunk_products() {
+  if (const char *e = std::getenv("QDSP_SPGEMM_CHUNK")) {
+    const long long v = std::atoll(e);
+    if (v > 0) return std::min<long long>(v, 1ll << 29);
+  }
+  return 1ll << 26;
+}
+
+// A*B (cusparseSpGEMM, sparse_matrix.cpp:522-598) by expand - sort - collapse, in row chunks: the rows of A are cut so
+// that no chunk expands to more than spgemm_chunk_products() partial products (a single heavier row forms its own chunk,
+// up to the sort's 2^30 limit); each chunk becomes the CSR of its rows through the same deterministic pipeline as the
+// builder, and the chunks are concatenated.  The result does not depend on the chunking: every output entry is the sum of
+// its partial products in (A entry, B entry) order.
 std::unique_ptr<CsrMatrix> CsrMatrix::matmul(const CsrMatrix &b, cudaStream_t stream) const {
   QDSP_REQUIRE(cols == b.rows, QDSP_ERR_INVALID, "sparse matrix product: dimension mismatch");
   QDSP_REQUIRE(dtype == b.dtype, QDSP_ERR_INVALID, "sparse matrix product: dtype mismatch");
@@ -126,31 +154,82 @@ std::unique_ptr<CsrMatrix> CsrMatrix::matmul(const CsrMatrix &b, cudaStream_t st
     DeviceBuffer dummy(16);
     return from_device_coo(rows, b.cols, 0, dummy.get<int>(), dummy.get<int>(), dummy.get(), dtype, stream);
   }
-  DeviceBuffer a_row(sizeof(int) * nnz), cnt(sizeof(int) * nnz + 64), scan_tmp(scan_tmp_bytes(nnz));
-  expand_rows(*this, a_row.get<int>(), 0, stream);
-  spgemm_count_kernel<<<grid_for(nnz), OP_THREADS, 0, stream>>>(nnz, indices.get<int>(), b.indptr.get<int>(), cnt.get<int>());
+  // symbolic pass: products per row, then the chunk boundaries on the host
+  DeviceBuffer d_rowprod(sizeof(long long) * rows);
+  spgemm_row_products_kernel<<<grid_for(static_cast<long long>(rows) * 32), OP_THREADS, 0, stream>>>(
+      rows, indptr.get<int>(), indices.get<int>(), b.indptr.get<int>(), d_rowprod.get<long long>());
   QDSP_LAUNCH_CHECK();
-  DeviceBuffer total64(sizeof(unsigned long long));
-  QDSP_CUDA(cudaMemsetAsync(total64.get(), 0, sizeof(unsigned long long), stream));
-  sum_counts_kernel<<<std::min<int64_t>(grid_for(nnz), 1184), OP_THREADS, 0, stream>>>(nnz, cnt.get<int>(), total64.get<unsigned long long>());
-  QDSP_LAUNCH_CHECK();
-  unsigned long long total_ull = 0;
-  QDSP_CUDA(cudaMemcpyAsync(&total_ull, total64.get(), sizeof(total_ull), cudaMemcpyDeviceToHost, stream));
+  std::vector<long long> rowprod(rows);
+  std::vector<int> a_ptr(rows + 1);
+  QDSP_CUDA(cudaMemcpyAsync(rowprod.data(), d_rowprod.get(), sizeof(long long) * rows, cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaMemcpyAsync(a_ptr.data(), indptr.get(), sizeof(int) * (rows + 1), cudaMemcpyDeviceToHost, stream));
   QDSP_CUDA(cudaStreamSynchronize(stream));
-  // the expansion is sorted by the onesweep sort (< 2^30 items); the reference (cusparseSpGEMM) errors out as well when
-  // its work buffers do not fit
-  QDSP_REQUIRE(total_ull < (1ull << 30), QDSP_ERR_UNSUPPORTED,
-               "sparse matrix product: more than 2^30 partial products (intermediate does not fit one sort)");
-  const int total = static_cast<int>(total_ull);
-  inclusive_scan_i32(cnt.get<int>(), nnz, scan_tmp.get(), scan_tmp.bytes(), stream);
+  const long long bound = spgemm_chunk_products();
+  std::vector<int> cuts{0};
+  std::vector<long long> chunk_total;
+  long long acc = 0;
+  for (int r = 0; r < rows; ++r) {
+    // the reference (cusparseSpGEMM) errors out as well when its work buffers do not fit
+    QDSP_REQUIRE(rowprod[r] < (1ll << 30), QDSP_ERR_UNSUPPORTED,
+                 "sparse matrix product: one row expands to more than 2^30 partial products");
+    if (acc > 0 && acc + rowprod[r] > bound) {
+      cuts.push_back(r);
+      chunk_total.push_back(acc);
+      acc = 0;
+    }
+    acc += rowprod[r];
+  }
+  cuts.push_back(rows);
+  chunk_total.push_back(acc);
   const size_t vb = value_bytes();
-  DeviceBuffer o_row(sizeof(int) * std::max(total, 1)), o_col(sizeof(int) * std::max(total, 1)), o_val(vb * std::max(total, 1));
-  if (dtype == QDSP_F32)
-    spgemm_expand_kernel<float><<<grid_for(nnz), OP_THREADS, 0, stream>>>(nnz, a_row.get<int>(), indices.get<int>(), values.get<float>(), b.indptr.get<int>(), b.indices.get<int>(), b.values.get<float>(), cnt.get<int>(), o_row.get<int>(), o_col.get<int>(), o_val.get<float>());
-  else
-    spgemm_expand_kernel<double><<<grid_for(nnz), OP_THREADS, 0, stream>>>(nnz, a_row.get<int>(), indices.get<int>(), values.get<double>(), b.indptr.get<int>(), b.indices.get<int>(), b.values.get<double>(), cnt.get<int>(), o_row.get<int>(), o_col.get<int>(), o_val.get<double>());
-  QDSP_LAUNCH_CHECK();
-  auto out = from_device_coo(rows, b.cols, total, o_row.get<int>(), o_col.get<int>(), o_val.get(), dtype, stream);
+  std::vector<std::unique_ptr<CsrMatrix>> parts;
+  for (size_t ch = 0; ch + 1 < cuts.size(); ++ch) {
+    const int r0 = cuts[ch], r1 = cuts[ch + 1];
+    const long long k0 = a_ptr[r0], nk = a_ptr[r1] - k0;
+    const int total = static_cast<int>(chunk_total[ch]);
+    if (nk == 0 || total == 0) {
+      DeviceBuffer dummy(16);
+      parts.push_back(from_device_coo(r1 - r0, b.cols, 0, dummy.get<int>(), dummy.get<int>(), dummy.get(), dtype, stream));
+      continue;
+    }
+    DeviceBuffer a_row(sizeof(int) * nk), cnt(sizeof(int) * nk + 64), scan_tmp(scan_tmp_bytes(nk));
+    expand_rows_kernel<<<grid_for(static_cast<long long>(r1 - r0) * 32), OP_THREADS, 0, stream>>>(
+        r1 - r0, indptr.get<int>() + r0, a_row.get<int>(), -k0);
+    QDSP_LAUNCH_CHECK();
+    spgemm_count_kernel<<<grid_for(nk), OP_THREADS, 0, stream>>>(nk, indices.get<int>() + k0, b.indptr.get<int>(), cnt.get<int>());
+    QDSP_LAUNCH_CHECK();
+    inclusive_scan_i32(cnt.get<int>(), nk, scan_tmp.get(), scan_tmp.bytes(), stream);
+    DeviceBuffer o_row(sizeof(int) * total), o_col(sizeof(int) * total), o_val(vb * total);
+    if (dtype == QDSP_F32)
+      spgemm_expand_kernel<float><<<grid_for(nk), OP_THREADS, 0, stream>>>(nk, a_row.get<int>(), indices.get<int>() + k0, values.get<float>() + k0, b.indptr.get<int>(), b.indices.get<int>(), b.values.get<float>(), cnt.get<int>(), o_row.get<int>(), o_col.get<int>(), o_val.get<float>());
+    else
+      spgemm_expand_kernel<double><<<grid_for(nk), OP_THREADS, 0, stream>>>(nk, a_row.get<int>(), indices.get<int>() + k0, values.get<double>() + k0, b.indptr.get<int>(), b.indices.get<int>(), b.values.get<double>(), cnt.get<int>(), o_row.get<int>(), o_col.get<int>(), o_val.get<double>());
+    QDSP_LAUNCH_CHECK();
+    parts.push_back(from_device_coo(r1 - r0, b.cols, total, o_row.get<int>(), o_col.get<int>(), o_val.get(), dtype, stream));
+  }
+  if (parts.size() == 1) {
+    parts[0]->row_major_order = row_major_order;
+    return std::move(parts[0]);
+  }
+  long long out_nnz = 0;
+  for (auto &p : parts) out_nnz += p->nnz;
+  QDSP_REQUIRE(out_nnz < (1ll << 31), QDSP_ERR_UNSUPPORTED, "sparse matrix product: more than 2^31 non-zeros (INDEX_32I)");
+  auto out = std::make_unique<CsrMatrix>();
+  out->allocate(rows, b.cols, out_nnz, dtype);
+  long long at = 0;
+  for (size_t ch = 0; ch < parts.size(); ++ch) {
+    const CsrMatrix &p = *parts[ch];
+    const int r0 = cuts[ch];
+    offset_copy_kernel<<<grid_for(p.rows + 1), OP_THREADS, 0, stream>>>(p.rows + 1, p.indptr.get<int>(), static_cast<int>(at),
+                                                                      out->indptr.get<int>() + r0);
+    QDSP_LAUNCH_CHECK();
+    if (p.nnz) {
+      QDSP_CUDA(cudaMemcpyAsync(out->indices.get<int>() + at, p.indices.get(), sizeof(int) * p.nnz, cudaMemcpyDeviceToDevice, stream));
+      QDSP_CUDA(cudaMemcpyAsync(static_cast<char *>(out->values.get()) + vb * at, p.values.get(), vb * p.nnz, cudaMemcpyDeviceToDevice, stream));
+    }
+    at += p.nnz;
+  }
+  QDSP_CUDA(cudaStreamSynchronize(stream));  // the chunk matrices are released on return
   out->row_major_order = row_major_order;
   return out;
 }

@@ -1,0 +1,142 @@
+"""N3: the device matrix algebra (A +- B, alpha A, A^T, A B; quadrants/program/sparse_matrix.cpp:413-652) beyond the
+reference's 5x4 toy test (tests/python/test_sparse_matrix.py:454-523), against scipy on the same inputs.
+
+Bars: indptr / indices bit-exact for every op (canonical CSR: rows ascending, columns ascending, structural zeros from
+cancellation kept like cusparse's csrgeam2 / SpGEMM keep them -- compared after scipy's pattern is taken WITHOUT
+eliminate_zeros); values bit-exact for +, -, scaling and transpose (one rounding each, no reassociation); A B within
+1e-5 (fp32) / 1e-12 (fp64) of sum |a_ik b_kj| (the summation order differs from scipy's).  Needs a B200.
+"""
+import os
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def qd():
+    import quadrants_b200 as qd
+
+    qd.init(arch=qd.cuda)
+    return qd
+
+
+def rand_csr(n, m, nnz, seed, dt):
+    rng = np.random.default_rng(seed)
+    r = rng.integers(0, n, nnz)
+    c = rng.integers(0, m, nnz)
+    v = rng.uniform(-1, 1, nnz).astype(dt)
+    a = sp.coo_matrix((v, (r, c)), shape=(n, m)).tocsr()  # duplicates summed (few)
+    a.sort_indices()
+    return a
+
+
+def to_qd(qd, a):
+    dt = qd.f32 if a.dtype == np.float32 else qd.f64
+    coo = a.tocoo()
+    K = qd.linalg.SparseMatrixBuilder(a.shape[0], a.shape[1], max_num_triplets=max(coo.nnz, 1), dtype=dt)
+    K.insert_triplets(coo.row.astype(np.int32), coo.col.astype(np.int32), coo.data)
+    return K.build()
+
+
+def arrays(Q):
+    ip, ix, v = Q.matrix.to_scipy_arrays()
+    return ip, ix, v
+
+
+def same_pattern(Q, S):
+    S = S.tocsr()
+    S.sort_indices()
+    ip, ix, v = arrays(Q)
+    assert Q.shape == S.shape
+    assert np.array_equal(ip, S.indptr) and np.array_equal(ix, S.indices)
+    return v, S.data
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32 if a.dtype.itemsize == 4 else np.uint64)
+
+
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+def test_add_sub_scale_transpose_200k(qd, dt):
+    n, m = 200_000, 150_000
+    S1, S2 = rand_csr(n, m, 2_000_000, 1, dt), rand_csr(n, m, 1_500_000, 2, dt)
+    A, B = to_qd(qd, S1), to_qd(qd, S2)
+    v, ref = same_pattern(A, S1)
+    assert np.array_equal(bits(v), bits(ref))
+    for Q, S in ((A + B, S1 + S2), (A - B, S1 - S2), (A * 2.5, S1 * dt(2.5)), (2.5 * A, S1 * dt(2.5)),
+                 (A.transpose(), S1.T)):
+        v, ref = same_pattern(Q, S)
+        assert np.array_equal(bits(v), bits(ref.astype(dt)))
+    # A - A: every entry cancels; the pattern stays (csrgeam2 keeps structural zeros)
+    Z = A - A
+    ip, ix, v = arrays(Z)
+    assert np.array_equal(ip, S1.indptr) and np.array_equal(ix, S1.indices) and not v.any()
+
+
+def check_product(Q, S1, S2, dt):
+    P = (S1 @ S2).tocsr()
+    P.sort_indices()
+    scale = (abs(S1) @ abs(S2)).tocsr()
+    scale.sort_indices()
+    ip, ix, v = arrays(Q)
+    # scipy drops nothing either: the pattern of |A| |B| is the structural pattern
+    assert np.array_equal(ip, scale.indptr) and np.array_equal(ix, scale.indices)
+    Pd = np.zeros(scale.nnz, np.float64)
+    # align P (which may have dropped exact-zero sums on some scipy versions) onto the structural pattern
+    key_s = np.repeat(np.arange(scale.shape[0]), np.diff(scale.indptr)).astype(np.int64) * scale.shape[1] + scale.indices
+    key_p = np.repeat(np.arange(P.shape[0]), np.diff(P.indptr)).astype(np.int64) * P.shape[1] + P.indices
+    Pd[np.searchsorted(key_s, key_p)] = P.data
+    eps = 1e-5 if dt == np.float32 else 1e-12
+    assert np.all(np.abs(v.astype(np.float64) - Pd) <= eps * scale.data + 1e-300)
+    return ip, ix, v
+
+
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+def test_matmul_200k_and_chunking_is_invisible(qd, dt):
+    n = 200_000
+    S1, S2 = rand_csr(n, n, 1_200_000, 3, dt), rand_csr(n, n, 1_400_000, 4, dt)
+    A, B = to_qd(qd, S1), to_qd(qd, S2)
+    ip, ix, v = check_product(A @ B, S1, S2, dt)
+    os.environ["QDSP_SPGEMM_CHUNK"] = "1000000"  # ~9 chunks
+    try:
+        ip2, ix2, v2 = arrays(A @ B)
+    finally:
+        del os.environ["QDSP_SPGEMM_CHUNK"]
+    assert np.array_equal(ip, ip2) and np.array_equal(ix, ix2) and np.array_equal(bits(v), bits(v2))
+    # (A B)^T == B^T A^T structurally and to rounding
+    T1 = (A @ B).transpose()
+    T2 = B.transpose() @ A.transpose()
+    a1, a2 = arrays(T1), arrays(T2)
+    assert np.array_equal(a1[0], a2[0]) and np.array_equal(a1[1], a2[1])
+    assert np.allclose(a1[2], a2[2], rtol=1e-4 if dt == np.float32 else 1e-11, atol=1e-6 if dt == np.float32 else 1e-13)
+
+
+def test_matmul_poisson_1m_rows(qd):
+    """A A for the 1000 x 1000 5-point Laplacian (10^6 rows, 5 M nnz -> 13-point stencil, 25 M partial products)."""
+    nx = 1000
+    T = sp.diags([-1.0, 2.0, -1.0], [-1, 0, 1], shape=(nx, nx), format="csr")
+    I = sp.identity(nx, format="csr")
+    S = (sp.kron(I, T) + sp.kron(T, I)).tocsr()
+    S.eliminate_zeros()
+    S.sort_indices()
+    A = to_qd(qd, S)
+    ip, ix, v = check_product(A @ A, S, S, np.float64)
+    assert ip[-1] == (S @ S).nnz
+    # integer-valued matrix: the product is exact in any order
+    P = (S @ S).tocsr()
+    P.sort_indices()
+    assert np.array_equal(v, P.data)
+
+
+def test_matmul_errors_and_empty(qd):
+    S1 = rand_csr(50, 40, 300, 5, np.float32)
+    S2 = rand_csr(30, 20, 100, 6, np.float32)
+    A, B = to_qd(qd, S1), to_qd(qd, S2)
+    with pytest.raises(AssertionError):
+        A @ B
+    E = to_qd(qd, sp.csr_matrix((40, 20), dtype=np.float32))
+    Q = A @ E
+    assert Q.shape == (50, 20) and arrays(Q)[0][-1] == 0

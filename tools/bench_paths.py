@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Secondary throughput harness (NOT the driver's bench line): the other BASELINE.json configs on one B200.
 
-    python tools/bench_paths.py [c1] [scan] [sort] [build] [fem] [algos]        # default: all, one JSON line per config
+    python tools/bench_paths.py [c1] [scan] [sort] [build] [fem] [algos] [solver] [algebra]       # default: all, one JSON line per config
 
 C1  2-D Poisson 512 x 512 fp32: build, SpMV, SparseCG to 1e-6 (the reference's CPU-runnable case)
 C3  inclusive scan and key-value sort of 2^28 random i32                     (byte models of SURVEY 8(d))
@@ -250,13 +250,94 @@ def bench_algos(lib, stream):
          mtriplets_per_s=round(t / timed(run, 3, setup=reset) / 1e3, 1))
 
 
+def emit_plain(name, **kv):
+    print(json.dumps({"config": name, **kv}), flush=True)
+
+
+def bench_solver(lib, stream):
+    """A16: qd.linalg.SparseSolver (device LLT / LU) on 2-D Poisson matrices, fp64; the reference's Eigen SimplicialLLT
+    (AMD) on the host cores beside it when oracle/_ref is on the box.  Latency-bound (dependency chain), not HBM-bound:
+    reported as times, factor size and multiply-add rate."""
+    import time
+    from tests import workloads as W
+    import oracle
+    ref = oracle.EigenRef() if oracle.EigenRef.available() else None
+    for nx in (128, 256, 512):
+        n = nx * nx
+        r, c, v = W.poisson2d_triplets(nx, dtype=np.float64)
+        K = qd.linalg.SparseMatrixBuilder(n, n, max_num_triplets=int(r.shape[0]), dtype=qd.f64)
+        K.insert_triplets(r.astype(np.int32), c.astype(np.int32), v)
+        A = K.build()
+        b = qd.ndarray(qd.f64, n); b.tensor.uniform_(-1, 1)
+        for st in ("LLT", "LU"):
+            s = qd.linalg.SparseSolver(dtype=qd.f64, solver_type=st)
+            t0 = time.perf_counter(); s.analyze_pattern(A); t_an = (time.perf_counter() - t0) * 1e3
+            s.factorize(A)
+            ms_f = timed(lambda: s.factorize(A), 3)
+            x = s.solve(b)
+            ms_s = timed(lambda: s.solve(b), 5)
+            res = (A @ x).tensor - b.tensor
+            stt = s.solver.stats()
+            extra = {}
+            if ref is not None and st == "LLT":
+                m = ref.matrix(oracle.make_triplet_buffer(r, c, v, np.float64), n, n, row_major=False)
+                t0 = time.perf_counter(); m.direct_solve(b.to_numpy(), "LLT", "AMD"); extra["eigen_host_total_ms"] = round((time.perf_counter() - t0) * 1e3, 2)
+            emit_plain(f"A16 SparseSolver {st} fp64, 2-D Poisson {nx}x{nx}", rows=n, factor_nnz=stt["factor_nnz"],
+                       etree_height=stt["etree_height"], analyze_host_ms=round(t_an, 2), factorize_ms=round(ms_f, 3),
+                       solve_ms=round(ms_s, 3), gmadd_per_s=round(stt["flops"] * (2 if st == "LU" else 1) / 2 / ms_f / 1e6, 2),
+                       rel_residual=float(res.norm() / b.tensor.norm()), **extra)
+
+
+def bench_algebra(lib, stream):
+    """N3: A + B, A^T, A B on the device (expand -> onesweep sort -> collapse), fp32, against the bytes each must move."""
+    n, nnz = 4_000_000, 40_000_000
+    g = torch.Generator(device="cuda").manual_seed(1)
+    def mk(seed):
+        g.manual_seed(seed)
+        r = torch.randint(0, n, (nnz,), device="cuda", generator=g, dtype=torch.int32)
+        c = torch.randint(0, n, (nnz,), device="cuda", generator=g, dtype=torch.int32)
+        v = torch.rand(nnz, device="cuda", generator=g) * 2 - 1
+        K = qd.linalg.SparseMatrixBuilder(n, n, max_num_triplets=nnz, dtype=qd.f32)
+        K.insert_triplets(r, c, v)
+        return K.build()
+    A, B = mk(1), mk(2)
+    na, nb = A.matrix.nnz(), B.matrix.nnz()
+    out = []
+    for name, fn, model in (("A + B", lambda: out.append(A + B), (na + nb) * 8 * 2 + 2 * (n + 1) * 4),
+                            ("A^T", lambda: out.append(A.transpose()), na * 8 * 2 + 2 * (n + 1) * 4)):
+        fn(); out.clear()
+        ms = timed(fn, 3, setup=out.clear)
+        emit(f"N3 {name}, {n} x {n}, {na} nnz fp32 (model: read operands + write result once)", ms, model,
+             result_nnz=int(out[0].matrix.nnz()))
+        out.clear()
+    del B
+    torch.cuda.empty_cache()
+    m2 = 1_000_000
+    g.manual_seed(3)
+    def mk2(seed, k):
+        g.manual_seed(seed)
+        r = torch.randint(0, m2, (k,), device="cuda", generator=g, dtype=torch.int32)
+        c = torch.randint(0, m2, (k,), device="cuda", generator=g, dtype=torch.int32)
+        v = torch.rand(k, device="cuda", generator=g) * 2 - 1
+        K = qd.linalg.SparseMatrixBuilder(m2, m2, max_num_triplets=k, dtype=qd.f32)
+        K.insert_triplets(r, c, v)
+        return K.build()
+    P, Q = mk2(4, 8_000_000), mk2(5, 8_000_000)
+    fn = lambda: out.append(P @ Q)
+    fn(); prod_nnz = int(out[0].matrix.nnz()); out.clear()
+    ms = timed(fn, 3, setup=out.clear)
+    emit_plain(f"N3 A B, {m2} x {m2}, 8 M nnz each fp32 (~64 M partial products)", ms=round(ms, 3), result_nnz=prod_nnz,
+               mproducts_per_s=round(64.0 / ms * 1e3, 1))
+
+
 def main():
     qd.init(arch=qd.cuda, device=0)
     lib = _lib.load()
     stream = torch.cuda.current_stream().cuda_stream
-    which = sys.argv[1:] or ["c1", "scan", "sort", "build", "fem", "algos"]
+    which = sys.argv[1:] or ["c1", "scan", "sort", "build", "fem", "algos", "solver", "algebra"]
     for w in which:
-        {"c1": bench_c1, "scan": bench_scan, "sort": bench_sort, "build": bench_build, "fem": bench_fem, "algos": bench_algos}[w](lib, stream)
+        {"c1": bench_c1, "scan": bench_scan, "sort": bench_sort, "build": bench_build, "fem": bench_fem, "algos": bench_algos, "solver": bench_solver,
+         "algebra": bench_algebra}[w](lib, stream)
         torch.cuda.empty_cache()
 
 
