@@ -284,6 +284,20 @@ int qdsp_solver_analyze_host(int n, const int32_t *indptr, const int32_t *indice
                              int32_t *parent_out, int32_t *colptr_out, int32_t *rowidx_out, int64_t rowidx_capacity,
                              int64_t *factor_nnz, int *etree_height);
 
+/* ---- dense vector kernels of MatrixFreeCG / MatrixFreeBICGSTAB (python/quadrants/linalg/matrixfree_cg.py:23-310) --------
+ * The reference JIT-compiles `reduce`, `update_x`, `update_r`, `update_p`, ... per solve; these are their device
+ * counterparts.  Vectors are dense device arrays of n elements of `dtype`; dot products are accumulated in double in a
+ * fixed order (reproducible) and returned to the host (the reference's reduce kernels return host scalars too). */
+/* out[0] = a.b and, when c and d are given, out[1] = c.d, in one pass. */
+int qdsp_vec_dot2(const void *a, const void *b, const void *c, const void *d, int64_t n, int dtype, void *stream,
+                  double *out);
+/* out = sum_{i<k} coefs[i] * xs[i], 1 <= k <= 4; `out` may alias any xs[i]. */
+int qdsp_vec_lincomb(void *out, int64_t n, int dtype, int k, const void *const *xs, const double *coefs, void *stream);
+/* update_x + update_r + reduce(r, r) of the CG loop (matrixfree_cg.py:84-98,116-119) fused into one pass:
+ * x += alpha p, r -= alpha ap, *rr = r.r. */
+int qdsp_vec_cg_step(void *x, void *r, const void *p, const void *ap, double alpha, int64_t n, int dtype, void *stream,
+                     double *rr);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

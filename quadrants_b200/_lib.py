@@ -83,6 +83,9 @@ SIGNATURES = {
     "qdsp_sort": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "qdsp_builder_append": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
     "qdsp_builder_append_elements": (_i, [_vp, _vp, _vp, _i64, _i, _vp]),
+    "qdsp_vec_dot2": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp, _P(_d)]),
+    "qdsp_vec_lincomb": (_i, [_vp, _i64, _i, _i, _P(_vp), _P(_d), _vp]),
+    "qdsp_vec_cg_step": (_i, [_vp, _vp, _vp, _vp, _d, _i64, _i, _vp, _P(_d)]),
     "qdsp_solver_create": (_i, [_i, _i, _i, _P(_vp)]),
     "qdsp_solver_analyze_pattern": (_i, [_vp, _vp, _vp]),
     "qdsp_solver_factorize": (_i, [_vp, _vp, _vp, _P(_i), _P(_i)]),

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libqdsp.so")
-SOURCES = ["abi.cu", "scan.cu", "radix_sort.cu", "device_algos.cu", "csr_build.cu", "csr_ops.cu", "spmv.cu", "cg.cu", "dist.cu", "solver.cu"]
+SOURCES = ["abi.cu", "scan.cu", "radix_sort.cu", "device_algos.cu", "csr_build.cu", "csr_ops.cu", "spmv.cu", "cg.cu", "dist.cu", "solver.cu", "krylov.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",  # B200 only: no PTX for other architectures, no fallback
     "-std=c++17", "-O3", "-lineinfo",

@@ -444,4 +444,17 @@ int qdsp_solver_analyze_host(int n, const int32_t *indptr, const int32_t *indice
   });
 }
 
+// ---- dense vector kernels (krylov.cu) --------------------------------------------------------------------------------------------
+int qdsp_vec_dot2(const void *a, const void *b, const void *c, const void *d, int64_t n, int dtype, void *stream,
+                  double *out) {
+  return guarded([&] { vec_dot2(a, b, c, d, n, dtype, S(stream), out); });
+}
+int qdsp_vec_lincomb(void *out, int64_t n, int dtype, int k, const void *const *xs, const double *coefs, void *stream) {
+  return guarded([&] { vec_lincomb(out, n, dtype, k, xs, coefs, S(stream)); });
+}
+int qdsp_vec_cg_step(void *x, void *r, const void *p, const void *ap, double alpha, int64_t n, int dtype, void *stream,
+                     double *rr) {
+  return guarded([&] { vec_cg_step(x, r, p, ap, alpha, n, dtype, S(stream), rr); });
+}
+
 }  // extern "C"

@@ -1107,15 +1107,16 @@ void launch_spmv_dot(CgSolver::Impl &I) {
 template <typename T>
 void launch_spmv_dot_stream(CgSolver::Impl &I) {
   const CsrMatrix &A = I.A;
-  launch_pdl(cg_spmv_dot_stream_kernel<T>, I.spmv_grid, SPMV_THREADS, spmv_stream_smem_bytes<T>(), I.stream, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+  launch_pdl(cg_spmv_dot_stream_kernel<T>, I.spmv_grid, SPMV_THREADS, spmv_stream_smem_bytes<T>(A.spmv_plan_hot_n > 0), I.stream, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
       spmv_plan_dev(A), I.scalars.get<CgScalars>(), I.partials.get<double>(), I.dev(), I.use_nccl);
 }
 
 template <typename T>
-int spmv_dot_stream_occupancy() {
-  const size_t smem = spmv_stream_smem_bytes<T>();
+int spmv_dot_stream_occupancy(bool hot) {
+  const size_t smem = spmv_stream_smem_bytes<T>(hot);
   int occ = 0;
-  QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_dot_stream_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_dot_stream_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(spmv_stream_smem_bytes<T>(true))));
   QDSP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, cg_spmv_dot_stream_kernel<T>, SPMV_THREADS, smem));
   return std::max(1, occ);
 }
@@ -1200,7 +1201,7 @@ void fused_launch(CgSolver::Impl &I, T *x, int iters) {
   const int *ip = A.indptr.get<int>(), *ix = A.indices.get<int>();
   const T *vals = A.values.get<T>(), *dinv = I.dinv.get<T>();
   T *p = static_cast<T *>(I.p), *tmp = I.tmp.get<T>(), *r = I.r.get<T>();
-  SpmvPlanDev plan = STREAM ? spmv_plan_dev(A) : SpmvPlanDev{};
+  SpmvPlanDev plan = STREAM ? spmv_plan_dev(A, /*allow_hot=*/false) : SpmvPlanDev{};
   CgScalars *sc = I.scalars.get<CgScalars>();
   double *part = I.partials.get<double>();
   DistDev d = I.dev();
@@ -1491,7 +1492,8 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
   I.lpr = A.spmv_lpr;
   int occ = 1;
   if (A.spmv_mode == 2) {
-    occ = (A.dtype == QDSP_F32) ? spmv_dot_stream_occupancy<float>() : spmv_dot_stream_occupancy<double>();
+    const bool hot = A.spmv_plan_hot_n > 0;
+    occ = (A.dtype == QDSP_F32) ? spmv_dot_stream_occupancy<float>(hot) : spmv_dot_stream_occupancy<double>(hot);
     I.spmv_grid = std::max(1, std::min(A.spmv_plan_nblk, device_props().sm_count * occ));
   } else {
 #define QDSP_CALL(L) occ = (A.dtype == QDSP_F32) ? spmv_dot_occupancy<float, L>() : spmv_dot_occupancy<double, L>()

@@ -55,6 +55,10 @@ class CsrMatrix {
   mutable int spmv_max_block_nnz = 0;  // largest stage footprint of a uniform row block (spmv_prepare)
   mutable DeviceBuffer spmv_plan_blocks, spmv_plan_long, spmv_plan_partials, spmv_plan_ticket;
   mutable int spmv_plan_nblk = 0, spmv_plan_nlong = 0;
+  // stream path, hot columns (spmv_kernels.cuh): the most referenced columns, and `indices` with them stored as ~slot
+  mutable DeviceBuffer spmv_plan_hot_cols, spmv_plan_hot_idx;
+  mutable int spmv_plan_hot_n = 0;
+  mutable double spmv_plan_hot_coverage = 0.0;  // share of the non-zeros whose column is hot
   // work counters of the dynamically scheduled tail of the uniform path (spmv_kernels.cuh SpmvSched): 16 slots used
   // round-robin, so up to 16 products of one matrix may be in flight on different streams
   mutable DeviceBuffer spmv_sched_buf;
@@ -119,7 +123,7 @@ SpmvSched spmv_sched_for(int nblk, int grid, unsigned *counters);
 // pure host: the stream-path work partition (blocks {row0, nrows | -(segment+1), nz0, nz1}; long_rows {row, first segment})
 void spmv_plan_host(const int32_t *indptr, int rows, std::vector<int4> &blocks, std::vector<int2> &long_rows,
                     int &n_segments);
-SpmvPlanDev spmv_plan_dev(const CsrMatrix &A);
+SpmvPlanDev spmv_plan_dev(const CsrMatrix &A, bool allow_hot = true);
 // y = A x with the persistent TMA-fed kernel; `d` (world > 1) makes every CTA wait for the halo of x first (spmv.cu)
 void launch_spmv(const CsrMatrix &A, const void *x, void *y, const DistDev &d, cudaStream_t stream);
 
@@ -139,5 +143,12 @@ class CgSolver {
  private:
   std::unique_ptr<Impl> impl_;
 };
+
+// ---- dense vector kernels of the matrix-free Krylov solvers (krylov.cu; python/quadrants/linalg/matrixfree_cg.py) ------
+void vec_dot2(const void *a, const void *b, const void *c, const void *d, int64_t n, int dtype, cudaStream_t stream,
+              double *out);
+void vec_lincomb(void *out, int64_t n, int dtype, int k, const void *const *xs, const double *coefs, cudaStream_t stream);
+void vec_cg_step(void *x, void *r, const void *p, const void *ap, double alpha, int64_t n, int dtype, cudaStream_t stream,
+                 double *rr);
 
 }  // namespace qdsp

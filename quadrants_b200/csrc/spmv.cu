@@ -81,6 +81,62 @@ __global__ void __launch_bounds__(256) row_stats_kernel(int rows, int R, const i
   }
 }
 
+// ---- hot columns of the stream path (spmv_kernels.cuh) ------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) col_hist_kernel(int64_t nnz, int cols, const int *__restrict__ idx, int *__restrict__ counts) {
+  for (int64_t k = blockIdx.x * int64_t{256} + threadIdx.x; k < nnz; k += static_cast<int64_t>(gridDim.x) * 256) {
+    const int c = idx[k];
+    if (c >= 0 && c < cols) atomicAdd(counts + c, 1);
+  }
+}
+__global__ void __launch_bounds__(256) hot_remap_kernel(int64_t nnz, int cols, const int *__restrict__ idx,
+                                                        const int *__restrict__ slot_of, int *__restrict__ out) {
+  for (int64_t k = blockIdx.x * int64_t{256} + threadIdx.x; k < nnz; k += static_cast<int64_t>(gridDim.x) * 256) {
+    const int c = idx[k];
+    const int s = (c >= 0 && c < cols) ? slot_of[c] : -1;
+    out[k] = s >= 0 ? ~s : c;
+  }
+}
+
+// Picks the K = SPMV_HOT_BYTES / sizeof(T) most referenced columns (ties: lower column id) when they carry at least 15 %
+// of the non-zeros.  QDSP_SPMV_HOT=0 switches the cache off (measurement aid).
+static void spmv_plan_hot(const CsrMatrix &A, cudaStream_t stream) {
+  A.spmv_plan_hot_n = 0;
+  A.spmv_plan_hot_coverage = 0.0;
+  static const bool on = [] { const char *e = std::getenv("QDSP_SPMV_HOT"); return !(e && e[0] == '0'); }();
+  if (!on || A.nnz == 0 || A.cols == 0) return;
+  const int K = std::min<int>(A.cols, SPMV_HOT_BYTES / static_cast<int>(A.value_bytes()));
+  DeviceBuffer counts(sizeof(int) * static_cast<size_t>(A.cols));
+  QDSP_CUDA(cudaMemsetAsync(counts.get(), 0, counts.bytes(), stream));
+  const int grid = std::max(1, std::min(device_props().sm_count * 8, ceil_div(A.nnz, 256)));
+  col_hist_kernel<<<grid, 256, 0, stream>>>(A.nnz, A.cols, A.indices.get<int>(), counts.get<int>());
+  QDSP_LAUNCH_CHECK();
+  std::vector<int> h(A.cols);
+  QDSP_CUDA(cudaMemcpyAsync(h.data(), counts.get(), sizeof(int) * h.size(), cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+  std::vector<int> order(A.cols);
+  for (int i = 0; i < A.cols; ++i) order[i] = i;
+  auto hotter = [&](int a, int b) { return h[a] != h[b] ? h[a] > h[b] : a < b; };
+  if (K < A.cols) std::nth_element(order.begin(), order.begin() + K, order.end(), hotter);
+  order.resize(K);
+  std::sort(order.begin(), order.end());  // ascending ids: the per-CTA load of the hot x entries walks x forwards
+  int64_t covered = 0;
+  for (int c : order) covered += h[c];
+  A.spmv_plan_hot_coverage = static_cast<double>(covered) / static_cast<double>(A.nnz);
+  if (A.spmv_plan_hot_coverage < 0.15) return;
+  std::vector<int> slot_of(A.cols, -1);
+  for (int s = 0; s < K; ++s) slot_of[order[s]] = s;
+  DeviceBuffer d_slot(sizeof(int) * static_cast<size_t>(A.cols));
+  A.spmv_plan_hot_cols.alloc(sizeof(int) * static_cast<size_t>(K));
+  A.spmv_plan_hot_idx.alloc(sizeof(int32_t) * static_cast<size_t>(A.nnz) + 64);  // TMA reads whole 16-byte units
+  QDSP_CUDA(cudaMemcpyAsync(d_slot.get(), slot_of.data(), sizeof(int) * slot_of.size(), cudaMemcpyHostToDevice, stream));
+  QDSP_CUDA(cudaMemcpyAsync(A.spmv_plan_hot_cols.get(), order.data(), sizeof(int) * order.size(), cudaMemcpyHostToDevice, stream));
+  QDSP_CUDA(cudaMemsetAsync(A.spmv_plan_hot_idx.get(), 0, A.spmv_plan_hot_idx.bytes(), stream));
+  hot_remap_kernel<<<grid, 256, 0, stream>>>(A.nnz, A.cols, A.indices.get<int>(), d_slot.get<int>(), A.spmv_plan_hot_idx.get<int>());
+  QDSP_LAUNCH_CHECK();
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+  A.spmv_plan_hot_n = K;
+}
+
 // ---- plan ----------------------------------------------------------------------------------------------------------------
 // Pure host: cuts the rows into stream-path blocks.  blocks: {row0, nrows | -(segment + 1), nz0, nz1};
 // long_rows: {row, first segment} + sentinel.
@@ -158,10 +214,16 @@ void spmv_prepare(const CsrMatrix &A, cudaStream_t stream) {
   A.spmv_plan_nblk = static_cast<int>(blocks.size());
   A.spmv_plan_nlong = static_cast<int>(long_rows.size()) - 1;
   A.spmv_mode = 2;
+  spmv_plan_hot(A, stream);
 }
 
-SpmvPlanDev spmv_plan_dev(const CsrMatrix &A) {
+SpmvPlanDev spmv_plan_dev(const CsrMatrix &A, bool allow_hot) {
   SpmvPlanDev p;
+  if (allow_hot && A.spmv_plan_hot_n > 0) {
+    p.hot_n = A.spmv_plan_hot_n;
+    p.hot_cols = A.spmv_plan_hot_cols.get<int>();
+    p.hot_idx = A.spmv_plan_hot_idx.get<int>();
+  }
   p.blocks = A.spmv_plan_blocks.get<int4>();
   p.nblk = A.spmv_plan_nblk;
   p.n_long = A.spmv_plan_nlong;
@@ -175,10 +237,13 @@ namespace {
 
 template <typename T>
 void launch_spmv_stream(const CsrMatrix &A, const T *x, T *y, const DistDev &d, cudaStream_t stream) {
-  static int occ = 0;
-  const size_t smem = spmv_stream_smem_bytes<T>();
+  static int occs[2] = {0, 0};
+  const bool hot = A.spmv_plan_hot_n > 0;
+  const size_t smem = spmv_stream_smem_bytes<T>(hot);
+  int &occ = occs[hot ? 1 : 0];
   if (occ == 0) {
-    QDSP_CUDA(cudaFuncSetAttribute(spmv_stream_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    QDSP_CUDA(cudaFuncSetAttribute(spmv_stream_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   static_cast<int>(spmv_stream_smem_bytes<T>(true))));
     int o = 0;
     QDSP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, spmv_stream_kernel<T>, SPMV_THREADS, smem));
     occ = std::max(1, o);
