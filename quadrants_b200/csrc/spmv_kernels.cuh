@@ -92,6 +92,37 @@ __device__ __forceinline__ T ld_x(const T *p) {
   else return __ldg(p);
 }
 
+// Explicit shared-memory accesses for the stream path.  The stage pointers are computed from an aligned byte base, so the
+// compiler has lost the address space and emits GENERIC loads (LD.E): those queue behind the SM's outstanding divergent
+// gathers in the global-memory pipe (ncu, profiles/r02ae: a single descriptor read sampled at ~800 cycles) and serialised
+// the eight index reads of a gather batch.  ld.shared / st.shared take the short path.
+__device__ __forceinline__ int lds_i32(const int *p) {
+  int v;
+  asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)));
+  return v;
+}
+__device__ __forceinline__ int4 lds_i32x4(const int *p) {
+  int4 v;
+  asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
+  return v;
+}
+__device__ __forceinline__ float lds_val(const float *p) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(smem_u32(p)));
+  return v;
+}
+__device__ __forceinline__ double lds_val(const double *p) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(smem_u32(p)));
+  return v;
+}
+__device__ __forceinline__ void sts_val(float *p, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(smem_u32(p)), "f"(v) : "memory");
+}
+__device__ __forceinline__ void sts_val(double *p, double v) {
+  asm volatile("st.shared.f64 [%0], %1;" ::"r"(smem_u32(p)), "d"(v) : "memory");
+}
+
 // mbarrier ring of a persistent SpMV: `full` (1 arrival + tx bytes) and `empty` (one arrival per consumer warp) per stage
 template <int STAGES>
 __device__ __forceinline__ void spmv_ring_init(unsigned long long *full, unsigned long long *empty) {
@@ -516,27 +547,25 @@ __device__ __forceinline__ void spmv_stream(unsigned char *smem_raw, const int *
       const unsigned phase = ((ring0 + it) / SPMV_STREAM_STAGES) & 1;
       const SpmvStage<T> st = spmv_stage<T>(base, stage);
       if (!mbar_wait_b<FUSED>(&full[stage], phase)) return;
-      const int4 d = *reinterpret_cast<const int4 *>(st.ptr + SPMV_DESC_SLOT);
+      const int4 d = lds_i32x4(st.ptr + SPMV_DESC_SLOT);
       const int a0 = d.z & ~3;
       const int lo = d.z - a0, cnt = d.w - a0;
       // (1) products, in place
-      // (8 independent gathers in flight per thread: the x of an irregular matrix comes from L2, not L1)
+      // (8 independent gathers in flight per thread: the x of an irregular matrix comes from L2, not L1.  The eight column
+      // ids are read first, the eight gathers issued back to back, the eight products stored last.)
       for (int k = lo + t; k < cnt; k += 8 * SPMV_CONSUMERS) {
-        T xv[8];
+        int c[8];
+        T xv[8], av[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) c[j] = lds_i32(st.idx + min(k + j * SPMV_CONSUMERS, cnt - 1));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) xv[j] = (!FUSED && c[j] < 0) ? lds_val(hot + (~c[j])) : ld_x<FUSED>(x + c[j]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) av[j] = lds_val(st.val + min(k + j * SPMV_CONSUMERS, cnt - 1));
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const int kk = k + j * SPMV_CONSUMERS;
-          T v = T(0);
-          if (kk < cnt) {
-            const int c = st.idx[kk];
-            v = (!FUSED && c < 0) ? hot[~c] : ld_x<FUSED>(x + c);
-          }
-          xv[j] = v;
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int kk = k + j * SPMV_CONSUMERS;
-          if (kk < cnt) st.val[kk] = st.val[kk] * xv[j];
+          if (kk < cnt) sts_val(st.val + kk, av[j] * xv[j]);
         }
       }
       consumer_bar();
@@ -545,17 +574,17 @@ __device__ __forceinline__ void spmv_stream(unsigned char *smem_raw, const int *
         const int nr = d.y, poff = d.x & 3;
         if (nr > SPMV_STREAM_THREAD_ROWS) {
           if (t < nr) {
-            const int b = st.ptr[poff + t] - a0, e = st.ptr[poff + t + 1] - a0;
+            const int b = lds_i32(st.ptr + poff + t) - a0, e = lds_i32(st.ptr + poff + t + 1) - a0;
             T acc = T(0);
-            for (int k = b; k < e; ++k) acc += st.val[k];
+            for (int k = b; k < e; ++k) acc += lds_val(st.val + k);
             y[d.x + t] = acc;
             sink.row(d.x + t, acc, sink.pre(d.x + t, static_cast<const T *>(nullptr), 0));
           }
         } else {
           for (int r = warp; r < nr; r += SPMV_CONSUMERS / 32) {
-            const int b = st.ptr[poff + r] - a0, e = st.ptr[poff + r + 1] - a0;
+            const int b = lds_i32(st.ptr + poff + r) - a0, e = lds_i32(st.ptr + poff + r + 1) - a0;
             T acc = T(0);
-            for (int k = b + lane; k < e; k += 32) acc += st.val[k];
+            for (int k = b + lane; k < e; k += 32) acc += lds_val(st.val + k);
             acc = warp_sum(acc);
             if (lane == 0) {
               y[d.x + r] = acc;
@@ -566,14 +595,14 @@ __device__ __forceinline__ void spmv_stream(unsigned char *smem_raw, const int *
       } else {
         // one segment of a long row: block-wide sum -> partials[segment]
         T acc = T(0);
-        for (int k = lo + t; k < cnt; k += SPMV_CONSUMERS) acc += st.val[k];
+        for (int k = lo + t; k < cnt; k += SPMV_CONSUMERS) acc += lds_val(st.val + k);
         acc = warp_sum(acc);
         T *red = reinterpret_cast<T *>(st.ptr);  // the indptr slice is unused for a segment
-        if (lane == 0) red[warp] = acc;
+        if (lane == 0) sts_val(red + warp, acc);
         consumer_bar();
         if (t == 0) {
           T tot = T(0);
-          for (int w = 0; w < SPMV_CONSUMERS / 32; ++w) tot += red[w];
+          for (int w = 0; w < SPMV_CONSUMERS / 32; ++w) tot += lds_val(red + w);
           static_cast<T *>(plan.partials)[-d.y - 1] = tot;
           sink.segment(d.x, tot);
         }
