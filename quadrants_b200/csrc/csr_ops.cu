@@ -59,6 +59,9 @@ spgemm_expand_kernel(long long nnz_a, const int *__restrict__ a_row, const int *
   }
 }
 
+__device__ __forceinline__ float add_unfused(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double add_unfused(double a, double b) { return __dadd_rn(a, b); }
+
 static unsigned grid_for(long long n) { return static_cast<unsigned>(std::max<long long>(1, (n + OP_THREADS - 1) / OP_THREADS)); }
 
 static void expand_rows(const CsrMatrix &m, int *coo_row, long long offset, cudaStream_t s) {
@@ -82,24 +85,118 @@ std::unique_ptr<CsrMatrix> CsrMatrix::scale(double alpha, cudaStream_t stream) c
   return out;
 }
 
+static std::unique_ptr<CsrMatrix> add_by_sort(const CsrMatrix &a, const CsrMatrix &b, double alpha, double beta, cudaStream_t stream) {
+    const long long nnz = a.nnz;
+  const int rows = a.rows, cols = a.cols, dtype = a.dtype;
+  const long long n = nnz + b.nnz;
+  const size_t vb = a.value_bytes();
+  DeviceBuffer r(sizeof(int) * n), c(sizeof(int) * n), v(vb * n);
+  expand_rows(a, r.get<int>(), 0, stream);
+  expand_rows(b, r.get<int>(), nnz, stream);
+  if (nnz) { copy_int_kernel<<<grid_for(nnz), OP_THREADS, 0, stream>>>(nnz, a.indices.get<int>(), c.get<int>()); QDSP_LAUNCH_CHECK(); }
+  if (b.nnz) { copy_int_kernel<<<grid_for(b.nnz), OP_THREADS, 0, stream>>>(b.nnz, b.indices.get<int>(), c.get<int>() + nnz); QDSP_LAUNCH_CHECK(); }
+  if (dtype == QDSP_F32) {
+    scale_copy<float>(nnz, a.values.get<float>(), alpha, v.get<float>(), stream);
+    scale_copy<float>(b.nnz, b.values.get<float>(), beta, v.get<float>() + nnz, stream);
+  } else {
+    scale_copy<double>(nnz, a.values.get<double>(), alpha, v.get<double>(), stream);
+    scale_copy<double>(b.nnz, b.values.get<double>(), beta, v.get<double>() + nnz, stream);
+  }
+  auto out = CsrMatrix::from_device_coo(rows, cols, n, r.get<int>(), c.get<int>(), v.get(), dtype, stream);
+  out->row_major_order = a.row_major_order;
+  return out;
+}
+
+
+// ---- alpha A + beta B by row-wise merge (cusparseScsrgeam2, sparse_matrix.cpp:413-509) ------------------------------------------
+// Rows of canonical CSR are sorted and duplicate-free, so the union of two rows needs no sort: a two-pointer merge per row,
+// once to count and once to fill -- two passes over the operands and one write of the result instead of the builder's
+// sort of |A| + |B| triplets.  An entry present in both is alpha*a + beta*b with the products rounded first (the order the
+// sort path sums in, and scipy's); structural zeros from cancellation are kept, like csrgeam2.  One thread per row (rows
+// are short where this matters; neighbouring threads read neighbouring rows).  `unsorted` is raised when a row is not
+// strictly ascending -- matrices adopted through qdsp_csr_from_device_csr need not be canonical -- and the caller then
+// takes the sort path above.
+__global__ void __launch_bounds__(OP_THREADS)
+geam_count_kernel(int rows, const int *__restrict__ a_ptr, const int *__restrict__ a_idx, const int *__restrict__ b_ptr,
+                  const int *__restrict__ b_idx, int *__restrict__ out_cnt, int *__restrict__ unsorted) {
+  const int r = blockIdx.x * OP_THREADS + threadIdx.x;
+  if (r >= rows) return;
+  int i = a_ptr[r], j = b_ptr[r];
+  const int ie = a_ptr[r + 1], je = b_ptr[r + 1];
+  int n = 0, last = -1;
+  bool bad = false;
+  while (i < ie && j < je) {
+    const int ca = a_idx[i], cb = b_idx[j];
+    const int c = min(ca, cb);
+    bad |= c <= last;
+    last = c;
+    i += ca <= cb;
+    j += cb <= ca;
+    ++n;
+  }
+  for (; i < ie; ++i, ++n) { bad |= a_idx[i] <= last; last = a_idx[i]; }
+  for (; j < je; ++j, ++n) { bad |= b_idx[j] <= last; last = b_idx[j]; }
+  out_cnt[r] = n;
+  if (bad) *unsorted = 1;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(OP_THREADS)
+geam_fill_kernel(int rows, const int *__restrict__ a_ptr, const int *__restrict__ a_idx, const T *__restrict__ a_val,
+                 const int *__restrict__ b_ptr, const int *__restrict__ b_idx, const T *__restrict__ b_val, T alpha, T beta,
+                 const int *__restrict__ o_ptr, int *__restrict__ o_idx, T *__restrict__ o_val) {
+  const int r = blockIdx.x * OP_THREADS + threadIdx.x;
+  if (r >= rows) return;
+  int i = a_ptr[r], j = b_ptr[r], o = o_ptr[r];
+  const int ie = a_ptr[r + 1], je = b_ptr[r + 1];
+  while (i < ie && j < je) {
+    const int ca = a_idx[i], cb = b_idx[j];
+    T v;
+    if (ca < cb) { v = alpha * a_val[i]; ++i; }
+    else if (cb < ca) { v = beta * b_val[j]; ++j; }
+    else {
+      const T pa = alpha * a_val[i], pb = beta * b_val[j];
+      v = add_unfused(pa, pb);
+      ++i; ++j;
+    }
+    o_idx[o] = min(ca, cb);
+    o_val[o] = v;
+    ++o;
+  }
+  for (; i < ie; ++i, ++o) { o_idx[o] = a_idx[i]; o_val[o] = alpha * a_val[i]; }
+  for (; j < je; ++j, ++o) { o_idx[o] = b_idx[j]; o_val[o] = beta * b_val[j]; }
+}
+
 std::unique_ptr<CsrMatrix> CsrMatrix::add(const CsrMatrix &b, double alpha, double beta, cudaStream_t stream) const {
   QDSP_REQUIRE(rows == b.rows && cols == b.cols, QDSP_ERR_INVALID, "sparse matrix addition: dimension mismatch");
   QDSP_REQUIRE(dtype == b.dtype, QDSP_ERR_INVALID, "sparse matrix addition: dtype mismatch");
-  const long long n = nnz + b.nnz;
-  const size_t vb = value_bytes();
-  DeviceBuffer r(sizeof(int) * n), c(sizeof(int) * n), v(vb * n);
-  expand_rows(*this, r.get<int>(), 0, stream);
-  expand_rows(b, r.get<int>(), nnz, stream);
-  if (nnz) { copy_int_kernel<<<grid_for(nnz), OP_THREADS, 0, stream>>>(nnz, indices.get<int>(), c.get<int>()); QDSP_LAUNCH_CHECK(); }
-  if (b.nnz) { copy_int_kernel<<<grid_for(b.nnz), OP_THREADS, 0, stream>>>(b.nnz, b.indices.get<int>(), c.get<int>() + nnz); QDSP_LAUNCH_CHECK(); }
-  if (dtype == QDSP_F32) {
-    scale_copy<float>(nnz, values.get<float>(), alpha, v.get<float>(), stream);
-    scale_copy<float>(b.nnz, b.values.get<float>(), beta, v.get<float>() + nnz, stream);
-  } else {
-    scale_copy<double>(nnz, values.get<double>(), alpha, v.get<double>(), stream);
-    scale_copy<double>(b.nnz, b.values.get<double>(), beta, v.get<double>() + nnz, stream);
-  }
-  auto out = from_device_coo(rows, cols, n, r.get<int>(), c.get<int>(), v.get(), dtype, stream);
+  auto out = std::make_unique<CsrMatrix>();
+  out->rows = rows; out->cols = cols; out->dtype = dtype;
+  out->indptr.alloc(sizeof(int32_t) * (static_cast<size_t>(rows) + 1) + 64);
+  DeviceBuffer flag(sizeof(int)), scan_tmp(scan_tmp_bytes(rows));
+  QDSP_CUDA(cudaMemsetAsync(flag.get(), 0, sizeof(int), stream));
+  QDSP_CUDA(cudaMemsetAsync(out->indptr.get(), 0, sizeof(int32_t), stream));
+  int *optr = out->indptr.get<int>();
+  geam_count_kernel<<<grid_for(rows), OP_THREADS, 0, stream>>>(rows, indptr.get<int>(), indices.get<int>(), b.indptr.get<int>(),
+                                                              b.indices.get<int>(), optr + 1, flag.get<int>());
+  QDSP_LAUNCH_CHECK();
+  inclusive_scan_i32(optr + 1, rows, scan_tmp.get(), scan_tmp.bytes(), stream);
+  int h[2] = {0, 0};
+  QDSP_CUDA(cudaMemcpyAsync(&h[0], flag.get(), sizeof(int), cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaMemcpyAsync(&h[1], optr + rows, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+  if (h[0] != 0 || h[1] < 0) return add_by_sort(*this, b, alpha, beta, stream);  // not canonical, or > 2^31 entries
+  out->nnz = h[1];
+  out->indices.alloc(sizeof(int32_t) * static_cast<size_t>(out->nnz) + 64);
+  out->values.alloc(value_bytes() * static_cast<size_t>(out->nnz) + 64);
+  QDSP_CUDA(cudaMemsetAsync(out->indices.get<char>() + sizeof(int32_t) * out->nnz, 0, 64, stream));
+  QDSP_CUDA(cudaMemsetAsync(out->values.get<char>() + value_bytes() * out->nnz, 0, 64, stream));
+  if (dtype == QDSP_F32)
+    geam_fill_kernel<float><<<grid_for(rows), OP_THREADS, 0, stream>>>(rows, indptr.get<int>(), indices.get<int>(), values.get<float>(), b.indptr.get<int>(), b.indices.get<int>(), b.values.get<float>(), static_cast<float>(alpha), static_cast<float>(beta), optr, out->indices.get<int>(), out->values.get<float>());
+  else
+    geam_fill_kernel<double><<<grid_for(rows), OP_THREADS, 0, stream>>>(rows, indptr.get<int>(), indices.get<int>(), values.get<double>(), b.indptr.get<int>(), b.indices.get<int>(), b.values.get<double>(), alpha, beta, optr, out->indices.get<int>(), out->values.get<double>());
+  QDSP_LAUNCH_CHECK();
+  QDSP_CUDA(cudaStreamSynchronize(stream));
   out->row_major_order = row_major_order;
   return out;
 }

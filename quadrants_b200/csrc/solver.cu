@@ -284,15 +284,30 @@ __device__ __forceinline__ unsigned long long global_ns() {
   return t;
 }
 
-// Spins until flags[k] is set.  A wait that lasts longer than WAIT_TIMEOUT_NS (it cannot, unless the GPU is shared with a
-// kernel that starves the claimed columns' warps) raises the abort word, after which every wait returns at once.
+__device__ __forceinline__ int ld_relaxed_s32(const int *p) {
+  int v;
+  asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Spins until flags[k] is set.  Polls are relaxed loads with an exponential back-off (thousands of warps wait at any time;
+// acquire polls would invalidate the SM's L1 on every probe and crowd the L2 slice of the flag the critical path is about
+// to write); one acquire load after the flag was seen orders the reads of the published data.  A wait that lasts longer
+// than WAIT_TIMEOUT_NS (it cannot, unless the GPU is shared with a kernel that starves the claimed columns' warps) raises
+// the abort word, after which every wait returns at once.
 __device__ __forceinline__ void wait_flag(const int *flags, int n, int k) {
   if (ld_acquire_s32(flags + k) != 0) return;
   unsigned long long t0 = 0;
+  unsigned ns = 32;
   for (unsigned spin = 1;; ++spin) {
-    if (ld_acquire_s32(flags + k) != 0) return;
-    if ((spin & 1023u) == 0) {
-      if (ld_acquire_s32(flags + n + CTL_ABORT) != 0) return;
+    if (ld_relaxed_s32(flags + k) != 0) {
+      (void)ld_acquire_s32(flags + k);
+      return;
+    }
+    __nanosleep(ns);
+    if (ns < 256) ns <<= 1;
+    if ((spin & 255u) == 0) {
+      if (ld_relaxed_s32(flags + n + CTL_ABORT) != 0) return;
       const unsigned long long t = global_ns();
       if (t0 == 0) t0 = t;
       else if (t - t0 > WAIT_TIMEOUT_NS) {

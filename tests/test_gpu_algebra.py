@@ -140,3 +140,30 @@ def test_matmul_errors_and_empty(qd):
     E = to_qd(qd, sp.csr_matrix((40, 20), dtype=np.float32))
     Q = A @ E
     assert Q.shape == (50, 20) and arrays(Q)[0][-1] == 0
+
+
+def test_add_of_non_canonical_csr_takes_the_sort_path(qd):
+    """A matrix adopted through qdsp_csr_from_device_csr may have unsorted rows: A + B must still be right (the merge
+    kernel notices and the expand-sort-collapse path runs instead)."""
+    import ctypes as C
+
+    import torch
+
+    from quadrants_b200 import _core, _lib
+
+    lib = _lib.load()
+    ip = np.array([0, 3, 5, 5, 6], np.int32)
+    ix = np.array([2, 0, 1, 3, 1, 0], np.int32)           # rows 0 and 1 are not ascending
+    v = np.array([1, 2, 3, 4, 5, 6], np.float32)
+    t = [torch.from_numpy(a).cuda() for a in (ip, ix, v)]
+    h = C.c_void_p()
+    stream = torch.cuda.current_stream().cuda_stream
+    _lib.check(lib.qdsp_csr_from_device_csr(4, 4, 6, t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(), _lib.F32, 0,
+                                            stream, C.byref(h)))
+    A = qd.linalg.SparseMatrix(sm=_core.CuSparseMatrix._wrap(h), dtype=qd.f32)
+    S = sp.csr_matrix((v, ix, ip), shape=(4, 4))
+    Q = A + A
+    ip2, ix2, v2 = arrays(Q)
+    R = (S + S).tocsr()
+    R.sort_indices()
+    assert np.array_equal(ip2, R.indptr) and np.array_equal(ix2, R.indices) and np.array_equal(v2, R.data)
