@@ -417,67 +417,129 @@ __global__ void __launch_bounds__(SOLVER_THREADS) solver_factor_kernel(FactorDev
   }
 }
 
+// ---- triangular solves ------------------------------------------------------------------------------------------------------
+// The chain row -> row is the critical path of a solve (elimination-tree height x the latency of one hand-over), so the
+// hand-over is ONE memory word: the solution entry itself.  y (and, for the backward pass, the permuted x) starts as the
+// all-ones bit pattern -- a NaN no arithmetic produces (hardware NaNs are 0x7ff8.. / 0x7fc0..) -- and a consumer simply
+// polls the entry with relaxed gpu-scope loads until it is something else: an aligned 4/8-byte store is single-copy atomic,
+// so no flag, no fence and no second load sit between producer and consumer.
+template <typename T> struct SolveWord;
+template <> struct SolveWord<float> {
+  static __device__ __forceinline__ bool pending(float v) { return __float_as_uint(v) == 0xffffffffu; }
+  static __device__ __forceinline__ float load(const float *p) {
+    float v;
+    asm volatile("ld.relaxed.gpu.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+  }
+  static __device__ __forceinline__ void store(float *p, float v) {
+    asm volatile("st.relaxed.gpu.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+  }
+};
+template <> struct SolveWord<double> {
+  static __device__ __forceinline__ bool pending(double v) { return __double_as_longlong(v) == -1ll; }
+  static __device__ __forceinline__ double load(const double *p) {
+    double v;
+    asm volatile("ld.relaxed.gpu.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+  }
+  static __device__ __forceinline__ void store(double *p, double v) {
+    asm volatile("st.relaxed.gpu.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+  }
+};
+
+// Polls *p until it holds a value (see above); same time-out / abort protocol as wait_flag.
+template <typename T>
+__device__ __forceinline__ T wait_value(const T *p, int *ctl) {
+  T v = SolveWord<T>::load(p);
+  if (!SolveWord<T>::pending(v)) return v;
+  unsigned long long t0 = 0;
+  for (unsigned spin = 1;; ++spin) {
+    v = SolveWord<T>::load(p);
+    if (!SolveWord<T>::pending(v)) return v;
+    if ((spin & 63u) == 0) __nanosleep(64);
+    if ((spin & 1023u) == 0) {
+      if (ld_relaxed_s32(ctl + CTL_ABORT) != 0) return T(0);
+      const unsigned long long t = global_ns();
+      if (t0 == 0) t0 = t;
+      else if (t - t0 > WAIT_TIMEOUT_NS) {
+        atomicExch(ctl + CTL_ABORT, 1);
+        return T(0);
+      }
+    }
+  }
+}
+
 // forward substitution  L y = P b  (LLT: L;  LDLT, LU: unit L), one warp per row, rows claimed ascending
 template <typename T, int MODE>
 __global__ void __launch_bounds__(SOLVER_THREADS) solver_forward_kernel(FactorDev f, const T *__restrict__ b, T *y) {
   const int lane = threadIdx.x & 31;
   const int n = f.n;
   const T *lx = static_cast<const T *>(f.lx);
-  int *flags = f.flags;
+  int *ctl = f.flags + n;
   for (;;) {
     int j = 0;
-    if (lane == 0) j = atomicAdd(flags + n + CTL_COUNTER, 1);
+    if (lane == 0) j = atomicAdd(ctl + CTL_COUNTER, 1);
     j = __shfl_sync(FULL, j, 0);
     if (j >= n) return;
     const int r0 = __ldg(f.rowptr + j), cnt = __ldg(f.rowptr + j + 1) - r0;
+    // everything that does not depend on other rows is read BEFORE the waits
+    T bj = T(0), dj = T(1);
+    if (lane == 0) {
+      bj = b[__ldg(f.perm + j)];
+      if (MODE == SOLVER_LLT) dj = __ldcg(lx + __ldg(f.colptr + j));
+    }
     T acc = T(0);
     for (int m = lane; m < cnt; m += 32) {
       const int k = __ldg(f.rowcol + r0 + m);
-      wait_flag(flags, n, k);
-      acc += __ldcg(lx + __ldg(f.rowpos + r0 + m)) * __ldcg(y + k);
+      const T l = __ldcg(lx + __ldg(f.rowpos + r0 + m));
+      acc += l * wait_value(y + k, ctl);
     }
     acc = warp_sum(acc);
     if (lane == 0) {
-      T v = b[__ldg(f.perm + j)] - acc;
-      if (MODE == SOLVER_LLT) v /= __ldcg(lx + __ldg(f.colptr + j));
-      __stcg(y + j, v);
-      __threadfence();
-      st_release_s32(flags + j, 1);
+      T v = bj - acc;
+      if (MODE == SOLVER_LLT) v /= dj;
+      if (SolveWord<T>::pending(v)) v = T(0) / T(0);  // (cannot happen; keeps the sentinel out of the data)
+      SolveWord<T>::store(y + j, v);
     }
   }
 }
 
-// backward substitution, rows claimed descending; x is written in the caller's (unpermuted) numbering as well
+// backward substitution, rows claimed descending; xp = x in the permuted numbering (the hand-over words), x = the caller's
 template <typename T, int MODE>
-__global__ void __launch_bounds__(SOLVER_THREADS) solver_backward_kernel(FactorDev f, T *y, T *x) {
+__global__ void __launch_bounds__(SOLVER_THREADS) solver_backward_kernel(FactorDev f, const T *__restrict__ y, T *xp, T *x) {
   const int lane = threadIdx.x & 31;
   const int n = f.n;
   const T *lx = static_cast<const T *>(f.lx);
   const T *vx = MODE == SOLVER_LU ? static_cast<const T *>(f.ux) : lx;
-  int *flags = f.flags;
+  int *ctl = f.flags + n;
   for (;;) {
     int c = 0;
-    if (lane == 0) c = atomicAdd(flags + n + CTL_COUNTER, 1);
+    if (lane == 0) c = atomicAdd(ctl + CTL_COUNTER, 1);
     c = __shfl_sync(FULL, c, 0);
     if (c >= n) return;
     const int j = n - 1 - c;
     const int cj = __ldg(f.colptr + j), lenj = __ldg(f.colptr + j + 1) - cj;
+    T d = T(1), yj = T(0);
+    int dst = 0;
+    if (lane == 0) {
+      d = __ldcg(lx + cj);
+      yj = __ldcg(y + j);  // from the forward pass (previous launch)
+      dst = __ldg(f.perm + j);
+    }
     T acc = T(0);
     for (int t = 1 + lane; t < lenj; t += 32) {
       const int i = __ldg(f.rowidx + cj + t);
-      wait_flag(flags, n, i);
-      acc += __ldcg(vx + cj + t) * __ldcg(y + i);
+      const T l = __ldcg(vx + cj + t);
+      acc += l * wait_value(xp + i, ctl);
     }
     acc = warp_sum(acc);
     if (lane == 0) {
-      const T d = __ldcg(lx + cj);
-      T v = __ldcg(y + j);
-      if (MODE == SOLVER_LDLT) v = v / d - acc;
-      else v = (v - acc) / d;
-      __stcg(y + j, v);
-      x[__ldg(f.perm + j)] = v;
-      __threadfence();
-      st_release_s32(flags + j, 1);
+      T v;
+      if (MODE == SOLVER_LDLT) v = yj / d - acc;
+      else v = (yj - acc) / d;
+      if (SolveWord<T>::pending(v)) v = T(0) / T(0);
+      SolveWord<T>::store(xp + j, v);
+      x[dst] = v;
     }
   }
 }
@@ -543,7 +605,7 @@ void DirectSolver::analyze_pattern(const CsrMatrix &A, cudaStream_t stream) {
   d_lx_.alloc(static_cast<size_t>(sym_.factor_nnz) * vb);
   if (type_ == SOLVER_LU) d_ux_.alloc(static_cast<size_t>(sym_.factor_nnz) * vb);
   d_flags_.alloc(static_cast<size_t>(n + CTL_WORDS) * sizeof(int));
-  d_work_.alloc(static_cast<size_t>(std::max(n, 1)) * vb);
+  d_work_.alloc(2 * static_cast<size_t>(std::max(n, 1)) * vb);  // y | permuted x
   QDSP_CUDA(cudaStreamSynchronize(stream));  // the host vectors above go out of scope
   nnz_a_ = A.nnz;
   analyzed_ = true;
@@ -556,6 +618,10 @@ void reset_flags(int *flags, int n, cudaStream_t stream) {
   QDSP_CUDA(cudaMemsetAsync(flags, 0, static_cast<size_t>(n + CTL_WORDS) * sizeof(int), stream));
   const int big = INT_MAX;
   QDSP_CUDA(cudaMemcpyAsync(flags + n + CTL_ERROR, &big, sizeof(int), cudaMemcpyHostToDevice, stream));
+}
+void reset_ctl(int *flags, int n, cudaStream_t stream) {
+  static const int init[CTL_WORDS] = {0, INT_MAX, 0, 0};
+  QDSP_CUDA(cudaMemcpyAsync(flags + n, init, sizeof(init), cudaMemcpyHostToDevice, stream));
 }
 void read_ctl(const int *flags, int n, cudaStream_t stream, int *ctl) {
   QDSP_CUDA(cudaMemcpyAsync(ctl, flags + n, CTL_WORDS * sizeof(int), cudaMemcpyDeviceToHost, stream));
@@ -572,11 +638,13 @@ static void factor_launch(const FactorDev &f, cudaStream_t stream) {
 }
 template <typename T, int MODE>
 static void solve_launch(const FactorDev &f, const T *b, T *y, T *x, cudaStream_t stream) {
-  reset_flags(f.flags, f.n, stream);
+  // y and the permuted x (y + n) start as the all-ones "pending" pattern; only the control words of the flag block are used
+  QDSP_CUDA(cudaMemsetAsync(y, 0xff, 2 * static_cast<size_t>(f.n) * sizeof(T), stream));
+  reset_ctl(f.flags, f.n, stream);
   solver_forward_kernel<T, MODE><<<solver_grid(solver_forward_kernel<T, MODE>, f.n), SOLVER_THREADS, 0, stream>>>(f, b, y);
   QDSP_LAUNCH_CHECK();
-  reset_flags(f.flags, f.n, stream);
-  solver_backward_kernel<T, MODE><<<solver_grid(solver_backward_kernel<T, MODE>, f.n), SOLVER_THREADS, 0, stream>>>(f, y, x);
+  QDSP_CUDA(cudaMemsetAsync(f.flags + f.n + CTL_COUNTER, 0, sizeof(int), stream));
+  solver_backward_kernel<T, MODE><<<solver_grid(solver_backward_kernel<T, MODE>, f.n), SOLVER_THREADS, 0, stream>>>(f, y, y + f.n, x);
   QDSP_LAUNCH_CHECK();
 }
 
