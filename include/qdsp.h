@@ -64,6 +64,10 @@ int qdsp_init(int device);
 int qdsp_device_info(int *device, int *sm_count, int *cc_major, int *cc_minor, size_t *l2_bytes, size_t *hbm_bytes);
 /* Number of kernels of this library launched by the calling process so far (bench.py's gpu_launches). */
 int64_t qdsp_launch_count(void);
+/* The multi-GB temporaries of a build / sort are cached between calls instead of cudaMalloc'd and freed every time (cap:
+ * QDSP_SCRATCH_POOL_MB, default 16384; 0 = no cache).  This returns the cached blocks to the driver.  (The reference
+ * cuMemAllocs and frees its work buffers on every call, e.g. sparse_matrix.cpp:654-686.) */
+int qdsp_release_scratch(void);
 
 /* ---- SparseMatrixBuilder (quadrants/program/sparse_matrix.h:16-53) -------------------------------------------- */
 /* ctor + create_ndarray (sparse_matrix.cpp:70-85): allocates the device triplet buffer of 3*max_triplets+1 slots of

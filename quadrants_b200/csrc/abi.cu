@@ -1,6 +1,8 @@
 // abi.cu -- the extern "C" surface declared in include/qdsp.h.  Thin: argument checks, handle casts, and the
 // exception -> (status, thread-local message) translation.  No exception crosses this file.
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -9,6 +11,91 @@
 #include "solver.hpp"
 
 using namespace qdsp;
+
+// ---- scratch pool (common.cuh) -----------------------------------------------------------------------------------------------
+namespace qdsp {
+namespace {
+struct PoolBlock { void *p; size_t bytes; int device; };
+std::mutex g_pool_mutex;
+std::vector<PoolBlock> g_pool;  // free blocks, oldest first
+size_t g_pool_bytes = 0;
+size_t pool_cap_bytes() {
+  static const size_t cap = [] {
+    const char *e = std::getenv("QDSP_SCRATCH_POOL_MB");
+    const long long mb = e ? std::atoll(e) : 16384;
+    return static_cast<size_t>(mb < 0 ? 0 : mb) << 20;
+  }();
+  return cap;
+}
+constexpr size_t POOL_MIN_BYTES = size_t{1} << 20;  // smaller requests go straight to cudaMalloc
+constexpr size_t POOL_GRANULE = size_t{2} << 20;
+}  // namespace
+
+void *scratch_pool_acquire(size_t bytes, size_t *got) {
+  int dev = 0;
+  QDSP_CUDA(cudaGetDevice(&dev));
+  if (bytes >= POOL_MIN_BYTES && pool_cap_bytes() > 0) {
+    std::lock_guard<std::mutex> lock(g_pool_mutex);
+    int best = -1;
+    for (int i = 0; i < static_cast<int>(g_pool.size()); ++i) {
+      const PoolBlock &b = g_pool[i];
+      // best fit, and never burn a block more than twice the request
+      if (b.device == dev && b.bytes >= bytes && b.bytes <= 2 * bytes + POOL_GRANULE &&
+          (best < 0 || b.bytes < g_pool[best].bytes))
+        best = i;
+    }
+    if (best >= 0) {
+      PoolBlock b = g_pool[best];
+      g_pool.erase(g_pool.begin() + best);
+      g_pool_bytes -= b.bytes;
+      *got = b.bytes;
+      return b.p;
+    }
+  }
+  const size_t rounded = bytes >= POOL_MIN_BYTES ? (bytes + POOL_GRANULE - 1) / POOL_GRANULE * POOL_GRANULE : bytes;
+  void *p = nullptr;
+  cudaError_t e = cudaMalloc(&p, rounded);
+  if (e == cudaErrorMemoryAllocation) {
+    (void)cudaGetLastError();
+    scratch_pool_trim();
+    e = cudaMalloc(&p, rounded);
+  }
+  QDSP_CUDA(e);
+  *got = rounded;
+  return p;
+}
+
+void scratch_pool_release(void *p, size_t bytes) {
+  if (!p) return;
+  int dev = 0;
+  if (bytes < POOL_MIN_BYTES || bytes > pool_cap_bytes() || cudaGetDevice(&dev) != cudaSuccess) {
+    cudaFree(p);
+    return;
+  }
+  std::vector<void *> drop;
+  {
+    std::lock_guard<std::mutex> lock(g_pool_mutex);
+    g_pool.push_back({p, bytes, dev});
+    g_pool_bytes += bytes;
+    while (g_pool_bytes > pool_cap_bytes() && !g_pool.empty()) {  // evict the oldest
+      drop.push_back(g_pool.front().p);
+      g_pool_bytes -= g_pool.front().bytes;
+      g_pool.erase(g_pool.begin());
+    }
+  }
+  for (void *q : drop) cudaFree(q);
+}
+
+void scratch_pool_trim() {
+  std::vector<PoolBlock> all;
+  {
+    std::lock_guard<std::mutex> lock(g_pool_mutex);
+    all.swap(g_pool);
+    g_pool_bytes = 0;
+  }
+  for (const PoolBlock &b : all) cudaFree(b.p);
+}
+}  // namespace qdsp
 
 struct qdsp_builder_s { std::unique_ptr<Builder> impl; };
 struct qdsp_csr_s { std::unique_ptr<CsrMatrix> impl; };
@@ -47,6 +134,9 @@ extern "C" {
 const char *qdsp_last_error(void) { return g_last_error.c_str(); }
 int qdsp_abi_version(void) { return QDSP_ABI_VERSION; }
 int64_t qdsp_launch_count(void) { return g_launch_count.load(); }
+int qdsp_release_scratch(void) {
+  return guarded([&] { scratch_pool_trim(); });
+}
 
 int qdsp_init(int device) {
   return guarded([&] {

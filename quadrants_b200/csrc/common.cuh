@@ -6,6 +6,7 @@
 #include <atomic>
 #include <cstdint>
 #include <cstdio>
+#include <exception>
 #include <stdexcept>
 #include <string>
 
@@ -48,26 +49,54 @@ struct DeviceProps {
 const DeviceProps &device_props();  // of the current device; cached per device
 
 // ---- RAII device memory ----------------------------------------------------------------------------------------------
+// Scratch pool (scratch_pool_* in abi.cu): the multi-GB temporaries of a CSR build / sort (packed keys, the radix ping-pong
+// pair, the collapse spares) are taken from and returned to a per-process cache instead of cudaMalloc / cudaFree -- a
+// fresh multi-GB cudaMalloc maps new physical pages and was measured at 12-99 ms per build, more than the kernels.
+// Blocks are only handed back after the owning call has synchronised its stream, so reuse needs no event.  The cache is
+// capped (QDSP_SCRATCH_POOL_MB, default 16384; 0 disables), dropped by qdsp_release_scratch() and on any out-of-memory.
+void *scratch_pool_acquire(size_t bytes, size_t *got);
+void scratch_pool_release(void *p, size_t bytes);
+void scratch_pool_trim();
+
 class DeviceBuffer {
  public:
   DeviceBuffer() = default;
   explicit DeviceBuffer(size_t bytes) { alloc(bytes); }
   DeviceBuffer(const DeviceBuffer &) = delete;
   DeviceBuffer &operator=(const DeviceBuffer &) = delete;
-  DeviceBuffer(DeviceBuffer &&o) noexcept : p_(o.p_), n_(o.n_) { o.p_ = nullptr; o.n_ = 0; }
+  DeviceBuffer(DeviceBuffer &&o) noexcept : p_(o.p_), n_(o.n_), cap_(o.cap_), pooled_(o.pooled_) { o.p_ = nullptr; o.n_ = 0; }
   DeviceBuffer &operator=(DeviceBuffer &&o) noexcept {
-    if (this != &o) { release(); p_ = o.p_; n_ = o.n_; o.p_ = nullptr; o.n_ = 0; }
+    if (this != &o) { release(); p_ = o.p_; n_ = o.n_; cap_ = o.cap_; pooled_ = o.pooled_; o.p_ = nullptr; o.n_ = 0; }
     return *this;
   }
   ~DeviceBuffer() { release(); }
   void alloc(size_t bytes) {
     release();
     if (bytes == 0) bytes = 16;
-    QDSP_CUDA(cudaMalloc(&p_, bytes));
+    cudaError_t e = cudaMalloc(&p_, bytes);
+    if (e == cudaErrorMemoryAllocation) {  // give the cached scratch back and try once more
+      (void)cudaGetLastError();
+      scratch_pool_trim();
+      e = cudaMalloc(&p_, bytes);
+    }
+    QDSP_CUDA(e);
     n_ = bytes;
+    pooled_ = false;
+  }
+  // scratch that dies inside the call that made it (after that call has synchronised its stream)
+  void alloc_scratch(size_t bytes) {
+    release();
+    if (bytes == 0) bytes = 16;
+    p_ = scratch_pool_acquire(bytes, &cap_);
+    n_ = bytes;
+    pooled_ = true;
   }
   void release() {
-    if (p_) cudaFree(p_);
+    if (p_) {
+      // unwinding: kernels of the failed call may still be running on the block; cudaFree synchronises, the pool does not
+      if (pooled_ && std::uncaught_exceptions() == 0) scratch_pool_release(p_, cap_);
+      else cudaFree(p_);
+    }
     p_ = nullptr;
     n_ = 0;
   }
@@ -77,8 +106,14 @@ class DeviceBuffer {
 
  private:
   void *p_ = nullptr;
-  size_t n_ = 0;
+  size_t n_ = 0, cap_ = 0;
+  bool pooled_ = false;
 };
+inline DeviceBuffer scratch_buffer(size_t bytes) {
+  DeviceBuffer b;
+  b.alloc_scratch(bytes);
+  return b;
+}
 
 inline int ceil_div(int64_t a, int64_t b) { return static_cast<int>((a + b - 1) / b); }
 inline int bits_for(int64_t n) {  // number of bits needed to represent values in [0, n)

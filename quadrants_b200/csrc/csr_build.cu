@@ -180,7 +180,7 @@ std::unique_ptr<CsrMatrix> csr_from_packed(int rows, int cols, int64_t n, int dt
                                            DeviceBuffer &keys, DeviceBuffer &vals, cudaStream_t stream) {
   const int vb = dtype == QDSP_F64 ? 8 : 4;
   const int key_bits = bits_for(rows) + col_bits;
-  DeviceBuffer sort_tmp(sort_tmp_bytes(n, key_bytes, vb));
+  DeviceBuffer sort_tmp = scratch_buffer(sort_tmp_bytes(n, key_bytes, vb));
   void *ks = nullptr, *vs = nullptr;
   sort_build_keys(keys.get(), vals.get(), n, key_bytes, vb, key_bits, sort_tmp.get(), stream, &ks, &vs);
   // the buffer pair that does not hold the sorted data is free: collapse writes indices/values there first, because
@@ -194,8 +194,8 @@ std::unique_ptr<CsrMatrix> csr_from_packed(int rows, int cols, int64_t n, int dt
     idx_tmp = keys.get<int>();
     val_tmp = vals.get();
   } else {
-    spare_idx.alloc(sizeof(int) * static_cast<size_t>(n));
-    spare_val.alloc(static_cast<size_t>(vb) * n);
+    spare_idx.alloc_scratch(sizeof(int) * static_cast<size_t>(n));
+    spare_val.alloc_scratch(static_cast<size_t>(vb) * n);
     idx_tmp = spare_idx.get<int>();
     val_tmp = spare_val.get();
   }
@@ -407,7 +407,8 @@ std::unique_ptr<CsrMatrix> Builder::build(cudaStream_t stream) {
     const int col_bits = bits_for(cols_), row_bits = bits_for(rows_);
     const int key_bytes = (col_bits + row_bits <= 32) ? 4 : 8;
     const int vb = static_cast<int>(slot_bytes());
-    DeviceBuffer keys(static_cast<size_t>(key_bytes) * n), vals(static_cast<size_t>(vb) * n), err(sizeof(int));
+    DeviceBuffer keys = scratch_buffer(static_cast<size_t>(key_bytes) * n), vals = scratch_buffer(static_cast<size_t>(vb) * n),
+                 err(sizeof(int));
     QDSP_CUDA(cudaMemsetAsync(err.get(), 0, sizeof(int), stream));
     const unsigned grid = static_cast<unsigned>((n + CB_THREADS - 1) / CB_THREADS);
     const char *trip = buf_.get<char>() + slot_bytes();
@@ -460,7 +461,8 @@ std::unique_ptr<CsrMatrix> CsrMatrix::from_device_coo(int rows, int cols, int64_
   const int col_bits = bits_for(cols), row_bits = bits_for(rows);
   const int key_bytes = (col_bits + row_bits <= 32) ? 4 : 8;
   const int vb = dtype == QDSP_F64 ? 8 : 4;
-  DeviceBuffer keys(static_cast<size_t>(key_bytes) * n), vals(static_cast<size_t>(vb) * n), err(sizeof(int));
+  DeviceBuffer keys = scratch_buffer(static_cast<size_t>(key_bytes) * n), vals = scratch_buffer(static_cast<size_t>(vb) * n),
+               err(sizeof(int));
   QDSP_CUDA(cudaMemsetAsync(err.get(), 0, sizeof(int), stream));
   const unsigned grid = static_cast<unsigned>((n + CB_THREADS - 1) / CB_THREADS);
   if (vb == 4 && key_bytes == 4)

@@ -90,7 +90,7 @@ static std::unique_ptr<CsrMatrix> add_by_sort(const CsrMatrix &a, const CsrMatri
   const int rows = a.rows, cols = a.cols, dtype = a.dtype;
   const long long n = nnz + b.nnz;
   const size_t vb = a.value_bytes();
-  DeviceBuffer r(sizeof(int) * n), c(sizeof(int) * n), v(vb * n);
+  DeviceBuffer r = scratch_buffer(sizeof(int) * n), c = scratch_buffer(sizeof(int) * n), v = scratch_buffer(vb * n);
   expand_rows(a, r.get<int>(), 0, stream);
   expand_rows(b, r.get<int>(), nnz, stream);
   if (nnz) { copy_int_kernel<<<grid_for(nnz), OP_THREADS, 0, stream>>>(nnz, a.indices.get<int>(), c.get<int>()); QDSP_LAUNCH_CHECK(); }
@@ -202,7 +202,7 @@ std::unique_ptr<CsrMatrix> CsrMatrix::add(const CsrMatrix &b, double alpha, doub
 }
 
 std::unique_ptr<CsrMatrix> CsrMatrix::transpose(cudaStream_t stream) const {
-  DeviceBuffer r(sizeof(int) * std::max<int64_t>(nnz, 1));
+  DeviceBuffer r = scratch_buffer(sizeof(int) * std::max<int64_t>(nnz, 1));
   expand_rows(*this, r.get<int>(), 0, stream);
   // (row, col, v) -> (col, row, v); the stable sort keeps each output row ordered by the old row index
   auto out = from_device_coo(cols, rows, nnz, indices.get<int>(), r.get<int>(), values.get(), dtype, stream);
@@ -289,14 +289,14 @@ std::unique_ptr<CsrMatrix> CsrMatrix::matmul(const CsrMatrix &b, cudaStream_t st
       parts.push_back(from_device_coo(r1 - r0, b.cols, 0, dummy.get<int>(), dummy.get<int>(), dummy.get(), dtype, stream));
       continue;
     }
-    DeviceBuffer a_row(sizeof(int) * nk), cnt(sizeof(int) * nk + 64), scan_tmp(scan_tmp_bytes(nk));
+    DeviceBuffer a_row = scratch_buffer(sizeof(int) * nk), cnt = scratch_buffer(sizeof(int) * nk + 64), scan_tmp(scan_tmp_bytes(nk));
     expand_rows_kernel<<<grid_for(static_cast<long long>(r1 - r0) * 32), OP_THREADS, 0, stream>>>(
         r1 - r0, indptr.get<int>() + r0, a_row.get<int>(), -k0);
     QDSP_LAUNCH_CHECK();
     spgemm_count_kernel<<<grid_for(nk), OP_THREADS, 0, stream>>>(nk, indices.get<int>() + k0, b.indptr.get<int>(), cnt.get<int>());
     QDSP_LAUNCH_CHECK();
     inclusive_scan_i32(cnt.get<int>(), nk, scan_tmp.get(), scan_tmp.bytes(), stream);
-    DeviceBuffer o_row(sizeof(int) * total), o_col(sizeof(int) * total), o_val(vb * total);
+    DeviceBuffer o_row = scratch_buffer(sizeof(int) * total), o_col = scratch_buffer(sizeof(int) * total), o_val = scratch_buffer(vb * total);
     if (dtype == QDSP_F32)
       spgemm_expand_kernel<float><<<grid_for(nk), OP_THREADS, 0, stream>>>(nk, a_row.get<int>(), indices.get<int>() + k0, values.get<float>() + k0, b.indptr.get<int>(), b.indices.get<int>(), b.values.get<float>(), cnt.get<int>(), o_row.get<int>(), o_col.get<int>(), o_val.get<float>());
     else
