@@ -3,6 +3,8 @@
 
     python profiles/summarize.py launches gpurun_out/launches_X.csv  > profiles/rNN_launches_X.txt
     python profiles/summarize.py kernel   gpurun_out/prof_X.ncu-rep  > profiles/rNN_kernel_X.txt
+    python profiles/summarize.py sass     [quadrants_b200/lib/libqdsp.so] > profiles/sass_census.txt
+    python profiles/summarize.py stalls   gpurun_out/prof_X.ncu-rep  > profiles/rNN_stalls_X.txt   (needs --import-source on)
 """
 import collections
 import csv
@@ -68,5 +70,75 @@ def kernel(path):
             print(f"  {'traffic = dram read + write (bytes)':90s} {b('dram__bytes_read.sum') + b('dram__bytes_write.sum'):18.0f}")
 
 
+MNEMONICS = ["UBLKCP", "SYNCS", "LDGSTS", "LDS", "STS", "LDG", "STG", "LD.E", "ST.E", "ATOM", "RED", "VOTE", "SHFL", "MATCH",
+             "BAR", "MEMBAR", "CCTL", "FFMA", "DFMA", "DADD", "DMUL", "NANOSLEEP", "HMMA", "UTCMMA", "LDL", "STL"]
+
+
+def sass(path="quadrants_b200/lib/libqdsp.so"):
+    """Per-kernel SASS census (cuobjdump -sass): which instruction classes each kernel of the shipped library contains.
+    UBLKCP = cp.async.bulk (the TMA bulk-copy engine), SYNCS = mbarrier ops; no HMMA / UTCMMA anywhere: the path is
+    bandwidth-bound and uses no tensor cores.  LDL / STL > 0 would mean register spills."""
+    out = subprocess.run(["cuobjdump", "-sass", path], capture_output=True, text=True).stdout
+    demangled = {}
+    fn, counts, order = None, {}, []
+    for line in out.splitlines():
+        line = line.strip()
+        if line.startswith("Function :"):
+            fn = line.split(":", 1)[1].strip()
+            counts[fn] = collections.Counter()
+            order.append(fn)
+        elif fn and line.startswith("/*") and "*/" in line:
+            body = line.split("*/", 1)[1].strip()
+            if not body or body.startswith("/*"):
+                continue
+            toks = body.replace("@P", " @P").split()
+            op = next((t for t in toks if not t.startswith("@") and not t.startswith("{")), "")
+            counts[fn]["_all"] += 1
+            for m in MNEMONICS:
+                if op == m or op.startswith(m + "."):
+                    counts[fn][m] += 1
+    names = subprocess.run(["cu++filt"] + order, capture_output=True, text=True).stdout.splitlines() if order else []
+    for a, b in zip(order, names):
+        demangled[a] = b
+    arch = subprocess.run(["cuobjdump", "-lelf", path], capture_output=True, text=True).stdout
+    print(f"# {path}: SASS census per kernel ({len(order)} kernels; ELF images: "
+          f"{sorted(set(w for w in arch.replace('.', ' ').split() if w.startswith('sm_')))})")
+    print(f"{'kernel':100s} {'insts':>7s} " + " ".join(f"{m:>6s}" for m in MNEMONICS))
+    tot = collections.Counter()
+    for f in order:
+        c = counts[f]
+        tot.update(c)
+        name = demangled.get(f, f).replace("qdsp::", "").replace("(anonymous namespace)::", "")
+        name = name.replace("void ", "")[:100]
+        print(f"{name:100s} {c['_all']:7d} " + " ".join(f"{c[m]:6d}" for m in MNEMONICS))
+    print(f"{'TOTAL':100s} {tot['_all']:7d} " + " ".join(f"{tot[m]:6d}" for m in MNEMONICS))
+
+
+def stalls(path):
+    """Warp-stall samples per SASS line of the first kernel in the report, top lines and totals by stall reason."""
+    out = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    print("# " + path + ": " + rows[0][1][:150])
+    hdr = rows[1]
+    wi, si = hdr.index("Warp Stall Sampling (All Samples)"), hdr.index("Source")
+    reasons = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
+    tot, by = 0, collections.Counter()
+    lines = []
+    for n, r in enumerate(rows[2:]):
+        try:
+            w = int(r[wi])
+        except (ValueError, IndexError):
+            continue
+        tot += w
+        top = max(reasons, key=lambda k: int(r[hdr.index(k)] or 0))
+        for k in reasons:
+            by[k] += int(r[hdr.index(k)] or 0)
+        lines.append((w, n, r[si][:70], top))
+    print(f"total samples {tot}; by reason: " + ", ".join(f"{k[6:]} {100 * v / max(tot, 1):.1f}%" for k, v in by.most_common(8)))
+    for w, n, src, top in sorted(lines, reverse=True)[:40]:
+        print(f"  {100 * w / max(tot, 1):5.1f}%  line {n:5d}  {top[6:]:14s} {src}")
+
+
 if __name__ == "__main__":
-    {"launches": launches, "kernel": kernel}[sys.argv[1]](sys.argv[2])
+    fn = {"launches": launches, "kernel": kernel, "sass": sass, "stalls": stalls}[sys.argv[1]]
+    fn(*sys.argv[2:3])
