@@ -1547,7 +1547,9 @@ CgSolver::CgSolver(const CsrMatrix &A, int max_iters, double tol, int mode, bool
       if (focc < 1) I.fused = false;
       else {
         const int work = A.spmv_mode == 2 ? A.spmv_plan_nblk : ceil_div(A.rows, SPMV_CONSUMERS / I.lpr);
-        I.fused_grid = std::max(1, std::min(work, device_props().sm_count * focc));
+        int per_sm = focc;
+        if (const char *g = std::getenv("QDSP_CG_FUSED_CTAS")) per_sm = std::max(1, std::min(focc, std::atoi(g)));
+        I.fused_grid = std::max(1, std::min(work, device_props().sm_count * per_sm));
       }
     }
   }

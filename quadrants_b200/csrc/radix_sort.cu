@@ -423,10 +423,11 @@ static void *rs_run_items(KeyT *keys, ValT *vals, KeyT *kalt, ValT *valt, void *
 
   auto kernel = rs_onesweep_kernel<KeyT, ValT, ITEMS, MINB>;
   const size_t smem = rs_vals_offset<KeyT, ValT, ITEMS>() + static_cast<size_t>(TILE) * (VB ? VB : 0);
-  static bool attr_set = false;  // per instantiation
-  if (!attr_set) {
+  static std::atomic<unsigned> attr_set{0};  // per instantiation; one bit per device (function attributes are per device)
+  const unsigned dev_bit = 1u << (device_props().device & 31);
+  if (!(attr_set.load(std::memory_order_acquire) & dev_bit)) {
     QDSP_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    attr_set = true;
+    attr_set.fetch_or(dev_bit, std::memory_order_release);
   }
   KeyT *kin = keys, *kout = kalt;
   ValT *vin = vals, *vout = valt;

@@ -237,10 +237,10 @@ namespace {
 
 template <typename T>
 void launch_spmv_stream(const CsrMatrix &A, const T *x, T *y, const DistDev &d, cudaStream_t stream) {
-  static int occs[2] = {0, 0};
+  static int occs[16][2] = {};  // per device (function attributes and occupancy are per device), per smem size
   const bool hot = A.spmv_plan_hot_n > 0;
   const size_t smem = spmv_stream_smem_bytes<T>(hot);
-  int &occ = occs[hot ? 1 : 0];
+  int &occ = occs[device_props().device & 15][hot ? 1 : 0];
   if (occ == 0) {
     QDSP_CUDA(cudaFuncSetAttribute(spmv_stream_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    static_cast<int>(spmv_stream_smem_bytes<T>(true))));
@@ -257,7 +257,8 @@ void launch_spmv_stream(const CsrMatrix &A, const T *x, T *y, const DistDev &d, 
 // persistent grid = SM count x resident CTAs of this instantiation (queried once per instantiation)
 template <typename T, int LPR>
 int spmv_ctas_per_sm() {
-  static int occ = 0;
+  static int occs[16] = {};  // per device
+  int &occ = occs[device_props().device & 15];
   if (occ == 0) {
     const size_t smem = spmv_smem_bytes<T>();
     QDSP_CUDA(cudaFuncSetAttribute(spmv_kernel<T, LPR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
