@@ -76,7 +76,7 @@ def stencil_probe(n, lo, hi, device):
     return x.reshape(-1).contiguous(), y.reshape(-1).contiguous()
 
 
-def live_spmv_traffic(n, timeout_s=240):
+def live_spmv_traffic(n, timeout_s=240, compress=False):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE spmv_kernel launch, captured now, on this box, by running
     `bench.py --spmv-once` under ncu in a child process (after the timed regions; nothing timed runs under the profiler).
     -> (bytes, source string) or (None, why)."""
@@ -89,6 +89,7 @@ def live_spmv_traffic(n, timeout_s=240):
            "base", "-k", "regex:spmv_kernel", "--launch-skip", "2", "--launch-count", "1", "--csv", sys.executable,
            os.path.join(ROOT, "bench.py"), "--spmv-once", "--grid", str(n)]
     env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    env["QDSP_SPMV_COMPRESS"] = "1" if compress else "0"  # canonical 4-byte indices unless asked for the coded stream
     try:
         out = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout_s, env=env, cwd=ROOT)
     except (OSError, subprocess.TimeoutExpired) as e:
@@ -464,8 +465,40 @@ def run_gpu(args):
     nnz_loc = A.matrix.nnz()
     n_cols_loc = n_loc + (ctx.n_ghost if world > 1 else 0)
     alg = spmv_bytes(n_loc, n_cols_loc, nnz_loc, sv)
+    # The shipped SpMV streams ONE-BYTE diagonal codes instead of the 4-byte column indices when the matrix allows it
+    # (qdsp_csr_spmv_config; the Poisson stencil does): fewer bytes than SURVEY 8(d)'s canonical-CSR model.  The roofline
+    # of the line stays the CANONICAL kernel (a copy of the matrix with the codes switched off, timed the same way, N = 1);
+    # the coded kernel is reported beside it under roofline.compressed with the bytes it actually has to move.
+    info = A.matrix.spmv_info()
+    coded = info["index_bytes_per_nnz"] == 1
+    moved = alg - 3 * nnz_loc if coded else alg
+    compressed = None
+    if coded:
+        compressed = {"index_bytes_per_nnz": 1, "ms_per_launch": spmv_ms, "bytes_moved_model": moved,
+                      "achieved": moved / (spmv_ms * 1e-3) / 1e9,
+                      "canonical_equivalent_gbs": alg / (spmv_ms * 1e-3) / 1e9,
+                      "note": "same entries, same order, same arithmetic: bit-identical y (parity gate above ran on this kernel)"}
+        if world == 1:
+            from quadrants_b200 import _core
+            ip_t, ix_t, vv_t = A.matrix.csr_tensors()
+            h0 = C.c_void_p()
+            _lib.check(lib.qdsp_csr_from_device_csr(n_rows, n_rows, nnz_loc, ip_t.data_ptr(), ix_t.data_ptr(), vv_t.data_ptr(),
+                                                    _lib.F32, 0, stream.cuda_stream, C.byref(h0)))
+            A0 = _core.CuSparseMatrix._wrap(h0)
+            A0.spmv_config(0)
+            for _ in range(5):
+                A0.spmv(None, xs, ys)
+            torch.cuda.synchronize()
+            e0.record(stream)
+            for _ in range(reps):
+                A0.spmv(None, xs, ys)
+            e1.record(stream)
+            torch.cuda.synchronize()
+            spmv_ms = e0.elapsed_time(e1) / reps   # the canonical kernel: what the roofline below is about
+            del A0, ip_t, ix_t, vv_t
+            moved = alg
     per_rank = all_ranks({"rank": rank, "ms_per_launch": spmv_ms, "algorithmic_bytes_per_launch": alg,
-                          "achieved": alg / (spmv_ms * 1e-3) / 1e9})
+                          "bytes_moved_model": moved, "achieved": moved / (spmv_ms * 1e-3) / 1e9})
     spmv_gbs = sum(p["achieved"] for p in per_rank)          # whole job
     per_gpu = min(p["achieved"] for p in per_rank)           # the slowest rank is the one the roofline is about
     peaks = {}
@@ -485,6 +518,14 @@ def run_gpu(args):
     if world > 1:
         roofline["per_rank"] = per_rank
         roofline["note"] = "achieved/frac = the slowest rank's per-GPU figure; spmv_gbs on the line = sum over ranks"
+        if coded:
+            roofline["note"] += ("; the ranks stream one-byte diagonal codes: achieved = bytes_moved_model / time, "
+                                 "canonical-CSR bytes / time is in compressed.canonical_equivalent_gbs")
+    if compressed is not None:
+        compressed["frac"] = compressed["achieved"] / peak
+        compressed["frac_of_nominal_8000"] = compressed["achieved"] / 8000.0
+        compressed["traffic"] = None
+        roofline["compressed"] = compressed
     del xs, ys
 
     # ---- e2e: the host-buffer C-ABI call (qdsp_cg_solve_host): b H2D + x D2H inside the timed region; for N > 1 every
@@ -568,6 +609,9 @@ def run_gpu(args):
         roofline["traffic"], roofline["traffic_source"] = traffic, src
         if world > 1:
             roofline["traffic_note"] = "single-GPU launch over the whole matrix; a rank streams 1/N of it"
+        if compressed is not None and not args.no_live_traffic:
+            ctraffic, csrc = live_spmv_traffic(n, compress=True)
+            compressed["traffic"], compressed["traffic_source"] = ctraffic, csrc
 
     if rank == 0:
         iter_bytes = cg_iter_bytes(n_rows, nnz_total, sv)
@@ -580,10 +624,17 @@ def run_gpu(args):
                            "partition": (f"row-block x{world} (z-slabs), halo by NVLink peer stores, dots all-reduced "
                                          + ("by NCCL" if os.environ.get("QDSP_ALLREDUCE") == "nccl" else
                                             "in-kernel over peer memory")) if world > 1 else "single GPU",
-                           "l2": "no flush: matrix stream 0.94 GB per iteration >> 126 MB L2",
+                           "l2": ("no flush: the matrix stream of one iteration (0.59 GB coded / 0.94 GB canonical over all "
+                                  "ranks) exceeds the 126 MB L2 of a GPU up to 4 ranks; at 8 ranks a rank's share (73 / 117 MB "
+                                  "+ 42 MB of vectors) is L2-sized -- strong scaling of the fixed 256^3 problem"),
                            "csr_build_ms": build_ms},
                 "cg_gbs": value * iter_bytes / 1e9, "cg_algorithmic_bytes_per_iter": iter_bytes,
                 "spmv_gbs": spmv_gbs, "gpu_launches": int(launches), "clocks": clocks}
+        if compressed is not None:
+            # the CG's A.p kernel streams the one-byte codes: the bytes an iteration has to move are 3 * nnz below the
+            # canonical-CSR model that cg_gbs is quoted on (cg_gbs may therefore exceed the HBM peak)
+            line["cg_bytes_moved_per_iter"] = iter_bytes - 3 * int(nnz_total)
+            line["cg_gbs_moved"] = value * (iter_bytes - 3 * int(nnz_total)) / 1e9
         line["roofline"] = roofline
         line["e2e"] = e2e
         line["parity_checked"] = True

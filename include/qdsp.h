@@ -108,6 +108,15 @@ int qdsp_csr_info(qdsp_csr_t m, int *rows, int *cols, int64_t *nnz, int *dtype);
 int qdsp_csr_export(qdsp_csr_t m, const int32_t **indptr, const int32_t **indices, const void **values);
 /* spmv / nd_spmv (sparse_matrix.cpp:654-686): y = A x, x has cols elements, y rows elements, both dense device. */
 int qdsp_csr_spmv(qdsp_csr_t m, const void *x, void *y, void *stream);
+/* SpMV storage option of one matrix.  compress: 1 = stream one-byte diagonal codes instead of the 4-byte column indices
+ * when the matrix has at most 256 distinct (column - row) values (stencils, banded matrices; the plan keeps an extra
+ * nnz-byte array, the canonical arrays stay exportable and the results are bit-identical), 0 = always stream the
+ * canonical indices, -1 = the process default (QDSP_SPMV_COMPRESS, on unless "0").  Drops the matrix's SpMV plan: call it
+ * before creating solvers on the matrix.  No reference counterpart (cuSPARSE has no such format for CSR_ALG1). */
+int qdsp_csr_spmv_config(qdsp_csr_t m, int compress);
+/* What the plan of `m` streams per product (plans the matrix if needed): *index_bytes_per_nnz = 1 (diagonal codes) or 4,
+ * *path = 1 uniform row blocks / 2 irregular (stream) path, *hot_columns = columns cached in shared memory (stream path). */
+int qdsp_csr_spmv_info(qdsp_csr_t m, void *stream, int *index_bytes_per_nnz, int *path, int *hot_columns);
 /* Pure host helper (no CUDA needed): how the SpMV of an irregular matrix (row lengths far above the mean) cuts the rows
  * into work blocks of at most 2044 non-zeros and 256 rows; a longer row becomes several single-row segments.
  * blocks_out: 4 int32 per block {row0, nrows (> 0) or -(segment id + 1), nz_begin, nz_end}.  No reference counterpart

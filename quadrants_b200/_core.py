@@ -235,6 +235,16 @@ class CuSparseMatrix:
         ip, ix, v = self.csr_tensors()
         return ip.cpu().numpy(), ix.cpu().numpy(), v.cpu().numpy()
 
+    def spmv_config(self, compress):
+        """qdsp_csr_spmv_config: 1 / 0 / -1 (default) -- one-byte diagonal codes instead of column indices in the SpMV."""
+        _lib.check(self._lib.qdsp_csr_spmv_config(self._need(), int(compress)))
+
+    def spmv_info(self):
+        ib, path, hot = C.c_int(), C.c_int(), C.c_int()
+        _lib.check(self._lib.qdsp_csr_spmv_info(self._need(), _stream(), C.byref(ib), C.byref(path), C.byref(hot)))
+        return {"index_bytes_per_nnz": ib.value, "path": {1: "uniform", 2: "stream"}.get(path.value, "none"),
+                "hot_columns": hot.value}
+
     def spmv(self, prog, x, y):
         """nd_spmv(Program*, const Ndarray& x, const Ndarray& y)"""
         _lib.check(self._lib.qdsp_csr_spmv(self._need(), x.data_ptr(), y.data_ptr(), _stream(prog)))

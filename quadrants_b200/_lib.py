@@ -46,6 +46,8 @@ SIGNATURES = {
     "qdsp_csr_info": (_i, [_vp, _P(_i), _P(_i), _P(_i64), _P(_i)]),
     "qdsp_csr_export": (_i, [_vp, _P(_vp), _P(_vp), _P(_vp)]),
     "qdsp_csr_spmv": (_i, [_vp, _vp, _vp, _vp]),
+    "qdsp_csr_spmv_config": (_i, [_vp, _i]),
+    "qdsp_csr_spmv_info": (_i, [_vp, _vp, _P(_i), _P(_i), _P(_i)]),
     "qdsp_spmv_plan_host": (_i, [_vp, _i, _vp, _i64, _P(_i64), _P(_i), _P(_i)]),
     "qdsp_csr_spmv_host": (_i, [_vp, _vp, _vp, _vp]),
     "qdsp_csr_get_element": (_i, [_vp, _i, _i, _P(_d)]),

@@ -314,6 +314,23 @@ int qdsp_cg_destroy(qdsp_cg_t s) {
   return guarded([&] { delete s; });
 }
 
+int qdsp_csr_spmv_config(qdsp_csr_t m, int compress) {
+  return guarded([&] {
+    NOT_NULL(m);
+    m->impl->spmv_compress = compress < 0 ? -1 : (compress ? 1 : 0);
+    m->impl->spmv_mode = 0;  // re-plan on next use
+  });
+}
+int qdsp_csr_spmv_info(qdsp_csr_t m, void *stream, int *index_bytes_per_nnz, int *path, int *hot_columns) {
+  return guarded([&] {
+    NOT_NULL(m);
+    spmv_prepare(*m->impl, S(stream));
+    if (index_bytes_per_nnz) *index_bytes_per_nnz = m->impl->spmv_ntab > 0 ? 1 : 4;
+    if (path) *path = m->impl->spmv_mode;
+    if (hot_columns) *hot_columns = m->impl->spmv_mode == 2 ? m->impl->spmv_plan_hot_n : 0;
+  });
+}
+
 // ---- SpMV plan (pure host) ------------------------------------------------------------------------------------------------
 int qdsp_spmv_plan_host(const int32_t *indptr, int rows, int32_t *blocks_out, int64_t block_capacity, int64_t *n_blocks,
                         int *n_long_rows, int *n_segments) {

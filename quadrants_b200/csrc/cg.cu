@@ -1095,7 +1095,8 @@ void launch_spmv_dot(CgSolver::Impl &I) {
   const CsrMatrix &A = I.A;
   auto *sc = I.scalars.get<CgScalars>();
   const size_t smem = spmv_smem_bytes<T>();
-  const SpmvSched sched = spmv_sched_for(ceil_div(I.n, SPMV_CONSUMERS / LPR), I.spmv_grid, I.sched.get<unsigned>());
+  SpmvSched sched = spmv_sched_for(ceil_div(I.n, SPMV_CONSUMERS / LPR), I.spmv_grid, I.sched.get<unsigned>());
+  if (LPR == 1) spmv_attach_codes(A, sched);
   if (A.row_major_order && LPR == 1)
     launch_pdl(cg_spmv_dot_kernel<T, LPR, true>, I.spmv_grid, SPMV_THREADS, smem, I.stream, I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
         sc, I.partials.get<double>(), I.dev(), I.use_nccl, sched);

@@ -55,6 +55,10 @@ class CsrMatrix {
   mutable int spmv_max_block_nnz = 0;  // largest stage footprint of a uniform row block (spmv_prepare)
   mutable DeviceBuffer spmv_plan_blocks, spmv_plan_long, spmv_plan_partials, spmv_plan_ticket;
   mutable int spmv_plan_nblk = 0, spmv_plan_nlong = 0;
+  // uniform path, diagonal-coded indices (spmv_kernels.cuh SpmvSched): one byte per non-zero + the table of offsets
+  mutable DeviceBuffer spmv_codes, spmv_code_tab;
+  mutable int spmv_ntab = 0;        // 0 = canonical indices are streamed
+  mutable int spmv_compress = -1;   // -1: QDSP_SPMV_COMPRESS decides (default on), 0: off, 1: on (qdsp_csr_spmv_config)
   // stream path, hot columns (spmv_kernels.cuh): the most referenced columns, and `indices` with them stored as ~slot
   mutable DeviceBuffer spmv_plan_hot_cols, spmv_plan_hot_idx;
   mutable int spmv_plan_hot_n = 0;
@@ -120,6 +124,8 @@ struct SpmvPlanDev;
 struct SpmvSched;
 // scheduling of a uniform-path launch of `grid` CTAs over `nblk` row blocks; counters = 2 zeroed unsigned words (or nullptr)
 SpmvSched spmv_sched_for(int nblk, int grid, unsigned *counters);
+// attaches the diagonal codes of A (if the plan made any) to a launch
+void spmv_attach_codes(const CsrMatrix &A, SpmvSched &sched);
 // pure host: the stream-path work partition (blocks {row0, nrows | -(segment+1), nz0, nz1}; long_rows {row, first segment})
 void spmv_plan_host(const int32_t *indptr, int rows, std::vector<int4> &blocks, std::vector<int2> &long_rows,
                     int &n_segments);

@@ -5,6 +5,7 @@
 #include <string>
 #include <fstream>
 #include <algorithm>
+#include <climits>
 #include <vector>
 
 #include "host.hpp"
@@ -78,6 +79,98 @@ __global__ void __launch_bounds__(256) row_stats_kernel(int rows, int R, const i
   if (lane_id() == 0) {
     if (m > 0) atomicMax(out, m);
     if (mb > 0) atomicMax(out + 1, mb);
+  }
+}
+
+// ---- diagonal-coded indices of the uniform path (spmv_kernels.cuh SpmvSched) ----------------------------------------------------
+constexpr int CODE_SLOTS = 1024;          // open-addressing set of distinct (col - row); more than 256 entries = give up
+constexpr int CODE_EMPTY = INT_MIN;
+__global__ void __launch_bounds__(256) code_collect_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ idx,
+                                                           int *__restrict__ set, int *__restrict__ count) {
+  for (int r = blockIdx.x * 256 + threadIdx.x; r < rows; r += gridDim.x * 256) {
+    if (*reinterpret_cast<volatile int *>(count) > 256) return;  // too many distinct offsets: the host gives up anyway
+    for (int k = indptr[r]; k < indptr[r + 1]; ++k) {
+      const int off = idx[k] - r;
+      unsigned h = (static_cast<unsigned>(off) * 2654435761u) >> 22;  // 10 bits
+      for (int probe = 0; probe < CODE_SLOTS; ++probe, h = (h + 1) & (CODE_SLOTS - 1)) {
+        const int cur = set[h];
+        if (cur == off) break;
+        if (cur == CODE_EMPTY) {
+          const int old = atomicCAS(set + h, CODE_EMPTY, off);
+          if (old == CODE_EMPTY) { atomicAdd(count, 1); break; }
+          if (old == off) break;
+        }
+      }
+    }
+  }
+}
+__global__ void __launch_bounds__(256) code_encode_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ idx,
+                                                          const int *__restrict__ tab, int ntab, unsigned char *__restrict__ codes,
+                                                          int *__restrict__ failed) {
+  __shared__ int s_tab[256];
+  for (int i = threadIdx.x; i < ntab; i += 256) s_tab[i] = tab[i];
+  __syncthreads();
+  for (int r = blockIdx.x * 256 + threadIdx.x; r < rows; r += gridDim.x * 256) {
+    for (int k = indptr[r]; k < indptr[r + 1]; ++k) {
+      const int off = idx[k] - r;
+      int lo = 0, hi = ntab;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (s_tab[mid] < off) lo = mid + 1;
+        else hi = mid;
+      }
+      if (lo < ntab && s_tab[lo] == off) codes[k] = static_cast<unsigned char>(lo);
+      else *failed = 1;
+    }
+  }
+}
+
+// Makes the one-byte codes when the matrix has <= 256 distinct (col - row).  QDSP_SPMV_COMPRESS=0 switches it off
+// process-wide; qdsp_csr_spmv_config per matrix.
+static void spmv_plan_codes(const CsrMatrix &A, cudaStream_t stream) {
+  A.spmv_ntab = 0;
+  static const bool env_on = [] { const char *e = std::getenv("QDSP_SPMV_COMPRESS"); return !(e && e[0] == '0'); }();
+  const bool on = A.spmv_compress < 0 ? env_on : A.spmv_compress != 0;
+  if (!on || A.nnz == 0 || A.spmv_lpr != 1) return;
+  DeviceBuffer set(sizeof(int) * (CODE_SLOTS + 2));
+  std::vector<int> h(CODE_SLOTS + 2, CODE_EMPTY);
+  h[CODE_SLOTS] = h[CODE_SLOTS + 1] = 0;
+  QDSP_CUDA(cudaMemcpyAsync(set.get(), h.data(), sizeof(int) * h.size(), cudaMemcpyHostToDevice, stream));
+  const int grid = std::max(1, std::min(device_props().sm_count * 8, ceil_div(A.rows, 256)));
+  code_collect_kernel<<<grid, 256, 0, stream>>>(A.rows, A.indptr.get<int>(), A.indices.get<int>(), set.get<int>(),
+                                                set.get<int>() + CODE_SLOTS);
+  QDSP_LAUNCH_CHECK();
+  QDSP_CUDA(cudaMemcpyAsync(h.data(), set.get(), sizeof(int) * h.size(), cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+  if (h[CODE_SLOTS] > 256 || h[CODE_SLOTS] <= 0) return;
+  std::vector<int> tab;
+  for (int i = 0; i < CODE_SLOTS; ++i)
+    if (h[i] != CODE_EMPTY) tab.push_back(h[i]);
+  std::sort(tab.begin(), tab.end());
+  if (tab.size() > 256) return;
+  A.spmv_code_tab.alloc(sizeof(int) * 256);
+  A.spmv_codes.alloc(static_cast<size_t>(A.nnz) + 64);  // TMA reads whole 16-byte units
+  QDSP_CUDA(cudaMemsetAsync(A.spmv_codes.get(), 0, A.spmv_codes.bytes(), stream));
+  QDSP_CUDA(cudaMemcpyAsync(A.spmv_code_tab.get(), tab.data(), sizeof(int) * tab.size(), cudaMemcpyHostToDevice, stream));
+  int *failed = set.get<int>() + CODE_SLOTS + 1;
+  code_encode_kernel<<<grid, 256, 0, stream>>>(A.rows, A.indptr.get<int>(), A.indices.get<int>(), A.spmv_code_tab.get<int>(),
+                                               static_cast<int>(tab.size()), A.spmv_codes.get<unsigned char>(), failed);
+  QDSP_LAUNCH_CHECK();
+  int bad = 0;
+  QDSP_CUDA(cudaMemcpyAsync(&bad, failed, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  QDSP_CUDA(cudaStreamSynchronize(stream));
+  if (bad) {  // (cannot happen: the set holds every offset)
+    A.spmv_codes.release();
+    return;
+  }
+  A.spmv_ntab = static_cast<int>(tab.size());
+}
+
+void spmv_attach_codes(const CsrMatrix &A, SpmvSched &sched) {
+  if (A.spmv_ntab > 0) {
+    sched.codes = A.spmv_codes.get<unsigned char>();
+    sched.tab = A.spmv_code_tab.get<int>();
+    sched.ntab = A.spmv_ntab;
   }
 }
 
@@ -194,6 +287,7 @@ void spmv_prepare(const CsrMatrix &A, cudaStream_t stream) {
     QDSP_CUDA(cudaMemsetAsync(A.spmv_sched_buf.get(), 0, A.spmv_sched_buf.bytes(), stream));
     QDSP_CUDA(cudaStreamSynchronize(stream));
     A.spmv_mode = 1;
+    spmv_plan_codes(A, stream);
     return;
   }
   std::vector<int32_t> ip(static_cast<size_t>(A.rows) + 1);
@@ -278,7 +372,8 @@ void launch_spmv_t(const CsrMatrix &A, const T *x, T *y, const DistDev &d, cudaS
   const int *ip = A.indptr.get<int>(), *ix = A.indices.get<int>();
   unsigned *counters = A.spmv_sched_buf.get<unsigned>();
   if (counters) counters += 2 * (A.spmv_sched_next++ % 16);
-  const SpmvSched sched = spmv_sched_for(ceil_div(A.rows, R), grid, counters);
+  SpmvSched sched = spmv_sched_for(ceil_div(A.rows, R), grid, counters);
+  if (LPR == 1) spmv_attach_codes(A, sched);
   if (A.row_major_order && LPR == 1)
     spmv_kernel<T, LPR, true><<<grid, SPMV_THREADS, smem, stream>>>(A.rows, ip, ix, A.values.get<T>(), x, y, d, sched);
   else

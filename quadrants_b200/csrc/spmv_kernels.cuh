@@ -182,6 +182,15 @@ struct SpmvSched {
   unsigned *done = nullptr;  // producers that have finished
   int static_blocks = 0;
   int chunk = 2;
+  // Diagonal-coded column indices (uniform path, one thread per row; spmv.cu spmv_plan_codes): when the matrix has at
+  // most 256 distinct values of (column - row) -- stencils, banded and block-banded matrices, also after the multi-GPU
+  // renumbering -- the plan keeps ONE BYTE per non-zero, codes[k] = position of (col - row) in the sorted table `tab`,
+  // and the kernel streams that instead of the 4-byte index: nnz * (sv + 1) instead of nnz * (sv + 4) bytes per product
+  // (fp32 7-point stencil: 0.63 of the canonical traffic).  Same entries, same order, same arithmetic => the same bits;
+  // the canonical `indices` array stays (export, oversized blocks).  nullptr = canonical indices.
+  const unsigned char *codes = nullptr;
+  const int *tab = nullptr;
+  int ntab = 0;
 };
 
 __device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(SPMV_CONSUMERS) : "memory"); }
@@ -255,7 +264,11 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
   auto *full = reinterpret_cast<unsigned long long *>(base + SPMV_STAGES * spmv_stage_bytes<T, AUX, CAP>());
   auto *empty = full + SPMV_STAGES;
   const int t = threadIdx.x;
-  if constexpr (!FUSED) spmv_ring_init<SPMV_STAGES>(full, empty);
+  __shared__ int s_tab[256];  // column - row of every code (diagonal-coded indices, see SpmvSched)
+  const bool coded = !FUSED && LPR == 1 && sched.codes != nullptr;
+  if (coded)
+    for (int i = t; i < sched.ntab; i += SPMV_THREADS) s_tab[i] = sched.tab[i];
+  if constexpr (!FUSED) spmv_ring_init<SPMV_STAGES>(full, empty);  // (its __syncthreads also publishes s_tab)
   // no per-block ghost map for this block size: every CTA waits for the halo before its first gather
   const bool lazy_halo = dist.world > 1 && dist.ghost_blocks != nullptr && dist.ghost_block_rows == R;
   if constexpr (!FUSED) {
@@ -338,11 +351,13 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
             tma_bulk_g2s(st.aux + k * SPMV_CONSUMERS, sink.aux_src(k) + r0, aux_bytes, &full[stage], pol);
         }
         if (cnt <= CAP && cnt > 0) {
-          const unsigned ib = static_cast<unsigned>((cnt * 4 + 15) & ~15);
+          const int a0c = s & ~15;  // codes: one byte each, 16 to a TMA unit
+          const unsigned ib = coded ? static_cast<unsigned>((e - a0c + 15) & ~15) : static_cast<unsigned>((cnt * 4 + 15) & ~15);
           const unsigned vb = static_cast<unsigned>((cnt * static_cast<int>(sizeof(T)) + 15) & ~15);
           mbar_expect_tx(&full[stage], ptr_bytes + ib + vb + AUX * aux_bytes);
           tma_bulk_g2s(st.ptr, indptr + r0, ptr_bytes, &full[stage], pol);
-          tma_bulk_g2s(st.idx, indices + a0, ib, &full[stage], pol);
+          if (coded) tma_bulk_g2s(st.idx, sched.codes + a0c, ib, &full[stage], pol);
+          else tma_bulk_g2s(st.idx, indices + a0, ib, &full[stage], pol);
           tma_bulk_g2s(st.val, values + a0, vb, &full[stage], pol);
         } else {
           mbar_expect_tx(&full[stage], ptr_bytes + AUX * aux_bytes);
@@ -391,12 +406,15 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
           const int lo = st.ptr[row_in_blk] - a0, hi = st.ptr[row_in_blk + 1] - a0;
           if (LPR == 1) {
             T acc_a = T(0), acc_b = T(0);
+            const unsigned char *code = reinterpret_cast<const unsigned char *>(st.idx) + (a0 - (s & ~15));
+            const int grow = r0 + row_in_blk;
             for (int k = lo; k < hi; k += 8) {
               T v[8], xv[8];
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 const bool ok = k + j < hi;
-                const int c = ok ? st.idx[k + j] : 0;
+                int c = 0;
+                if (ok) c = coded ? grow + s_tab[code[k + j]] : st.idx[k + j];
                 v[j] = ok ? st.val[k + j] : T(0);
                 xv[j] = ok ? ld_x<FUSED>(x + c) : T(0);
               }

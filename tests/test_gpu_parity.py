@@ -715,3 +715,60 @@ def test_scan_unaligned_pointer(qd, oracle, shift, n):
     out = t.cpu().numpy()
     assert np.array_equal(out[shift:shift + n], oracle.inclusive_scan(a[shift:shift + n]))
     assert np.array_equal(out[:shift], a[:shift]) and np.array_equal(out[shift + n:], a[shift + n:])
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# diagonal-coded column indices (qdsp_csr_spmv_config): same bits as the canonical stream
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dt,storage", [(np.float32, "col_major"), (np.float32, "row_major"), (np.float64, "col_major")])
+def test_spmv_and_cg_diagonal_codes_are_bit_identical(qd, oracle, dt, storage):
+    n = 40
+    r, c, v = W.poisson3d_triplets(n, dtype=dt)
+    buf = make_triplet_buffer(r, c, v, dt)
+    N = n ** 3
+    A = build_from_buffer(qd, buf, N, N, storage)
+    x = np.random.default_rng(4).uniform(-1, 1, N).astype(dt)
+    xd = to_nd(qd, x)
+    assert A.matrix.spmv_info() == {"index_bytes_per_nnz": 1, "path": "uniform", "hot_columns": 0}
+    y1 = (A @ xd).to_numpy()
+    A.matrix.spmv_config(0)
+    assert A.matrix.spmv_info()["index_bytes_per_nnz"] == 4
+    y0 = (A @ xd).to_numpy()
+    assert np.array_equal(bits(y1), bits(y0))
+    oo, oi, ov = oracle.build_matrix(buf, N, N, storage == "row_major")
+    yref = oracle.spmv(oo, oi, ov, x, N, N, storage == "row_major")
+    assert np.array_equal(bits(y1), bits(yref)), "coded SpMV differs from Eigen's product"
+    # CG on both plans: identical iterates (the solver is created after the plan it runs on)
+    b = to_nd(qd, np.ones(N, dt))
+    cg0 = qd.linalg.SparseCG(A, b, max_iter=300, atol=1e-6)
+    x0, ok0 = cg0.solve()
+    x0 = x0.to_numpy().copy()
+    A.matrix.spmv_config(1)
+    cg1 = qd.linalg.SparseCG(A, b, max_iter=300, atol=1e-6)
+    x1, ok1 = cg1.solve()
+    assert ok0 and ok1 and cg0.iterations == cg1.iterations and np.array_equal(bits(x0), bits(x1.to_numpy()))
+
+
+def test_diagonal_codes_decline_unsuitable_matrices(qd):
+    # more than 256 distinct (col - row): canonical indices are streamed
+    rng = np.random.default_rng(5)
+    n = 20000
+    r = np.repeat(np.arange(n), 5)
+    c = rng.integers(0, n, r.shape[0])
+    v = rng.uniform(-1, 1, r.shape[0]).astype(np.float32)
+    A = build_from_buffer(qd, make_triplet_buffer(r, c, v, np.float32), n, n)
+    assert A.matrix.spmv_info()["index_bytes_per_nnz"] == 4
+    # a banded matrix with exactly 256 offsets is coded; one more offset and it is not
+    for width, want in ((256, 1), (257, 4)):
+        rr = np.repeat(np.arange(2000), width)
+        cc = (rr + np.tile(np.arange(width), 2000) * 3) % 9000
+        vv = rng.uniform(-1, 1, rr.shape[0]).astype(np.float64)
+        B = build_from_buffer(qd, make_triplet_buffer(rr, cc, vv, np.float64), 2000, 9000)
+        info = B.matrix.spmv_info()
+        if info["path"] == "uniform" and B.matrix.spmv_info()["index_bytes_per_nnz"] == 1:
+            x = rng.uniform(-1, 1, 9000)
+            y1 = (B @ to_nd(qd, x)).to_numpy()
+            B.matrix.spmv_config(0)
+            assert np.array_equal(bits(y1), bits((B @ to_nd(qd, x)).to_numpy()))
+        if want == 4:
+            assert info["index_bytes_per_nnz"] == 4
