@@ -385,7 +385,7 @@ __global__ void __launch_bounds__(CG_THREADS) cg_push_direction_kernel(int n, co
 }
 
 // ---- iteration kernels --------------------------------------------------------------------------------------------------
-template <typename T, int LPR, bool ROW_MAJOR_ORDER>
+template <typename T, int LPR, bool ROW_MAJOR_ORDER, bool CODED = false>
 __global__ void __launch_bounds__(SPMV_THREADS)
 cg_spmv_dot_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ indices,
                    const T *__restrict__ values, const T *__restrict__ p, T *__restrict__ tmp,
@@ -407,7 +407,7 @@ cg_spmv_dot_kernel(int rows, const int *__restrict__ indptr, const int *__restri
   if (chain && blockIdx.x == 0 && threadIdx.x == 0) sc->flag_A = sc->flag_B = 0u;  // ordered before the raise by CTA 0's ticket
   cg_tl_begin(sc, 0);
   DotSink<T> sink{p};
-  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, p, tmp, sink, d, 0, sched);
+  spmv_persistent<T, LPR, ROW_MAJOR_ORDER, DotSink<T>, false, CODED>(smem_raw, rows, indptr, indices, values, p, tmp, sink, d, 0, sched);
   pdl_trigger();
   double v[1] = {sink.acc};
   if (grid_sum_last_block<1>(v, partials, &sc->ticket[1], s_red, &s_flag)) {
@@ -1096,7 +1096,18 @@ void launch_spmv_dot(CgSolver::Impl &I) {
   auto *sc = I.scalars.get<CgScalars>();
   const size_t smem = spmv_smem_bytes<T>();
   SpmvSched sched = spmv_sched_for(ceil_div(I.n, SPMV_CONSUMERS / LPR), I.spmv_grid, I.sched.get<unsigned>());
-  if (LPR == 1) spmv_attach_codes(A, sched);
+  if constexpr (LPR == 1) {
+    spmv_attach_codes(A, sched);
+    if (sched.codes != nullptr) {  // the diagonal-coded instantiation: same footprint, same grid
+      if (A.row_major_order)
+        launch_pdl(cg_spmv_dot_kernel<T, 1, true, true>, I.spmv_grid, SPMV_THREADS, smem, I.stream, I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+            sc, I.partials.get<double>(), I.dev(), I.use_nccl, sched);
+      else
+        launch_pdl(cg_spmv_dot_kernel<T, 1, false, true>, I.spmv_grid, SPMV_THREADS, smem, I.stream, I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
+            sc, I.partials.get<double>(), I.dev(), I.use_nccl, sched);
+      return;
+    }
+  }
   if (A.row_major_order && LPR == 1)
     launch_pdl(cg_spmv_dot_kernel<T, LPR, true>, I.spmv_grid, SPMV_THREADS, smem, I.stream, I.n, A.indptr.get<int>(), A.indices.get<int>(), A.values.get<T>(), static_cast<const T *>(I.p), I.tmp.get<T>(),
         sc, I.partials.get<double>(), I.dev(), I.use_nccl, sched);
@@ -1128,6 +1139,10 @@ int spmv_dot_occupancy() {
   int occ = 0;
   QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_dot_kernel<T, LPR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_dot_kernel<T, LPR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  if constexpr (LPR == 1) {
+    QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_dot_kernel<T, 1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    QDSP_CUDA(cudaFuncSetAttribute(cg_spmv_dot_kernel<T, 1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  }
   QDSP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, cg_spmv_dot_kernel<T, LPR, false>, SPMV_THREADS, smem));
   return std::max(1, occ);
 }

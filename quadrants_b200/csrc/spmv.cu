@@ -32,13 +32,13 @@ const DeviceProps &device_props() {
   return cached;
 }
 
-template <typename T, int LPR, bool ROW_MAJOR_ORDER>
+template <typename T, int LPR, bool ROW_MAJOR_ORDER, bool CODED = false>
 __global__ void __launch_bounds__(SPMV_THREADS)
 spmv_kernel(int rows, const int *__restrict__ indptr, const int *__restrict__ indices, const T *__restrict__ values,
             const T *__restrict__ x, T *__restrict__ y, DistDev d, SpmvSched sched) {
   extern __shared__ unsigned char smem_raw[];
   NoSink sink;
-  spmv_persistent<T, LPR, ROW_MAJOR_ORDER>(smem_raw, rows, indptr, indices, values, x, y, sink, d, 0, sched);
+  spmv_persistent<T, LPR, ROW_MAJOR_ORDER, NoSink, false, CODED>(smem_raw, rows, indptr, indices, values, x, y, sink, d, 0, sched);
 }
 
 // Static run per CTA = 3/4 of an even share; the rest is handed out two blocks at a time.  Small launches (< 8 blocks per
@@ -373,7 +373,23 @@ void launch_spmv_t(const CsrMatrix &A, const T *x, T *y, const DistDev &d, cudaS
   unsigned *counters = A.spmv_sched_buf.get<unsigned>();
   if (counters) counters += 2 * (A.spmv_sched_next++ % 16);
   SpmvSched sched = spmv_sched_for(ceil_div(A.rows, R), grid, counters);
-  if (LPR == 1) spmv_attach_codes(A, sched);
+  if constexpr (LPR == 1) {
+    spmv_attach_codes(A, sched);
+    if (sched.codes != nullptr) {  // the coded instantiation (same shared-memory footprint, same grid)
+      static bool attr[16] = {};
+      if (!attr[device_props().device & 15]) {
+        QDSP_CUDA(cudaFuncSetAttribute(spmv_kernel<T, 1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        QDSP_CUDA(cudaFuncSetAttribute(spmv_kernel<T, 1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        attr[device_props().device & 15] = true;
+      }
+      if (A.row_major_order)
+        spmv_kernel<T, 1, true, true><<<grid, SPMV_THREADS, smem, stream>>>(A.rows, ip, ix, A.values.get<T>(), x, y, d, sched);
+      else
+        spmv_kernel<T, 1, false, true><<<grid, SPMV_THREADS, smem, stream>>>(A.rows, ip, ix, A.values.get<T>(), x, y, d, sched);
+      QDSP_LAUNCH_CHECK();
+      return;
+    }
+  }
   if (A.row_major_order && LPR == 1)
     spmv_kernel<T, LPR, true><<<grid, SPMV_THREADS, smem, stream>>>(A.rows, ip, ix, A.values.get<T>(), x, y, d, sched);
   else

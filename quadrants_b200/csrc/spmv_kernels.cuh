@@ -101,6 +101,11 @@ __device__ __forceinline__ int lds_i32(const int *p) {
   asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)));
   return v;
 }
+__device__ __forceinline__ int lds_u8(const unsigned char *p) {
+  unsigned v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)));
+  return static_cast<int>(v);
+}
 __device__ __forceinline__ int4 lds_i32x4(const int *p) {
   int4 v;
   asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
@@ -252,7 +257,7 @@ struct MergedSink {
 // per CG iteration `iter` from the producer thread and from the consumers INDEPENDENTLY (the producer streams the constant
 // matrix arrays and may run ahead of the consumers by the depth of the ring); ring positions continue across calls;
 // nothing here synchronises the whole CTA; the halo wait moves to the consumers; x is read coherently (ld_x).
-template <typename T, int LPR, bool ROW_MAJOR_ORDER, typename Sink, bool FUSED = false>
+template <typename T, int LPR, bool ROW_MAJOR_ORDER, typename Sink, bool FUSED = false, bool CODED = false>
 __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int rows, const int *__restrict__ indptr,
                                                 const int *__restrict__ indices, const T *__restrict__ values,
                                                 const T *x, T *y, Sink &sink, const DistDev &dist, int iter = 0,
@@ -265,7 +270,8 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
   auto *empty = full + SPMV_STAGES;
   const int t = threadIdx.x;
   __shared__ int s_tab[256];  // column - row of every code (diagonal-coded indices, see SpmvSched)
-  const bool coded = !FUSED && LPR == 1 && sched.codes != nullptr;
+  static_assert(!CODED || (LPR == 1 && !FUSED), "diagonal codes: one thread per row, stand-alone kernels only");
+  constexpr bool coded = CODED;  // a separate instantiation: the canonical kernel's code is untouched by the coded path
   if (coded)
     for (int i = t; i < sched.ntab; i += SPMV_THREADS) s_tab[i] = sched.tab[i];
   if constexpr (!FUSED) spmv_ring_init<SPMV_STAGES>(full, empty);  // (its __syncthreads also publishes s_tab)
@@ -396,25 +402,60 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
       }
       const int r0 = blk * R;
       const int nr = min(R, rows - r0);
-      const int s = st.ptr[0], e = st.ptr[nr];
+      // (coded instantiation: explicit ld.shared for the row pointers as well; the canonical kernel is left as measured)
+      const int s = CODED ? lds_i32(st.ptr) : st.ptr[0], e = CODED ? lds_i32(st.ptr + nr) : st.ptr[nr];
       const int a0 = s & ~3;
       if (e - a0 <= CAP) {
         T result = T(0);
         typename Sink::Pre pre{};
         if (row_in_blk < nr) {
           if (q == 0) pre = sink.pre(r0 + row_in_blk, st.aux, row_in_blk);
-          const int lo = st.ptr[row_in_blk] - a0, hi = st.ptr[row_in_blk + 1] - a0;
-          if (LPR == 1) {
-            T acc_a = T(0), acc_b = T(0);
+          const int lo = (CODED ? lds_i32(st.ptr + row_in_blk) : st.ptr[row_in_blk]) - a0,
+                    hi = (CODED ? lds_i32(st.ptr + row_in_blk + 1) : st.ptr[row_in_blk + 1]) - a0;
+          if constexpr (CODED) {
+            // one byte per entry: column = row + s_tab[code].  Same batch-of-eight shape as the canonical body (the eight
+            // codes, then the eight table look-ups, then the eight gathers are issued together; the products are added in
+            // Eigen's order), with explicit ld.shared -- the stage pointers are generic to the compiler and generic loads
+            // of shared memory wait in the global-memory pipe (ncu, profiles/r02as: the dependent chain code -> offset ->
+            // x -> fma was 65 % long-scoreboard stalls).  The coded stream moves 0.63 of the canonical bytes, so issue
+            // slots, not HBM, are what this body has to watch.
             const unsigned char *code = reinterpret_cast<const unsigned char *>(st.idx) + (a0 - (s & ~15));
-            const int grow = r0 + row_in_blk;
+            const T *xr = x + (r0 + row_in_blk);
+            T acc_a = T(0), acc_b = T(0);
+            for (int k = lo; k < hi; k += 8) {
+              int cd[8];
+              T v[8], xv[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) cd[j] = lds_u8(code + min(k + j, hi - 1));
+#pragma unroll
+              for (int j = 0; j < 8; ++j) cd[j] = s_tab[cd[j]];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const bool ok = k + j < hi;
+                v[j] = ok ? lds_val(st.val + k + j) : T(0);
+                xv[j] = ok ? __ldg(xr + cd[j]) : T(0);
+              }
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                if (k + j < hi) {
+                  if (ROW_MAJOR_ORDER) {
+                    if ((j & 1) == 0) acc_a = mad_unfused(v[j], xv[j], acc_a);
+                    else acc_b = fma_t(v[j], xv[j], acc_b);
+                  } else {
+                    acc_a = fma_t(v[j], xv[j], acc_a);
+                  }
+                }
+              }
+            }
+            result = ROW_MAJOR_ORDER ? (T(0) + (acc_a + acc_b)) : acc_a;
+          } else if (LPR == 1) {
+            T acc_a = T(0), acc_b = T(0);
             for (int k = lo; k < hi; k += 8) {
               T v[8], xv[8];
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 const bool ok = k + j < hi;
-                int c = 0;
-                if (ok) c = coded ? grow + s_tab[code[k + j]] : st.idx[k + j];
+                const int c = ok ? st.idx[k + j] : 0;
                 v[j] = ok ? st.val[k + j] : T(0);
                 xv[j] = ok ? ld_x<FUSED>(x + c) : T(0);
               }
