@@ -111,8 +111,9 @@ int qdsp_csr_spmv(qdsp_csr_t m, const void *x, void *y, void *stream);
 /* SpMV storage option of one matrix.  compress: 1 = stream one-byte diagonal codes instead of the 4-byte column indices
  * when the matrix has at most 256 distinct (column - row) values (stencils, banded matrices; the plan keeps an extra
  * nnz-byte array, the canonical arrays stay exportable and the results are bit-identical), 0 = always stream the
- * canonical indices, -1 = the process default (QDSP_SPMV_COMPRESS, on unless "0").  Drops the matrix's SpMV plan: call it
- * before creating solvers on the matrix.  No reference counterpart (cuSPARSE has no such format for CSR_ALG1). */
+ * canonical indices, -1 = the process default (QDSP_SPMV_COMPRESS, on unless "0").  Applies to products and solvers
+ * started afterwards; a solver created earlier keeps the path it was created with (the code arrays are never moved or
+ * freed while the matrix lives).  No reference counterpart (cuSPARSE has no such format for CSR_ALG1). */
 int qdsp_csr_spmv_config(qdsp_csr_t m, int compress);
 /* What the plan of `m` streams per product (plans the matrix if needed): *index_bytes_per_nnz = 1 (diagonal codes) or 4,
  * *path = 1 uniform row blocks / 2 irregular (stream) path, *hot_columns = columns cached in shared memory (stream path). */

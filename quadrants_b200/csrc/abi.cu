@@ -317,8 +317,7 @@ int qdsp_cg_destroy(qdsp_cg_t s) {
 int qdsp_csr_spmv_config(qdsp_csr_t m, int compress) {
   return guarded([&] {
     NOT_NULL(m);
-    m->impl->spmv_compress = compress < 0 ? -1 : (compress ? 1 : 0);
-    m->impl->spmv_mode = 0;  // re-plan on next use
+    spmv_set_compress(*m->impl, compress, nullptr);
   });
 }
 int qdsp_csr_spmv_info(qdsp_csr_t m, void *stream, int *index_bytes_per_nnz, int *path, int *hot_columns) {

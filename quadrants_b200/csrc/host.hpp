@@ -58,6 +58,7 @@ class CsrMatrix {
   // uniform path, diagonal-coded indices (spmv_kernels.cuh SpmvSched): one byte per non-zero + the table of offsets
   mutable DeviceBuffer spmv_codes, spmv_code_tab;
   mutable int spmv_ntab = 0;        // 0 = canonical indices are streamed
+  mutable int spmv_ntab_built = 0;  // entries of the table once made (kept when the codes are switched off); -1 = not codable
   mutable int spmv_compress = -1;   // -1: QDSP_SPMV_COMPRESS decides (default on), 0: off, 1: on (qdsp_csr_spmv_config)
   // stream path, hot columns (spmv_kernels.cuh): the most referenced columns, and `indices` with them stored as ~slot
   mutable DeviceBuffer spmv_plan_hot_cols, spmv_plan_hot_idx;
@@ -126,6 +127,7 @@ struct SpmvSched;
 SpmvSched spmv_sched_for(int nblk, int grid, unsigned *counters);
 // attaches the diagonal codes of A (if the plan made any) to a launch
 void spmv_attach_codes(const CsrMatrix &A, SpmvSched &sched);
+void spmv_set_compress(const CsrMatrix &A, int compress, cudaStream_t stream);
 // pure host: the stream-path work partition (blocks {row0, nrows | -(segment+1), nz0, nz1}; long_rows {row, first segment})
 void spmv_plan_host(const int32_t *indptr, int rows, std::vector<int4> &blocks, std::vector<int2> &long_rows,
                     int &n_segments);

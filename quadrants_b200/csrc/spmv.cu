@@ -132,6 +132,12 @@ static void spmv_plan_codes(const CsrMatrix &A, cudaStream_t stream) {
   static const bool env_on = [] { const char *e = std::getenv("QDSP_SPMV_COMPRESS"); return !(e && e[0] == '0'); }();
   const bool on = A.spmv_compress < 0 ? env_on : A.spmv_compress != 0;
   if (!on || A.nnz == 0 || A.spmv_lpr != 1) return;
+  if (A.spmv_ntab_built > 0) {  // made before and switched off in between: the arrays are still there (see spmv_set_compress)
+    A.spmv_ntab = A.spmv_ntab_built;
+    return;
+  }
+  if (A.spmv_ntab_built < 0) return;  // tried before: the matrix has too many distinct offsets
+  A.spmv_ntab_built = -1;
   DeviceBuffer set(sizeof(int) * (CODE_SLOTS + 2));
   std::vector<int> h(CODE_SLOTS + 2, CODE_EMPTY);
   h[CODE_SLOTS] = h[CODE_SLOTS + 1] = 0;
@@ -148,22 +154,28 @@ static void spmv_plan_codes(const CsrMatrix &A, cudaStream_t stream) {
     if (h[i] != CODE_EMPTY) tab.push_back(h[i]);
   std::sort(tab.begin(), tab.end());
   if (tab.size() > 256) return;
-  A.spmv_code_tab.alloc(sizeof(int) * 256);
-  A.spmv_codes.alloc(static_cast<size_t>(A.nnz) + 64);  // TMA reads whole 16-byte units
-  QDSP_CUDA(cudaMemsetAsync(A.spmv_codes.get(), 0, A.spmv_codes.bytes(), stream));
-  QDSP_CUDA(cudaMemcpyAsync(A.spmv_code_tab.get(), tab.data(), sizeof(int) * tab.size(), cudaMemcpyHostToDevice, stream));
+  DeviceBuffer d_tab(sizeof(int) * 256), d_codes(static_cast<size_t>(A.nnz) + 64);  // TMA reads whole 16-byte units
+  QDSP_CUDA(cudaMemsetAsync(d_codes.get(), 0, d_codes.bytes(), stream));
+  QDSP_CUDA(cudaMemcpyAsync(d_tab.get(), tab.data(), sizeof(int) * tab.size(), cudaMemcpyHostToDevice, stream));
   int *failed = set.get<int>() + CODE_SLOTS + 1;
-  code_encode_kernel<<<grid, 256, 0, stream>>>(A.rows, A.indptr.get<int>(), A.indices.get<int>(), A.spmv_code_tab.get<int>(),
-                                               static_cast<int>(tab.size()), A.spmv_codes.get<unsigned char>(), failed);
+  code_encode_kernel<<<grid, 256, 0, stream>>>(A.rows, A.indptr.get<int>(), A.indices.get<int>(), d_tab.get<int>(),
+                                               static_cast<int>(tab.size()), d_codes.get<unsigned char>(), failed);
   QDSP_LAUNCH_CHECK();
   int bad = 0;
   QDSP_CUDA(cudaMemcpyAsync(&bad, failed, sizeof(int), cudaMemcpyDeviceToHost, stream));
   QDSP_CUDA(cudaStreamSynchronize(stream));
-  if (bad) {  // (cannot happen: the set holds every offset)
-    A.spmv_codes.release();
-    return;
-  }
-  A.spmv_ntab = static_cast<int>(tab.size());
+  if (bad) return;  // (cannot happen: the set holds every offset)
+  A.spmv_code_tab = std::move(d_tab);
+  A.spmv_codes = std::move(d_codes);
+  A.spmv_ntab = A.spmv_ntab_built = static_cast<int>(tab.size());
+}
+
+// qdsp_csr_spmv_config.  Only the choice "codes or canonical indices" changes: the rest of the plan and, above all, the
+// code arrays themselves stay where they are -- CG solvers made earlier hold their addresses in captured graphs and keep
+// running the path they were created with.
+void spmv_set_compress(const CsrMatrix &A, int compress, cudaStream_t stream) {
+  A.spmv_compress = compress < 0 ? -1 : (compress ? 1 : 0);
+  if (A.spmv_mode == 1) spmv_plan_codes(A, stream);
 }
 
 void spmv_attach_codes(const CsrMatrix &A, SpmvSched &sched) {
@@ -267,6 +279,7 @@ void spmv_plan_host(const int32_t *indptr, int rows, std::vector<int4> &blocks, 
 
 void spmv_prepare(const CsrMatrix &A, cudaStream_t stream) {
   if (A.spmv_mode != 0 || A.rows == 0) return;
+  A.spmv_ntab = A.spmv_ntab_built = 0;  // a new plan (first use, or the column renumbering of qdsp_dist_localize): codes are made afresh
   // uniform row blocks (bit-exact Eigen order when one lane per row) iff no block of R rows overflows a stage
   const int L = spmv_lanes_per_row(A.nnz, A.rows);
   DeviceBuffer mx(2 * sizeof(int));
