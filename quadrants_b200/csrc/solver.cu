@@ -208,42 +208,47 @@ void solver_symbolic_host(int n, const int32_t *indptr, const int32_t *indices, 
         }
       }
   }
-  // row patterns by walking the tree from each B(i,k) up to the first marked node (row subtree)
+  // row patterns by walking the tree from each B(i,k) up to the first marked node (row subtree); the walk yields a row in
+  // no particular order, which is all the column fill below needs
   std::vector<int32_t> mark(n, -1), colcount(n, 1);
-  out.rowptr.assign(n + 1, 0);
-  std::vector<int32_t> &rowcol = out.rowcol;
-  rowcol.clear();
+  std::vector<int32_t> walk_ptr(n + 1, 0), walk;
   int64_t total = n;
   for (int i = 0; i < n; ++i) {
     mark[i] = i;
-    const size_t start = rowcol.size();
     for (int q = lptr[i]; q < lptr[i + 1]; ++q)
       for (int r = low[q]; mark[r] != i; r = out.parent[r]) {
         mark[r] = i;
-        rowcol.push_back(r);
+        walk.push_back(r);
         ++colcount[r];
       }
-    std::sort(rowcol.begin() + start, rowcol.end());
-    total += static_cast<int64_t>(rowcol.size() - start);
+    total = n + static_cast<int64_t>(walk.size());
     QDSP_REQUIRE(total < INT_MAX, QDSP_ERR_INVALID, "solver: the factor has more than 2^31 entries");
-    out.rowptr[i + 1] = static_cast<int32_t>(rowcol.size());
+    walk_ptr[i + 1] = static_cast<int32_t>(walk.size());
   }
   out.factor_nnz = total;
   out.colptr.assign(n + 1, 0);
   for (int j = 0; j < n; ++j) out.colptr[j + 1] = out.colptr[j] + colcount[j];
   out.rowidx.assign(static_cast<size_t>(total), 0);
-  out.rowpos.assign(rowcol.size(), 0);
   std::vector<int32_t> next(n);
   for (int j = 0; j < n; ++j) {
     out.rowidx[out.colptr[j]] = j;  // the diagonal leads its column
     next[j] = out.colptr[j] + 1;
     out.flops += static_cast<double>(colcount[j]) * colcount[j];
   }
+  // columns: rows arrive in ascending order because the rows are visited in ascending order
   for (int i = 0; i < n; ++i)
-    for (int q = out.rowptr[i]; q < out.rowptr[i + 1]; ++q) {
-      const int k = rowcol[q];
-      out.rowpos[q] = next[k];
-      out.rowidx[next[k]++] = i;
+    for (int q = walk_ptr[i]; q < walk_ptr[i + 1]; ++q) out.rowidx[next[walk[q]]++] = i;
+  // rows, sorted by column without a sort: transpose the columns (visited in ascending order) back into the rows
+  out.rowptr = walk_ptr;
+  std::vector<int32_t>().swap(walk);
+  out.rowcol.assign(static_cast<size_t>(total - n), 0);
+  out.rowpos.assign(static_cast<size_t>(total - n), 0);
+  for (int i = 0; i < n; ++i) next[i] = out.rowptr[i];
+  for (int k = 0; k < n; ++k)
+    for (int p = out.colptr[k] + 1; p < out.colptr[k + 1]; ++p) {
+      const int q = next[out.rowidx[p]]++;
+      out.rowcol[q] = k;
+      out.rowpos[q] = p;
     }
   std::vector<int32_t> depth(n, 1);
   for (int j = 0; j < n; ++j) {  // parents have larger indices
