@@ -1,5 +1,7 @@
 // abi.cu -- the extern "C" surface declared in include/qdsp.h.  Thin: argument checks, handle casts, and the
 // exception -> (status, thread-local message) translation.  No exception crosses this file.
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -534,10 +536,16 @@ int qdsp_solver_analyze_host(int n, const int32_t *indptr, const int32_t *indice
     QDSP_REQUIRE(n >= 0, QDSP_ERR_INVALID, "solver analyse: negative size");
     QDSP_REQUIRE(indices != nullptr || indptr[n] == 0, QDSP_ERR_INVALID, "solver analyse: null indices");
     std::vector<int32_t> perm(n);
+    const auto t0 = std::chrono::steady_clock::now();
     if (natural_order) for (int i = 0; i < n; ++i) perm[i] = i;
     else solver_order_host(n, indptr, indices, perm);
+    const auto t1 = std::chrono::steady_clock::now();
     SymbolicFactor f;
     solver_symbolic_host(n, indptr, indices, perm, f);
+    if (std::getenv("QDSP_SOLVER_TIMING"))
+      std::fprintf(stderr, "[qdsp solver] ordering %.1f ms, symbolic %.1f ms\n",
+                   std::chrono::duration<double, std::milli>(t1 - t0).count(),
+                   std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count());
     if (perm_out) std::memcpy(perm_out, f.perm.data(), sizeof(int32_t) * n);
     if (parent_out) std::memcpy(parent_out, f.parent.data(), sizeof(int32_t) * n);
     if (colptr_out) std::memcpy(colptr_out, f.colptr.data(), sizeof(int32_t) * (n + 1));
