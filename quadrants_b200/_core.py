@@ -436,12 +436,20 @@ class CuSparseSolver:
         return self.info()
 
     def solve_rf(self, prog, sm, b, x):
+        n = sm.num_rows()
+        if b.tensor.shape[0] != n or x.tensor.shape[0] != n:
+            raise QuadrantsRuntimeError(f"SparseSolver.solve: vectors of length {b.tensor.shape[0]} / {x.tensor.shape[0]} "
+                                        f"for a system of {n} rows")
         _lib.check(self._lib.qdsp_solver_solve(self._h, b.data_ptr(), x.data_ptr(), _stream(prog)))
 
     def solve(self, b: np.ndarray) -> np.ndarray:
         """EigenSparseSolver::solve(b) with a numpy right-hand side (export_lang.cpp solve overloads)."""
         npdt = np.float64 if self._dt is f64 else np.float32
-        bb = np.ascontiguousarray(b, dtype=npdt)
+        bb = np.ascontiguousarray(b, dtype=npdt).reshape(-1)
+        if self._A is None or bb.shape[0] != self._A.num_rows():
+            raise QuadrantsRuntimeError(
+                f"SparseSolver.solve: right-hand side of length {bb.shape[0]} for a system of "
+                f"{None if self._A is None else self._A.num_rows()} rows")
         x = np.empty_like(bb)
         _lib.check(self._lib.qdsp_solver_solve_host(self._h, bb.ctypes.data, x.ctypes.data, _stream()))
         return x

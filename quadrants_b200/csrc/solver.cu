@@ -333,14 +333,16 @@ __device__ __forceinline__ int lower_bound_dev(const int *a, int len, int key) {
   return lo;
 }
 
-// A's values into the factor slots (amap: >= 0 slot of lx, <= -2 slot -2-v of ux, -1 not used by this factorisation)
+// A's values into the (zeroed) factor slots (amap: >= 0 slot of lx, <= -2 slot -2-v of ux, -1 not used by this
+// factorisation).  Added, not stored: a matrix adopted through qdsp_csr_from_device_csr may hold duplicate entries, which
+// Eigen's solvers sum as well (canonical matrices have one entry per slot, so the order of the additions never matters).
 template <typename T>
 __global__ void solver_scatter_kernel(const T *__restrict__ aval, const int *__restrict__ amap, int64_t nnz, T *lx, T *ux) {
   for (int64_t q = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < nnz;
        q += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     const int s = amap[q];
-    if (s >= 0) lx[s] = aval[q];
-    else if (s <= -2) ux[-2 - s] = aval[q];
+    if (s >= 0) atomicAdd(lx + s, aval[q]);
+    else if (s <= -2) atomicAdd(ux + (-2 - s), aval[q]);
   }
 }
 

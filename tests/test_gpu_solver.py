@@ -194,3 +194,33 @@ def test_solver_failures(qd):
     s = qd.linalg.SparseSolver(dtype=qd.f64)
     with pytest.raises(_lib.QdspError):  # factorize before analyze_pattern
         s.factorize(A)
+
+
+def test_solver_rejects_wrong_length_and_sums_duplicates(qd):
+    a = psd10(6, np.float64)
+    A = fill_dense(qd, a, np.float64)
+    s = qd.linalg.SparseSolver(dtype=qd.f64)
+    s.compute(A)
+    with pytest.raises(qd.QuadrantsRuntimeError):
+        s.solve(np.ones(11))
+    with pytest.raises(qd.QuadrantsRuntimeError):
+        s.solve(qd.ndarray(qd.f64, 9))
+    # a non-canonical CSR (every entry stored twice with half the value) factorises to the same solution
+    import ctypes as C
+
+    import torch
+
+    from quadrants_b200 import _core, _lib
+
+    ip = (np.arange(11) * 20).astype(np.int32)
+    ix = np.tile(np.repeat(np.arange(10), 2), 10).astype(np.int32)
+    vv = np.repeat(a.reshape(-1), 2) * 0.5
+    t = [torch.from_numpy(z).cuda() for z in (ip, ix, vv)]
+    h = C.c_void_p()
+    _lib.check(_lib.load().qdsp_csr_from_device_csr(10, 10, 200, t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(), _lib.F64, 0,
+                                                    torch.cuda.current_stream().cuda_stream, C.byref(h)))
+    D = qd.linalg.SparseMatrix(sm=_core.CuSparseMatrix._wrap(h), dtype=qd.f64)
+    s2 = qd.linalg.SparseSolver(dtype=qd.f64, solver_type="LU")
+    s2.compute(D)
+    b = np.arange(1, 11, dtype=np.float64)
+    assert np.allclose(s2.solve(b), np.linalg.solve(a, b), rtol=1e-10)
