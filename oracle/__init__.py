@@ -83,6 +83,8 @@ class Oracle:
         for name in ("f32", "f64"):
             getattr(L, f"qdo_direct_{name}").restype = C.c_int
             getattr(L, f"qdo_direct_{name}").argtypes = [C.c_int, _VOIDP, _VOIDP, _VOIDP, C.c_int, _VOIDP, _VOIDP]
+            getattr(L, f"qdo_lu_{name}").restype = C.c_int
+            getattr(L, f"qdo_lu_{name}").argtypes = [C.c_int, _VOIDP, _VOIDP, _VOIDP, _VOIDP, _VOIDP]
 
     # -- A16 ------------------------------------------------------------------------------------------------------
     def direct_solve(self, indptr, indices, vals, b, ldlt=False):
@@ -95,6 +97,17 @@ class Oracle:
         x = np.zeros_like(b)
         rc = getattr(self.lib, f"qdo_direct_{name}")(indptr.shape[0] - 1, indptr.ctypes.data, indices.ctypes.data,
                                                      vals.ctypes.data, int(ldlt), b.ctypes.data, x.ctypes.data)
+        return x, rc == 0
+
+    def lu_solve(self, indptr, indices, vals, b):
+        """LU with partial pivoting of a CSR matrix (dense workspace: small systems) + solve.  Returns (x, ok)."""
+        indptr, indices = (np.ascontiguousarray(a, dtype=np.int32) for a in (indptr, indices))
+        vals = np.ascontiguousarray(vals)
+        name = "f64" if vals.dtype == np.float64 else "f32"
+        b = np.ascontiguousarray(b, dtype=vals.dtype)
+        x = np.zeros_like(b)
+        rc = getattr(self.lib, f"qdo_lu_{name}")(indptr.shape[0] - 1, indptr.ctypes.data, indices.ctypes.data,
+                                                 vals.ctypes.data, b.ctypes.data, x.ctypes.data)
         return x, rc == 0
 
     # -- A3 -------------------------------------------------------------------------------------------------------

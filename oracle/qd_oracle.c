@@ -553,3 +553,55 @@ QDO_API double qdo_csr_get_f32(const int32_t *outer, const int32_t *inner, const
   }
 QDO_DIRECT(qdo_direct_f32, float, sqrtf)
 QDO_DIRECT(qdo_direct_f64, double, sqrt)
+
+/* ------------------------------------------------------------------------- */
+/* LU solve (solver_type "LU").  The reference's solver is    */
+/* Eigen::SparseLU<SparseMatrix<dt>, {AMD,COLAMD}Ordering<int>>               */
+/* (quadrants/program/sparse_solver.h:15-20): a supernodal left-looking LU     */
+/* with PARTIAL (row) PIVOTING.  Restated here as Gaussian elimination with    */
+/* partial pivoting on the dense expansion of the CSR matrix (duplicates       */
+/* summed) -- the same factorisation P A = L U up to the column ordering,      */
+/* which changes rounding, not the solution; the GPU path (no pivoting, static */
+/* ordering) and this one are both compared with the reference's solutions     */
+/* with a tolerance.  Returns 0, or 1 + k when no non-zero pivot exists in     */
+/* column k.  Dense O(n^2) workspace: small systems only.                      */
+/* ------------------------------------------------------------------------- */
+#define QDO_LU(NAME, VAL_T, FABS)                                                                  \
+  QDO_API int NAME(int n, const int32_t *outer, const int32_t *inner, const VAL_T *vals,           \
+                   const VAL_T *b, VAL_T *x) {                                                     \
+    VAL_T *A = (VAL_T *)calloc((size_t)n * n, sizeof(VAL_T));                                      \
+    int rc = 0;                                                                                    \
+    for (int r = 0; r < n; ++r)                                                                    \
+      for (int32_t p = outer[r]; p < outer[r + 1]; ++p) A[(size_t)r * n + inner[p]] += vals[p];    \
+    for (int i = 0; i < n; ++i) x[i] = b[i];                                                       \
+    for (int k = 0; k < n && rc == 0; ++k) {                                                       \
+      int piv = k;                                                                                 \
+      for (int r = k + 1; r < n; ++r)                                                              \
+        if (FABS(A[(size_t)r * n + k]) > FABS(A[(size_t)piv * n + k])) piv = r;                    \
+      if (A[(size_t)piv * n + k] == (VAL_T)0) { rc = 1 + k; break; }                               \
+      if (piv != k) {                                                                              \
+        for (int c = 0; c < n; ++c) {                                                              \
+          const VAL_T t = A[(size_t)k * n + c];                                                    \
+          A[(size_t)k * n + c] = A[(size_t)piv * n + c];                                           \
+          A[(size_t)piv * n + c] = t;                                                              \
+        }                                                                                          \
+        const VAL_T t = x[k]; x[k] = x[piv]; x[piv] = t;                                           \
+      }                                                                                            \
+      for (int r = k + 1; r < n; ++r) {                                                            \
+        const VAL_T l = A[(size_t)r * n + k] / A[(size_t)k * n + k];                               \
+        if (l == (VAL_T)0) continue;                                                               \
+        for (int c = k + 1; c < n; ++c) A[(size_t)r * n + c] -= l * A[(size_t)k * n + c];          \
+        x[r] -= l * x[k];                                                                          \
+      }                                                                                            \
+    }                                                                                              \
+    if (rc == 0)                                                                                   \
+      for (int i = n - 1; i >= 0; --i) {                                                           \
+        VAL_T s = x[i];                                                                            \
+        for (int c = i + 1; c < n; ++c) s -= A[(size_t)i * n + c] * x[c];                          \
+        x[i] = s / A[(size_t)i * n + i];                                                           \
+      }                                                                                            \
+    free(A);                                                                                       \
+    return rc;                                                                                     \
+  }
+QDO_LU(qdo_lu_f32, float, fabsf)
+QDO_LU(qdo_lu_f64, double, fabs)

@@ -55,6 +55,25 @@ def test_oracle_direct_solve_matches_reference_eigen(oracle, tag, dt):
                                b.astype(dt).astype(np.float64))
 
 
+@pytest.mark.parametrize("tag,dt", [("f32", np.float32), ("f64", np.float64)])
+def test_oracle_lu_matches_reference_eigen(oracle, tag, dt):
+    gold = np.load(GOLD)
+    for name, n, r, c, v, b, sym in W.solver_cases():
+        ip, ix, vals = _csr(oracle, r, c, v, n, dt)
+        x, ok = oracle.lu_solve(ip, ix, vals, b.astype(dt))
+        assert ok
+        for od in ("AMD", "COLAMD"):
+            check_solution(name, tag, x, gold[f"{name}/{tag}/LU/{od}"], dense_of(n, r, c, v, dt),
+                           b.astype(dt).astype(np.float64))
+    # a matrix that NEEDS a row exchange: zero leading pivot
+    ip = np.array([0, 1, 3], np.int32)
+    ix = np.array([1, 0, 1], np.int32)
+    x, ok = oracle.lu_solve(ip, ix, np.array([2.0, 3.0, 1.0]), np.array([4.0, 5.0]))   # [[0,2],[3,1]]
+    assert ok and np.allclose(np.array([[0.0, 2.0], [3.0, 1.0]]) @ x, [4.0, 5.0])
+    _, ok = oracle.lu_solve(ip, ix, np.array([0.0, 3.0, 1.0]), np.array([4.0, 5.0]))   # singular
+    assert not ok
+
+
 def test_golden_is_current_when_reference_present(eigen_ref):
     gold = np.load(GOLD)
     for name, n, r, c, v, b, sym in W.solver_cases():
