@@ -200,6 +200,21 @@ int qdsp_sort_pairs(void *keys, void *values, int64_t n, int key_kind, int value
 /* PrefixSumExecutor.run (_algorithms.py:109-163): in-place inclusive i32 prefix sum, wrapping. */
 size_t qdsp_scan_tmp_bytes(int64_t n);
 int qdsp_inclusive_scan_i32(int32_t *inout, int64_t n, void *tmp, size_t tmp_bytes, void *stream);
+/* The same prefix sum for a caller that has nowhere to get `tmp` from.  No counterpart in the reference.  Some hosts can
+ * neither cudaMalloc nor carve scratch out of an allocator of their own: all device memory was given to a fixed arena
+ * when the application started, or the call sits in a fixed-rate loop where the device-wide stall of cudaMalloc /
+ * cudaFree is not acceptable.  For them the scan's bookkeeping (tile descriptors, ticket counter) lives in an array
+ * compiled into the library: about 1 MB on every GPU that loads libqdsp.so, kept until the process exits.  The call
+ * allocates and frees nothing, on the device or through any library; inout is the caller's, as above.
+ *   - n may be at most qdsp_scan_static_max_n() (2^26 elements); a longer array is refused with QDSP_ERR_INVALID and a
+ *     message that names the limit.  Use qdsp_inclusive_scan_i32 for those.
+ *   - The first call on each device looks up where that device keeps the array (with that device current).  Make this
+ *     first call once during start-up, outside any stream capture.
+ *   - There is ONE array per device and every call uses it.  Each call clears what it needs first (stream-ordered), so
+ *     back-to-back calls on one stream are fine; two calls that can run on the GPU at the same time (different streams,
+ *     different host threads without ordering) race on it and give wrong sums. */
+int64_t qdsp_scan_static_max_n(void);
+int qdsp_inclusive_scan_i32_static(int32_t *inout, int64_t n, void *stream);
 
 
 /* ---- qd.algorithms device-wide ops ------------------------------------------------------------ */

@@ -78,6 +78,8 @@ SIGNATURES = {
     "qdsp_sort_pairs": (_i, [_vp, _vp, _i64, _i, _i, _vp, _sz, _vp]),
     "qdsp_scan_tmp_bytes": (_sz, [_i64]),
     "qdsp_inclusive_scan_i32": (_i, [_vp, _i64, _vp, _sz, _vp]),
+    "qdsp_scan_static_max_n": (_i64, []),
+    "qdsp_inclusive_scan_i32_static": (_i, [_vp, _i64, _vp]),
     "qdsp_algo_scratch_bytes": (_sz, [_i, _i64, _i]),
     "qdsp_reduce": (_i, [_vp, _vp, _i64, _vp, _i, _i, _vp, _sz, _vp]),
     "qdsp_exclusive_scan": (_i, [_vp, _vp, _i64, _vp, _i, _i, _vp, _sz, _vp]),

@@ -437,6 +437,10 @@ size_t qdsp_scan_tmp_bytes(int64_t n) { return n < 0 ? 0 : scan_tmp_bytes(n); }
 int qdsp_inclusive_scan_i32(int32_t *inout, int64_t n, void *tmp, size_t tmp_bytes, void *stream) {
   return guarded([&] { inclusive_scan_i32(inout, n, tmp, tmp_bytes, S(stream)); });
 }
+int64_t qdsp_scan_static_max_n(void) { return scan_static_max_n(); }
+int qdsp_inclusive_scan_i32_static(int32_t *inout, int64_t n, void *stream) {
+  return guarded([&] { inclusive_scan_i32_static(inout, n, S(stream)); });
+}
 
 // ---- device-wide algorithms ---------------------------------------------------------------------------------
 size_t qdsp_algo_scratch_bytes(int algo, int64_t capacity, int elem_bytes) {

@@ -13,6 +13,8 @@ namespace qdsp {
 // ---- algorithms (scan.cu, radix_sort.cu) -----------------------------------------------------------------------------
 size_t scan_tmp_bytes(int64_t n);
 void inclusive_scan_i32(int32_t *inout, int64_t n, void *tmp, size_t tmp_bytes, cudaStream_t stream);
+int64_t scan_static_max_n();
+void inclusive_scan_i32_static(int32_t *inout, int64_t n, cudaStream_t stream);  // scratch = a static __device__ array
 size_t sort_tmp_bytes(int64_t n, int key_bytes, int value_bytes);
 void sort_pairs(void *keys, void *values, int64_t n, int key_kind, int value_bytes, void *tmp, size_t tmp_bytes,
                 cudaStream_t stream);

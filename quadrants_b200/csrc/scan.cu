@@ -24,6 +24,8 @@
 // Fallback (cooperative launch unavailable): the same kernel with ticket order and the Merrill-Garland walk.
 #include <algorithm>
 #include <cstdlib>
+#include <mutex>
+#include <string>
 
 #include "lookback.cuh"
 #include "tma.cuh"
@@ -288,6 +290,54 @@ void inclusive_scan_i32(int32_t *inout, int64_t n, void *tmp, size_t tmp_bytes, 
     scan_inclusive_i32_kernel<false><<<grid, SCAN_THREADS, SCAN_SMEM_BYTES, stream>>>(inout, n, head_skip, n_tiles, counter, desc);
   }
   QDSP_LAUNCH_CHECK();
+}
+
+// ---- the same scan for callers that cannot allocate device memory ----------------------------------------------------
+// qdsp_inclusive_scan_i32_static: the tile descriptors and the ticket counter live in a fixed array that is part of the
+// library image instead of in a buffer the caller brings.  Meant for hosts that own no allocator of their own to draw a
+// tmp buffer from and must not call cudaMalloc either: an embedding whose device memory was handed, whole, to a
+// pre-sized arena at start-up (the reference's runtime works like that: one pool, ndarrays carved out of it), or a
+// fixed-rate stepping loop in which cudaMalloc / cudaFree -- which stall every stream of the device -- are banned.
+// Cost: SCAN_STATIC_BYTES (about 1 MB) of every GPU that loads libqdsp.so, held until the process exits, and a length
+// limit of SCAN_STATIC_MAX_N elements.
+constexpr int64_t SCAN_STATIC_MAX_N = int64_t(1) << 26;
+constexpr size_t SCAN_STATIC_BYTES =
+    SCAN_HEADER_BYTES + (2 * static_cast<size_t>((SCAN_STATIC_MAX_N + 3 + SCAN_TILE - 1) / SCAN_TILE) + 2) *
+                            (sizeof(unsigned long long) << SCAN_DESC_SHIFT);
+static __device__ __align__(256) unsigned char g_scan_static_scratch[SCAN_STATIC_BYTES];
+
+int64_t scan_static_max_n() { return SCAN_STATIC_MAX_N; }
+
+void inclusive_scan_i32_static(int32_t *inout, int64_t n, cudaStream_t stream) {
+  QDSP_REQUIRE(n >= 0, QDSP_ERR_INVALID, "scan (static scratch): negative length");
+  QDSP_REQUIRE(n <= SCAN_STATIC_MAX_N && scan_tmp_bytes(n) <= SCAN_STATIC_BYTES, QDSP_ERR_INVALID,
+               "scan (static scratch): " + std::to_string(n) + " elements exceed the built-in scratch array, which covers " +
+                   std::to_string(SCAN_STATIC_MAX_N) + "; use qdsp_inclusive_scan_i32 with a caller-owned tmp buffer");
+  if (n == 0) return;
+  // In host code `g_scan_static_scratch` is only a handle for the runtime, not an address a kernel may be given.  The
+  // real address differs per device (each GPU has its own copy of the array), so it is looked up once per device, with
+  // that device current, on the first call made there.
+  constexpr int MAX_DEVICES = 64;
+  static std::mutex mu;
+  static void *dev_ptr[MAX_DEVICES] = {};
+  int dev = 0;
+  QDSP_CUDA(cudaGetDevice(&dev));
+  QDSP_REQUIRE(dev >= 0 && dev < MAX_DEVICES, QDSP_ERR_UNSUPPORTED, "scan (static scratch): device ordinal above 63");
+  void *scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev_ptr[dev] == nullptr) {
+      void *p = nullptr;
+      QDSP_CUDA(cudaGetSymbolAddress(&p, g_scan_static_scratch));
+      QDSP_REQUIRE(p != nullptr, QDSP_ERR_CUDA, "scan (static scratch): the scratch array has no device address");
+      dev_ptr[dev] = p;
+    }
+    scratch = dev_ptr[dev];
+  }
+  // From here on this is the ordinary scan: it zeroes the part of the scratch it is about to use with a stream-ordered
+  // memset (the array still holds the previous call's descriptors) and launches the same kernel.  Nothing on this path
+  // allocates or frees device memory.
+  inclusive_scan_i32(inout, n, scratch, SCAN_STATIC_BYTES, stream);
 }
 
 }  // namespace qdsp
