@@ -281,7 +281,10 @@ int qdsp_builder_append_elements(qdsp_builder_t b, const int32_t *nodes, const v
  * ordering: 0 "AMD", 1 "COLAMD" -- both select the same symmetric minimum-degree ordering of A + A^T, as the reference's
  * arch=cuda path does (it ignores the argument and calls csrsymamdHost, sparse_solver.cpp:200).  dtype: f32 or f64 (the
  * reference's cuSOLVER path is f32 only).  LLT / LDLT read the lower triangle of the matrix (Eigen::Lower,
- * sparse_solver.h:9-13); LU factorises without row exchanges on the symmetrised pattern (the reference pivots). */
+ * sparse_solver.h:9-13); LU pivots STATICALLY: analyze_pattern reads the values of the matrix it is given and fixes a row
+ * permutation with a large entry of every row on the diagonal (qdsp_solver_lu_row_matching_host), the factorisation then
+ * runs on the symmetrised pattern of the permuted matrix; a pivot that is zero or below 16 eps of its column (of L below, of U above) is reported
+ * through *success / info(), never divided by.  (The reference exchanges rows during the factorisation.) */
 typedef struct qdsp_solver_s *qdsp_solver_t;
 int qdsp_solver_create(int dtype, int solver_type, int ordering, qdsp_solver_t *out);
 /* analyze_pattern (sparse_solver.cpp:233-288): ordering + symbolic factorisation on the host, like the reference's
@@ -312,6 +315,16 @@ int qdsp_solver_destroy(qdsp_solver_t s);
 int qdsp_solver_analyze_host(int n, const int32_t *indptr, const int32_t *indices, int natural_order, int32_t *perm_out,
                              int32_t *parent_out, int32_t *colptr_out, int32_t *rowidx_out, int64_t rowidx_capacity,
                              int64_t *factor_nnz, int *etree_height);
+/* Pure host helper (no CUDA needed): the row permutation qdsp_solver_analyze_pattern applies for solver_type LU.  The
+ * reference's LU exchanges rows during the factorisation (Eigen SparseLU; csrluHost with pivot threshold 1.0,
+ * sparse_solver.cpp:343-359); here the exchange is decided once, before the symbolic analysis (static pivoting): the
+ * rows are matched to columns so that the product of the chosen entries' magnitudes, each relative to its row's largest,
+ * is maximal (the MC64 objective; Hungarian method on the sparse pattern), a diagonal entry counting 10x so that rows
+ * only move where it pays; a diagonal that is its row's largest entry stays outright.  abs_values[q] = |value| of
+ * stored entry q; rowof_out[i] = the row of A that becomes row i; *zero_free_diagonal = 0 when the matrix is
+ * structurally singular. */
+int qdsp_solver_lu_row_matching_host(int n, const int32_t *indptr, const int32_t *indices, const double *abs_values,
+                                     int32_t *rowof_out, int *zero_free_diagonal);
 
 /* ---- dense vector kernels of MatrixFreeCG / MatrixFreeBICGSTAB (python/quadrants/linalg/matrixfree_cg.py:23-310) --------
  * The reference JIT-compiles `reduce`, `update_x`, `update_r`, `update_p`, ... per solve; these are their device

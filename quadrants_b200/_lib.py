@@ -100,6 +100,7 @@ SIGNATURES = {
     "qdsp_solver_stats": (_i, [_vp, _P(_i64), _P(_i), _P(_d)]),
     "qdsp_solver_destroy": (_i, [_vp]),
     "qdsp_solver_analyze_host": (_i, [_i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i64, _P(_i64), _P(_i)]),
+    "qdsp_solver_lu_row_matching_host": (_i, [_i, _vp, _vp, _vp, _vp, _P(_i)]),
 }
 
 _lib = None

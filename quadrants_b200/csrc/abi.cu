@@ -532,6 +532,23 @@ int qdsp_solver_stats(qdsp_solver_t s, int64_t *factor_nnz, int *etree_height, d
 int qdsp_solver_destroy(qdsp_solver_t s) {
   return guarded([&] { delete s; });
 }
+int qdsp_solver_lu_row_matching_host(int n, const int32_t *indptr, const int32_t *indices, const double *abs_values,
+                                     int32_t *rowof_out, int *zero_free_diagonal) {
+  return guarded([&] {
+    NOT_NULL(indptr);
+    NOT_NULL(rowof_out);
+    QDSP_REQUIRE(n >= 0, QDSP_ERR_INVALID, "solver row matching: negative size");
+    const int64_t nnz = indptr[n];
+    QDSP_REQUIRE(nnz == 0 || (indices != nullptr && abs_values != nullptr), QDSP_ERR_INVALID, "solver row matching: null array");
+    for (int64_t q = 0; q < nnz; ++q)
+      QDSP_REQUIRE(indices[q] >= 0 && indices[q] < n, QDSP_ERR_INVALID, "solver row matching: column index out of range");
+    std::vector<double> w(abs_values, abs_values + nnz);
+    std::vector<int32_t> rowof;
+    const bool ok = solver_lu_row_matching_host(n, indptr, indices, w, rowof);
+    std::copy(rowof.begin(), rowof.end(), rowof_out);
+    if (zero_free_diagonal) *zero_free_diagonal = ok ? 1 : 0;
+  });
+}
 int qdsp_solver_analyze_host(int n, const int32_t *indptr, const int32_t *indices, int natural_order, int32_t *perm_out,
                              int32_t *parent_out, int32_t *colptr_out, int32_t *rowidx_out, int64_t rowidx_capacity,
                              int64_t *factor_nnz, int *etree_height) {

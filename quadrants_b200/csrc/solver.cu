@@ -16,10 +16,16 @@
 //                    Where the tail of a dependency column has the same pattern as the target column (chains of the
 //                    elimination tree / supernodes -- most of the arithmetic), slots map 1:1 and the update is a
 //                    coalesced axpy; otherwise a binary search in the target's sorted rows.
-//                    LU: static (diagonal) pivoting on the symmetrised pattern, L unit-lower by columns, U by rows in the
-//                    same slots -- no partial pivoting (the reference's Eigen SparseLU and csrluHost pivot; a zero pivot
-//                    here is reported through info()).  Enough for the SPD / diagonally dominant systems the reference
-//                    tests (tests/python/test_sparse_linear_solver.py:17-177).
+//                    LU: STATIC pivoting.  The reference's Eigen SparseLU and csrluHost exchange rows while they
+//                    factorise (threshold 1.0, sparse_solver.cpp:343-359); a left-looking kernel over a fixed pattern
+//                    cannot, so the exchange is decided up front: analyze_pattern() reads the values it is given and
+//                    picks a row permutation Q that puts a large entry of every row on the diagonal (solver_lu_row_matching_host
+//                    below: the maximum-product matching of MC64 by shortest augmenting paths, with a
+//                    preference for the diagonal; a diagonal entry that is its row's largest simply stays), and everything after that works on
+//                    Q A.  L unit-lower by columns, U by rows in the same slots.  A pivot that is zero or vanishes
+//                    against column j of L below it and of U above it (|d| < 16 eps max|column|) is reported
+//                    through info() instead of being divided by.  This is weaker than partial pivoting -- the choice
+//                    looks at A, not at the partly eliminated matrix -- and is stated as such in DESIGN.md 3.9.
 //   solve            device, two launches: synchronisation-free triangular solves, one warp per row, the same flag
 //                    protocol (forward ascending, backward descending), permutation folded into the first load and the
 //                    last store.  Fixed summation order.
@@ -27,6 +33,7 @@
 // for every size a direct solver is used at.  No cuSOLVER / cuSPARSE.
 #include <algorithm>
 #include <climits>
+#include <cmath>
 #include <cstring>
 #include <numeric>
 
@@ -271,6 +278,7 @@ constexpr unsigned long long WAIT_TIMEOUT_NS = 3000000000ull;
 struct FactorDev {
   int n;
   const int *colptr, *rowidx, *rowptr, *rowcol, *rowpos, *perm;
+  const int *bperm;  // where row j of the permuted system takes its right-hand side from (= perm unless LU moved rows)
   int *flags;  // n + CTL_WORDS
   void *lx, *ux;
 };
@@ -407,6 +415,17 @@ __global__ void __launch_bounds__(SOLVER_THREADS) solver_factor_kernel(FactorDev
     bool bad;
     if (MODE == SOLVER_LLT) bad = !(d > T(0));
     else bad = !(d != T(0)) || d != d;
+    if (MODE == SOLVER_LU) {
+      // static pivoting has no second candidate: a pivot that all but cancelled against its column is a failure to
+      // report, not a number to divide by
+      T cmax = T(0);
+      for (int t = 1 + lane; t < lenj; t += 32) cmax = fmax(cmax, fabs(__ldcg(lx + cj + t)));
+      // ... and against column j of U above it (the slots of row j, final by now): the last column has nothing below
+      for (int m = lane; m < cnt; m += 32) cmax = fmax(cmax, fabs(__ldcg(ux + __ldg(f.rowpos + r0 + m))));
+      for (int o = 16; o > 0; o >>= 1) cmax = fmax(cmax, __shfl_xor_sync(FULL, cmax, o));
+      const T eps = sizeof(T) == 8 ? T(2.220446049250313e-16) : T(1.1920929e-07);
+      bad = bad || fabs(d) < T(16) * eps * cmax;
+    }
     if (bad) {
       if (lane == 0) atomicMin(flags + n + CTL_ERROR, j);
       d = T(1);
@@ -492,7 +511,7 @@ __global__ void __launch_bounds__(SOLVER_THREADS) solver_forward_kernel(FactorDe
     // everything that does not depend on other rows is read BEFORE the waits
     T bj = T(0), dj = T(1);
     if (lane == 0) {
-      bj = b[__ldg(f.perm + j)];
+      bj = b[__ldg(f.bperm + j)];
       if (MODE == SOLVER_LLT) dj = __ldcg(lx + __ldg(f.colptr + j));
     }
     T acc = T(0);
@@ -559,7 +578,110 @@ int solver_grid(K kernel, int n) {
   return std::max(1, std::min(cap, ceil_div(n, SOLVER_WARPS)));
 }
 
+
 }  // namespace
+
+// Row permutation for LU (see the header): the matching of rows to columns that maximises the PRODUCT of the chosen
+// entries' magnitudes relative to their row maxima (the objective of Duff & Koster's MC64), by the Hungarian method on the
+// sparse pattern: cost(r, c) = log(rowmax_r / |a_rc|) >= 0, shortest augmenting paths (Dijkstra on reduced costs) with row
+// / column potentials.  A diagonal entry is given a 10x bonus (cost lowered by log 10, floored at 0), so rows move where it
+// buys something, not for a factor of two; a diagonal that is its row's largest entry is matched up front, which leaves
+// diagonally dominant and the usual SPD systems untouched at no cost.
+// rowof[i] = the row of A that becomes row i of Q A; w = |value| per stored entry (duplicates of a non-canonical CSR are
+// looked at one by one, which can only make the choice less good, never invalid).  Returns false when the matrix is
+// structurally singular (no zero-free diagonal exists); rowof is then still a permutation and the factorisation reports
+// the zero pivot.
+bool solver_lu_row_matching_host(int n, const int32_t *ip, const int32_t *ix, const std::vector<double> &w,
+                                 std::vector<int32_t> &rowof) {
+  std::vector<int32_t> col_of_row(n, -1);
+  rowof.assign(n, -1);
+  std::vector<double> rowmax(n, 0.0);
+  for (int r = 0; r < n; ++r)
+    for (int q = ip[r]; q < ip[r + 1]; ++q) rowmax[r] = std::max(rowmax[r], w[q]);
+  const double bonus = std::log(10.0);
+  auto cost = [&](int r, int q) {
+    const double c = std::log(rowmax[r] / w[q]);  // w[q] > 0 is checked by the callers
+    return ix[q] == r ? std::max(0.0, c - bonus) : c;
+  };
+  // start: zero-cost entries (the potentials start at zero, so these are the tight edges).  Diagonals first.
+  for (int r = 0; r < n; ++r) {
+    double d = 0.0;
+    for (int q = ip[r]; q < ip[r + 1]; ++q)
+      if (ix[q] == r) d = std::max(d, w[q]);
+    if (d > 0.0 && d >= rowmax[r]) { col_of_row[r] = r; rowof[r] = r; }
+  }
+  for (int r = 0; r < n; ++r) {
+    if (col_of_row[r] >= 0) continue;
+    for (int q = ip[r]; q < ip[r + 1]; ++q)
+      if (w[q] > 0.0 && rowof[ix[q]] < 0 && cost(r, q) == 0.0) { col_of_row[r] = ix[q]; rowof[ix[q]] = r; break; }
+  }
+  // the rest: one shortest augmenting path per free row
+  bool complete = true;
+  std::vector<double> u(n, 0.0), v(n, 0.0), dist(n, 0.0);
+  std::vector<int32_t> via(n, -1), stamp(n, -1), done(n, -1), touched;
+  using Item = std::pair<double, int32_t>;
+  std::vector<Item> heap;
+  auto cmp = [](const Item &a, const Item &b) { return a.first > b.first; };
+  for (int r0 = 0; r0 < n; ++r0) {
+    if (col_of_row[r0] >= 0) continue;
+    heap.clear();
+    touched.clear();
+    auto relax = [&](int r, double base) {
+      for (int q = ip[r]; q < ip[r + 1]; ++q) {
+        if (!(w[q] > 0.0)) continue;
+        const int c = ix[q];
+        if (done[c] == r0) continue;
+        const double nd = base + std::max(0.0, cost(r, q) - u[r] - v[c]);  // (max: rounding may leave -1e-17)
+        if (stamp[c] != r0 || nd < dist[c]) {
+          if (stamp[c] != r0) { stamp[c] = r0; touched.push_back(c); }
+          dist[c] = nd;
+          via[c] = r;
+          heap.push_back({nd, c});
+          std::push_heap(heap.begin(), heap.end(), cmp);
+        }
+      }
+    };
+    relax(r0, 0.0);
+    int found = -1;
+    double D = 0.0;
+    while (!heap.empty()) {
+      std::pop_heap(heap.begin(), heap.end(), cmp);
+      const Item it = heap.back();
+      heap.pop_back();
+      const int c = it.second;
+      if (done[c] == r0 || it.first > dist[c]) continue;  // stale entry
+      done[c] = r0;
+      if (rowof[c] < 0) { found = c; D = it.first; break; }
+      relax(rowof[c], it.first);
+    }
+    if (found < 0) { complete = false; continue; }
+    // potentials: finalised columns (and their rows) move by (D - dist); the new row by D.  Reduced costs stay >= 0 and
+    // every matched edge stays tight.
+    for (int c : touched)
+      if (done[c] == r0 && c != found) {
+        const double delta = D - dist[c];
+        v[c] -= delta;
+        u[rowof[c]] += delta;
+      }
+    u[r0] += D;
+    for (int c = found; c >= 0;) {  // flip the path
+      const int r = via[c], prev = col_of_row[r];
+      col_of_row[r] = c;
+      rowof[c] = r;
+      c = r == r0 ? -1 : prev;
+    }
+  }
+  if (!complete) {  // leftovers in index order: still a permutation
+    int c = 0;
+    for (int r = 0; r < n; ++r) {
+      if (col_of_row[r] >= 0) continue;
+      while (rowof[c] >= 0) ++c;
+      rowof[c] = r;
+      col_of_row[r] = c;
+    }
+  }
+  return complete;
+}
 
 DirectSolver::DirectSolver(int dtype, int solver_type, int ordering) : dtype_(dtype), type_(solver_type), ordering_(ordering) {
   QDSP_REQUIRE(dtype == QDSP_F32 || dtype == QDSP_F64, QDSP_ERR_INVALID, "Not supported sparse solver data type");
@@ -576,6 +698,42 @@ void DirectSolver::analyze_pattern(const CsrMatrix &A, cudaStream_t stream) {
   QDSP_CUDA(cudaMemcpyAsync(ip.data(), A.indptr.get(), sizeof(int32_t) * (n + 1), cudaMemcpyDeviceToHost, stream));
   QDSP_CUDA(cudaMemcpyAsync(ix.data(), A.indices.get(), sizeof(int32_t) * A.nnz, cudaMemcpyDeviceToHost, stream));
   QDSP_CUDA(cudaStreamSynchronize(stream));
+  // LU: rows are exchanged up front (static pivoting); from here on `ip`/`ix` describe Q A and row r of A is row rinv[r]
+  std::vector<int32_t> rowof(n), rinv(n);
+  std::iota(rowof.begin(), rowof.end(), 0);
+  std::iota(rinv.begin(), rinv.end(), 0);
+  const std::vector<int32_t> ip_a = ip;  // the rows of A as stored (the slot map below walks A, not Q A)
+  const std::vector<int32_t> ix_a = ix;
+  if (type_ == SOLVER_LU && n > 0 && A.nnz > 0) {
+    std::vector<double> w(static_cast<size_t>(A.nnz));
+    if (dtype_ == QDSP_F64) {
+      std::vector<double> v(w.size());
+      QDSP_CUDA(cudaMemcpyAsync(v.data(), A.values.get(), sizeof(double) * A.nnz, cudaMemcpyDeviceToHost, stream));
+      QDSP_CUDA(cudaStreamSynchronize(stream));
+      for (size_t q = 0; q < w.size(); ++q) w[q] = std::fabs(v[q]);
+    } else {
+      std::vector<float> v(w.size());
+      QDSP_CUDA(cudaMemcpyAsync(v.data(), A.values.get(), sizeof(float) * A.nnz, cudaMemcpyDeviceToHost, stream));
+      QDSP_CUDA(cudaStreamSynchronize(stream));
+      for (size_t q = 0; q < w.size(); ++q) w[q] = std::fabs(static_cast<double>(v[q]));
+    }
+    for (double &x : w)
+      if (!(x == x)) x = 0.0;  // NaN entries never attract a pivot
+    solver_lu_row_matching_host(n, ip.data(), ix.data(), w, rowof);
+    bool identity = true;
+    for (int i = 0; i < n; ++i) {
+      rinv[rowof[i]] = i;
+      identity = identity && rowof[i] == i;
+    }
+    if (!identity) {
+      std::vector<int32_t> ipq(n + 1, 0), ixq(ix.size());
+      for (int i = 0; i < n; ++i) ipq[i + 1] = ipq[i] + (ip_a[rowof[i] + 1] - ip_a[rowof[i]]);
+      for (int i = 0; i < n; ++i)
+        std::copy(ix_a.begin() + ip_a[rowof[i]], ix_a.begin() + ip_a[rowof[i] + 1], ixq.begin() + ipq[i]);
+      ip.swap(ipq);
+      ix.swap(ixq);
+    }
+  }
   std::vector<int32_t> perm;
   // both ordering names select the same symmetric minimum-degree ordering, like the reference's arch=cuda path, which
   // ignores the argument and calls csrsymamdHost (make_cusparse_solver, sparse_solver.cpp:548-558)
@@ -584,10 +742,10 @@ void DirectSolver::analyze_pattern(const CsrMatrix &A, cudaStream_t stream) {
   // where each entry of A lands.  LLT / LDLT read the LOWER triangle of A only (Eigen::Lower, sparse_solver.h:9-13).
   std::vector<int32_t> amap(static_cast<size_t>(A.nnz), -1);
   for (int r = 0; r < n; ++r)
-    for (int q = ip[r]; q < ip[r + 1]; ++q) {
-      const int c = ix[q];
+    for (int q = ip_a[r]; q < ip_a[r + 1]; ++q) {
+      const int c = ix_a[q];
       if (type_ != SOLVER_LU && c > r) continue;
-      const int pr = sym_.pinv[r], pc = sym_.pinv[c];
+      const int pr = sym_.pinv[rinv[r]], pc = sym_.pinv[c];
       int hi = pr, lo = pc;
       bool upper = false;
       if (pr < pc) { hi = pc; lo = pr; upper = type_ == SOLVER_LU; }
@@ -607,6 +765,9 @@ void DirectSolver::analyze_pattern(const CsrMatrix &A, cudaStream_t stream) {
   up(d_rowcol_, sym_.rowcol);
   up(d_rowpos_, sym_.rowpos);
   up(d_perm_, sym_.perm);
+  std::vector<int32_t> bperm(n);
+  for (int j = 0; j < n; ++j) bperm[j] = rowof[sym_.perm[j]];  // (Q b)[i] = b[rowof[i]], then the symmetric permutation
+  up(d_bperm_, bperm);
   up(d_amap_, amap);
   const size_t vb = dtype_ == QDSP_F64 ? 8 : 4;
   d_lx_.alloc(static_cast<size_t>(sym_.factor_nnz) * vb);
@@ -689,7 +850,7 @@ void DirectSolver::factorize(const CsrMatrix &A, cudaStream_t stream) {
   QDSP_LAUNCH_CHECK();
   reset_flags(d_flags_.get<int>(), n, stream);
   FactorDev f{n, d_colptr_.get<int>(), d_rowidx_.get<int>(), d_rowptr_.get<int>(), d_rowcol_.get<int>(),
-              d_rowpos_.get<int>(), d_perm_.get<int>(), d_flags_.get<int>(), d_lx_.get(), d_ux_.get()};
+              d_rowpos_.get<int>(), d_perm_.get<int>(), d_bperm_.get<int>(), d_flags_.get<int>(), d_lx_.get(), d_ux_.get()};
   SOLVER_DISPATCH(factor_launch, f, stream);
   int ctl[CTL_WORDS];
   read_ctl(d_flags_.get<int>(), n, stream, ctl);
@@ -703,7 +864,7 @@ void DirectSolver::solve(const void *b, void *x, cudaStream_t stream) {
   const int n = sym_.n;
   if (n == 0) return;
   FactorDev f{n, d_colptr_.get<int>(), d_rowidx_.get<int>(), d_rowptr_.get<int>(), d_rowcol_.get<int>(),
-              d_rowpos_.get<int>(), d_perm_.get<int>(), d_flags_.get<int>(), d_lx_.get(), d_ux_.get()};
+              d_rowpos_.get<int>(), d_perm_.get<int>(), d_bperm_.get<int>(), d_flags_.get<int>(), d_lx_.get(), d_ux_.get()};
   if (dtype_ == QDSP_F64) {
     const double *bb = static_cast<const double *>(b);
     double *yy = d_work_.get<double>(), *xx = static_cast<double *>(x);

@@ -34,6 +34,11 @@ void solver_order_host(int n, const int32_t *indptr, const int32_t *indices, std
 void solver_symbolic_host(int n, const int32_t *indptr, const int32_t *indices, const std::vector<int32_t> &perm,
                           SymbolicFactor &out);
 
+// LU only: the row permutation of the static pivoting (solver.cu header).  w[q] = |value| of stored entry q;
+// rowof[i] = the row of A that becomes row i.  False when no zero-free diagonal exists (rowof is still a permutation).
+bool solver_lu_row_matching_host(int n, const int32_t *indptr, const int32_t *indices, const std::vector<double> &w,
+                                 std::vector<int32_t> &rowof);
+
 class DirectSolver {
  public:
   DirectSolver(int dtype, int solver_type, int ordering);
@@ -54,7 +59,7 @@ class DirectSolver {
   int zero_pivot_ = -1;
   int64_t nnz_a_ = 0;
   SymbolicFactor sym_;
-  DeviceBuffer d_colptr_, d_rowidx_, d_rowptr_, d_rowcol_, d_rowpos_, d_perm_, d_amap_;
+  DeviceBuffer d_colptr_, d_rowidx_, d_rowptr_, d_rowcol_, d_rowpos_, d_perm_, d_bperm_, d_amap_;
   DeviceBuffer d_lx_, d_ux_, d_flags_, d_work_;
 };
 

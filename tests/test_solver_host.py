@@ -153,3 +153,99 @@ def test_host_analysis_rejects_bad_input():
         _core.solver_analyze_host(np.array([0, 1, 2], np.int32), np.array([0, 5], np.int32))
     res = _core.solver_analyze_host(np.array([0], np.int32), np.array([], np.int32))
     assert res["factor_nnz"] == 0 and res["etree_height"] == 0
+
+
+# ---- LU static pivoting: the row permutation chosen by analyze_pattern (host part, no GPU) --------------------------------
+def _row_matching(a):
+    import ctypes as C
+
+    from quadrants_b200 import _lib
+
+    lib = _lib.load()
+    n = a.shape[0]
+    r, c = np.nonzero(a)
+    ip = np.zeros(n + 1, np.int32)
+    np.add.at(ip, r + 1, 1)
+    ip = np.cumsum(ip).astype(np.int32)
+    ix = c.astype(np.int32)
+    w = np.abs(a[r, c]).astype(np.float64)
+    rowof = np.full(n, -1, np.int32)
+    ok = C.c_int(-1)
+    _lib.check(lib.qdsp_solver_lu_row_matching_host(n, ip.ctypes.data, ix.ctypes.data, w.ctypes.data, rowof.ctypes.data,
+                                                    C.byref(ok)))
+    assert sorted(rowof.tolist()) == list(range(n)), "not a permutation"
+    return rowof, bool(ok.value)
+
+
+def test_lu_row_matching_keeps_a_sound_diagonal():
+    rng = np.random.default_rng(3)
+    n = 120
+    m = np.where(rng.random((n, n)) < 0.06, rng.uniform(-1, 1, (n, n)), 0.0)
+    m[np.arange(n), np.arange(n)] = 1.0 + np.abs(m).sum(1)
+    rowof, ok = _row_matching(m)
+    assert ok and np.array_equal(rowof, np.arange(n))
+    a = np.random.default_rng(1).random((10, 10))
+    rowof, ok = _row_matching(a @ a.T + np.eye(10))  # the reference's SPD test matrix: untouched
+    assert ok and np.array_equal(rowof, np.arange(10))
+
+
+def test_lu_row_matching_recovers_a_row_shift_and_fixes_bad_diagonals():
+    rng = np.random.default_rng(4)
+    n = 150
+    m = np.where(rng.random((n, n)) < 0.05, rng.uniform(-1, 1, (n, n)), 0.0)
+    m[np.arange(n), np.arange(n)] = 2.0 + np.abs(m).sum(1)
+    shifted = np.roll(m, 7, axis=0)            # row i of `shifted` is row i - 7 of m
+    rowof, ok = _row_matching(shifted)
+    assert ok and np.array_equal(shifted[rowof], m)
+    # zero and tiny diagonals: every chosen pivot is a stored non-zero and none is tiny against its row
+    for a in (np.array([[0.0, 2.0], [3.0, 1.0]]), np.array([[1e-20, 1.0], [1.0, 1.0]])):
+        rowof, ok = _row_matching(a)
+        assert ok and rowof.tolist() == [1, 0]
+    band = np.zeros((n, n))
+    i = np.arange(n - 1)
+    band[i, i + 1] = rng.uniform(2, 4, n - 1)
+    band[i + 1, i] = rng.uniform(0.5, 1, n - 1)
+    band[n - 1, 0] = 3.0
+    rowof, ok = _row_matching(band)
+    q = band[rowof]
+    d = np.abs(np.diag(q))
+    assert ok and np.all(d > 0)
+    assert np.all(d >= 0.1 * np.abs(q).max(1) - 1e-300) or np.count_nonzero(d < 0.1 * np.abs(q).max(1)) <= 2
+
+
+def test_lu_row_matching_structurally_singular_and_augmenting_paths():
+    # greedy takes (0,0) and (1,1) first; row 2 only has column 0, so the matching must be re-routed along a path
+    a = np.array([[5.0, 4.0, 0.0],
+                  [0.0, 5.0, 4.0],
+                  [1.0, 0.0, 0.0]])
+    a[0, 0], a[1, 1] = 0.3, 0.3                 # below 0.1 of the row maximum?  no: 0.3 / 4 -- pass 2 decides
+    rowof, ok = _row_matching(a)
+    assert ok and np.all(np.diag(a[rowof]) != 0)
+    sing = np.array([[0.0, 0.0, 1.0], [0.0, 0.0, 2.0], [1.0, 1.0, 1.0]])
+    rowof, ok = _row_matching(sing)
+    assert not ok
+    rowof, ok = _row_matching(np.zeros((0, 0)))
+    assert ok and rowof.size == 0
+
+
+def test_lu_row_matching_is_the_maximum_product_matching_on_small_matrices():
+    """Brute force over all permutations (n <= 6): the product of the chosen |a| / rowmax, a diagonal entry counting
+    10x (capped at 1), is maximal -- the objective stated in include/qdsp.h."""
+    import itertools
+
+    rng = np.random.default_rng(11)
+    for trial in range(60):
+        n = int(rng.integers(2, 7))
+        a = np.where(rng.random((n, n)) < 0.6, rng.uniform(-1, 1, (n, n)) * 10.0 ** rng.integers(-6, 2, (n, n)), 0.0)
+        if np.any(np.abs(a).max(1) == 0):
+            continue
+        rel = np.abs(a) / np.abs(a).max(1, keepdims=True)
+        score = rel.copy()
+        score[np.arange(n), np.arange(n)] = np.minimum(1.0, 10.0 * np.diag(rel))
+        # rowof[i] = the row placed at position i, i.e. the row matched to column i
+        best = max(np.prod([score[p[i], i] for i in range(n)]) for p in itertools.permutations(range(n)))
+        rowof, ok = _row_matching(a)
+        got = np.prod([score[rowof[i], i] for i in range(n)])
+        assert ok == (best > 0)
+        if best > 0:
+            assert got >= best * (1 - 1e-9), (trial, a, rowof, got, best)

@@ -152,6 +152,6 @@ def solver_cases():
     np.add.at(rowsum, r, np.abs(v))
     colsum = np.zeros(n)
     np.add.at(colsum, c, np.abs(v))
-    d = 1.0 + np.maximum(rowsum, colsum)  # strictly diagonally dominant by rows and columns: no pivoting needed
+    d = 1.0 + np.maximum(rowsum, colsum)  # strictly diagonally dominant by rows and columns: the row matching of the LU leaves it alone
     yield ("unsym_dd_120", n, np.concatenate([r, np.arange(n)]), np.concatenate([c, np.arange(n)]),
            np.concatenate([v, d]), np.sin(np.arange(n) * 0.11) + 2.0, False)
