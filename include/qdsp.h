@@ -65,9 +65,13 @@ int qdsp_device_info(int *device, int *sm_count, int *cc_major, int *cc_minor, s
 /* Number of kernels of this library launched by the calling process so far (bench.py's gpu_launches). */
 int64_t qdsp_launch_count(void);
 /* The multi-GB temporaries of a build / sort are cached between calls instead of cudaMalloc'd and freed every time (cap:
- * QDSP_SCRATCH_POOL_MB, default 16384; 0 = no cache).  This returns the cached blocks to the driver.  (The reference
- * cuMemAllocs and frees its work buffers on every call, e.g. sparse_matrix.cpp:654-686.) */
+ * QDSP_SCRATCH_POOL_MB, default 16384; 0 = no cache -- and never more than a quarter of the device memory that would be
+ * free without the cache, re-checked whenever a block comes back, so the cache shrinks as other allocators fill the
+ * device).  This returns the cached blocks to the driver.  (The reference cuMemAllocs and frees its work buffers on every
+ * call, e.g. sparse_matrix.cpp:654-686.) */
 int qdsp_release_scratch(void);
+/* Bytes cached right now and the cap that applies right now on the current device (diagnostics; no reference counterpart). */
+int qdsp_scratch_info(size_t *cached_bytes, size_t *cap_bytes);
 
 /* ---- SparseMatrixBuilder (quadrants/program/sparse_matrix.h:16-53) -------------------------------------------- */
 /* ctor + create_ndarray (sparse_matrix.cpp:70-85): allocates the device triplet buffer of 3*max_triplets+1 slots of
@@ -106,7 +110,10 @@ int qdsp_csr_from_device_csr(int rows, int cols, int64_t nnz, const int32_t *ind
 int qdsp_csr_info(qdsp_csr_t m, int *rows, int *cols, int64_t *nnz, int *dtype);
 /* Borrowed device pointers to csr_row_ptr_/csr_col_ind_/csr_val_ (valid until qdsp_csr_destroy). */
 int qdsp_csr_export(qdsp_csr_t m, const int32_t **indptr, const int32_t **indices, const void **values);
-/* spmv / nd_spmv (sparse_matrix.cpp:654-686): y = A x, x has cols elements, y rows elements, both dense device. */
+/* spmv / nd_spmv (sparse_matrix.cpp:654-686): y = A x, x has cols elements, y rows elements, both dense device.
+ * Concurrency: the first product of a matrix plans it and must not race with another call on the same matrix; after
+ * that, host threads may launch products of one matrix concurrently, with at most 16 of them in flight at a time
+ * (on different streams) -- beyond that the caller has to order them. */
 int qdsp_csr_spmv(qdsp_csr_t m, const void *x, void *y, void *stream);
 /* SpMV storage option of one matrix.  compress: 1 = stream one-byte diagonal codes instead of the 4-byte column indices
  * when the matrix has at most 256 distinct (column - row) values (stencils, banded matrices; the plan keeps an extra

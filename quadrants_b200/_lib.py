@@ -33,6 +33,7 @@ SIGNATURES = {
     "qdsp_device_info": (_i, [_P(_i), _P(_i), _P(_i), _P(_i), _P(_sz), _P(_sz)]),
     "qdsp_launch_count": (_i64, []),
     "qdsp_release_scratch": (_i, []),
+    "qdsp_scratch_info": (_i, [_P(_sz), _P(_sz)]),
     "qdsp_builder_create": (_i, [_i, _i, _i64, _i, C.c_char_p, _P(_vp)]),
     "qdsp_builder_buffer_ptr": (_i, [_vp, _P(_vp)]),
     "qdsp_builder_count": (_i, [_vp, _vp, _P(_i64)]),

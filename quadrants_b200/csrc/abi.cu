@@ -29,6 +29,28 @@ size_t pool_cap_bytes() {
   }();
   return cap;
 }
+// What the pool may hold right now: the configured cap, but never more than a quarter of the device memory that would be
+// free without it.  Other allocators on the device (torch's caching allocator in the host application) cannot reclaim
+// blocks parked here, so the pool shrinks as the device fills up instead of sitting on gigabytes next to an OOM.
+// (cudaMemGetInfo is a driver round trip: the answer is reused for 20 ms, a build releases half a dozen blocks in a row.)
+size_t pool_cap_now(size_t pool_bytes, bool refresh = false) {
+  size_t cap = pool_cap_bytes();
+  if (cap == 0) return 0;
+  static std::chrono::steady_clock::time_point stamp{};
+  static size_t other_free = ~size_t{0};  // free + pooled at the last look (callers hold g_pool_mutex)
+  const auto now = std::chrono::steady_clock::now();
+  if (refresh || other_free == ~size_t{0} || now - stamp > std::chrono::milliseconds(20)) {
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+      other_free = free_b + pool_bytes;
+      stamp = now;
+    } else {
+      (void)cudaGetLastError();
+    }
+  }
+  if (other_free != ~size_t{0}) cap = std::min(cap, other_free / 4);
+  return cap;
+}
 constexpr size_t POOL_MIN_BYTES = size_t{1} << 20;  // smaller requests go straight to cudaMalloc
 constexpr size_t POOL_GRANULE = size_t{2} << 20;
 }  // namespace
@@ -79,13 +101,20 @@ void scratch_pool_release(void *p, size_t bytes) {
     std::lock_guard<std::mutex> lock(g_pool_mutex);
     g_pool.push_back({p, bytes, dev});
     g_pool_bytes += bytes;
-    while (g_pool_bytes > pool_cap_bytes() && !g_pool.empty()) {  // evict the oldest
+    const size_t cap_now = pool_cap_now(g_pool_bytes);
+    while (g_pool_bytes > cap_now && !g_pool.empty()) {  // evict the oldest
       drop.push_back(g_pool.front().p);
       g_pool_bytes -= g_pool.front().bytes;
       g_pool.erase(g_pool.begin());
     }
   }
   for (void *q : drop) cudaFree(q);
+}
+
+void scratch_pool_info(size_t *cached, size_t *cap_now) {
+  std::lock_guard<std::mutex> lock(g_pool_mutex);
+  if (cached) *cached = g_pool_bytes;
+  if (cap_now) *cap_now = pool_cap_now(g_pool_bytes, true);
 }
 
 void scratch_pool_trim() {
@@ -136,6 +165,9 @@ extern "C" {
 const char *qdsp_last_error(void) { return g_last_error.c_str(); }
 int qdsp_abi_version(void) { return QDSP_ABI_VERSION; }
 int64_t qdsp_launch_count(void) { return g_launch_count.load(); }
+int qdsp_scratch_info(size_t *cached_bytes, size_t *cap_bytes) {
+  return guarded([&] { scratch_pool_info(cached_bytes, cap_bytes); });
+}
 int qdsp_release_scratch(void) {
   return guarded([&] { scratch_pool_trim(); });
 }

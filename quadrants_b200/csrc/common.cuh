@@ -57,6 +57,7 @@ const DeviceProps &device_props();  // of the current device; cached per device
 void *scratch_pool_acquire(size_t bytes, size_t *got);
 void scratch_pool_release(void *p, size_t bytes);
 void scratch_pool_trim();
+void scratch_pool_info(size_t *cached, size_t *cap_now);
 
 class DeviceBuffer {
  public:

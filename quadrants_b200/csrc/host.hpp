@@ -1,6 +1,7 @@
 // host.hpp -- C++ host orchestration layer above the kernels and below the C ABI (include/qdsp.h).
 // One class per reference class of quadrants/program/{sparse_matrix,conjugate_gradient}.h.
 #pragma once
+#include <atomic>
 #include <memory>
 #include <string>
 #include <vector>
@@ -67,9 +68,12 @@ class CsrMatrix {
   mutable int spmv_plan_hot_n = 0;
   mutable double spmv_plan_hot_coverage = 0.0;  // share of the non-zeros whose column is hot
   // work counters of the dynamically scheduled tail of the uniform path (spmv_kernels.cuh SpmvSched): 16 slots used
-  // round-robin, so up to 16 products of one matrix may be in flight on different streams
+  // round-robin (atomic: host threads launching on the same matrix draw distinct slots), so up to 16 products of one
+  // matrix may be in flight at once.  A 17th concurrent product would share a counter with the 1st and both would skip
+  // row blocks: callers that keep more than 16 products of ONE matrix in flight on different streams must order them.
+  // The plan itself (first product of a matrix, spmv_prepare) is not thread-safe: make the first call from one thread.
   mutable DeviceBuffer spmv_sched_buf;
-  mutable unsigned spmv_sched_next = 0;
+  mutable std::atomic<unsigned> spmv_sched_next{0};
 
   size_t value_bytes() const { return dtype == QDSP_F64 ? 8 : 4; }
   void allocate(int rows_, int cols_, int64_t nnz_, int dtype_);

@@ -384,7 +384,7 @@ void launch_spmv_t(const CsrMatrix &A, const T *x, T *y, const DistDev &d, cudaS
   const size_t smem = spmv_smem_bytes<T>();
   const int *ip = A.indptr.get<int>(), *ix = A.indices.get<int>();
   unsigned *counters = A.spmv_sched_buf.get<unsigned>();
-  if (counters) counters += 2 * (A.spmv_sched_next++ % 16);
+  if (counters) counters += 2 * (A.spmv_sched_next.fetch_add(1u, std::memory_order_relaxed) % 16);
   SpmvSched sched = spmv_sched_for(ceil_div(A.rows, R), grid, counters);
   if constexpr (LPR == 1) {
     spmv_attach_codes(A, sched);

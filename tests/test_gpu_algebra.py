@@ -167,3 +167,48 @@ def test_add_of_non_canonical_csr_takes_the_sort_path(qd):
     R = (S + S).tocsr()
     R.sort_indices()
     assert np.array_equal(ip2, R.indptr) and np.array_equal(ix2, R.indices) and np.array_equal(v2, R.data)
+
+
+def test_scratch_pool_gives_way_when_the_device_fills_up(qd):
+    """blocks parked in the scratch pool are invisible to every other allocator on the device (torch's in the
+    host application).  The pool therefore never keeps more than a quarter of the memory that would be free without it,
+    re-checked whenever a block comes back (qdsp_scratch_info reports both numbers)."""
+    import ctypes as C
+    import time
+
+    import torch
+
+    from quadrants_b200 import _lib
+
+    lib = _lib.load()
+
+    def info():
+        cached, cap = C.c_size_t(0), C.c_size_t(0)
+        _lib.check(lib.qdsp_scratch_info(C.byref(cached), C.byref(cap)))
+        return cached.value, cap.value
+
+    if os.environ.get("QDSP_SCRATCH_POOL_MB") == "0":
+        pytest.skip("pool disabled")
+    _lib.check(lib.qdsp_release_scratch())
+    assert info()[0] == 0
+    A = to_qd(qd, rand_csr(300_000, 300_000, 3_000_000, 5, np.float32))
+    At = A.transpose()
+    cached, cap = info()
+    assert 0 < cached <= cap, (cached, cap)          # ample memory: the temporaries of the transpose stay cached
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    free, _ = torch.cuda.mem_get_info()
+    keep = 2 * cached                                 # leaves the pool above a quarter of (free + cached): it has to shrink
+    hog = torch.empty(max(free - keep, 0), dtype=torch.uint8, device="cuda")  # the host application takes the device
+    try:
+        time.sleep(0.05)                              # (the pool re-reads the free memory at most every 20 ms)
+        At2 = A.transpose()                           # re-uses cached blocks and hands them back: the cap is re-applied
+        torch.cuda.synchronize()
+        cached2, cap2 = info()
+        free2, _ = torch.cuda.mem_get_info()
+        assert cap2 <= (free2 + cached2) // 4 + (2 << 20), (cap2, free2, cached2)
+        assert cached2 <= cap2 and cached2 < cached, (cached, cached2, cap2)
+        assert np.array_equal(arrays(At2)[1], arrays(At)[1])
+    finally:
+        del hog
+        torch.cuda.empty_cache()
