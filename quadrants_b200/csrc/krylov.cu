@@ -5,7 +5,8 @@
 // Here: one deterministic dot kernel that forms up to two products in a single pass (fixed tree: per-thread strided sums
 // -> warp shuffle -> block -> the last block adds the block sums in index order; accumulated in double for both dtypes),
 // one linear-combination kernel out = sum_i c_i x_i (i <= 4, out may alias an input), and the fused CG step
-// x += a p, r -= a Ap, r.r in one pass.  All HBM-bound streaming kernels: 128-bit loads, grid = a multiple of the SM count.
+// x += a p, r -= a Ap, r.r in one pass.  All HBM-bound streaming kernels: grid-stride loops of coalesced element-wide
+// loads (a warp reads 128 / 256 contiguous bytes per instruction), grid = a multiple of the SM count.
 #include "host.hpp"
 
 namespace qdsp {
@@ -37,16 +38,28 @@ __device__ __forceinline__ void block_dot_finish(double s0, double s1, const Dot
     last = atomicAdd(sc.ticket, 1u) == gridDim.x - 1;
   }
   __syncthreads();
-  if (last && threadIdx.x == 0) {
+  if (last) {
+    // the last block adds the block sums: thread t takes blocks t, t + 256, ... in index order, then the same fixed
+    // warp / block tree as above -- the order depends on the grid only, so the result is reproducible run to run
     __threadfence();
     double a = 0, b = 0;
-    for (unsigned g = 0; g < gridDim.x; ++g) {
+    for (unsigned g = threadIdx.x; g < gridDim.x; g += KV_THREADS) {
       a += __ldcg(sc.partials + 2 * g);
       b += __ldcg(sc.partials + 2 * g + 1);
     }
-    sc.out[0] = a;
-    sc.out[1] = b;
-    *sc.ticket = 0u;
+    a = warp_sum(a);
+    b = warp_sum(b);
+    __syncthreads();  // sh0 / sh1 were read by thread 0 above
+    if (lane == 0) { sh0[warp] = a; sh1[warp] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      a = 0;
+      b = 0;
+      for (int w = 0; w < KV_THREADS / 32; ++w) { a += sh0[w]; b += sh1[w]; }
+      sc.out[0] = a;
+      sc.out[1] = b;
+      *sc.ticket = 0u;
+    }
   }
 }
 

@@ -6,12 +6,17 @@ arrays (e.g. `lambda v, mv: A.matrix.spmv(None, v, mv)` for a SparseMatrix, or a
 vector work runs in the kernels of quadrants_b200/csrc/krylov.cu through the C ABI (qdsp_vec_dot2 / qdsp_vec_lincomb /
 qdsp_vec_cg_step): the recurrences, the start from the caller's x, the absolute tolerance on sqrt(r.r), the return value
 and its quirk (the final check compares r.r, not its root, with tol) are the reference's.  Dot products are accumulated
-in double and in a fixed order.
+in double and in a fixed order (the reference sums in the solver dtype, in whatever order its atomics land), and every
+scalar of the recurrence -- the dot results, alpha, beta, omega, rho -- is then rounded to the solver dtype, because the
+reference keeps them in fields of that dtype and its reductions return it (matrixfree_cg.py:67-68,80-86,194-198): an f32
+solve follows the f32 recurrence, not a double-precision one.
 """
 from __future__ import annotations
 
 import ctypes as C
 from math import sqrt
+
+import numpy as np
 
 from .. import _lib
 from ..lang import Ndarray, QuadrantsRuntimeError, f32, f64, get_runtime
@@ -39,17 +44,19 @@ class _Vec:
         self.dt = _lib.F64 if dtype is f64 else _lib.F32
         self.n = int(n)
         self.stream = get_runtime().prog.stream()
+        # a scalar as the reference holds it: a field / kernel return value of the solver dtype
+        self.q = float if dtype is f64 else (lambda v: float(np.float32(v)))
 
     def dot(self, a, b):
         out = (C.c_double * 2)()
         _lib.check(self.lib.qdsp_vec_dot2(a.data_ptr(), b.data_ptr(), None, None, self.n, self.dt, self.stream, out))
-        return out[0]
+        return self.q(out[0])
 
     def dot2(self, a, b, c, d):
         out = (C.c_double * 2)()
         _lib.check(self.lib.qdsp_vec_dot2(a.data_ptr(), b.data_ptr(), c.data_ptr(), d.data_ptr(), self.n, self.dt,
                                           self.stream, out))
-        return out[0], out[1]
+        return self.q(out[0]), self.q(out[1])
 
     def lincomb(self, out, *terms):
         """out = sum coef * vec over (coef, vec) terms."""
@@ -62,7 +69,7 @@ class _Vec:
         rr = C.c_double()
         _lib.check(self.lib.qdsp_vec_cg_step(x.data_ptr(), r.data_ptr(), p.data_ptr(), ap.data_ptr(), float(alpha),
                                              self.n, self.dt, self.stream, C.byref(rr)))
-        return rr.value
+        return self.q(rr.value)
 
 
 def _check_args(b, x, name):
@@ -103,14 +110,14 @@ def MatrixFreeCG(A, b, x, tol=1e-6, maxiter=5000, quiet=True):
         for i in range(maxiter):
             A._matvec(p, Ap)
             pAp = V.dot(p, Ap)
-            alpha = old_rTr / pAp
+            alpha = V.q(old_rTr / pAp)
             new_rTr = V.cg_step(x, r, p, Ap, alpha)  # update_x + update_r + reduce(r, r) in one pass
             if sqrt(new_rTr) < tol:
                 if not quiet:
                     print(">>> Conjugate Gradient method converged.")
                     print(f">>> #iterations {i}")
                 break
-            beta = new_rTr / old_rTr
+            beta = V.q(new_rTr / old_rTr)
             V.lincomb(p, (1.0, r), (beta, p))
             old_rTr = new_rTr
             if not quiet:
@@ -150,14 +157,14 @@ def MatrixFreeBICGSTAB(A, b, x, tol=1e-6, maxiter=5000, quiet=True):
             if i == 0:
                 V.lincomb(p, (1.0, r))
             else:
-                beta = (rho / rho_1) * (alpha / omega)
+                beta = V.q((rho / rho_1) * (alpha / omega))
                 V.lincomb(p, (1.0, r), (beta, p), (-beta * omega, Ap))   # p = r + beta (p - omega Ap)
             A._matvec(p, Ap)                                             # p_hat = p (no preconditioner)
-            alpha = rho / V.dot(r_tld, Ap)
+            alpha = V.q(rho / V.dot(r_tld, Ap))
             V.lincomb(s, (1.0, r), (-alpha, Ap))
             A._matvec(s, t)                                              # s_hat = s; t = A s_hat
             omega_upper, omega_lower = V.dot2(t, s, t, t)
-            omega = omega_upper / (omega_lower + 1e-16) if omega_lower == 0.0 else omega_upper / omega_lower
+            omega = V.q(omega_upper / (omega_lower + 1e-16) if omega_lower == 0.0 else omega_upper / omega_lower)
             V.lincomb(x, (1.0, x), (alpha, p), (omega, s))
             V.lincomb(r, (1.0, s), (-omega, t))
             rTr = V.dot(r, r)

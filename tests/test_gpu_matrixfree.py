@@ -69,7 +69,10 @@ def test_vector_kernels_against_numpy(qd, dt):
         V = _Vec(qdt, n)
         a64 = [a.astype(np.float64) for a in arrs]
         d0, d1 = V.dot2(nd[0], nd[1], nd[2], nd[3])
-        assert abs(d0 - a64[0] @ a64[1]) <= 1e-12 * n and abs(d1 - a64[2] @ a64[3]) <= 1e-12 * n
+        # accumulated in double; the value handed back is rounded to the solver dtype like the reference's reductions
+        rnd = 2.0 ** -24 if dt == np.float32 else 0.0
+        e0, e1 = a64[0] @ a64[1], a64[2] @ a64[3]
+        assert abs(d0 - e0) <= 1e-12 * n + rnd * abs(e0) and abs(d1 - e1) <= 1e-12 * n + rnd * abs(e1)
         assert V.dot(nd[0], nd[0]) == V.dot(nd[0], nd[0])  # reproducible
         out = qd.ndarray(qdt, n)
         V.lincomb(out, (0.5, nd[0]), (-2.0, nd[1]), (3.0, nd[2]))
@@ -131,3 +134,72 @@ def test_matrixfree_bicgstab_unsymmetric_and_failures(qd):
         qd.linalg.MatrixFreeCG(A, b, qd.ndarray(qd.f64, n + 1))
     with pytest.raises(qd.QuadrantsRuntimeError):
         A.matvec(b, qd.ndarray(qd.f64, n + 1))
+
+
+def _cg_f32_restatement(matvec, b, tol, maxiter):
+    """The reference's MatrixFreeCG loop (python/quadrants/linalg/matrixfree_cg.py:104-131) for solver_dtype f32, in numpy:
+    vectors in f32, and every scalar -- the reductions' return values, alpha, beta -- held in f32 like the reference's
+    fields.  (The reduction itself is summed in double here and on the device; the reference's summation order is not
+    defined.)  Returns (x, iteration index at convergence or None)."""
+    q = lambda v: float(np.float32(v))
+    dot = lambda u, w: q(u.astype(np.float64) @ w.astype(np.float64))
+    x = np.zeros_like(b)
+    r = (b - matvec(x)).astype(np.float32)
+    p = r.copy()
+    old = new = dot(r, r)
+    if math.sqrt(old) < tol:
+        return x, -1
+    for i in range(maxiter):
+        Ap = matvec(p)
+        alpha = np.float32(q(old / dot(p, Ap)))
+        x = x + alpha * p
+        r = r - alpha * Ap
+        new = dot(r, r)
+        if math.sqrt(new) < tol:
+            return x, i
+        beta = np.float32(q(new / old))
+        p = r + beta * p
+        old = new
+    return x, None
+
+
+def test_matrixfree_cg_f32_keeps_its_scalars_in_the_solver_dtype(qd, capsys):
+    """an f32 solve must follow the f32 recurrence of the reference (alpha, beta and the reduction results are
+    f32 there), not a double-precision one.  Pinned against the numpy restatement above on a 5-point operator with a
+    weak diagonal (4.05: condition number ~160, so the recurrence runs for dozens of iterations): same iteration count
+    within 2 (fused multiply-adds differ from numpy's two roundings) and the same x to 1e-4."""
+    import torch
+
+    DIAG = 4.05
+
+    def apply(a, out):
+        out[1:, :] -= a[:-1, :]
+        out[:-1, :] -= a[1:, :]
+        out[:, 1:] -= a[:, :-1]
+        out[:, :-1] -= a[:, 1:]
+        return out
+
+    def compute_Ax(v, mv):
+        a = v.tensor.view(GRID, GRID)
+        mv.tensor.copy_(apply(a, DIAG * a).reshape(-1))
+
+    def matvec(v):
+        a = v.reshape(GRID, GRID)
+        return apply(a, np.float32(DIAG) * a).reshape(-1)
+
+    A = qd.linalg.LinearOperator(compute_Ax)
+    b_np = np.random.default_rng(12).uniform(-1, 1, GRID * GRID).astype(np.float32)
+    tol = 1e-4
+    x_ref, it_ref = _cg_f32_restatement(matvec, b_np, tol, 500)
+    assert it_ref is not None and it_ref > 20, it_ref
+    x = qd.ndarray(qd.f32, GRID * GRID)
+    b = qd.ndarray(qd.f32, GRID * GRID)
+    b.from_numpy(b_np)
+    capsys.readouterr()
+    assert qd.linalg.MatrixFreeCG(A, b, x, tol=tol, maxiter=500, quiet=False)
+    out = capsys.readouterr().out
+    its = [int(l.split()[-1]) for l in out.splitlines() if "#iterations" in l]
+    assert its, out
+    assert abs(its[0] - it_ref) <= 2, (its[0], it_ref)
+    xg = x.to_numpy().reshape(-1)
+    assert np.linalg.norm(xg - x_ref) <= 1e-4 * np.linalg.norm(x_ref)
