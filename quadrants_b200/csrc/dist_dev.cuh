@@ -279,8 +279,8 @@ __device__ __forceinline__ void dist_halo_wait(const DistDev &d) {
                                    : *reinterpret_cast<volatile unsigned *>(&d.counters[1]);
   const long long t0 = clock64();
   for (int r = 0; r < d.n_recv; ++r) {
-    // (relaxed polls, ONE acquire at the end: every acquire load invalidates the SM's L1, which the other CTAs of the SM are
-    // gathering x through)
+    // (relaxed polls first: every acquire invalidates the SM's L1, which the other CTAs of the SM are gathering x
+    // through, so acquiring polls would do that once per spin)
     const unsigned long long *f = dist_flag(d.self, d.recv_peer[r]);
     while (ld_sys_u64(f) < want) {
       if (clock64() - t0 > DIST_SPIN_LIMIT) {
@@ -289,7 +289,16 @@ __device__ __forceinline__ void dist_halo_wait(const DistDev &d) {
       }
     }
   }
+  // The polls above are relaxed; the reads of the ghost entries have to be ordered after EVERY peer's release store, and an
+  // acquire load of one flag only synchronises with the peer that wrote that flag: so one acquire load per peer (the flags
+  // are already at their final values, these loads hit at once).  Measured at 4 GPUs on one box, C2 CG (profiles/
+  // r03i_halo_wait_ab.txt): one acquire on peer 0 only (round 2, formally unordered for the other peers) 12 008 it/s, one
+  // per peer 11 852 (-1.3 %), a fence.acq_rel.sys after the polls instead 11 191 (-6.8 %).
+#if defined(QDSP_HALO_WAIT_ONE_ACQUIRE)   // round-2 behaviour, kept as a build switch for A/B timing only
   if (d.n_recv > 0) (void)ld_acquire_sys_u64(dist_flag(d.self, d.recv_peer[0]));
+#else
+  for (int r = 0; r < d.n_recv; ++r) (void)ld_acquire_sys_u64(dist_flag(d.self, d.recv_peer[r]));
+#endif
 }
 // The same for the z channel (thread 0 of a CTA, before its first read of a z-ghost; follow with __syncthreads()).
 __device__ __forceinline__ void dist_halo_wait_z(const DistDev &d) {
@@ -305,7 +314,11 @@ __device__ __forceinline__ void dist_halo_wait_z(const DistDev &d) {
       }
     }
   }
+#if defined(QDSP_HALO_WAIT_ONE_ACQUIRE)
   if (d.n_recv > 0) (void)ld_acquire_sys_u64(dist_flag_z(d.self, d.recv_peer[0]));
+#else
+  for (int r = 0; r < d.n_recv; ++r) (void)ld_acquire_sys_u64(dist_flag_z(d.self, d.recv_peer[r]));  // see dist_halo_wait
+#endif
 }
 #endif  // __CUDACC__
 

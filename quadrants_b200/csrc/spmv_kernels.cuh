@@ -88,8 +88,17 @@ __host__ __device__ constexpr size_t spmv_stream_smem_bytes(bool hot = false) {
 // halo wait orders after those writes (the acquire invalidates the SM's L1); .nc loads are outside the memory model.
 template <bool COHERENT, typename T>
 __device__ __forceinline__ T ld_x(const T *p) {
+  // -DQDSP_GATHER_COHERENT makes every gather a coherent load, which is what the memory model asks for where peers write
+  // ghost entries during a stand-alone kernel's lifetime (amode / lazy halo).  Measured on one B200, same box, round 3
+  // (profiles/r03e_gather_ab.txt): C2 CG and both SpMV paths unchanged, but the C5 (irregular, fp64) CG drops from 4714
+  // to 4374 it/s, so the default stays .nc for the stand-alone kernels; the halo waits end in an acquire (load or
+  // fence, dist_dev.cuh), which on sm_100 invalidates the L1 lines an .nc load would otherwise hit.
+#ifdef QDSP_GATHER_COHERENT
+  return __ldca(p);
+#else
   if constexpr (COHERENT) return __ldca(p);
   else return __ldg(p);
+#endif
 }
 
 // Explicit shared-memory accesses for the stream path.  The stage pointers are computed from an aligned byte base, so the
@@ -435,7 +444,7 @@ __device__ __forceinline__ void spmv_persistent(unsigned char *smem_raw, int row
               for (int j = 0; j < 8; ++j) {
                 const bool ok = k + j < hi;
                 v[j] = ok ? lds_val(st.val + k + j) : T(0);
-                xv[j] = ok ? __ldg(xr + cd[j]) : T(0);
+                xv[j] = ok ? ld_x<FUSED>(xr + cd[j]) : T(0);
               }
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
@@ -562,7 +571,7 @@ __device__ __forceinline__ void spmv_stream(unsigned char *smem_raw, const int *
   if constexpr (!FUSED) {
     if (use_hot) {
       if (blk0 < blk1)
-        for (int i = t; i < plan.hot_n; i += SPMV_THREADS) hot[i] = __ldg(x + __ldg(plan.hot_cols + i));
+        for (int i = t; i < plan.hot_n; i += SPMV_THREADS) hot[i] = ld_x<FUSED>(x + __ldg(plan.hot_cols + i));
       __syncthreads();
     }
     if (use_hot) indices = plan.hot_idx;
